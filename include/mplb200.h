@@ -1,0 +1,118 @@
+/*
+ * mplb200.h -- C ABI of libmplb200.so: the B200 (sm_100a) implementation of the data-parallel
+ * hot path of josefmaierfl/matchinglib_poselib (brute-force descriptor k-NN + Lowe ratio test;
+ * RANSAC 5-point essential matrix hypothesis generation + Sampson scoring).
+ *
+ * Plain pointers and sizes only: this is what the reference's C++ API functions
+ * (matchinglib::getMatches, poselib::estimateEssentialMat, poselib::getPoseTriangPts) bind to in
+ * the drop-in shim include/matchinglib_poselib_b200.hpp, and what the Python host mirror
+ * (matchinglib_poselib_b200/*.py) calls through ctypes.  Reference paths below are relative to
+ * /root/reference/matchinglib_poselib/source ("MP/").
+ *
+ * Conventions
+ *   - every function returns 0 (MPL_OK) or a negative status; mpl_last_error() gives the text.
+ *     The *_api functions return the REFERENCE's own codes (documented per function).
+ *   - "host" entry points take host pointers, copy to the device, run the kernels on the
+ *     library's stream, copy back and synchronise: they are synchronous like the reference API.
+ *   - "*_dev" entry points take DEVICE pointers and a cudaStream_t (passed as void*), enqueue
+ *     work and return without synchronising; scratch memory comes from the caller.
+ *   - There is no CPU fallback anywhere: without a usable CUDA device every call fails with
+ *     MPL_ERR_NO_DEVICE / MPL_ERR_CUDA.
+ */
+#ifndef MPLB200_H_
+#define MPLB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPL_OK              0
+#define MPL_ERR_BAD_ARG    -1
+#define MPL_ERR_CUDA      -100
+#define MPL_ERR_NO_DEVICE -101
+#define MPL_ERR_LIMIT     -102
+#define MPL_ERR_ASSERT    -103   /* a CV_Assert of the reference would have thrown */
+
+/* cv::DMatch memory layout (16 bytes): queryIdx, trainIdx, imgIdx, distance. */
+typedef struct mpl_dmatch { int32_t queryIdx, trainIdx, imgIdx; float distance; } mpl_dmatch;
+
+/* ---- library / device --------------------------------------------------------------------- */
+int         mpl_init(int device);            /* select device, create stream + scratch; idempotent */
+int         mpl_shutdown(void);
+const char* mpl_last_error(void);            /* thread-local text of the last failure */
+int         mpl_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+long long   mpl_kernel_launch_count(void);   /* kernels launched by this library since mpl_init */
+
+/* ---- brute-force k-NN, host pointers -------------------------------------------------------
+ * mpl_knn2_hamming replaces cvflann::Index<HammingLUT>(LinearIndexParams).knnSearch
+ *   (MP/matchinglib/source/matchers.cpp:567-588; OpenCV 4.2.0 flann linear_index.h/result_set.h)
+ *   with ignore_tail_bytes = 0, and the NMSLIB seq_search/bit_hamming scan of
+ *   nmslibMatching<int> (MP/matchinglib/include/nmslib/nmslib_matchers.h:159-424,
+ *   similarity_search/src/space/space_bit_hamming.cc:33-42) with ignore_tail_bytes = 2 (even
+ *   nbytes) or 1 (odd nbytes) -- the reference's "last packed word is dropped" behaviour.
+ *   q/t: row-major uint8, row strides q_step/t_step bytes (cv::Mat::step). k = 1 or 2.
+ *   idx/dist: [nq*k] int32; neighbours ordered by (dist, trainIdx); missing neighbour = (-1, INT_MAX).
+ * mpl_knn2_l2f32 replaces cvflann::Index<L2<float>>(LinearIndexParams).knnSearch
+ *   (matchers.cpp:634-664; SQUARED distances, cvflann fp32 accumulation order; sqrt_out = 0) and
+ *   nmslibMatching<float> seq_search/l2 (sqrt distances, NMSLIB 4-lane order; sqrt_out = 1).
+ *   Every returned distance is bit-exact fp32 in the stated order; with sqrt_out = 0 the
+ *   tensor-core kernel only ranks candidates and the result is certified.
+ */
+int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step,
+                     int nbytes, int ignore_tail_bytes, int k, int32_t* idx, int32_t* dist);
+int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt, size_t t_step,
+                   int dim, int sqrt_out, int k, int32_t* idx, float* dist);
+/* force a float path: 0 = auto, 1 = exact SIMT scan only, 2 = tensor-core ranking + exact re-rank */
+int mpl_set_l2_path(int path);
+
+/* Lowe ratio test + cv::DMatch emission (matchers.cpp:601-625, 677-701; nmslib_matchers.h:399-415):
+ * keep q iff d0 < 0.75f*d1 (ratio_test != 0; needs k == 2), emit every query otherwise.
+ * out must hold nq entries; *n_out receives the count; matches are in ascending queryIdx. */
+int mpl_ratio_matches_i32(const int32_t* idx, const int32_t* dist, int nq, int k, int ratio_test,
+                          mpl_dmatch* out, int* n_out);
+int mpl_ratio_matches_f32(const int32_t* idx, const float* dist, int nq, int k, int ratio_test,
+                          mpl_dmatch* out, int* n_out);
+
+/* matchinglib::getMatches for matcher_name in {"LINEAR","BRUTEFORCENMS"} over raw cv::Mat fields
+ * (MP/matchinglib/source/matchers.cpp:115-135, 476-519, 525-714).  cv_type: 0 = CV_8U, 5 = CV_32F.
+ * Returns the REFERENCE codes: 0 ok, -1 wrong input, -2 matcher not supported (every other
+ * matcher_name: no CPU fallback), -3 fewer than 2 matches (LINEAR only), -4 fewer than 15
+ * keypoints on either side; device failures map to -3 with mpl_last_error() set.
+ * out must hold rows1 entries. */
+int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
+                        const void* desc1, int rows1, int cols1, size_t step1, int cv_type1,
+                        const void* desc2, int rows2, int cols2, size_t step2, int cv_type2,
+                        const char* matcher_name, int ratio_test, int nr_threads /*ignored*/,
+                        mpl_dmatch* out, int* n_out);
+
+/* ---- brute-force k-NN, device pointers (bench `value`, multi-GPU plumbing) ------------------
+ * Descriptor rows must be in the library's device layout: row stride = w16*16 bytes, zero padded
+ * (mpl_pack_rows_u8_dev produces it; 32-byte ORB rows already are, with w16 = 2).
+ * keys_out[nq*2]: 64-bit keys (dist << 32 | global trainIdx) of the two nearest train rows of this
+ * shard, global trainIdx = train_offset + local row.  scratch: mpl_knn_hamming_scratch_bytes().
+ * mpl_merge_top2_dev: merge n_parts key lists laid out [part][nq][2] (e.g. the NCCL all-gather of
+ * every rank's keys_out) into idx/dist (is_float: 0 int32 Hamming, 1 float bits) and/or merged keys. */
+size_t mpl_knn_hamming_scratch_bytes(int nq, int nt, int w16);
+int    mpl_pack_rows_u8_dev(const void* d_src, int n, size_t src_step, int nbytes_used, void* d_dst, int w16, void* stream);
+int    mpl_knn2_hamming_dev(const void* d_q, int nq, const void* d_t, int nt, int w16, long long train_offset,
+                            void* d_scratch, size_t scratch_bytes, void* d_keys_out, void* stream);
+int    mpl_merge_top2_dev(const void* d_keys_parts, int n_parts, int nq, int k, int is_float,
+                          void* d_idx, void* d_dist, void* d_keys_merged, void* stream);
+/* Same problem for a batch of independent image pairs (config C4): pair p uses queries
+ * d_q + p*nq*w16*16 and train rows d_t + p*nt*w16*16; keys_out [n_pairs][nq][2], train indices local
+ * to the pair.  No scratch needed (no train split). */
+int    mpl_knn2_hamming_batch_dev(const void* d_q, const void* d_t, int n_pairs, int nq, int nt, int w16,
+                                  void* d_keys_out, void* stream);
+
+size_t mpl_knn_l2_scratch_bytes(int nq, int nt, int dim);
+int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t, int nt, size_t t_ld, int dim,
+                          int sqrt_out, long long train_offset, void* d_scratch, size_t scratch_bytes,
+                          void* d_keys_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPLB200_H_ */

@@ -1,0 +1,388 @@
+// capi.cu -- the C ABI (include/mplb200.h): context, scratch memory, host-pointer entry points and the
+// getMatches mirror.  Host logic only; kernels live in knn_hamming.cu / knn_l2_exact.cu / knn_l2_tc.cu /
+// ransac5pt.cu.  There is no CPU compute path here: every entry point needs a CUDA device.
+#include "mpl_common.cuh"
+#include "mpl_ctx.h"
+#include "../../include/mplb200.h"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+#include <climits>
+#include <cfloat>
+#include <mutex>
+#include <string>
+#include <vector>
+
+// ------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void mpl_set_error(const char* fmt, ...)
+{
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void mpl_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static MplCtx g_ctx;
+static std::mutex g_mu;            // serialises host-pointer entry points (they share scratch + stream)
+
+MplCtx* mpl_ctx() { return &g_ctx; }
+std::mutex& mpl_ctx_mutex() { return g_mu; }
+
+int MplBuf::ensure(size_t bytes)
+{
+    if (bytes <= cap) return MPL_OK;
+    if (ptr) { MPL_CUDA_CHECK(cudaFree(ptr)); ptr = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 4 + 256;
+    MPL_CUDA_CHECK(cudaMalloc(&ptr, want));
+    cap = want;
+    return MPL_OK;
+}
+void MplBuf::release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
+
+static int init_locked(int device)
+{
+    if (g_ctx.ready && g_ctx.device == device) return MPL_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        mpl_set_error("no CUDA device available (%s); libmplb200 has no CPU fallback",
+                      e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return MPL_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) { mpl_set_error("device %d out of range (0..%d)", device, n - 1); return MPL_ERR_BAD_ARG; }
+    if (g_ctx.ready) { for (auto& b : g_ctx.bufs) b.release(); cudaStreamDestroy(g_ctx.stream); g_ctx.ready = false; }
+    MPL_CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp p;
+    MPL_CUDA_CHECK(cudaGetDeviceProperties(&p, device));
+    if (p.major != 10) {
+        mpl_set_error("device %d is sm_%d%d; libmplb200 is built for sm_100a (B200) only", device, p.major, p.minor);
+        return MPL_ERR_NO_DEVICE;
+    }
+    g_ctx.device = device; g_ctx.sm_count = p.multiProcessorCount; g_ctx.cc_major = p.major; g_ctx.cc_minor = p.minor;
+    g_ctx.total_mem = p.totalGlobalMem;
+    MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    g_ctx.ready = true;
+    return MPL_OK;
+}
+
+int mpl_ensure_ctx_locked()
+{
+    if (g_ctx.ready) { MPL_CUDA_CHECK(cudaSetDevice(g_ctx.device)); return MPL_OK; }
+    return init_locked(0);
+}
+
+extern "C" int mpl_init(int device) { std::lock_guard<std::mutex> g(g_mu); return init_locked(device); }
+
+extern "C" int mpl_shutdown(void)
+{
+    std::lock_guard<std::mutex> g(g_mu);
+    if (!g_ctx.ready) return MPL_OK;
+    cudaSetDevice(g_ctx.device);
+    cudaStreamSynchronize(g_ctx.stream);
+    for (auto& b : g_ctx.bufs) b.release();
+    cudaStreamDestroy(g_ctx.stream);
+    g_ctx.ready = false;
+    return MPL_OK;
+}
+
+extern "C" const char* mpl_last_error(void) { return g_err; }
+extern "C" long long mpl_kernel_launch_count(void) { return g_launches.load(); }
+
+extern "C" int mpl_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem)
+{
+    std::lock_guard<std::mutex> g(g_mu);
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    if (sm_count) *sm_count = g_ctx.sm_count;
+    if (cc_major) *cc_major = g_ctx.cc_major;
+    if (cc_minor) *cc_minor = g_ctx.cc_minor;
+    if (total_mem) *total_mem = g_ctx.total_mem;
+    return MPL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Hamming
+// ------------------------------------------------------------------------------------------------
+static int round_w16(int nbytes_used)
+{
+    int w = (nbytes_used + 15) / 16;
+    int r = 1;
+    while (r < w) r *= 2;
+    return r;     // 1,2,4,8,16
+}
+
+extern "C" size_t mpl_knn_hamming_scratch_bytes(int nq, int nt, int w16)
+{
+    if (nq <= 0 || nt <= 0) return 16;
+    int sm = g_ctx.ready ? g_ctx.sm_count : 148;
+    int splits = mpl_hamming_pick_splits(nq, nt, w16, sm);
+    return (size_t)splits * nq * 2 * sizeof(mpl_key64);
+}
+
+extern "C" int mpl_pack_rows_u8_dev(const void* d_src, int n, size_t src_step, int nbytes_used, void* d_dst, int w16, void* stream)
+{
+    return mpl_launch_pack_rows_u8((const uint8_t*)d_src, n, src_step, nbytes_used, (uint8_t*)d_dst, w16, (cudaStream_t)stream);
+}
+
+extern "C" int mpl_knn2_hamming_dev(const void* d_q, int nq, const void* d_t, int nt, int w16, long long train_offset,
+                                    void* d_scratch, size_t scratch_bytes, void* d_keys_out, void* stream)
+{
+    if (nq <= 0) return MPL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
+    int sm = g_ctx.ready ? g_ctx.sm_count : 148;
+    const int splits = mpl_hamming_pick_splits(nq, nt, w16, sm);
+    if (splits == 1)
+        return mpl_launch_hamming_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, 1, 1, train_offset,
+                                       (mpl_key64*)d_keys_out, st);
+    const size_t need = (size_t)splits * nq * 2 * sizeof(mpl_key64);
+    if (scratch_bytes < need || !d_scratch) { mpl_set_error("hamming_dev: scratch %zu < %zu bytes", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
+    int rc = mpl_launch_hamming_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, splits, 1, train_offset,
+                                     (mpl_key64*)d_scratch, st);
+    if (rc) return rc;
+    return mpl_launch_merge_top2((const mpl_key64*)d_scratch, splits, nq, 2, nullptr, nullptr, -1, (mpl_key64*)d_keys_out, st);
+}
+
+extern "C" int mpl_knn2_hamming_batch_dev(const void* d_q, const void* d_t, int n_pairs, int nq, int nt, int w16,
+                                          void* d_keys_out, void* stream)
+{
+    if (nq <= 0 || n_pairs <= 0) return MPL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)n_pairs * nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
+    if (nt > (1 << 20)) { mpl_set_error("hamming_batch: nt=%d exceeds 2^20 rows per pair", nt); return MPL_ERR_LIMIT; }
+    return mpl_launch_hamming_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, 1, n_pairs, 0,
+                                   (mpl_key64*)d_keys_out, st);
+}
+
+extern "C" int mpl_merge_top2_dev(const void* d_keys_parts, int n_parts, int nq, int k, int is_float,
+                                  void* d_idx, void* d_dist, void* d_keys_merged, void* stream)
+{
+    if (k != 1 && k != 2) { mpl_set_error("merge: k must be 1 or 2"); return MPL_ERR_BAD_ARG; }
+    return mpl_launch_merge_top2((const mpl_key64*)d_keys_parts, n_parts, nq, k, (int32_t*)d_idx, d_dist,
+                                 is_float ? 0 : -1, (mpl_key64*)d_keys_merged, (cudaStream_t)stream);
+}
+
+// upload a strided host matrix (rows x row_bytes, stride step) into a dense device buffer
+static int upload_rows(MplBuf& buf, const void* h, int rows, size_t row_bytes, size_t step, size_t dst_pitch, cudaStream_t st)
+{
+    int rc = buf.ensure((size_t)rows * dst_pitch + 16);
+    if (rc) return rc;
+    if (rows == 0) return MPL_OK;
+    if (step == row_bytes && dst_pitch == row_bytes)
+        MPL_CUDA_CHECK(cudaMemcpyAsync(buf.ptr, h, (size_t)rows * row_bytes, cudaMemcpyHostToDevice, st));
+    else
+        MPL_CUDA_CHECK(cudaMemcpy2DAsync(buf.ptr, dst_pitch, h, step, row_bytes, rows, cudaMemcpyHostToDevice, st));
+    return MPL_OK;
+}
+
+extern "C" int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step,
+                                int nbytes, int ignore_tail_bytes, int k, int32_t* idx, int32_t* dist)
+{
+    if (nq < 0 || nt < 0 || nbytes <= 0 || (k != 1 && k != 2) || ignore_tail_bytes < 0 || ignore_tail_bytes >= nbytes ||
+        (nq > 0 && (!q || !idx || !dist)) || (nt > 0 && !t) || q_step < (size_t)nbytes || t_step < (size_t)nbytes) {
+        mpl_set_error("mpl_knn2_hamming: bad argument"); return MPL_ERR_BAD_ARG;
+    }
+    if (nbytes - ignore_tail_bytes > 256) { mpl_set_error("mpl_knn2_hamming: descriptors longer than 256 bytes are not supported"); return MPL_ERR_LIMIT; }
+    std::lock_guard<std::mutex> g(g_mu);
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    if (nq == 0) return MPL_OK;
+    if (nt == 0) { for (int i = 0; i < nq * k; ++i) { idx[i] = -1; dist[i] = INT_MAX; } return MPL_OK; }
+    cudaStream_t st = g_ctx.stream;
+    const int used = nbytes - ignore_tail_bytes;
+    const int w16 = round_w16(used);
+    const size_t rowb = (size_t)w16 * 16;
+    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T], &braw = g_ctx.bufs[MPL_BUF_RAW];
+    // queries and train rows -> packed device layout
+    const uint8_t* src[2] = {q, t}; const int n[2] = {nq, nt}; const size_t stp[2] = {q_step, t_step};
+    MplBuf* dst[2] = {&bq, &bt};
+    for (int s = 0; s < 2; ++s) {
+        if ((size_t)used == rowb) {                       // already in device layout: strided copy only
+            rc = upload_rows(*dst[s], src[s], n[s], rowb, stp[s], rowb, st);
+            if (rc) return rc;
+        } else {
+            rc = upload_rows(braw, src[s], n[s], (size_t)nbytes, stp[s], (size_t)nbytes, st);
+            if (rc) return rc;
+            rc = dst[s]->ensure((size_t)n[s] * rowb);
+            if (rc) return rc;
+            rc = mpl_launch_pack_rows_u8((const uint8_t*)braw.ptr, n[s], (size_t)nbytes, used, (uint8_t*)dst[s]->ptr, w16, st);
+            if (rc) return rc;
+        }
+    }
+    const int splits = mpl_hamming_pick_splits(nq, nt, w16, g_ctx.sm_count);
+    MplBuf &bpart = g_ctx.bufs[MPL_BUF_PART], &bidx = g_ctx.bufs[MPL_BUF_IDX], &bdist = g_ctx.bufs[MPL_BUF_DIST];
+    if ((rc = bpart.ensure((size_t)splits * nq * 2 * sizeof(mpl_key64)))) return rc;
+    if ((rc = bidx.ensure((size_t)nq * k * 4))) return rc;
+    if ((rc = bdist.ensure((size_t)nq * k * 4))) return rc;
+    rc = mpl_launch_hamming_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, splits, 1, 0, (mpl_key64*)bpart.ptr, st);
+    if (rc) return rc;
+    rc = mpl_launch_merge_top2((const mpl_key64*)bpart.ptr, splits, nq, k, (int32_t*)bidx.ptr, bdist.ptr, -1, nullptr, st);
+    if (rc) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(idx, bidx.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(dist, bdist.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    return MPL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// float L2
+// ------------------------------------------------------------------------------------------------
+static int g_l2_path = 0;
+extern "C" int mpl_set_l2_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_l2_path = path; return MPL_OK; }
+
+extern "C" size_t mpl_knn_l2_scratch_bytes(int nq, int nt, int dim)
+{
+    (void)dim;
+    if (nq <= 0 || nt <= 0) return 16;
+    int sm = g_ctx.ready ? g_ctx.sm_count : 148;
+    size_t exact = (size_t)mpl_l2_pick_splits(nq, nt, sm) * nq * 2 * sizeof(mpl_key64);
+    size_t tc = mpl_l2tc_scratch_bytes(nq, nt, dim, sm);
+    return exact > tc ? exact : tc;
+}
+
+extern "C" int mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t, int nt, size_t t_ld, int dim,
+                                  int sqrt_out, long long train_offset, void* d_scratch, size_t scratch_bytes,
+                                  void* d_keys_out, void* stream)
+{
+    if (nq <= 0) return MPL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
+    int sm = g_ctx.ready ? g_ctx.sm_count : 148;
+    const bool want_tc = (g_l2_path == 2) || (g_l2_path == 0 && sqrt_out == 0 && mpl_l2tc_supported(nq, nt, dim));
+    if (want_tc) {
+        if (!mpl_l2tc_supported(nq, nt, dim)) { mpl_set_error("l2: tensor-core path forced but shape unsupported (dim=%d)", dim); return MPL_ERR_BAD_ARG; }
+        return mpl_l2tc_top2((const float*)d_q, nq, q_ld, (const float*)d_t, nt, t_ld, dim, sqrt_out, train_offset,
+                             d_scratch, scratch_bytes, (mpl_key64*)d_keys_out, sm, st);
+    }
+    const int splits = mpl_l2_pick_splits(nq, nt, sm);
+    const size_t need = (size_t)splits * nq * 2 * sizeof(mpl_key64);
+    if (splits == 1)
+        return mpl_launch_l2_exact_top2((const float*)d_q, nq, q_ld, (const float*)d_t, nt, t_ld, dim, sqrt_out ? 1 : 0, 1,
+                                        train_offset, (mpl_key64*)d_keys_out, st);
+    if (scratch_bytes < need || !d_scratch) { mpl_set_error("l2_dev: scratch %zu < %zu bytes", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
+    int rc = mpl_launch_l2_exact_top2((const float*)d_q, nq, q_ld, (const float*)d_t, nt, t_ld, dim, sqrt_out ? 1 : 0, splits,
+                                      train_offset, (mpl_key64*)d_scratch, st);
+    if (rc) return rc;
+    return mpl_launch_merge_top2((const mpl_key64*)d_scratch, splits, nq, 2, nullptr, nullptr, 0, (mpl_key64*)d_keys_out, st);
+}
+
+extern "C" int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt, size_t t_step,
+                              int dim, int sqrt_out, int k, int32_t* idx, float* dist)
+{
+    if (nq < 0 || nt < 0 || dim <= 0 || (k != 1 && k != 2) || (nq > 0 && (!q || !idx || !dist)) || (nt > 0 && !t) ||
+        q_step < (size_t)dim * 4 || t_step < (size_t)dim * 4) {
+        mpl_set_error("mpl_knn2_l2f32: bad argument"); return MPL_ERR_BAD_ARG;
+    }
+    std::lock_guard<std::mutex> g(g_mu);
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    if (nq == 0) return MPL_OK;
+    if (nt == 0) { for (int i = 0; i < nq * k; ++i) { idx[i] = -1; dist[i] = FLT_MAX; } return MPL_OK; }
+    cudaStream_t st = g_ctx.stream;
+    const size_t ld = (size_t)((dim + 3) / 4) * 4;           // device row pitch in floats (16-byte aligned rows)
+    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T];
+    if (ld != (size_t)dim) {                                  // pad columns are never read as payload, but keep them clean
+        if ((rc = bq.ensure((size_t)nq * ld * 4 + 16))) return rc;
+        if ((rc = bt.ensure((size_t)nt * ld * 4 + 16))) return rc;
+        MPL_CUDA_CHECK(cudaMemsetAsync(bq.ptr, 0, (size_t)nq * ld * 4, st));
+        MPL_CUDA_CHECK(cudaMemsetAsync(bt.ptr, 0, (size_t)nt * ld * 4, st));
+    }
+    if ((rc = upload_rows(bq, q, nq, (size_t)dim * 4, q_step, ld * 4, st))) return rc;
+    if ((rc = upload_rows(bt, t, nt, (size_t)dim * 4, t_step, ld * 4, st))) return rc;
+    MplBuf &bscr = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS], &bidx = g_ctx.bufs[MPL_BUF_IDX], &bdist = g_ctx.bufs[MPL_BUF_DIST];
+    const size_t scr = mpl_knn_l2_scratch_bytes(nq, nt, dim);
+    if ((rc = bscr.ensure(scr))) return rc;
+    if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
+    if ((rc = bidx.ensure((size_t)nq * k * 4))) return rc;
+    if ((rc = bdist.ensure((size_t)nq * k * 4))) return rc;
+    rc = mpl_knn2_l2f32_dev(bq.ptr, nq, ld, bt.ptr, nt, ld, dim, sqrt_out, 0, bscr.ptr, scr, bkeys.ptr, (void*)st);
+    if (rc) return rc;
+    rc = mpl_launch_merge_top2((const mpl_key64*)bkeys.ptr, 1, nq, k, (int32_t*)bidx.ptr, bdist.ptr, 0, nullptr, st);
+    if (rc) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(idx, bidx.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(dist, bdist.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    return MPL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ratio test + getMatches mirror (host logic, O(nq))
+// ------------------------------------------------------------------------------------------------
+extern "C" int mpl_ratio_matches_i32(const int32_t* idx, const int32_t* dist, int nq, int k, int ratio_test,
+                                     mpl_dmatch* out, int* n_out)
+{
+    if (nq < 0 || (k != 1 && k != 2) || (ratio_test && k != 2) || !n_out) { mpl_set_error("ratio_matches: bad argument"); return MPL_ERR_BAD_ARG; }
+    int n = 0;
+    for (int q = 0; q < nq; ++q) {
+        // matchers.cpp:603 "dists[q][0] < (0.75f * dists[q][1])": int -> float promotion on both sides
+        if (ratio_test && !((float)dist[(size_t)q * k] < 0.75f * (float)dist[(size_t)q * k + 1])) continue;
+        out[n].queryIdx = q; out[n].trainIdx = idx[(size_t)q * k]; out[n].imgIdx = -1;   // cv::DMatch() default imgIdx
+        out[n].distance = (float)dist[(size_t)q * k];
+        ++n;
+    }
+    *n_out = n;
+    return MPL_OK;
+}
+
+extern "C" int mpl_ratio_matches_f32(const int32_t* idx, const float* dist, int nq, int k, int ratio_test,
+                                     mpl_dmatch* out, int* n_out)
+{
+    if (nq < 0 || (k != 1 && k != 2) || (ratio_test && k != 2) || !n_out) { mpl_set_error("ratio_matches: bad argument"); return MPL_ERR_BAD_ARG; }
+    int n = 0;
+    for (int q = 0; q < nq; ++q) {
+        if (ratio_test && !(dist[(size_t)q * k] < 0.75f * dist[(size_t)q * k + 1])) continue;
+        out[n].queryIdx = q; out[n].trainIdx = idx[(size_t)q * k]; out[n].imgIdx = -1;
+        out[n].distance = dist[(size_t)q * k];
+        ++n;
+    }
+    *n_out = n;
+    return MPL_OK;
+}
+
+extern "C" int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
+                                   const void* desc1, int rows1, int cols1, size_t step1, int cv_type1,
+                                   const void* desc2, int rows2, int cols2, size_t step2, int cv_type2,
+                                   const char* matcher_name, int ratio_test, int nr_threads,
+                                   mpl_dmatch* out, int* n_out)
+{
+    (void)nr_threads;   // matchers.cpp:121 NMSLIB worker threads: meaningless on the device path
+    const int CV_8U_ = 0, CV_32F_ = 5;
+    if (n_out) *n_out = 0;
+    if (!matcher_name || !n_out) { mpl_set_error("getMatches: null argument"); return -1; }
+    // matchers.cpp:119 CV_Assert(descriptors1.type() == descriptors2.type()) -- the C++ shim throws
+    if (cv_type1 != cv_type2) { mpl_set_error("CV_Assert(descriptors1.type() == descriptors2.type())"); return MPL_ERR_ASSERT; }
+    if (n_keypoints1 < 15 || n_keypoints2 < 15) { mpl_set_error("Too less keypoits!"); return -4; }             // :123-127
+    if (n_keypoints1 != rows1 || n_keypoints2 != rows2) {                                                        // :129-133
+        mpl_set_error("Number of descriptors must be equal to the number of keypoints!"); return -1;
+    }
+    const std::string m(matcher_name);
+    const bool linear = (m == "LINEAR"), nms = (m == "BRUTEFORCENMS");
+    if (!linear && !nms) { mpl_set_error("Matcher %s is not supported.", matcher_name); return -2; }            // :715-719 (no CPU fallback)
+    if (cv_type1 != CV_8U_ && cv_type1 != CV_32F_) {
+        // LINEAR :540-547 "Format of descriptors not supported!"; BRUTEFORCENMS CV_64F (:502-513) is out of scope
+        mpl_set_error("Format of descriptors not supported!"); return -1;
+    }
+    if (cols1 != cols2) { mpl_set_error("descriptor lengths differ (%d vs %d)", cols1, cols2); return -1; }
+    const int k = linear ? (ratio_test ? 2 : 1) : 2;       // :529-538 nn = ratioTest ? 2 : 1; nmslib_matchers.h:180 K = 2
+    std::vector<int32_t> idx((size_t)rows1 * k);
+    int rc;
+    if (cv_type1 == CV_8U_) {
+        std::vector<int32_t> d((size_t)rows1 * k);
+        const int ignore = nms ? ((cols1 & 1) ? 1 : 2) : 0;  // last packed 16-bit word never compared
+        if (nms && cols1 - ignore <= 0) { for (auto& v : d) v = 0; for (int qi = 0; qi < rows1; ++qi) for (int c = 0; c < k; ++c) idx[(size_t)qi * k + c] = c; rc = 0; }
+        else rc = mpl_knn2_hamming((const uint8_t*)desc1, rows1, step1, (const uint8_t*)desc2, rows2, step2, cols1, ignore, k, idx.data(), d.data());
+        if (rc) return -3;
+        mpl_ratio_matches_i32(idx.data(), d.data(), rows1, k, ratio_test, out, n_out);
+    } else {
+        std::vector<float> d((size_t)rows1 * k);
+        rc = mpl_knn2_l2f32((const float*)desc1, rows1, step1, (const float*)desc2, rows2, step2, cols1, nms ? 1 : 0, k, idx.data(), d.data());
+        if (rc) return -3;
+        mpl_ratio_matches_f32(idx.data(), d.data(), rows1, k, ratio_test, out, n_out);
+    }
+    if (linear && *n_out < 2) { mpl_set_error("Too less remaining matches using the LINEAR matcher."); return -3; }  // :709-713
+    return 0;
+}

@@ -1,0 +1,294 @@
+// knn_hamming.cu -- brute-force Hamming k-NN (k = 2) for binary descriptors, sm_100a.
+//
+// Replaces the hot loop of the reference's LINEAR matcher for CV_8U descriptors
+//   cvflann::Index<HammingLUT>(LinearIndexParams).knnSearch   (matchers.cpp:567-588, OpenCV 4.2.0 flann)
+// and of BRUTEFORCENMS (NMSLIB seq_search + bit_hamming, nmslib_matchers.h:159-424,
+// seqsearch.cc:146-152, space_bit_hamming.cc:33-42).  The BRUTEFORCENMS "last 16-bit word is
+// ignored" quirk is applied by the row packer (nbytes_used < nbytes), not by the scan kernel.
+//
+// Data layout in HBM: every descriptor row is w16 x 16 bytes, zero padded (ORB 32 B -> w16 = 2;
+// BRISK/FREAK 64 B and AKAZE 61 B -> w16 = 4).  Zero padding adds 0 to every XOR/popcount.
+//
+// Scan kernel (hamming_top2_kernel):
+//   * one thread owns RQ query descriptors in registers (RQ*W16*4 32-bit words);
+//   * the CTA's train split is streamed through a 4-stage shared-memory ring, each 8 KB tile
+//     fetched by ONE elected thread with a 1-D TMA bulk copy (cp.async.bulk ... mbarrier
+//     complete_tx; SASS: UBLKCP) -- 128-bit coalesced by construction;
+//   * every thread reads the same train row (LDS.128 broadcast), XORs against its RQ queries,
+//     __popc, and keeps a register-resident top-2 as two 32-bit keys (dist << 20 | row-in-split)
+//     updated with 3 integer min/max per pair; key order == (dist, trainIdx) lexicographic,
+//     i.e. cvflann's KNNUniqueResultSet order (ties -> lowest train index);
+//   * grid = (query blocks) x (train splits) sized to a multiple of the SM count; per-split
+//     results are 64-bit keys (dist << 32 | global trainIdx) merged by merge_top2_kernel,
+//     which is also the merge applied after the NCCL all-gather of the train-sharded path.
+//
+// Roofline: POPC issue rate (16 lanes/clk/SM), W16*4 POPC per pair; HBM traffic is compulsory
+// bytes x (query blocks), irrelevant except for nq of a few rows.
+#include "mpl_common.cuh"
+
+namespace {
+
+constexpr int kThreads   = 256;
+constexpr int kTileBytes = 8192;      // bytes per TMA stage
+constexpr int kStages    = 4;
+constexpr int kIdxBits   = 20;        // rows per split <= 2^20 (key = dist << 20 | row)
+constexpr unsigned kKeyInvalid = 0xFFFFFFFFu;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (bytes % 16 == 0).
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int W16> struct HammingCfg {
+    static constexpr int RQ = (W16 <= 2) ? 4 : (W16 <= 4 ? 2 : 1);   // queries per thread
+    static constexpr int kTileRows = kTileBytes / (16 * W16);
+    static constexpr int kQueriesPerCta = kThreads * RQ;
+};
+
+template <int W16>
+__global__ void __launch_bounds__(kThreads)
+hamming_top2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t, int nt,
+                    int rows_per_split, long long train_offset, mpl_key64* __restrict__ partial)
+{
+    using Cfg = HammingCfg<W16>;
+    constexpr int RQ = Cfg::RQ;
+    constexpr int TR = Cfg::kTileRows;
+    __shared__ __align__(128) uint4 tile[kStages][kTileBytes / 16];
+    __shared__ __align__(8) uint64_t full_bar[kStages];
+
+    // blockIdx.z = image pair of a batch (independent problems of identical shape)
+    q += (size_t)blockIdx.z * nq * W16;
+    t += (size_t)blockIdx.z * nt * W16;
+    partial += (size_t)blockIdx.z * gridDim.y * nq * 2;
+    const int tid   = threadIdx.x;
+    const int split = blockIdx.y;
+    const int row0  = split * rows_per_split;                        // first train row of this split
+    const int rows  = min(rows_per_split, nt - row0);                // > 0 by construction
+    const int n_tiles = (rows + TR - 1) / TR;
+
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int tile_i) {
+        const int s = tile_i % kStages;
+        const int r = min(TR, rows - tile_i * TR);
+        const uint32_t bytes = (uint32_t)r * 16u * W16;
+        mbar_expect_tx(&full_bar[s], bytes);
+        tma_bulk_g2s(&tile[s][0], t + (size_t)(row0 + tile_i * TR) * W16, bytes, &full_bar[s]);
+    };
+    if (tid == 0)
+        for (int i = 0; i < kStages && i < n_tiles; ++i) issue(i);
+
+    // ---- this thread's RQ query descriptors -> registers ----
+    uint32_t qr[RQ][W16 * 4];
+    const int qbase = blockIdx.x * Cfg::kQueriesPerCta;
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        const int qi = qbase + j * kThreads + tid;
+#pragma unroll
+        for (int w = 0; w < W16; ++w) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (qi < nq) v = __ldg(q + (size_t)qi * W16 + w);
+            qr[j][4 * w + 0] = v.x; qr[j][4 * w + 1] = v.y; qr[j][4 * w + 2] = v.z; qr[j][4 * w + 3] = v.w;
+        }
+    }
+    unsigned k1[RQ], k2[RQ];
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) { k1[j] = kKeyInvalid; k2[j] = kKeyInvalid; }
+
+    for (int ti = 0; ti < n_tiles; ++ti) {
+        const int s = ti % kStages;
+        mbar_wait(&full_bar[s], (uint32_t)((ti / kStages) & 1));
+        const int r_in_tile = min(TR, rows - ti * TR);
+        const uint4* srow = &tile[s][0];
+        unsigned lrow = (unsigned)(ti * TR);
+#pragma unroll 2
+        for (int r = 0; r < r_in_tile; ++r, ++lrow) {
+            uint32_t tr[W16 * 4];
+#pragma unroll
+            for (int w = 0; w < W16; ++w) {
+                const uint4 v = srow[r * W16 + w];                     // LDS.128, warp-wide broadcast
+                tr[4 * w + 0] = v.x; tr[4 * w + 1] = v.y; tr[4 * w + 2] = v.z; tr[4 * w + 3] = v.w;
+            }
+#pragma unroll
+            for (int j = 0; j < RQ; ++j) {
+                unsigned d = 0;
+#pragma unroll
+                for (int w = 0; w < W16 * 4; ++w) d += __popc(qr[j][w] ^ tr[w]);
+                const unsigned key = (d << kIdxBits) | lrow;
+                const unsigned hi  = max(k1[j], key);
+                k1[j] = min(k1[j], key);
+                k2[j] = min(k2[j], hi);
+            }
+        }
+        __syncthreads();                                               // every warp is done with stage s
+        if (tid == 0 && ti + kStages < n_tiles) issue(ti + kStages);
+    }
+
+    // ---- per-split result: 64-bit keys with GLOBAL train indices ----
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        const int qi = qbase + j * kThreads + tid;
+        if (qi >= nq) continue;
+        const unsigned kk[2] = {k1[j], k2[j]};
+        ulonglong2 out;
+        mpl_key64 o[2];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            if (kk[c] == kKeyInvalid) o[c] = MPL_KEY_INVALID;
+            else {
+                const unsigned d = kk[c] >> kIdxBits;
+                const long long gi = train_offset + row0 + (long long)(kk[c] & ((1u << kIdxBits) - 1));
+                o[c] = ((mpl_key64)d << 32) | (mpl_key64)(uint32_t)gi;
+            }
+        }
+        out.x = o[0]; out.y = o[1];
+        reinterpret_cast<ulonglong2*>(partial)[(size_t)split * nq + qi] = out;
+    }
+}
+
+// Pack rows of `nbytes_used` payload bytes (src stride src_step) into w16*16-byte zero-padded rows.
+__global__ void pack_rows_u8_kernel(const uint8_t* __restrict__ src, int n, size_t src_step, int nbytes_used,
+                                    uint8_t* __restrict__ dst, int row_bytes)
+{
+    const size_t total = (size_t)n * row_bytes;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / row_bytes;
+        const int c = (int)(i - r * row_bytes);
+        dst[i] = c < nbytes_used ? src[r * src_step + c] : (uint8_t)0;
+    }
+}
+
+// Top-2 of n_parts candidate pairs per query.  One thread per query, coalesced 16-byte loads.
+// Used (a) across the train splits of one GPU, (b) across ranks after the NCCL all-gather.
+__global__ void merge_top2_kernel(const ulonglong2* __restrict__ partial, int n_parts, int nq, int k,
+                                  int32_t* __restrict__ idx, uint32_t* __restrict__ dist, int float_sqrt,
+                                  ulonglong2* __restrict__ merged)
+{
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
+    for (int p = 0; p < n_parts; ++p) {
+        const ulonglong2 v = partial[(size_t)p * nq + qi];
+        // v.x <= v.y inside one part
+        mpl_key64 hi = max(b0, v.x);
+        b0 = min(b0, v.x);
+        b1 = min(b1, hi);
+        b1 = min(b1, v.y);
+    }
+    if (merged) merged[qi] = make_ulonglong2(b0, b1);
+    if (idx) {
+        const mpl_key64 kk[2] = {b0, b1};
+        for (int c = 0; c < k; ++c) {
+            int32_t id; uint32_t dv;
+            if (kk[c] == MPL_KEY_INVALID) { id = -1; dv = float_sqrt >= 0 ? 0x7F7FFFFFu /*FLT_MAX*/ : 0x7FFFFFFFu /*INT_MAX*/; }
+            else {
+                id = (int32_t)(uint32_t)(kk[c] & 0xFFFFFFFFull);
+                dv = (uint32_t)(kk[c] >> 32);
+                if (float_sqrt == 1) dv = __float_as_uint(sqrtf(__uint_as_float(dv)));
+            }
+            idx[(size_t)qi * k + c] = id;
+            dist[(size_t)qi * k + c] = dv;
+        }
+    }
+}
+
+template <int W16>
+int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, int n_pairs, long long train_offset,
+             mpl_key64* partial, cudaStream_t st)
+{
+    using Cfg = HammingCfg<W16>;
+    int rows_per_split = (nt + n_splits - 1) / n_splits;
+    rows_per_split = ((rows_per_split + Cfg::kTileRows - 1) / Cfg::kTileRows) * Cfg::kTileRows;
+    if (rows_per_split > (1 << kIdxBits)) { mpl_set_error("hamming: split of %d rows exceeds 2^20", rows_per_split); return MPL_ERR_LIMIT; }
+    const int eff_splits = (nt + rows_per_split - 1) / rows_per_split;
+    if (eff_splits != n_splits) { mpl_set_error("hamming: internal split mismatch %d vs %d", eff_splits, n_splits); return MPL_ERR_BAD_ARG; }
+    dim3 grid((nq + Cfg::kQueriesPerCta - 1) / Cfg::kQueriesPerCta, n_splits, n_pairs);
+    hamming_top2_kernel<W16><<<grid, kThreads, 0, st>>>((const uint4*)q, nq, (const uint4*)t, nt, rows_per_split,
+                                                         train_offset, partial);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}
+
+int queries_per_cta(int w16) { return w16 <= 2 ? kThreads * 4 : (w16 <= 4 ? kThreads * 2 : kThreads); }
+int tile_rows(int w16) { return kTileBytes / (16 * w16); }
+
+}  // namespace
+
+// Number of train splits so that grid = q-blocks x splits is ~4 CTAs per SM (a multiple of the SM
+// count when the split count is free), every split <= 2^20 rows and a whole number of TMA tiles.
+int mpl_hamming_pick_splits(int nq, int nt, int w16, int sm_count)
+{
+    const int qblocks = (nq + queries_per_cta(w16) - 1) / queries_per_cta(w16);
+    const int tr = tile_rows(w16);
+    int want = (4 * sm_count + qblocks - 1) / qblocks;
+    const int max_splits = (nt + tr - 1) / tr;
+    const int min_splits = (nt + (1 << kIdxBits) - 1) / (1 << kIdxBits);
+    if (want > max_splits) want = max_splits;
+    if (want < min_splits) want = min_splits;
+    if (want < 1) want = 1;
+    // normalise so that ceil(nt / rows_per_split) == splits after rounding rows_per_split up to a tile
+    int rps = (nt + want - 1) / want;
+    rps = ((rps + tr - 1) / tr) * tr;
+    return (nt + rps - 1) / rps;
+}
+
+int mpl_launch_pack_rows_u8(const uint8_t* src, int n, size_t src_step, int nbytes_used, uint8_t* dst, int w16,
+                            cudaStream_t st)
+{
+    if (n <= 0) return MPL_OK;
+    const size_t total = (size_t)n * w16 * 16;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    pack_rows_u8_kernel<<<blocks, 256, 0, st>>>(src, n, src_step, nbytes_used, dst, w16 * 16);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_hamming_top2(const uint8_t* q, int nq, const uint8_t* t, int nt, int w16, int n_splits, int n_pairs,
+                            long long train_offset, mpl_key64* partial, cudaStream_t st)
+{
+    if (nq <= 0 || nt <= 0 || n_pairs <= 0) return MPL_OK;
+    if (n_pairs > 65535) { mpl_set_error("hamming: at most 65535 pairs per batch launch"); return MPL_ERR_LIMIT; }
+    switch (w16) {
+        case 1:  return launch_w<1>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        case 2:  return launch_w<2>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        case 4:  return launch_w<4>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        case 8:  return launch_w<8>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        case 16: return launch_w<16>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        default: mpl_set_error("hamming: unsupported row width w16=%d (use 1,2,4,8,16)", w16); return MPL_ERR_BAD_ARG;
+    }
+}
+
+int mpl_launch_merge_top2(const mpl_key64* partial, int n_parts, int nq, int k, int32_t* idx, void* dist,
+                          int float_sqrt, mpl_key64* merged_keys, cudaStream_t st)
+{
+    if (nq <= 0) return MPL_OK;
+    merge_top2_kernel<<<(nq + 127) / 128, 128, 0, st>>>((const ulonglong2*)partial, n_parts, nq, k, idx,
+                                                        (uint32_t*)dist, float_sqrt, (ulonglong2*)merged_keys);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}

@@ -1,0 +1,35 @@
+// mpl_ctx.h -- process-wide device context of libmplb200 (one device, one stream, growable scratch).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <mutex>
+#include "mpl_common.cuh"
+
+struct MplBuf {
+    void*  ptr = nullptr;
+    size_t cap = 0;
+    int  ensure(size_t bytes);   // grow (never shrinks); contents are NOT preserved
+    void release();
+};
+
+enum { MPL_BUF_Q = 0, MPL_BUF_T, MPL_BUF_RAW, MPL_BUF_PART, MPL_BUF_KEYS, MPL_BUF_IDX, MPL_BUF_DIST,
+       MPL_BUF_R0, MPL_BUF_R1, MPL_BUF_R2, MPL_BUF_R3, MPL_BUF_R4, MPL_BUF_R5, MPL_BUF_COUNT };
+
+struct MplCtx {
+    bool ready = false;
+    int device = -1, sm_count = 148, cc_major = 0, cc_minor = 0;
+    size_t total_mem = 0;
+    cudaStream_t stream = nullptr;
+    MplBuf bufs[MPL_BUF_COUNT];
+};
+
+MplCtx*     mpl_ctx();
+std::mutex& mpl_ctx_mutex();
+int         mpl_ensure_ctx_locked();   // caller holds mpl_ctx_mutex()
+
+// ---- knn_l2_tc.cu: tcgen05 ranking kernel + exact re-rank --------------------------------------
+bool   mpl_l2tc_supported(int nq, int nt, int dim);
+size_t mpl_l2tc_scratch_bytes(int nq, int nt, int dim, int sm_count);
+int    mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int nt, size_t t_ld, int dim, int sqrt_out,
+                     long long train_offset, void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out,
+                     int sm_count, cudaStream_t st);
