@@ -1,0 +1,80 @@
+"""ctypes binding of libmplb200.so (include/mplb200.h).
+
+The product path FAILS LOUDLY when the CUDA library is missing or no B200 is visible: there is
+no CPU fallback and nothing here imports oracle/.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmplb200.so")
+
+c_int, c_size_t, c_void_p, c_char_p = ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_char_p
+c_ll, c_double = ctypes.c_longlong, ctypes.c_double
+
+
+class MplError(RuntimeError):
+    pass
+
+
+class DMatch(ctypes.Structure):
+    """cv::DMatch layout (16 bytes)."""
+    _fields_ = [("queryIdx", ctypes.c_int32), ("trainIdx", ctypes.c_int32), ("imgIdx", ctypes.c_int32),
+                ("distance", ctypes.c_float)]
+
+
+# name -> (restype, argtypes).  Every symbol include/mplb200.h declares is listed here; the CPU test
+# suite checks that the built library exports each of them.
+SIGNATURES = {
+    "mpl_init": (c_int, [c_int]),
+    "mpl_shutdown": (c_int, []),
+    "mpl_last_error": (c_char_p, []),
+    "mpl_device_info": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_kernel_launch_count": (c_ll, []),
+    "mpl_knn2_hamming": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_knn2_l2f32": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_set_l2_path": (c_int, [c_int]),
+    "mpl_ratio_matches_i32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_ratio_matches_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_get_matches_api": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_size_t, c_int,
+                                    c_void_p, c_int, c_int, c_size_t, c_int, c_char_p, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_knn_hamming_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mpl_pack_rows_u8_dev": (c_int, [c_void_p, c_int, c_size_t, c_int, c_void_p, c_int, c_void_p]),
+    "mpl_knn2_hamming_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "mpl_merge_top2_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_knn2_hamming_batch_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_knn_l2_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mpl_knn2_l2f32_dev": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen libmplb200.so and set the prototypes.  Raises MplError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MplError("libmplb200.so is not built (%s); run `python -c 'import __graft_entry__ as g; g.build()'`. "
+                       "There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)       # AttributeError if the .so is stale
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().mpl_last_error().decode("utf-8", "replace")
+
+
+def check(rc, what):
+    if rc != 0:
+        raise MplError("%s failed (%d): %s" % (what, rc, last_error()))
+
+
+def ptr(a):
+    """Host pointer of a numpy array (None -> NULL)."""
+    return None if a is None else ctypes.c_void_p(a.ctypes.data)

@@ -1,0 +1,100 @@
+"""Host-side mirror of the reference's matchinglib API for the hot path.
+
+`getMatches` keeps the reference's name, argument meaning, defaults and return codes
+(matchinglib_poselib/source/matchinglib/include/matchinglib/matchinglib_matchers.h:61-64,
+source/matchers.cpp:115-736) for matcher_name in {"LINEAR", "BRUTEFORCENMS"}; every other matcher
+returns -2 (the B200 build has no CPU fallback).  cv::Mat -> numpy array (uint8 or float32, 2-D),
+std::vector<cv::KeyPoint> -> anything with len(), std::vector<cv::DMatch> -> list filled in place
+with (queryIdx, trainIdx, distance) tuples or a structured numpy array via getMatchesArray.
+All arithmetic runs in libmplb200.so on the GPU.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+CV_8U, CV_32F, CV_64F = 0, 5, 6
+DMATCH_DTYPE = np.dtype([("queryIdx", "<i4"), ("trainIdx", "<i4"), ("imgIdx", "<i4"), ("distance", "<f4")])
+
+_NP_TO_CV = {np.dtype(np.uint8): CV_8U, np.dtype(np.float32): CV_32F, np.dtype(np.float64): CV_64F,
+             np.dtype(np.int8): 1, np.dtype(np.uint16): 2, np.dtype(np.int16): 3, np.dtype(np.int32): 4}
+
+
+def _mat_fields(m):
+    """(data pointer keep-alive array, rows, cols, step, cv type) of a 2-D row-major array.
+    Like the reference (matchers.cpp:567, 634) the data is read in place with cols as row length;
+    arrays whose rows are not unit-stride are made contiguous first."""
+    a = np.asarray(m)
+    if a.ndim != 2:
+        raise ValueError("descriptor matrix must be 2-D")
+    if a.dtype not in _NP_TO_CV:
+        raise ValueError("unsupported descriptor dtype %s" % a.dtype)
+    if a.shape[1] > 0 and a.strides[1] != a.itemsize:
+        a = np.ascontiguousarray(a)
+    step = a.strides[0] if a.shape[0] > 1 else a.shape[1] * a.itemsize
+    if step < a.shape[1] * a.itemsize:
+        a = np.ascontiguousarray(a)
+        step = a.shape[1] * a.itemsize
+    return a, a.shape[0], a.shape[1], step, _NP_TO_CV[a.dtype]
+
+
+def getMatchesArray(keypoints1, keypoints2, descriptors1, descriptors2, imgSi=None, matcher_name="GMBSOF",
+                    VFCrefine=False, ratioTest=True, descriptor_name="", idxPars_NMSLIB="", queryPars_NMSLIB="",
+                    nr_threads=0):
+    """Returns (err, matches) with matches a numpy array of DMATCH_DTYPE (cv::DMatch layout)."""
+    lib = _lib.load()
+    if VFCrefine:
+        # matchers.cpp:722-733: optional VFC post-filter, outside the hot path (out of scope)
+        raise NotImplementedError("VFCrefine is outside the B200 hot path")
+    a1, r1, c1, s1, t1 = _mat_fields(descriptors1)
+    a2, r2, c2, s2, t2 = _mat_fields(descriptors2)
+    out = np.zeros(max(r1, 1), dtype=DMATCH_DTYPE)
+    n_out = ctypes.c_int(0)
+    err = lib.mpl_get_matches_api(len(keypoints1), len(keypoints2), _lib.ptr(a1), r1, c1, s1, t1,
+                                  _lib.ptr(a2), r2, c2, s2, t2, matcher_name.encode(), int(bool(ratioTest)),
+                                  int(nr_threads), _lib.ptr(out), ctypes.byref(n_out))
+    if err == -103:
+        raise AssertionError(_lib.last_error())          # cv::Exception from CV_Assert in the reference
+    return err, out[: n_out.value].copy()
+
+
+def getMatches(keypoints1, keypoints2, descriptors1, descriptors2, imgSi, finalMatches, matcher_name="GMBSOF",
+               VFCrefine=False, ratioTest=True, descriptor_name="", idxPars_NMSLIB="", queryPars_NMSLIB="",
+               nr_threads=0):
+    """matchinglib::getMatches.  finalMatches (a list) is cleared and filled; returns the reference's
+    int code: 0 ok, -1 wrong input, -2 matcher not supported, -3 matching failed, -4 too few keypoints."""
+    err, arr = getMatchesArray(keypoints1, keypoints2, descriptors1, descriptors2, imgSi, matcher_name, VFCrefine,
+                               ratioTest, descriptor_name, idxPars_NMSLIB, queryPars_NMSLIB, nr_threads)
+    del finalMatches[:]
+    if err in (0, -3):
+        finalMatches.extend((int(m["queryIdx"]), int(m["trainIdx"]), float(m["distance"])) for m in arr)
+    return err
+
+
+def knn2_hamming(query, train, k=2, ignore_tail_bytes=0):
+    """Raw k-NN (the cvflann / NMSLIB scan): returns (idx[nq,k] int32, dist[nq,k] int32)."""
+    lib = _lib.load()
+    q, nq, nb, qs, tq = _mat_fields(query)
+    t, nt, nb2, ts, tt = _mat_fields(train)
+    if tq != CV_8U or tt != CV_8U or (nb != nb2 and nq and nt):
+        raise ValueError("knn2_hamming needs uint8 matrices of equal width")
+    idx = np.empty((nq, k), np.int32)
+    dist = np.empty((nq, k), np.int32)
+    _lib.check(lib.mpl_knn2_hamming(_lib.ptr(q), nq, qs, _lib.ptr(t), nt, ts, nb, ignore_tail_bytes, k,
+                                    _lib.ptr(idx), _lib.ptr(dist)), "mpl_knn2_hamming")
+    return idx, dist
+
+
+def knn2_l2(query, train, k=2, sqrt_out=False):
+    """Raw k-NN for float32 descriptors: (idx[nq,k] int32, dist[nq,k] float32; squared unless sqrt_out)."""
+    lib = _lib.load()
+    q, nq, d, qs, tq = _mat_fields(query)
+    t, nt, d2, ts, tt = _mat_fields(train)
+    if tq != CV_32F or tt != CV_32F or (d != d2 and nq and nt):
+        raise ValueError("knn2_l2 needs float32 matrices of equal width")
+    idx = np.empty((nq, k), np.int32)
+    dist = np.empty((nq, k), np.float32)
+    _lib.check(lib.mpl_knn2_l2f32(_lib.ptr(q), nq, qs, _lib.ptr(t), nt, ts, d, int(bool(sqrt_out)), k,
+                                  _lib.ptr(idx), _lib.ptr(dist)), "mpl_knn2_l2f32")
+    return idx, dist

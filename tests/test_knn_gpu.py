@@ -1,0 +1,140 @@
+"""GPU parity: CUDA k-NN through the C ABI against the CPU oracle and the committed golden vectors.
+Bar: Hamming bit-exact (idx + dist); float LINEAR distances bit-exact, indices equal (ties resolved to the
+lowest train index on both sides); BRUTEFORCENMS float within 1e-5 relative."""
+import os
+
+import numpy as np
+import pytest
+
+import datagen
+from oracle import knn as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def m():
+    import __graft_entry__ as g
+    g.build()
+    import matchinglib_poselib_b200 as mod
+    mod._lib.check(mod._lib.load().mpl_init(0), "mpl_init")
+    return mod
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    return np.load(os.path.join(golden_dir, "knn_golden.npz"))
+
+
+@pytest.mark.parametrize("name", ["orb32", "akaze61", "brisk64", "odd7"])
+def test_hamming_golden(m, gold, name):
+    q, t = gold[name + "_q"], gold[name + "_t"]
+    idx, dist = m.knn2_hamming(q, t, 2, 0)
+    assert np.array_equal(idx, gold[name + "_lin_idx"]) and np.array_equal(dist, gold[name + "_lin_dist"])
+    nb = q.shape[1]
+    idx, dist = m.knn2_hamming(q, t, 2, 1 if nb & 1 else 2)
+    assert np.array_equal(dist, gold[name + "_nms_dist"])
+    strict = dist[:, 0] < dist[:, 1]
+    assert np.array_equal(idx[strict, 0], gold[name + "_nms_idx"][strict, 0])
+
+
+@pytest.mark.parametrize("nq,nt,nb", [(1, 1, 32), (1, 2, 32), (17, 5000, 32), (1500, 3000, 32), (1025, 257, 64),
+                                      (300, 4097, 61), (64, 700, 16), (50, 600, 128), (33, 300, 200), (8192, 8192, 32)])
+def test_hamming_vs_oracle(m, nq, nt, nb):
+    q, t = datagen.binary_descriptors(nq, nt, nb, seed=nq * 7 + nt)
+    for k in (1, 2):
+        for mode, ign in ((0, 0), (1, 1 if nb & 1 else 2)):
+            idx, dist = m.knn2_hamming(q, t, k, ign)
+            oi, od = orc.knn_hamming(q, t, k, mode, threads=8)
+            assert np.array_equal(dist, od), (nq, nt, nb, k, mode)
+            assert np.array_equal(idx, oi), (nq, nt, nb, k, mode)
+
+
+def test_hamming_strided_and_empty(m):
+    q, t = datagen.binary_descriptors(100, 300, 32, seed=9)
+    big_q = np.zeros((100, 48), np.uint8); big_q[:, :32] = q
+    big_t = np.zeros((300, 40), np.uint8); big_t[:, :32] = t
+    idx, dist = m.knn2_hamming(big_q[:, :32], big_t[:, :32])        # row stride != row bytes (cv::Mat::step)
+    oi, od = orc.knn_hamming(q, t)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    idx, dist = m.knn2_hamming(np.zeros((0, 32), np.uint8), t)
+    assert idx.shape == (0, 2)
+    idx, dist = m.knn2_hamming(q, np.zeros((0, 32), np.uint8))
+    assert (idx == -1).all() and (dist == np.iinfo(np.int32).max).all()
+
+
+@pytest.mark.parametrize("name", ["sift128", "surf64", "odd61"])
+def test_l2_golden(m, gold, name):
+    q, t = gold[name + "_q"], gold[name + "_t"]
+    idx, dist = m.knn2_l2(q, t, 2, False)
+    assert np.array_equal(idx, gold[name + "_lin_idx"])
+    assert np.array_equal(dist.view(np.int32), gold[name + "_lin_dist"].view(np.int32))
+    idx, dist = m.knn2_l2(q, t, 2, True)
+    np.testing.assert_allclose(dist, gold[name + "_nms_dist"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("nq,nt,d,kind", [(1, 1, 128, "sift"), (70, 1000, 128, "sift"), (1000, 3000, 128, "sift"),
+                                           (129, 777, 64, "signed"), (200, 1500, 128, "signed"), (64, 300, 61, "signed"),
+                                           (2500, 20000, 128, "sift")])
+def test_l2_vs_oracle(m, path, nq, nt, d, kind):
+    """path 1 = exact SIMT scan, 2 = tcgen05 ranking + exact re-rank.  Distances bit-exact in cvflann order;
+    indices equal (both sides break exact ties toward the lowest train index)."""
+    lib = m._lib.load()
+    q, t = datagen.sift_like(nq, nt, d, seed=nq + nt) if kind == "sift" else datagen.signed_float(nq, nt, d, seed=nq + nt)
+    lib.mpl_set_l2_path(path)
+    try:
+        try:
+            idx, dist = m.knn2_l2(q, t, 2, False)
+        except m._lib.MplError as e:
+            if path == 2 and "unsupported" in str(e):
+                pytest.skip("tensor-core path does not take this shape")
+            raise
+    finally:
+        lib.mpl_set_l2_path(0)
+    oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)), (path, nq, nt, d)
+    assert np.array_equal(idx, oi)
+
+
+def test_l2_nmslib_mode(m):
+    q, t = datagen.signed_float(150, 900, 64, seed=3)
+    idx, dist = m.knn2_l2(q, t, 2, True)
+    oi, od = orc.knn_l2(q, t, 2, 1)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
+
+
+@pytest.mark.parametrize("matcher", ["LINEAR", "BRUTEFORCENMS"])
+@pytest.mark.parametrize("dtype", ["u8", "f32"])
+@pytest.mark.parametrize("ratio", [True, False])
+def test_get_matches_api(m, matcher, dtype, ratio):
+    if dtype == "u8":
+        d1, d2 = datagen.binary_descriptors(400, 500, 32, seed=11)
+    else:
+        d1, d2 = datagen.sift_like(400, 500, 128, seed=12)
+    kp1, kp2 = [None] * 400, [None] * 500
+    err, got = m.getMatchesArray(kp1, kp2, d1, d2, None, matcher, False, ratio)
+    oerr, exp = orc.get_matches(d1, d2, matcher, ratio)
+    assert err == oerr == 0
+    assert np.array_equal(got["queryIdx"], exp["queryIdx"])
+    if dtype == "u8" or matcher == "LINEAR":
+        if ratio:
+            assert np.array_equal(got["trainIdx"], exp["trainIdx"])
+        assert np.array_equal(got["distance"].view(np.int32), exp["distance"].view(np.int32))
+    else:
+        np.testing.assert_allclose(got["distance"], exp["distance"], rtol=1e-5)
+    lst = []
+    assert m.getMatches(kp1, kp2, d1, d2, None, lst, matcher, False, ratio) == 0 and len(lst) == len(exp)
+
+
+def test_get_matches_error_codes(m):
+    d1, d2 = datagen.binary_descriptors(40, 50, 32, seed=13, adversarial=False)
+    d1 = np.random.default_rng(0).integers(0, 256, (40, 32), dtype=np.uint8)
+    kp1, kp2 = [None] * 40, [None] * 50
+    assert m.getMatchesArray(kp1[:10], kp2, d1[:10], d2, None, "LINEAR")[0] == -4
+    assert m.getMatchesArray(kp1[:39], kp2, d1, d2, None, "LINEAR")[0] == -1
+    assert m.getMatchesArray(kp1, kp2, d1, d2, None, "GMBSOF")[0] == -2
+    assert m.getMatchesArray(kp1, kp2, d1, d2, None, "LINEAR")[0] == -3
+    assert m.getMatchesArray(kp1, kp2, d1.astype(np.float64), d2.astype(np.float64), None, "LINEAR")[0] == -1
+    with pytest.raises(AssertionError):
+        m.getMatchesArray(kp1, kp2, d1, d2.astype(np.float32), None, "LINEAR")
