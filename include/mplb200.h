@@ -112,6 +112,38 @@ int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t,
                           int sqrt_out, long long train_offset, void* d_scratch, size_t scratch_bytes,
                           void* d_keys_out, void* stream);
 
+/* ---- RANSAC 5-point essential matrix ---------------------------------------------------------
+ * mpl_ransac5pt replaces CvModelEstimator3::runRANSAC with CvEMEstimator kernels
+ *   (MP/poselib/source/five-point-nister/modelest.cpp:343-474; five-point.cpp:366-503):
+ *   p1, p2: n x 2 doubles (camera-normalised coordinates, row-major, contiguous);
+ *   samples: h x 5 int32 PRE-DRAWN minimal samples (NULL: max_iters samples are drawn inside with the
+ *   getSubset/checkSubset rules of modelest.cpp:567-650 from an internal generator, mpl_ransac_set_seed);
+ *   th: Sampson threshold (inlier iff (float)err <= th*th); max_iters (reference: 1000) and conf
+ *   (reference: 0.999) drive the same sequential selection + adaptive stop as modelest.cpp:377-416, replayed
+ *   over per-model (count, sum err) computed on the device; refine != 0 adds the least-squares refit on all
+ *   inliers (modelest.cpp:420-464).  Outputs: E[9] row-major (unit Frobenius norm), mask[n] 0/1, *n_inl
+ *   (0 = no model: runRANSAC returned false), *iters_run.  Optional debug outputs (NULL to skip; when any is
+ *   given all h samples are solved and scored): models [<=10h][9] dense in sample-major order,
+ *   n_models[h], counts[<=10h], errsums[<=10h].
+ * mpl_estimate_essential_api mirrors poselib::estimateEssentialMat(E, p1, p2, "RANSAC", threshold, refine, mask)
+ *   (MP/poselib/source/pose_estim.cpp:857-890 -> findEssentialMat five-point.cpp:69-148): returns 1/0 like the
+ *   reference's bool (negative MPL_ERR_* on failure; MPL_ERR_ASSERT where CV_Assert would throw; any method
+ *   other than "RANSAC" is refused -- no CPU fallback).  n == 5: solver only, *n_E models stacked in E_out. */
+int mpl_ransac_set_seed(unsigned long long seed);
+int mpl_ransac_draw_samples(const double* p1, const double* p2, int n, int h, int32_t* samples, int* n_drawn);
+int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double th,
+                  int max_iters, double conf, int refine, double* E, uint8_t* mask, int* n_inl, int* iters_run,
+                  double* models, int32_t* n_models, int32_t* counts, double* errsums);
+int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const char* method, double threshold,
+                               int refine, double* E_out, int* n_E, uint8_t* mask);
+/* device-pointer stages (enqueue only): corr = n x 32-byte records (x1,y1,x2,y2); models h x 90 doubles;
+ * offsets h+1 int32 (offsets[h] = number of dense models); dense up to 10h x 9 doubles. */
+int mpl_ransac_pack_corr_dev(const void* d_p1, const void* d_p2, int n, void* d_corr, void* stream);
+int mpl_ransac_solve_dev(const void* d_corr, int n, const void* d_samples, int h, void* d_models, void* d_n_models,
+                         void* d_offsets, void* d_dense, void* stream);
+int mpl_ransac_score_dev(const void* d_dense, int m, const void* d_corr, int n, double th, void* d_counts,
+                         void* d_errsums, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,7 +6,8 @@ josefmaierfl/matchinglib_poselib behind the reference's own API names.
 
 Everything computes in lib/libmplb200.so (hand-written CUDA, C ABI in include/mplb200.h).
 """
-from . import _lib, matchinglib  # noqa: F401
+from . import _lib, matchinglib, poselib  # noqa: F401
 from .matchinglib import getMatches, getMatchesArray, knn2_hamming, knn2_l2  # noqa: F401
+from .poselib import estimateEssentialMat, ransac5pt  # noqa: F401
 
-__all__ = ["getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib"]
+__all__ = ["getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib", "poselib", "estimateEssentialMat", "ransac5pt"]

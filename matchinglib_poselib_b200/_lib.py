@@ -45,6 +45,14 @@ SIGNATURES = {
     "mpl_knn2_hamming_batch_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_knn_l2_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mpl_knn2_l2f32_dev": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "mpl_ransac_set_seed": (c_int, [ctypes.c_ulonglong]),
+    "mpl_ransac_draw_samples": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_ransac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_double, c_int,
+                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_estimate_essential_api": (c_int, [c_void_p, c_void_p, c_int, c_char_p, c_double, c_int, c_void_p, c_void_p, c_void_p]),
+    "mpl_ransac_pack_corr_dev": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "mpl_ransac_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_ransac_score_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None

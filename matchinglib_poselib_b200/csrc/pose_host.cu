@@ -1,0 +1,313 @@
+// pose_host.cu -- host side of the pose half of the hot path (C ABI in include/mplb200.h):
+//   mpl_ransac5pt              runRANSAC over pre-drawn (or internally drawn) minimal samples
+//   mpl_estimate_essential_api poselib::estimateEssentialMat(..., "RANSAC", ...) over raw arrays
+//   mpl_ransac_*_dev           device-pointer stages for the benchmark / device-resident pipelines
+// Host logic here is what the reference also does sequentially and cheaply: the model selection replay
+// (modelest.cpp:394-415), cvRANSACUpdateNumIters1 (:86-109), getSubset/checkSubset (:567-650) and the small
+// dense linear algebra of the refit (9x9 symmetric eigenproblem).  Every O(models x correspondences) and
+// O(samples) computation runs in ransac5pt.cu on the device.
+#include "mpl_common.cuh"
+#include "mpl_ctx.h"
+#include "mpl_ransac.h"
+#include "../../include/mplb200.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+// cvRANSACUpdateNumIters1 (modelest.cpp:86-109)
+static int update_num_iters(double p, double ep, int model_points, int max_iters)
+{
+    p = std::fmax(p, 0.); p = std::fmin(p, 1.);
+    ep = std::fmax(ep, 0.); ep = std::fmin(ep, 1.);
+    double num = std::fmax(1. - p, DBL_MIN);
+    double denom = 1. - std::pow(1. - ep, model_points);
+    if (denom < DBL_MIN) return 0;
+    num = std::log(num); denom = std::log(denom);
+    return denom >= 0 || -num >= (double)max_iters * (-denom) ? max_iters : (int)std::round(num / denom);
+}
+
+struct Replay { int best_model = -1; int best_count = 0; int iters_run = 0; double errminsum = DBL_MAX; };
+
+// modelest.cpp:377-416 applied to precomputed per-model (count, errsum); models of sample s are
+// offsets[s] .. offsets[s+1]-1 in solver order.
+static Replay replay_selection(const int32_t* counts, const double* errsums, const int32_t* offsets, int h, int n,
+                               double conf, int max_iters)
+{
+    Replay r;
+    int niters = max_iters;
+    int it = 0;
+    for (; it < niters && it < h; ++it) {
+        for (int m = offsets[it]; m < offsets[it + 1]; ++m) {
+            const int good = counts[m];
+            if (good > std::max(r.best_count, 4)) {
+                r.best_model = m; r.best_count = good;
+                niters = update_num_iters(conf, (double)(n - good) / n, 5, niters);
+                r.errminsum = errsums[m];
+            } else if (good == std::max(r.best_count, 5) && r.errminsum < DBL_MAX && r.errminsum > errsums[m]) {
+                r.best_model = m; r.errminsum = errsums[m];
+            }
+        }
+    }
+    r.iters_run = it;
+    return r;
+}
+
+// cyclic Jacobi eigen-decomposition of a symmetric 9x9 matrix; V columns = eigenvectors
+static void jacobi_eig9(double A[9][9], double V[9][9], double w[9])
+{
+    for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) V[i][j] = (i == j);
+    for (int sweep = 0; sweep < 100; ++sweep) {
+        double off = 0, diag = 0;
+        for (int i = 0; i < 9; ++i) { diag += A[i][i] * A[i][i]; for (int j = i + 1; j < 9; ++j) off += A[i][j] * A[i][j]; }
+        if (off <= 1e-60 * diag || off == 0) break;
+        for (int p = 0; p < 8; ++p)
+            for (int q = p + 1; q < 9; ++q) {
+                if (A[p][q] == 0) continue;
+                const double theta = (A[q][q] - A[p][p]) / (2 * A[p][q]);
+                const double t = (theta >= 0 ? 1 : -1) / (std::fabs(theta) + std::sqrt(theta * theta + 1));
+                const double c = 1 / std::sqrt(t * t + 1), s = t * c;
+                for (int k = 0; k < 9; ++k) { const double x = A[k][p], y = A[k][q]; A[k][p] = c * x - s * y; A[k][q] = s * x + c * y; }
+                for (int k = 0; k < 9; ++k) { const double x = A[p][k], y = A[q][k]; A[p][k] = c * x - s * y; A[q][k] = s * x + c * y; }
+                for (int k = 0; k < 9; ++k) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - s * y; V[k][q] = s * x + c * y; }
+            }
+    }
+    for (int i = 0; i < 9; ++i) w[i] = A[i][i];
+}
+
+// ---- minimal-sample drawing: getSubset + checkSubset (modelest.cpp:567-650) ---------------------------
+static uint64_t g_seed = 0x9E3779B97F4A7C15ull;
+extern "C" int mpl_ransac_set_seed(unsigned long long seed) { g_seed = seed ? seed : 0x9E3779B97F4A7C15ull; return MPL_OK; }
+static inline uint32_t next_rand(uint64_t& s) { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16) & 0x7FFFFFFF; }
+
+static bool subset_ok(const double* p, const int* idx, int count)
+{   // checkSubset with checkPartialSubsets: only the last point of the prefix is tested
+    const int i = count - 1;
+    const double xi = p[2 * idx[i]], yi = p[2 * idx[i] + 1];
+    for (int j = 0; j < i; ++j) {
+        const double dx1 = p[2 * idx[j]] - xi, dy1 = p[2 * idx[j] + 1] - yi;
+        for (int k = 0; k < j; ++k) {
+            const double dx2 = p[2 * idx[k]] - xi, dy2 = p[2 * idx[k] + 1] - yi;
+            if (std::fabs(dx2 * dy1 - dy2 * dx1) <= (double)FLT_EPSILON * (std::fabs(dx1) + std::fabs(dy1) + std::fabs(dx2) + std::fabs(dy2)))
+                return false;
+        }
+    }
+    return true;
+}
+
+// Draws up to h samples; stops early (returns the number drawn) when getSubset fails after 300 attempts.
+extern "C" int mpl_ransac_draw_samples(const double* p1, const double* p2, int n, int h, int32_t* samples, int* n_drawn)
+{
+    if (!p1 || !p2 || !samples || !n_drawn || n < 5 || h < 0) { mpl_set_error("draw_samples: bad argument"); return MPL_ERR_BAD_ARG; }
+    uint64_t s = g_seed;
+    int drawn = 0;
+    for (; drawn < h; ++drawn) {
+        int idx[5]; int i = 0, iters = 0;
+        const int max_attempts = 300;
+        for (; iters < max_attempts; ++iters) {
+            for (i = 0; i < 5 && iters < max_attempts;) {
+                const int c = (int)(next_rand(s) % (uint32_t)n);
+                idx[i] = c;
+                int j = 0;
+                for (; j < i; ++j) if (c == idx[j]) break;
+                if (j < i) continue;
+                if (!subset_ok(p1, idx, i + 1) || !subset_ok(p2, idx, i + 1)) { ++iters; continue; }
+                ++i;
+            }
+            break;
+        }
+        if (!(i == 5 && iters < max_attempts)) break;
+        for (int j = 0; j < 5; ++j) samples[5 * drawn + j] = idx[j];
+    }
+    g_seed = s;
+    *n_drawn = drawn;
+    return MPL_OK;
+}
+
+// ---- device-pointer stages -----------------------------------------------------------------------------
+extern "C" int mpl_ransac_pack_corr_dev(const void* d_p1, const void* d_p2, int n, void* d_corr, void* stream)
+{
+    return mpl_launch_pack_corr((const double*)d_p1, (const double*)d_p2, n, d_corr, (cudaStream_t)stream);
+}
+extern "C" int mpl_ransac_solve_dev(const void* d_corr, int n, const void* d_samples, int h, void* d_models, void* d_n_models,
+                                    void* d_offsets, void* d_dense, void* stream)
+{
+    int rc = mpl_launch_fivept_solve(d_corr, n, (const int32_t*)d_samples, h, (double*)d_models, (int32_t*)d_n_models, (cudaStream_t)stream);
+    if (rc) return rc;
+    return mpl_launch_compact_models((const double*)d_models, (const int32_t*)d_n_models, h, (int32_t*)d_offsets, (double*)d_dense, (cudaStream_t)stream);
+}
+extern "C" int mpl_ransac_score_dev(const void* d_dense, int m, const void* d_corr, int n, double th, void* d_counts, void* d_errsums, void* stream)
+{
+    return mpl_launch_sampson_score((const double*)d_dense, m, d_corr, n, th, (int32_t*)d_counts, (double*)d_errsums, (cudaStream_t)stream);
+}
+
+// ---- runRANSAC ---------------------------------------------------------------------------------------
+extern "C" int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double th,
+                             int max_iters, double conf, int refine, double* E, uint8_t* mask, int* n_inl, int* iters_run,
+                             double* models_out, int32_t* n_models_out, int32_t* counts_out, double* errsums_out)
+{
+    if (!p1 || !p2 || n < 5 || h < 0 || !E || !n_inl || max_iters < 0) { mpl_set_error("mpl_ransac5pt: bad argument"); return MPL_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> g(mpl_ctx_mutex());
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    MplCtx* ctx = mpl_ctx();
+    cudaStream_t st = ctx->stream;
+    *n_inl = 0;
+    if (iters_run) *iters_run = 0;
+    std::vector<int32_t> drawn;
+    if (!samples) {                                           // draw like getSubset does
+        h = max_iters;
+        drawn.resize((size_t)5 * (h > 0 ? h : 1));
+        int nd = 0;
+        if ((rc = mpl_ransac_draw_samples(p1, p2, n, h, drawn.data(), &nd))) return rc;
+        h = nd; samples = drawn.data();
+    }
+    const bool want_all = models_out || n_models_out || counts_out || errsums_out;
+    const int h_use = want_all ? h : std::min(h, max_iters);   // later samples can never be reached by the loop
+    if (h_use == 0) return MPL_OK;
+    MplBuf* B = ctx->bufs;
+    if ((rc = B[MPL_BUF_R0].ensure((size_t)n * 32 + (size_t)n * 32))) return rc;     // p1|p2 staging then corr
+    if ((rc = B[MPL_BUF_R1].ensure((size_t)n * 32))) return rc;
+    if ((rc = B[MPL_BUF_R2].ensure((size_t)h_use * 20 + (size_t)(h_use + 1) * 8))) return rc;   // samples | n_models | offsets
+    if ((rc = B[MPL_BUF_R3].ensure((size_t)h_use * 90 * 8))) return rc;              // models [h][10][9]
+    if ((rc = B[MPL_BUF_R4].ensure((size_t)h_use * 90 * 8))) return rc;              // dense models
+    if ((rc = B[MPL_BUF_R5].ensure((size_t)h_use * 10 * 12 + (size_t)n * 8 + 4096 + 148 * 45 * 8))) return rc;   // counts | errsums | mask | misc
+    double* d_p1 = (double*)B[MPL_BUF_R0].ptr; double* d_p2 = d_p1 + 2 * (size_t)n;
+    void* d_corr = B[MPL_BUF_R1].ptr;
+    int32_t* d_samples = (int32_t*)B[MPL_BUF_R2].ptr;
+    int32_t* d_nm = d_samples + 5 * (size_t)h_use;
+    int32_t* d_off = d_nm + h_use;
+    double* d_models = (double*)B[MPL_BUF_R3].ptr;
+    double* d_dense = (double*)B[MPL_BUF_R4].ptr;
+    double* d_errsums = (double*)B[MPL_BUF_R5].ptr;
+    int32_t* d_counts = (int32_t*)(d_errsums + (size_t)h_use * 10);
+    double* d_misc;
+    d_misc = (double*)(((uintptr_t)(d_counts + (size_t)h_use * 10) + 63) & ~(uintptr_t)63);      // 64-byte aligned: basis[36] models[90] nm gram[...]
+    uint8_t* d_mask = (uint8_t*)(d_misc + 36 + 90 + 8 + 148 * 45);
+
+    MPL_CUDA_CHECK(cudaMemcpyAsync(d_p1, p1, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(d_p2, p2, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(d_samples, samples, (size_t)h_use * 20, cudaMemcpyHostToDevice, st));
+    if ((rc = mpl_launch_pack_corr(d_p1, d_p2, n, d_corr, st))) return rc;
+    if ((rc = mpl_launch_fivept_solve(d_corr, n, d_samples, h_use, d_models, d_nm, st))) return rc;
+    if ((rc = mpl_launch_compact_models(d_models, d_nm, h_use, d_off, d_dense, st))) return rc;
+    std::vector<int32_t> off((size_t)h_use + 1);
+    MPL_CUDA_CHECK(cudaMemcpyAsync(off.data(), d_off, ((size_t)h_use + 1) * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    const int m = off[h_use];
+    std::vector<int32_t> counts((size_t)std::max(m, 1));
+    std::vector<double> errsums((size_t)std::max(m, 1));
+    if (m > 0) {
+        if ((rc = mpl_launch_sampson_score(d_dense, m, d_corr, n, th, d_counts, d_errsums, st))) return rc;
+        MPL_CUDA_CHECK(cudaMemcpyAsync(counts.data(), d_counts, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(errsums.data(), d_errsums, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+    }
+    if (models_out) MPL_CUDA_CHECK(cudaMemcpyAsync(models_out, d_dense, (size_t)m * 72, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (n_models_out) for (int s = 0; s < h_use; ++s) n_models_out[s] = off[s + 1] - off[s];
+    if (counts_out) memcpy(counts_out, counts.data(), (size_t)m * 4);
+    if (errsums_out) memcpy(errsums_out, errsums.data(), (size_t)m * 8);
+
+    Replay r = replay_selection(counts.data(), errsums.data(), off.data(), h_use, n, conf, max_iters);
+    if (iters_run) *iters_run = r.iters_run;
+    if (r.best_model < 0) return MPL_OK;                      // runRANSAC returns false (maxGoodCount == 0)
+    double bestE[9];
+    MPL_CUDA_CHECK(cudaMemcpyAsync(bestE, d_dense + (size_t)r.best_model * 9, 72, cudaMemcpyDeviceToHost, st));
+    if ((rc = mpl_launch_sampson_mask(d_dense + (size_t)r.best_model * 9, d_corr, n, th, d_mask, nullptr, st))) return rc;
+    int best_count = r.best_count;
+    double errminsum = r.errminsum;
+
+    if (refine) {                                              // modelest.cpp:420-464
+        double* d_basis = d_misc; double* d_rmodels = d_misc + 36; int32_t* d_rnm = (int32_t*)(d_misc + 36 + 90);
+        double* d_gram = d_misc + 36 + 90 + 8;
+        const int gb = mpl_gram_blocks(n);
+        if ((rc = mpl_launch_gram(d_corr, d_mask, n, d_gram, st))) return rc;
+        std::vector<double> part((size_t)gb * 45);
+        MPL_CUDA_CHECK(cudaMemcpyAsync(part.data(), d_gram, part.size() * 8, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        double G[9][9], V[9][9], w[9];
+        int k = 0;
+        for (int a = 0; a < 9; ++a) for (int b = a; b < 9; ++b, ++k) { double v = 0; for (int blk = 0; blk < gb; ++blk) v += part[(size_t)blk * 45 + k]; G[a][b] = G[b][a] = v; }
+        jacobi_eig9(G, V, w);
+        int ord[9]; for (int i = 0; i < 9; ++i) ord[i] = i;
+        for (int i = 0; i < 9; ++i) for (int j = i + 1; j < 9; ++j) if (w[ord[j]] > w[ord[i]]) std::swap(ord[i], ord[j]);   // descending, like singular values
+        double basis[36];
+        for (int b = 0; b < 4; ++b) for (int c = 0; c < 9; ++c) basis[9 * b + c] = V[c][ord[5 + b]];    // Vt rows 5..8 (five-point.cpp:388)
+        MPL_CUDA_CHECK(cudaMemcpyAsync(d_basis, basis, sizeof(basis), cudaMemcpyHostToDevice, st));
+        if ((rc = mpl_launch_fivept_from_basis(d_basis, d_rmodels, d_rnm, st))) return rc;
+        int rnm = 0;
+        MPL_CUDA_CHECK(cudaMemcpyAsync(&rnm, d_rnm, 4, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        if (rnm > 0) {
+            int32_t rc_counts[10]; double rc_err[10];
+            if ((rc = mpl_launch_sampson_score(d_rmodels, rnm, d_corr, n, th, d_counts, d_errsums, st))) return rc;
+            MPL_CUDA_CHECK(cudaMemcpyAsync(rc_counts, d_counts, (size_t)rnm * 4, cudaMemcpyDeviceToHost, st));
+            MPL_CUDA_CHECK(cudaMemcpyAsync(rc_err, d_errsums, (size_t)rnm * 8, cudaMemcpyDeviceToHost, st));
+            MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+            int pick = -1;
+            for (int i = 0; i < rnm; ++i) {
+                if (rc_counts[i] > std::max(best_count, 4)) { pick = i; best_count = rc_counts[i]; errminsum = rc_err[i]; }
+                else if (rc_counts[i] == best_count && errminsum < DBL_MAX && errminsum > rc_err[i]) { pick = i; errminsum = rc_err[i]; }
+            }
+            if (pick >= 0) {
+                MPL_CUDA_CHECK(cudaMemcpyAsync(bestE, d_rmodels + 9 * pick, 72, cudaMemcpyDeviceToHost, st));
+                if ((rc = mpl_launch_sampson_mask(d_rmodels + 9 * pick, d_corr, n, th, d_mask, nullptr, st))) return rc;
+            }
+        }
+    }
+    if (mask) MPL_CUDA_CHECK(cudaMemcpyAsync(mask, d_mask, (size_t)n, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    memcpy(E, bestE, 72);
+    *n_inl = best_count;
+    return MPL_OK;
+}
+
+// poselib::estimateEssentialMat (pose_estim.cpp:857-890) -> findEssentialMat (five-point.cpp:69-148), method "RANSAC".
+// Returns 1 (true) / 0 (false) like the reference's bool, or a negative MPL_ERR_*.  E_out holds 9 doubles, or
+// 9 * (*n_E) doubles (up to 90) when n == 5 (solver only, mask all ones, five-point.cpp:108-114).
+extern "C" int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const char* method, double threshold,
+                                          int refine, double* E_out, int* n_E, uint8_t* mask)
+{
+    if (!method) { mpl_set_error("estimateEssentialMat: null method"); return MPL_ERR_BAD_ARG; }
+    const std::string m(method);
+    if (m != "RANSAC") {
+        // pose_estim.cpp:878-887: USAC / unknown methods print and exit(1); ARRSAC / LMEDS are other algorithms.
+        mpl_set_error("estimateEssentialMat: method %s is not served by the B200 hot path (only RANSAC; no CPU fallback)", method);
+        return MPL_ERR_BAD_ARG;
+    }
+    if (n < 5 || !p1 || !p2) { mpl_set_error("CV_Assert(npoints >= 5 && points2.checkVector(2) == npoints)"); return MPL_ERR_ASSERT; }
+    if (!E_out) return 0;                                      // five-point.cpp:137-144: E not requested -> false
+    if (n_E) *n_E = 1;
+    if (n == 5) {
+        std::lock_guard<std::mutex> g(mpl_ctx_mutex());
+        int rc = mpl_ensure_ctx_locked();
+        if (rc) return rc;
+        MplCtx* ctx = mpl_ctx(); cudaStream_t st = ctx->stream; MplBuf* B = ctx->bufs;
+        if ((rc = B[MPL_BUF_R0].ensure(4096))) return rc;
+        char* base = (char*)B[MPL_BUF_R0].ptr;
+        double* d_p1 = (double*)base; double* d_p2 = d_p1 + 10; void* d_corr = base + 256; int32_t* d_s = (int32_t*)(base + 512);
+        double* d_models = (double*)(base + 1024); int32_t* d_nm = (int32_t*)(base + 2048);
+        const int32_t s[5] = {0, 1, 2, 3, 4};
+        MPL_CUDA_CHECK(cudaMemcpyAsync(d_p1, p1, 80, cudaMemcpyHostToDevice, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(d_p2, p2, 80, cudaMemcpyHostToDevice, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(d_s, s, 20, cudaMemcpyHostToDevice, st));
+        if ((rc = mpl_launch_pack_corr(d_p1, d_p2, 5, d_corr, st))) return rc;
+        if ((rc = mpl_launch_fivept_solve(d_corr, 5, d_s, 1, d_models, d_nm, st))) return rc;
+        int cnt = 0;
+        MPL_CUDA_CHECK(cudaMemcpyAsync(&cnt, d_nm, 4, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(E_out, d_models, (size_t)cnt * 72, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        if (n_E) *n_E = cnt;
+        if (mask) memset(mask, 1, 5);
+        return 1;
+    }
+    int n_inl = 0, iters = 0;
+    int rc = mpl_ransac5pt(p1, p2, n, nullptr, 0, threshold, 1000, 0.999, refine, E_out, mask, &n_inl, &iters,
+                           nullptr, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    return n_inl > 0 ? 1 : 0;
+}

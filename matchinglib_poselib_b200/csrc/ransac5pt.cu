@@ -1,0 +1,305 @@
+// ransac5pt.cu -- RANSAC 5-point essential-matrix kernels for sm_100a.
+//
+// Replaces the hypothesise-and-verify loop of CvModelEstimator3::runRANSAC (poselib/source/five-point-nister/
+// modelest.cpp:343-474) with three data-parallel stages over PRE-DRAWN minimal samples:
+//   fivept_solve_kernel    one thread = one minimal sample -> up to 10 essential matrices (fivept_device.cuh;
+//                          reference: CvEMEstimator::run5Point, five-point.cpp:366-471)
+//   compact_*              exclusive scan of the per-sample model counts + gather into a dense model list
+//                          (deterministic order: sample-major, solver root order)
+//   sampson_score_kernel   one thread = one model, the CTA streams all correspondences through shared memory
+//                          (1-D TMA bulk copies, 2-stage ring, warp-wide broadcast reads) and evaluates the
+//                          reference's Sampson error (five-point.cpp:476-503) in ITS operation order with
+//                          explicit round-to-nearest fp64 ops (no FMA contraction), casts to float, compares
+//                          err <= th*th (modelest.cpp:69-83), counts inliers and accumulates sum(err).
+// The sequential selection / tie-break / adaptive-stop rule (modelest.cpp:394-415) is then replayed on the
+// host over the (count, errsum) arrays (pose_host.cu), exactly as the reference applies it model by model.
+//
+// Roofline: fp64 pipe.  One Sampson evaluation = 32 fp64 mul/add + 1 divide + 1 cvt.
+#include "mpl_common.cuh"
+#include "fivept_device.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// corr[i] = (x1, y1, x2, y2): 32-byte records so that one correspondence is two 128-bit shared loads
+__global__ void pack_corr_kernel(const double* __restrict__ p1, const double* __restrict__ p2, int n, double4* __restrict__ corr)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) corr[i] = make_double4(p1[2 * i], p1[2 * i + 1], p2[2 * i], p2[2 * i + 1]);
+}
+
+__global__ void __launch_bounds__(64)
+fivept_solve_kernel(const double4* __restrict__ corr, int n, const int32_t* __restrict__ samples, int h,
+                    double* __restrict__ models /* [h][10][9] */, int32_t* __restrict__ n_models)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= h) return;
+    double x1[5], y1[5], x2[5], y2[5];
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int id = samples[5 * s + j];
+        if (id < 0 || id >= n) { ok = false; x1[j] = y1[j] = x2[j] = y2[j] = 0; continue; }
+        const double4 c = corr[id];
+        x1[j] = c.x; y1[j] = c.y; x2[j] = c.z; y2[j] = c.w;
+    }
+    int cnt = 0;
+    if (ok) {
+        double ee[4][9];
+        fivept::null_space_5x9(x1, y1, x2, y2, ee);
+        cnt = fivept::solve_from_basis(ee, models + (size_t)s * 90);
+    }
+    n_models[s] = cnt;
+}
+
+// models from a caller-supplied null-space basis (least-squares refit, modelest.cpp:420-464)
+__global__ void fivept_from_basis_kernel(const double* __restrict__ basis /* [4][9] */, double* __restrict__ models, int32_t* __restrict__ n_models)
+{
+    double ee[4][9];
+    for (int b = 0; b < 4; ++b) for (int k = 0; k < 9; ++k) ee[b][k] = basis[9 * b + k];
+    n_models[0] = fivept::solve_from_basis(ee, models);
+}
+
+// single-block exclusive scan of n_models -> offsets[h+1]
+__global__ void __launch_bounds__(1024) scan_counts_kernel(const int32_t* __restrict__ counts, int h, int32_t* __restrict__ offsets)
+{
+    __shared__ int warp_sums[32];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < h; base += 1024) {
+        const int i = base + tid;
+        const int v = i < h ? counts[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_sums[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        const int prefix = carry + (wid ? warp_sums[wid - 1] : 0) + x - v;
+        if (i < h) offsets[i] = prefix;
+        __syncthreads();
+        if (tid == 1023) carry = prefix + v;
+        __syncthreads();
+    }
+    if (tid == 0) offsets[h] = carry;
+}
+
+__global__ void gather_models_kernel(const double* __restrict__ models, const int32_t* __restrict__ n_models,
+                                     const int32_t* __restrict__ offsets, int h, double* __restrict__ dense)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (sample, slot, element)
+    const int s = t / 90, r = t - s * 90;
+    if (s >= h) return;
+    const int j = r / 9;
+    if (j < n_models[s]) dense[(size_t)(offsets[s] + j) * 9 + (r - j * 9)] = models[(size_t)s * 90 + r];
+}
+
+constexpr int kScoreThreads = 128;
+constexpr int kChunk = 1024;                 // correspondences per TMA stage (32 KB)
+constexpr int kScoreStages = 2;
+
+// One Sampson evaluation in the reference's operation order (five-point.cpp:490-503).
+__device__ __forceinline__ float sampson_err(const double (&E)[9], const double4 c)
+{
+    const double x1 = c.x, y1 = c.y, x2 = c.z, y2 = c.w;
+    const double Ex0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], x1), __dmul_rn(E[1], y1)), E[2]);
+    const double Ex1 = __dadd_rn(__dadd_rn(__dmul_rn(E[3], x1), __dmul_rn(E[4], y1)), E[5]);
+    const double Ex2 = __dadd_rn(__dadd_rn(__dmul_rn(E[6], x1), __dmul_rn(E[7], y1)), E[8]);
+    const double Et0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], x2), __dmul_rn(E[3], y2)), E[6]);
+    const double Et1 = __dadd_rn(__dadd_rn(__dmul_rn(E[1], x2), __dmul_rn(E[4], y2)), E[7]);
+    const double r = __dadd_rn(__dadd_rn(__dmul_rn(x2, Ex0), __dmul_rn(y2, Ex1)), Ex2);
+    const double den = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Ex0, Ex0), __dmul_rn(Ex1, Ex1)), __dmul_rn(Et0, Et0)), __dmul_rn(Et1, Et1));
+    return __double2float_rn(__ddiv_rn(__dmul_rn(r, r), den));
+}
+
+__global__ void __launch_bounds__(kScoreThreads)
+sampson_score_kernel(const double* __restrict__ models, int m, const double4* __restrict__ corr, int n, double th2,
+                     int32_t* __restrict__ counts, double* __restrict__ errsums)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double4* tile = reinterpret_cast<double4*>(smem_raw);                 // [kScoreStages][kChunk]
+    __shared__ __align__(8) uint64_t full_bar[kScoreStages];
+    const int tid = threadIdx.x;
+    const int mi = blockIdx.x * kScoreThreads + tid;
+    const int n_chunks = (n + kChunk - 1) / kChunk;
+    if (tid == 0) {
+        for (int s = 0; s < kScoreStages; ++s) mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int ci) {
+        const int s = ci % kScoreStages;
+        const int cnt = min(kChunk, n - ci * kChunk);
+        mbar_expect_tx(&full_bar[s], (uint32_t)cnt * 32u);
+        tma_bulk_g2s(tile + s * kChunk, corr + (size_t)ci * kChunk, (uint32_t)cnt * 32u, &full_bar[s]);
+    };
+    if (tid == 0) for (int i = 0; i < kScoreStages && i < n_chunks; ++i) issue(i);
+
+    double E[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) E[k] = mi < m ? models[(size_t)mi * 9 + k] : 0.0;
+    int good = 0;
+    double esum = 0.0;
+    for (int ci = 0; ci < n_chunks; ++ci) {
+        const int s = ci % kScoreStages;
+        mbar_wait(&full_bar[s], (uint32_t)((ci / kScoreStages) & 1));
+        const double4* t = tile + s * kChunk;
+        const int cnt = min(kChunk, n - ci * kChunk);
+#pragma unroll 4
+        for (int i = 0; i < cnt; ++i) {
+            const float e = sampson_err(E, t[i]);                        // two LDS.128, warp-wide broadcast
+            good += ((double)e <= th2) ? 1 : 0;
+            esum = __dadd_rn(esum, (double)e);
+        }
+        __syncthreads();
+        if (tid == 0 && ci + kScoreStages < n_chunks) issue(ci + kScoreStages);
+    }
+    if (mi < m) { counts[mi] = good; if (errsums) errsums[mi] = esum; }
+}
+
+// inlier mask of ONE model (the selected hypothesis): mask[i] = err_i <= th^2
+__global__ void sampson_mask_kernel(const double* __restrict__ model, const double4* __restrict__ corr, int n, double th2,
+                                    uint8_t* __restrict__ mask, float* __restrict__ err)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double E[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) E[k] = model[k];
+    const float e = sampson_err(E, corr[i]);
+    mask[i] = ((double)e <= th2) ? 1 : 0;
+    if (err) err[i] = e;
+}
+
+// Gram matrix Q^T Q (9x9, upper triangle) of the epipolar constraint rows of the masked correspondences
+// (least-squares refit, modelest.cpp:420-446).  Deterministic: per-block partial sums in a fixed order;
+// the host adds the blocks in order.
+__global__ void __launch_bounds__(256) gram_kernel(const double4* __restrict__ corr, const uint8_t* __restrict__ mask, int n,
+                                                   double* __restrict__ partial /* [gridDim.x][45] */)
+{
+    __shared__ double sm[8][45];
+    double acc[45];
+#pragma unroll
+    for (int k = 0; k < 45; ++k) acc[k] = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (!mask[i]) continue;
+        const double4 c = corr[i];
+        const double r[9] = {c.x * c.z, c.y * c.z, c.z, c.x * c.w, c.y * c.w, c.w, c.x, c.y, 1.0};
+        int k = 0;
+#pragma unroll
+        for (int a = 0; a < 9; ++a)
+#pragma unroll
+            for (int b = a; b < 9; ++b) acc[k++] += r[a] * r[b];
+    }
+#pragma unroll
+    for (int k = 0; k < 45; ++k) {
+        double v = acc[k];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 45) {
+        double v = 0;
+        for (int w = 0; w < 8; ++w) v += sm[w][threadIdx.x];
+        partial[blockIdx.x * 45 + threadIdx.x] = v;
+    }
+}
+
+}  // namespace
+
+// ---- launch wrappers (declared in mpl_ransac.h) ------------------------------------------------------
+#include "mpl_ransac.h"
+
+int mpl_launch_pack_corr(const double* p1, const double* p2, int n, void* corr, cudaStream_t st)
+{
+    if (n <= 0) return MPL_OK;
+    pack_corr_kernel<<<(n + 255) / 256, 256, 0, st>>>(p1, p2, n, (double4*)corr);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_fivept_solve(const void* corr, int n, const int32_t* samples, int h, double* models, int32_t* n_models, cudaStream_t st)
+{
+    if (h <= 0) return MPL_OK;
+    fivept_solve_kernel<<<(h + 63) / 64, 64, 0, st>>>((const double4*)corr, n, samples, h, models, n_models);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_fivept_from_basis(const double* basis, double* models, int32_t* n_models, cudaStream_t st)
+{
+    fivept_from_basis_kernel<<<1, 1, 0, st>>>(basis, models, n_models);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_compact_models(const double* models, const int32_t* n_models, int h, int32_t* offsets, double* dense, cudaStream_t st)
+{
+    if (h <= 0) return MPL_OK;
+    scan_counts_kernel<<<1, 1024, 0, st>>>(n_models, h, offsets);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    const long long total = (long long)h * 90;
+    gather_models_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(models, n_models, offsets, h, dense);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_sampson_score(const double* models, int m, const void* corr, int n, double th, int32_t* counts, double* errsums, cudaStream_t st)
+{
+    if (m <= 0) return MPL_OK;
+    static bool attr_set = false;
+    const size_t smem = (size_t)kScoreStages * kChunk * 32;
+    if (!attr_set) {
+        MPL_CUDA_CHECK(cudaFuncSetAttribute(sampson_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    sampson_score_kernel<<<(m + kScoreThreads - 1) / kScoreThreads, kScoreThreads, smem, st>>>(models, m, (const double4*)corr, n, th * th, counts, errsums);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_sampson_mask(const double* model, const void* corr, int n, double th, uint8_t* mask, float* err, cudaStream_t st)
+{
+    if (n <= 0) return MPL_OK;
+    sampson_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(model, (const double4*)corr, n, th * th, mask, err);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_gram_blocks(int n) { int b = (n + 255) / 256; return b > 148 ? 148 : (b < 1 ? 1 : b); }
+
+int mpl_launch_gram(const void* corr, const uint8_t* mask, int n, double* partial, cudaStream_t st)
+{
+    gram_kernel<<<mpl_gram_blocks(n), 256, 0, st>>>((const double4*)corr, mask, n, partial);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}

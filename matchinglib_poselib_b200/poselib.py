@@ -1,0 +1,86 @@
+"""Host-side mirror of the reference's poselib API for the hot path.
+
+`estimateEssentialMat` keeps the reference's name, argument meaning and bool return
+(matchinglib_poselib/source/poselib/include/poselib/pose_estim.h:204-210, source/pose_estim.cpp:857-890) for
+method == "RANSAC" (findEssentialMat, five-point-nister/five-point.cpp:69-148).  cv::Mat -> numpy arrays:
+p1, p2 are n x 2 (camera-normalised coordinates); E is returned 3 x 3 float64, mask 1 x n uint8.
+All O(models x correspondences) arithmetic runs in libmplb200.so on the GPU.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+
+def _pts(p):
+    a = np.asarray(p)
+    if a.ndim == 3 and a.shape[1] == 1:
+        a = a.reshape(a.shape[0], a.shape[2])
+    if a.ndim != 2 or a.shape[1] != 2:
+        raise AssertionError("CV_Assert(npoints >= 0 && points.checkVector(2) == npoints)")
+    return np.ascontiguousarray(a, np.float64)            # findEssentialMat converts to CV_64F (five-point.cpp:89-90)
+
+
+def ransac5pt(p1, p2, samples, threshold, max_iters=1000, confidence=0.999, refine=False, trace=False):
+    """runRANSAC over PRE-DRAWN minimal samples (h x 5 int32).  Returns a dict: ok, E (3x3), mask (n,), count,
+    iters and, with trace=True, n_models (h,), models (M x 9), counts (M,), errsums (M,) for every sample."""
+    lib = _lib.load()
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if p2.shape[0] != n:
+        raise AssertionError("CV_Assert(points2.checkVector(2) == npoints)")
+    s = None if samples is None else np.ascontiguousarray(samples, np.int32)
+    h = 0 if s is None else s.shape[0]
+    E = np.zeros(9); mask = np.zeros(n, np.uint8); cnt = ctypes.c_int(0); iters = ctypes.c_int(0)
+    hh = h if s is not None else max_iters
+    tm = np.zeros((10 * hh, 9)) if trace else None
+    tn = np.zeros(hh, np.int32) if trace else None
+    tc = np.zeros(10 * hh, np.int32) if trace else None
+    te = np.zeros(10 * hh) if trace else None
+    _lib.check(lib.mpl_ransac5pt(_lib.ptr(p1), _lib.ptr(p2), n, _lib.ptr(s), h, float(threshold), int(max_iters),
+                                 float(confidence), int(bool(refine)), _lib.ptr(E), _lib.ptr(mask), ctypes.byref(cnt),
+                                 ctypes.byref(iters), _lib.ptr(tm), _lib.ptr(tn), _lib.ptr(tc), _lib.ptr(te)), "mpl_ransac5pt")
+    out = dict(ok=cnt.value > 0, E=E.reshape(3, 3), mask=mask, count=cnt.value, iters=iters.value)
+    if trace:
+        tot = int(tn.sum())
+        out.update(n_models=tn, models=tm[:tot], counts=tc[:tot], errsums=te[:tot])
+    return out
+
+
+def estimateEssentialMat(p1, p2, method="ARRSAC", threshold=1.6, refine=True, want_mask=True):
+    """poselib::estimateEssentialMat.  Returns (ok, E, mask).  Only method "RANSAC" is served (the reference's
+    default "ARRSAC" and "LMEDS"/"USAC" are other algorithms; there is no CPU fallback)."""
+    lib = _lib.load()
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if n < 5 or p2.shape[0] != n:
+        raise AssertionError("CV_Assert(npoints >= 5 && points2.checkVector(2) == npoints)")
+    E = np.zeros((10, 9)); n_E = ctypes.c_int(0)
+    mask = np.zeros(n, np.uint8)
+    rc = lib.mpl_estimate_essential_api(_lib.ptr(p1), _lib.ptr(p2), n, method.encode(), float(threshold), int(bool(refine)),
+                                        _lib.ptr(E), ctypes.byref(n_E), _lib.ptr(mask))
+    if rc == -103:
+        raise AssertionError(_lib.last_error())
+    if rc < 0:
+        raise _lib.MplError("estimateEssentialMat failed (%d): %s" % (rc, _lib.last_error()))
+    if n == 5:
+        return bool(rc), E[: n_E.value].reshape(-1, 3), mask.reshape(1, -1)
+    return bool(rc), E[0].reshape(3, 3), (mask.reshape(1, -1) if want_mask else None)
+
+
+def _smoke():
+    """One small RANSAC run on cuda:0, checked against the oracle (called by __graft_entry__.smoke)."""
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tests"))
+    import datagen_pose
+    from oracle import ransac as orc
+    sc = datagen_pose.make_scene(400, 0.3, seed=5)
+    s = datagen_pose.draw_samples(sc["p1"], sc["p2"], 64, seed=6)
+    got = ransac5pt(sc["p1"], sc["p2"], s, sc["th"], refine=True)
+    exp = orc.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], refine=True)
+    assert got["count"] == exp["count"] and np.array_equal(got["mask"], exp["mask"]), "RANSAC inlier set differs from oracle"
+    d = min(np.linalg.norm(got["E"] - exp["E"]), np.linalg.norm(got["E"] + exp["E"]))
+    assert d < 1e-6, "E differs from oracle by %g" % d
