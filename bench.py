@@ -1,0 +1,518 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the B200 hot path on BASELINE.json's metric.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Headline workload (config C2 of BASELINE.json): SIFT-like 128-d float descriptors, 20 000 queries x
+20 000 train rows, brute-force L2 k = 2 + Lowe ratio test.  A "step" is one pass of the hot path over
+that batch.  `value` = descriptor pairs/s with the inputs resident in HBM; `e2e` = the same metric through
+the reference-facing call (getMatches -> mpl_get_matches_api) with HOST buffers, copies inside the timed
+region.  `parts` carries the other two legs of the metric on their own configs: Hamming k-NN (C1, ORB
+8192 x 8192 x 32 B) and RANSAC 5-point scoring (C3, 10 000 correspondences x 100 000 pre-drawn samples).
+
+N > 1 (torchrun, one rank per GPU): the database regime -- every rank holds its own 20 000-row train
+shard, the queries are replicated, per-rank top-2 keys are all-gathered over NCCL and merged
+(weak scaling: pairs grow with N).
+
+--impl reference: the reference's CPU path on the host cores (oracle/_ref = the reference's vendored
+NMSLIB compiled from its own sources; falls back to the oracle port), bounded sample per step.
+
+Only this file, tests/ and __graft_entry__.smoke() may touch oracle/.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+C2 = dict(nq=20000, nt=20000, dim=128, seed=1002)
+C1 = dict(nq=8192, nt=8192, nbytes=32, seed=1001)
+C3 = dict(n=10000, h=100000, seed=1003)
+L2_FLUSH_BYTES = 512 << 20       # > 126 MB L2: written between timed iterations
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        d["_src"] = "measured"
+        return d
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, sm_max_mhz=1965.0, _src="fallback")
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; same fields as the profiling guide's nvidia-smi line)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index=0, period=0.05):
+        self.index, self.period, self.samples, self.reasons = index, period, [], set()
+        self.max_mhz, self._stop, self._t = None, threading.Event(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {nv.nvmlClocksEventReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksEventReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksEventReasonSwPowerCap: "sw_power_cap"} \
+            if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else \
+                {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return dict(sm_mhz=None, sm_max_mhz=self.max_mhz, reasons=sorted(self.reasons), samples=0)
+        return dict(sm_mhz=float(np.median(self.samples)), sm_max_mhz=self.max_mhz, reasons=sorted(self.reasons), samples=len(self.samples))
+
+
+# ------------------------------------------------------------------------------------------------
+# device-side helpers
+# ------------------------------------------------------------------------------------------------
+class Gpu:
+    """torch supplies device memory, streams and events; every kernel is libmplb200's."""
+
+    def __init__(self, local_rank=0):
+        import torch
+        import matchinglib_poselib_b200 as m
+        self.torch, self.m = torch, m
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a B200: no CUDA device visible and there is no CPU fallback")
+        torch.cuda.set_device(local_rank)
+        self.dev = torch.device("cuda", local_rank)
+        self.lib = m._lib.load()
+        m._lib.check(self.lib.mpl_init(local_rank), "mpl_init")
+        self.flush_buf = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=self.dev)
+
+    def stream(self):
+        return ctypes.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+
+    def flush_l2(self):
+        self.flush_buf.zero_()
+
+    def launches(self):
+        return int(self.lib.mpl_kernel_launch_count())
+
+    def prof_read(self, cls):
+        ms, n = ctypes.c_double(0), ctypes.c_longlong(0)
+        self.lib.mpl_prof_read(cls, ctypes.byref(ms), ctypes.byref(n))
+        return ms.value, n.value
+
+    def time_steps(self, step, steps, warmup, barrier=None):
+        """W warm-up steps, then K timed steps.  Each timed step is bracketed by CUDA events on the launching
+        stream; L2 is flushed between steps (outside the events).  Returns per-step ms list."""
+        torch = self.torch
+        for _ in range(warmup):
+            self.flush_l2()
+            step()
+        torch.cuda.synchronize()
+        if barrier:
+            barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in ev:
+            self.flush_l2()
+            a.record()
+            step()
+            b.record()
+        torch.cuda.synchronize()
+        if barrier:
+            barrier()
+        return [a.elapsed_time(b) for a, b in ev]
+
+
+PROF = dict(hamming=0, l2_exact=1, l2_tc=2, l2_rerank=3, merge=4, solve=5, score=6, l2_prep=7)
+
+
+def pinned(arr, torch):
+    t = torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
+    return t, t.numpy()
+
+
+# ------------------------------------------------------------------------------------------------
+# C2: float L2 k-NN (headline)
+# ------------------------------------------------------------------------------------------------
+def make_c2(rank=0):
+    """Queries are identical on every rank (a quarter of them are noisy copies of rows of shard 0, so the ratio
+    test passes there); train shard `rank` is its own seeded 20 000 rows."""
+    import datagen
+
+    def shard(r):
+        return datagen.sift_like(16, C2["nt"], C2["dim"], seed=C2["seed"] + 7919 * (r + 1))[1]
+    q, _ = datagen.sift_like(C2["nq"], 16, C2["dim"], seed=C2["seed"])
+    t0 = shard(0)
+    rng = np.random.default_rng(C2["seed"])
+    sel = rng.choice(C2["nq"], C2["nq"] // 4, replace=False)
+    src = rng.integers(0, C2["nt"], len(sel))
+    noise = rng.standard_normal((len(sel), C2["dim"])) * (0.05 * 512.0 / np.sqrt(C2["dim"]))
+    q[sel] = np.clip(np.round(t0[src] + noise), 0, 255).astype(np.float32)
+    return q, (t0 if rank == 0 else shard(rank))
+
+
+def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
+    torch, lib, m = g.torch, g.lib, g.m
+    q, t = make_c2(rank)
+    nq, nt, dim = q.shape[0], t.shape[0], q.shape[1]
+    d_q, d_t = torch.from_numpy(q).to(g.dev), torch.from_numpy(t).to(g.dev)
+    scr_bytes = int(lib.mpl_knn_l2_scratch_bytes(nq, nt, dim))
+    d_scr = torch.empty(scr_bytes, dtype=torch.uint8, device=g.dev)
+    d_keys = torch.empty((nq, 2), dtype=torch.int64, device=g.dev)
+    d_all = torch.empty((world, nq, 2), dtype=torch.int64, device=g.dev) if world > 1 else d_keys
+    d_idx = torch.empty((nq, 2), dtype=torch.int32, device=g.dev)
+    d_dist = torch.empty((nq, 2), dtype=torch.float32, device=g.dev)
+
+    def step():
+        st = g.stream()
+        m._lib.check(lib.mpl_knn2_l2f32_dev(d_q.data_ptr(), nq, dim, d_t.data_ptr(), nt, dim, dim, 0, rank * nt,
+                                            d_scr.data_ptr(), scr_bytes, d_keys.data_ptr(), st), "knn2_l2f32_dev")
+        if world > 1:
+            dist.all_gather_into_tensor(d_all, d_keys)           # NCCL over NVLink: 16 B x nq per rank
+        m._lib.check(lib.mpl_merge_top2_dev(d_all.data_ptr(), world, nq, 2, 1, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
+
+    lib.mpl_prof_enable(0)
+    barrier = (lambda: dist.barrier()) if world > 1 else None
+    l0 = g.launches()
+    with ClockSampler(g.dev.index) as cs:
+        ms = g.time_steps(step, steps, warmup, barrier)
+        t_end = time.time() + 1.0
+        while len(cs.samples) < 8 and time.time() < t_end:       # very short runs: keep the GPU busy until sampled
+            step()
+        torch.cuda.synchronize()
+    launches = (g.launches() - l0)
+    # dominant kernel timed live with the library's own CUDA events (same stream), separate short pass
+    lib.mpl_prof_enable(1)
+    for _ in range(max(3, min(steps, 10))):
+        g.flush_l2()
+        step()
+    torch.cuda.synchronize()
+    lib.mpl_prof_enable(0)
+    kern = {k: g.prof_read(v) for k, v in PROF.items()}
+    res = dict(ms=ms, launches_per_step=None, kern=kern, clocks=cs.summary(), nq=nq, nt=nt, dim=dim,
+               idx=d_idx.cpu().numpy(), dist=d_dist.cpu().numpy(), q=q, t=t)
+    res["launches_timed"] = launches
+    return res
+
+
+def e2e_l2(g, q, t, reps):
+    """getMatches("LINEAR") through the C ABI with pinned HOST buffers: H2D + kernels + D2H + ratio test."""
+    torch, m = g.torch, g.m
+    (_, hq), (_, ht) = pinned(q, torch), pinned(t, torch)
+    kp1, kp2 = range(len(hq)), range(len(ht))
+    err, mt = m.getMatchesArray(kp1, kp2, hq, ht, None, "LINEAR", False, True)      # warm-up (allocations)
+    assert err == 0, err
+    ts = []
+    for _ in range(reps):
+        g.flush_l2()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        err, mt = m.getMatchesArray(kp1, kp2, hq, ht, None, "LINEAR", False, True)
+        ts.append(time.perf_counter() - t0)
+    return float(np.median(ts)), len(mt), hq.nbytes + ht.nbytes, len(hq) * 2 * 8
+
+
+# ------------------------------------------------------------------------------------------------
+# C1: Hamming k-NN (ORB 8192 x 8192 x 32 B)
+# ------------------------------------------------------------------------------------------------
+def bench_hamming(g, steps, warmup):
+    import datagen
+    torch, lib, m = g.torch, g.lib, g.m
+    q, t = datagen.binary_descriptors(C1["nq"], C1["nt"], C1["nbytes"], seed=C1["seed"])
+    nq, nt, nb = q.shape[0], t.shape[0], q.shape[1]
+    w16 = nb // 16
+    d_q, d_t = torch.from_numpy(q).to(g.dev), torch.from_numpy(t).to(g.dev)
+    scr_bytes = int(lib.mpl_knn_hamming_scratch_bytes(nq, nt, w16))
+    d_scr = torch.empty(scr_bytes, dtype=torch.uint8, device=g.dev)
+    d_keys = torch.empty((nq, 2), dtype=torch.int64, device=g.dev)
+    d_idx = torch.empty((nq, 2), dtype=torch.int32, device=g.dev)
+    d_dist = torch.empty((nq, 2), dtype=torch.int32, device=g.dev)
+
+    def step():
+        st = g.stream()
+        m._lib.check(lib.mpl_knn2_hamming_dev(d_q.data_ptr(), nq, d_t.data_ptr(), nt, w16, 0, d_scr.data_ptr(), scr_bytes,
+                                              d_keys.data_ptr(), st), "knn2_hamming_dev")
+        m._lib.check(lib.mpl_merge_top2_dev(d_keys.data_ptr(), 1, nq, 2, 0, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
+
+    ms = g.time_steps(step, steps, warmup)
+    lib.mpl_prof_enable(1)
+    for _ in range(5):
+        g.flush_l2()
+        step()
+    torch.cuda.synchronize()
+    lib.mpl_prof_enable(0)
+    k_ms, k_n = g.prof_read(PROF["hamming"])
+    g.prof_read(PROF["merge"])
+    # end to end through getMatches("LINEAR") with pinned host buffers
+    (_, hq), (_, ht) = pinned(q, torch), pinned(t, torch)
+    kp = range(nq)
+    err, mt = m.getMatchesArray(kp, range(nt), hq, ht, None, "LINEAR", False, True)
+    assert err == 0, err
+    ts = []
+    for _ in range(max(5, min(steps, 20))):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        err, mt = m.getMatchesArray(kp, range(nt), hq, ht, None, "LINEAR", False, True)
+        ts.append(time.perf_counter() - t0)
+    pairs = float(nq) * nt
+    step_ms = float(np.mean(ms))
+    kern_ms = k_ms / max(k_n, 1)
+    pk = peaks()
+    bytes_alg = (nq + nt) * nb + nq * 16
+    popc = pairs * (nb // 4)
+    return dict(
+        workload="C1: ORB 8192x8192x32B Hamming k=2 + ratio (LINEAR)", value=pairs / (step_ms * 1e-3), unit="pairs/s", ms_per_step=step_ms,
+        dtype="u32 popc",
+        roofline=dict(bound="hbm", achieved=bytes_alg / (kern_ms * 1e-3) / 1e9, peak=pk["hbm_gbs"], unit="GB/s",
+                      frac=bytes_alg / (kern_ms * 1e-3) / 1e9 / pk["hbm_gbs"], traffic=None, peak_src=pk["_src"],
+                      kernel="hamming_top2_kernel", kernel_ms=kern_ms,
+                      note="compute-bound on the integer pipe, not HBM (algorithmic bytes are 0.65 MB): see alu"),
+        alu=dict(achieved_gpopc_s=popc / (kern_ms * 1e-3) / 1e9, popc_per_pair=nb // 4),
+        e2e=dict(value=pairs / float(np.median(ts)), unit="pairs/s", h2d_bytes_per_step=int(hq.nbytes + ht.nbytes), d2h_bytes_per_step=int(nq * 16),
+                 matches=int(len(mt))))
+
+
+# ------------------------------------------------------------------------------------------------
+# C3: RANSAC 5-point, 10 000 correspondences x 100 000 pre-drawn samples
+# ------------------------------------------------------------------------------------------------
+def bench_ransac(g, steps, warmup):
+    import datagen_pose
+    torch, lib, m = g.torch, g.lib, g.m
+    n, h = C3["n"], C3["h"]
+    sc = datagen_pose.make_scene(n, 0.3, seed=C3["seed"])
+    samples = datagen_pose.draw_samples_fast(n, h, seed=C3["seed"] + 1)
+    d_p1, d_p2 = torch.from_numpy(sc["p1"]).to(g.dev), torch.from_numpy(sc["p2"]).to(g.dev)
+    d_s = torch.from_numpy(samples).to(g.dev)
+    d_corr = torch.empty(n * 4, dtype=torch.float64, device=g.dev)
+    d_models = torch.empty(h * 90, dtype=torch.float64, device=g.dev)
+    d_dense = torch.empty(h * 90, dtype=torch.float64, device=g.dev)
+    d_nm = torch.empty(h, dtype=torch.int32, device=g.dev)
+    d_off = torch.empty(h + 1, dtype=torch.int32, device=g.dev)
+    d_counts = torch.empty(h * 10, dtype=torch.int32, device=g.dev)
+    d_es = torch.empty(h * 10, dtype=torch.float64, device=g.dev)
+    th = ctypes.c_double(sc["th"])
+    st0 = g.stream()
+    m._lib.check(lib.mpl_ransac_pack_corr_dev(d_p1.data_ptr(), d_p2.data_ptr(), n, d_corr.data_ptr(), st0), "pack")
+    m._lib.check(lib.mpl_ransac_solve_dev(d_corr.data_ptr(), n, d_s.data_ptr(), h, d_models.data_ptr(), d_nm.data_ptr(), d_off.data_ptr(),
+                                          d_dense.data_ptr(), st0), "solve")
+    torch.cuda.synchronize()
+    n_models = int(d_off[h].item())          # fixed for the workload: known before the timed region
+
+    def step():
+        st = g.stream()
+        m._lib.check(lib.mpl_ransac_pack_corr_dev(d_p1.data_ptr(), d_p2.data_ptr(), n, d_corr.data_ptr(), st), "pack")
+        m._lib.check(lib.mpl_ransac_solve_dev(d_corr.data_ptr(), n, d_s.data_ptr(), h, d_models.data_ptr(), d_nm.data_ptr(), d_off.data_ptr(),
+                                              d_dense.data_ptr(), st), "solve")
+        m._lib.check(lib.mpl_ransac_score_dev(d_dense.data_ptr(), n_models, d_corr.data_ptr(), n, th, d_counts.data_ptr(), d_es.data_ptr(), st), "score")
+
+    ms = g.time_steps(step, steps, warmup)
+    lib.mpl_prof_enable(1)
+    for _ in range(3):
+        g.flush_l2()
+        step()
+    torch.cuda.synchronize()
+    lib.mpl_prof_enable(0)
+    sc_ms, sc_n = g.prof_read(PROF["score"])
+    so_ms, so_n = g.prof_read(PROF["solve"])
+    # end to end: mpl_ransac5pt with host buffers, every sample solved + scored, counts/errsums read back
+    p1, p2 = np.ascontiguousarray(sc["p1"]), np.ascontiguousarray(sc["p2"])
+    E = np.zeros(9); mask = np.zeros(n, np.uint8); cnt = ctypes.c_int(0); iters = ctypes.c_int(0)
+    tc = np.zeros(10 * h, np.int32); te = np.zeros(10 * h)
+    P = m._lib.ptr
+
+    def call():
+        m._lib.check(lib.mpl_ransac5pt(P(p1), P(p2), n, P(samples), h, sc["th"], h, 0.999, 0, P(E), P(mask), ctypes.byref(cnt), ctypes.byref(iters),
+                                       None, None, P(tc), P(te)), "mpl_ransac5pt")
+    call()
+    ts = []
+    for _ in range(max(3, min(steps, 10))):
+        t0 = time.perf_counter()
+        call()
+        ts.append(time.perf_counter() - t0)
+    evals = float(n_models) * n
+    step_ms = float(np.mean(ms))
+    score_ms = sc_ms / max(sc_n, 1)
+    return dict(
+        workload="C3: RANSAC 5pt, 10000 correspondences x 100000 pre-drawn samples (%d real models)" % n_models,
+        value=evals / (step_ms * 1e-3), unit="model*correspondence Sampson evaluations/s", ms_per_step=step_ms, dtype="f64",
+        hypotheses_per_ms=h / step_ms, models_per_ms=n_models / step_ms,
+        kernels=dict(sampson_score_ms=score_ms, fivept_solve_ms=so_ms / max(so_n, 1),
+                     score_evals_per_s=evals / (score_ms * 1e-3), score_fp64_tflops=evals * 33 / (score_ms * 1e-3) / 1e12),
+        best_inliers=int(d_counts[:n_models].max().item()),
+        e2e=dict(value=evals / float(np.median(ts)), unit="evaluations/s", h2d_bytes_per_step=int(p1.nbytes + p2.nbytes + samples.nbytes),
+                 d2h_bytes_per_step=int(n_models * 12 + n), inliers=int(cnt.value)))
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs: the reference's own CPU path on the host cores (the ONLY place bench.py executes oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_l2_runner():
+    """Returns (kind, fn(q, t, threads) -> (idx, dist)).  "reference" = the reference's vendored NMSLIB
+    (seq_search + l2: the BRUTEFORCENMS matcher's hot loop) compiled from its own sources into oracle/_ref;
+    "port" = the C restatement of cvflann's linear L2 scan, query-striped over threads."""
+    from oracle import knn as orc
+    if orc.ref_lib() is not None:
+        return "reference", lambda q, t, th: orc.ref_nmslib_l2(q, t, threads=th)
+    return "port", lambda q, t, th: orc.knn_l2(q, t, 2, 0, threads=th)
+
+
+def cpu_l2_sample(q, t, budget_s=12.0):
+    """Bounded sample of the C2 workload: a prefix of the queries against the full train set, all host threads."""
+    kind, fn = cpu_l2_runner()
+    cores = os.cpu_count() or 1
+    n0 = min(len(q), 64 * cores)
+    t0 = time.perf_counter(); fn(q[:n0], t, cores); dt0 = time.perf_counter() - t0
+    n1 = int(min(len(q), max(n0, n0 * budget_s / max(dt0, 1e-6))))
+    t0 = time.perf_counter(); idx, dist = fn(q[:n1], t, cores); dt = time.perf_counter() - t0
+    return dict(value=float(n1) * len(t) / dt, unit="pairs/s", cores=cores, kind=kind,
+                sample="first %d of %d queries x %d train rows, %.1f s, %d threads (%s)" %
+                       (n1, len(q), len(t), dt, cores, "reference NMSLIB seq_search/l2, q%%T striping" if kind == "reference" else "oracle port of cvflann linear L2")), idx
+
+
+def run_reference(args):
+    """--impl reference: K steps, each a bounded sample of C2 on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    q, t = make_c2(0)
+    kind, fn = cpu_l2_runner()
+    cores = os.cpu_count() or 1
+    # size a step at ~2 s so that steps + warm-up stay within a few minutes
+    n0 = min(len(q), 32 * cores)
+    t0 = time.perf_counter(); fn(q[:n0], t, cores); dt0 = time.perf_counter() - t0
+    per_step_s = min(2.0, 150.0 / max(args.steps + args.warmup, 1))
+    n1 = int(min(len(q), max(n0, n0 * per_step_s / max(dt0, 1e-6))))
+    for _ in range(args.warmup):
+        fn(q[:n1], t, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn(q[:n1], t, cores)
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    v = float(n1) * len(t) / dt
+    sample = "each step: first %d of %d queries x %d train rows on %d host threads" % (n1, len(q), len(t), cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": dict(workload=WORKLOAD, sample=sample),
+        "cpu_baseline": dict(value=v, unit="pairs/s", cores=cores, kind=kind, sample=sample),
+        "e2e": dict(value=v, unit="pairs/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), "gpu_launches": 0}))
+
+
+METRIC = "descriptor pairs/s (brute-force L2 k=2 + ratio test)"
+WORKLOAD = "C2: SIFT-like 128-d f32, 20000 queries x 20000 train rows per GPU, L2 k=2 + Lowe ratio (LINEAR)"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-parts", action="store_true", help="skip the Hamming (C1) and RANSAC (C3) legs")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        raise SystemExit("launch N > 1 with torchrun (python -m torch.distributed.run --nproc-per-node N bench.py --gpus N)")
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()                                   # no-op when the .so files travelled with the snapshot
+    g = Gpu(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=g.dev)
+        dist.barrier()
+
+    r = bench_l2(g, args.steps, args.warmup, world, rank, dist)
+    torch = g.torch
+    step_ms = float(np.mean(r["ms"]))
+    if world > 1:
+        tm = torch.tensor([step_ms], device=g.dev)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)    # device-timed, max over ranks
+        step_ms = float(tm.item())
+    pairs = float(r["nq"]) * r["nt"] * world
+    pk = peaks()
+    out = None
+    if rank == 0:
+        kern = r["kern"]
+        tc_ms, tc_n = kern["l2_tc"]
+        ex_ms, ex_n = kern["l2_exact"]
+        if tc_n:
+            kname, k_ms, peak, peak_name = "l2_tc_rank_kernel (tcgen05)", tc_ms / tc_n, pk["bf16_tflops"], "bf16_tflops (burst, cuBLAS bf16)"
+        else:
+            kname, k_ms, peak, peak_name = "l2_exact_top2_kernel (fp32 SIMT)", ex_ms / max(ex_n, 1), pk["bf16_tflops"], "bf16_tflops (burst, cuBLAS bf16)"
+        flops = 2.0 * r["dim"] * r["nq"] * r["nt"]           # per launch: one rank's shard
+        ach = flops / (k_ms * 1e-3) / 1e12
+        e2e_s, n_matches, bi, bo = e2e_l2(g, r["q"], r["t"], max(5, min(args.steps, 20)))
+        out = {
+            "metric": METRIC, "value": pairs / (step_ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16/tf32 tensor-core ranking, exact fp32 re-rank)",
+            "data": "synthetic",
+            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else "train rows sharded over %d ranks, NCCL all-gather of top-2 keys + merge" % world),
+            "clocks": r["clocks"],
+            "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=None, kernel=kname, kernel_ms=k_ms,
+                             peak_src="%s: %s" % (pk["_src"], peak_name), flops_per_launch=flops,
+                             step_share={k: (v[0] / max(v[1], 1)) for k, v in kern.items() if v[1]}),
+            "e2e": dict(value=float(r["nq"]) * r["nt"] / e2e_s, unit="pairs/s", h2d_bytes_per_step=int(bi), d2h_bytes_per_step=int(bo), ms=e2e_s * 1e3,
+                        matches=int(n_matches), api="getMatches(LINEAR) -> mpl_get_matches_api, pinned host buffers, 1 GPU"),
+            "gpu_launches": int(r["launches_timed"]),
+        }
+        if not args.no_cpu and world == 1:
+            cb, cidx = cpu_l2_sample(r["q"], r["t"])
+            n1 = len(cidx)
+            agree = float((cidx[:, 0] == r["idx"][:n1, 0]).mean())
+            cb["nn_agreement_with_gpu"] = agree
+            out["cpu_baseline"] = cb
+        if not args.no_parts and world == 1:
+            out["parts"] = dict(hamming_c1=bench_hamming(g, args.steps, args.warmup), ransac_c3=bench_ransac(g, max(3, args.steps // 4), 3))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -45,6 +45,12 @@ int         mpl_shutdown(void);
 const char* mpl_last_error(void);            /* thread-local text of the last failure */
 int         mpl_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
 long long   mpl_kernel_launch_count(void);   /* kernels launched by this library since mpl_init */
+/* Device timers per kernel class (CUDA events on the launching stream), off by default.  Class ids:
+ * 0 Hamming scan, 1 exact L2 scan, 2 tensor-core L2 ranking, 3 L2 re-rank/certify, 4 top-2 merge,
+ * 5 five-point solve, 6 Sampson scoring, 7 L2 operand preparation.  mpl_prof_read waits for the recorded
+ * launches of one class, returns their summed duration and count, and resets that class. */
+int         mpl_prof_enable(int on);
+int         mpl_prof_read(int kernel_class, double* total_ms, long long* launches);
 
 /* ---- brute-force k-NN, host pointers -------------------------------------------------------
  * mpl_knn2_hamming replaces cvflann::Index<HammingLUT>(LinearIndexParams).knnSearch

@@ -26,6 +26,50 @@ void mpl_set_error(const char* fmt, ...)
 }
 void mpl_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
+// ---- device timers ----------------------------------------------------------------------------
+struct ProfSlot { std::vector<std::pair<cudaEvent_t, cudaEvent_t>> used, pool; };
+static ProfSlot g_prof[MPL_PROF_COUNT];
+static std::atomic<int> g_prof_on{0};
+static std::mutex g_prof_mu;
+
+void mpl_prof_begin(int id, cudaStream_t st)
+{
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    ProfSlot& s = g_prof[id];
+    std::pair<cudaEvent_t, cudaEvent_t> ev;
+    if (!s.pool.empty()) { ev = s.pool.back(); s.pool.pop_back(); }
+    else { cudaEventCreate(&ev.first); cudaEventCreate(&ev.second); }
+    cudaEventRecord(ev.first, st);
+    s.used.push_back(ev);
+}
+void mpl_prof_end(int id, cudaStream_t st)
+{
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    ProfSlot& s = g_prof[id];
+    if (!s.used.empty()) cudaEventRecord(s.used.back().second, st);
+}
+extern "C" int mpl_prof_enable(int on) { g_prof_on.store(on ? 1 : 0); return MPL_OK; }
+// Sum of the device durations recorded for kernel class `id` since the last read (waits for them).
+extern "C" int mpl_prof_read(int id, double* total_ms, long long* launches)
+{
+    if (id < 0 || id >= MPL_PROF_COUNT) { mpl_set_error("prof_read: bad id"); return MPL_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    ProfSlot& s = g_prof[id];
+    double tot = 0; long long n = 0;
+    for (auto& ev : s.used) {
+        float ms = 0;
+        if (cudaEventSynchronize(ev.second) == cudaSuccess && cudaEventElapsedTime(&ms, ev.first, ev.second) == cudaSuccess) { tot += ms; ++n; }
+        s.pool.push_back(ev);
+    }
+    s.used.clear();
+    (void)cudaGetLastError();
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = n;
+    return MPL_OK;
+}
+
 static MplCtx g_ctx;
 static std::mutex g_mu;            // serialises host-pointer entry points (they share scratch + stream)
 

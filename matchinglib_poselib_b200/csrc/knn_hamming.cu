@@ -224,6 +224,7 @@ int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, i
     const int eff_splits = (nt + rows_per_split - 1) / rows_per_split;
     if (eff_splits != n_splits) { mpl_set_error("hamming: internal split mismatch %d vs %d", eff_splits, n_splits); return MPL_ERR_BAD_ARG; }
     dim3 grid((nq + Cfg::kQueriesPerCta - 1) / Cfg::kQueriesPerCta, n_splits, n_pairs);
+    MplProfScope prof(MPL_PROF_HAMMING, st);
     hamming_top2_kernel<W16><<<grid, kThreads, 0, st>>>((const uint4*)q, nq, (const uint4*)t, nt, rows_per_split,
                                                          train_offset, partial);
     MPL_CUDA_CHECK(cudaGetLastError());
@@ -286,6 +287,7 @@ int mpl_launch_merge_top2(const mpl_key64* partial, int n_parts, int nq, int k, 
                           int float_sqrt, mpl_key64* merged_keys, cudaStream_t st)
 {
     if (nq <= 0) return MPL_OK;
+    MplProfScope prof(MPL_PROF_MERGE, st);
     merge_top2_kernel<<<(nq + 127) / 128, 128, 0, st>>>((const ulonglong2*)partial, n_parts, nq, k, idx,
                                                         (uint32_t*)dist, float_sqrt, (ulonglong2*)merged_keys);
     MPL_CUDA_CHECK(cudaGetLastError());

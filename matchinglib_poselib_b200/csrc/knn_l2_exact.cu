@@ -246,6 +246,7 @@ int mpl_launch_l2_exact_top2(const float* q, int nq, size_t q_ld, const float* t
     rps = ((rps + TT - 1) / TT) * TT;
     if ((nt + rps - 1) / rps != n_splits) { mpl_set_error("l2 exact: internal split mismatch"); return MPL_ERR_BAD_ARG; }
     dim3 grid((nq + TQ - 1) / TQ, n_splits);
+    MplProfScope prof(MPL_PROF_L2_EXACT, st);
     if (order_mode == 0)
         l2_exact_top2_kernel<0><<<grid, 256, 0, st>>>(q, nq, q_ld, t, nt, t_ld, dim, rps, train_offset, partial);
     else
@@ -264,6 +265,7 @@ int mpl_launch_l2_rerank(const float* q, int nq, size_t q_ld, const float* t, si
     while (threads < n_cand) threads *= 2;
     if (threads > 1024) { mpl_set_error("l2 rerank: too many candidates (%d)", n_cand); return MPL_ERR_LIMIT; }
     const size_t smem = threads * sizeof(mpl_key64);
+    MplProfScope prof(MPL_PROF_L2_RERANK, st);
     if (order_mode == 0)
         l2_rerank_kernel<0><<<nq, threads, smem, st>>>(q, nq, q_ld, t, t_ld, dim, cand, n_cand, train_offset, out);
     else

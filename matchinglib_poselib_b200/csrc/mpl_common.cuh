@@ -16,6 +16,18 @@
 void mpl_set_error(const char* fmt, ...);
 void mpl_count_launch();   // bumps the counter behind mpl_kernel_launch_count()
 
+// ---- per-kernel-class device timers (CUDA events on the launching stream; off by default) -------
+// bench.py enables them to time the dominant kernel of each path live (roofline.achieved).
+enum { MPL_PROF_HAMMING = 0, MPL_PROF_L2_EXACT, MPL_PROF_L2_TC, MPL_PROF_L2_RERANK, MPL_PROF_MERGE,
+       MPL_PROF_SOLVE, MPL_PROF_SCORE, MPL_PROF_L2_PREP, MPL_PROF_COUNT };
+void mpl_prof_begin(int id, cudaStream_t st);
+void mpl_prof_end(int id, cudaStream_t st);
+struct MplProfScope {
+    int id; cudaStream_t st;
+    MplProfScope(int id_, cudaStream_t st_) : id(id_), st(st_) { mpl_prof_begin(id, st); }
+    ~MplProfScope() { mpl_prof_end(id, st); }
+};
+
 #define MPL_CUDA_CHECK(expr)                                                                   \
     do {                                                                                       \
         cudaError_t _e = (expr);                                                               \

@@ -250,6 +250,7 @@ int mpl_launch_pack_corr(const double* p1, const double* p2, int n, void* corr, 
 int mpl_launch_fivept_solve(const void* corr, int n, const int32_t* samples, int h, double* models, int32_t* n_models, cudaStream_t st)
 {
     if (h <= 0) return MPL_OK;
+    MplProfScope prof(MPL_PROF_SOLVE, st);
     fivept_solve_kernel<<<(h + 63) / 64, 64, 0, st>>>((const double4*)corr, n, samples, h, models, n_models);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
@@ -282,6 +283,7 @@ int mpl_launch_sampson_score(const double* models, int m, const void* corr, int 
         MPL_CUDA_CHECK(cudaFuncSetAttribute(sampson_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
+    MplProfScope prof(MPL_PROF_SCORE, st);
     sampson_score_kernel<<<(m + kScoreThreads - 1) / kScoreThreads, kScoreThreads, smem, st>>>(models, m, (const double4*)corr, n, th * th, counts, errsums);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
