@@ -64,8 +64,8 @@ int         mpl_prof_read(int kernel_class, double* total_ms, long long* launche
  * mpl_knn2_l2f32 replaces cvflann::Index<L2<float>>(LinearIndexParams).knnSearch
  *   (matchers.cpp:634-664; SQUARED distances, cvflann fp32 accumulation order; sqrt_out = 0) and
  *   nmslibMatching<float> seq_search/l2 (sqrt distances, NMSLIB 4-lane order; sqrt_out = 1).
- *   Every returned distance is bit-exact fp32 in the stated order; with sqrt_out = 0 the
- *   tensor-core kernel only ranks candidates and the result is certified.
+ *   Every returned distance is bit-exact fp32 in the stated order: the tensor-core kernel only ranks
+ *   candidates, the exact re-rank certifies each query and uncertified ones are rescanned exactly.
  */
 int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step,
                      int nbytes, int ignore_tail_bytes, int k, int32_t* idx, int32_t* dist);
@@ -113,7 +113,13 @@ int    mpl_merge_top2_dev(const void* d_keys_parts, int n_parts, int nq, int k, 
 int    mpl_knn2_hamming_batch_dev(const void* d_q, const void* d_t, int n_pairs, int nq, int nt, int w16,
                                   void* d_keys_out, void* stream);
 
+/* d_scratch of the float path must be 256-byte aligned.  mpl_knn_l2_last_stats reads back (synchronising the stream) how
+ * many queries of the last tensor-core call on that scratch buffer failed certification and went through the exact
+ * scan, and whether the operands were bf16-exact (tf32_mode = 0) or ranked in tf32 (1).  *_host: same for the last
+ * mpl_knn2_l2f32 / getMatches call (meaningful only when that call took the tensor-core path). */
 size_t mpl_knn_l2_scratch_bytes(int nq, int nt, int dim);
+int    mpl_knn_l2_last_stats(const void* d_scratch, unsigned* fallbacks, unsigned* tf32_mode, void* stream);
+int    mpl_knn_l2_last_stats_host(unsigned* fallbacks, unsigned* tf32_mode);
 int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t, int nt, size_t t_ld, int dim,
                           int sqrt_out, long long train_offset, void* d_scratch, size_t scratch_bytes,
                           void* d_keys_out, void* stream);

@@ -46,6 +46,8 @@ SIGNATURES = {
     "mpl_merge_top2_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_knn2_hamming_batch_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_knn_l2_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mpl_knn_l2_last_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_knn_l2_last_stats_host": (c_int, [c_void_p, c_void_p]),
     "mpl_knn2_l2f32_dev": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
     "mpl_ransac_set_seed": (c_int, [ctypes.c_ulonglong]),
     "mpl_ransac_draw_samples": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),

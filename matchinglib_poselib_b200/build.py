@@ -15,7 +15,7 @@ SOURCES = ["capi.cu", "knn_hamming.cu", "knn_l2_exact.cu", "knn_l2_tc.cu", "rans
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",            # fp contraction is opted into per expression (__fma_rn / fma()); parity code relies on it being off
-    "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-fast-math", "-shared", "-lcuda",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-fast-math", "-shared",
 ]
 
 

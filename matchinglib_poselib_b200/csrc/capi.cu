@@ -296,7 +296,8 @@ extern "C" int mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const vo
     cudaStream_t st = (cudaStream_t)stream;
     if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
     int sm = g_ctx.ready ? g_ctx.sm_count : 148;
-    const bool want_tc = (g_l2_path == 2) || (g_l2_path == 0 && sqrt_out == 0 && mpl_l2tc_supported(nq, nt, dim));
+    // auto: the tensor-core path pays off once the scan is big enough to hide its 5 launches (prep, pack, rank, certify, list)
+    const bool want_tc = (g_l2_path == 2) || (g_l2_path == 0 && mpl_l2tc_supported(nq, nt, dim) && (long long)nq * nt >= (1ll << 22));
     if (want_tc) {
         if (!mpl_l2tc_supported(nq, nt, dim)) { mpl_set_error("l2: tensor-core path forced but shape unsupported (dim=%d)", dim); return MPL_ERR_BAD_ARG; }
         return mpl_l2tc_top2((const float*)d_q, nq, q_ld, (const float*)d_t, nt, t_ld, dim, sqrt_out, train_offset,
@@ -312,6 +313,21 @@ extern "C" int mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const vo
                                       train_offset, (mpl_key64*)d_scratch, st);
     if (rc) return rc;
     return mpl_launch_merge_top2((const mpl_key64*)d_scratch, splits, nq, 2, nullptr, nullptr, 0, (mpl_key64*)d_keys_out, st);
+}
+
+extern "C" int mpl_knn_l2_last_stats(const void* d_scratch, unsigned* fallbacks, unsigned* tf32_mode, void* stream)
+{
+    if (!d_scratch) { mpl_set_error("knn_l2_last_stats: null scratch"); return MPL_ERR_BAD_ARG; }
+    return mpl_l2tc_last_fallbacks(d_scratch, fallbacks, tf32_mode, (cudaStream_t)stream);
+}
+// same for the host-pointer entry point (library-owned scratch)
+extern "C" int mpl_knn_l2_last_stats_host(unsigned* fallbacks, unsigned* tf32_mode)
+{
+    std::lock_guard<std::mutex> g(g_mu);
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    if (!g_ctx.bufs[MPL_BUF_PART].ptr) { mpl_set_error("knn_l2_last_stats_host: no float k-NN call yet"); return MPL_ERR_BAD_ARG; }
+    return mpl_l2tc_last_fallbacks(g_ctx.bufs[MPL_BUF_PART].ptr, fallbacks, tf32_mode, g_ctx.stream);
 }
 
 extern "C" int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt, size_t t_step,

@@ -28,16 +28,19 @@ __device__ __forceinline__ void top2_push(mpl_key64& b0, mpl_key64& b1, mpl_key6
     b1 = min(b1, hi);
 }
 
+// One (query block, train split) tile job.  Query positions [q0, q0 + TQ) of a list of n_pos positions; position
+// p reads query row qmap[p] (or p itself when qmap is null) and writes partial[split * n_pos + p].
 template <int MODE>
-__global__ void __launch_bounds__(256)
-l2_exact_top2_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float* __restrict__ t, int nt, size_t t_ld,
-                     int dim, int rows_per_split, long long train_offset, mpl_key64* __restrict__ partial)
+__device__ __forceinline__ void
+l2_exact_tile(const float* __restrict__ q, int n_pos, const int* __restrict__ qmap, size_t q_ld, const float* __restrict__ t, int nt,
+              size_t t_ld, int dim, int rows_per_split, long long train_offset, int qblock, int split,
+              mpl_key64* __restrict__ partial)
 {
     __shared__ __align__(16) float sq[TQ][KC + PAD];
     __shared__ __align__(16) float st[TT][KC + PAD];
+    const int nq = n_pos;
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int q0 = blockIdx.x * TQ;
-    const int split = blockIdx.y;
+    const int q0 = qblock * TQ;
     const int row0 = split * rows_per_split;
     const int row_end = min(nt, row0 + rows_per_split);
     const int dim4 = (dim / 4) * 4;
@@ -61,10 +64,11 @@ l2_exact_top2_kernel(const float* __restrict__ q, int nq, size_t q_ld, const flo
             // stage 64 x 16 floats of each operand (zero filled past the matrix edges)
             {
                 const int r = tid >> 2, c = (tid & 3) * 4;
+                const int qrow = (q0 + r < nq) ? (qmap ? qmap[q0 + r] : q0 + r) : 0;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const int kk = k0 + c + e;
-                    sq[r][c + e] = (q0 + r < nq && kk < dim) ? q[(size_t)(q0 + r) * q_ld + kk] : 0.f;
+                    sq[r][c + e] = (q0 + r < nq && kk < dim) ? q[(size_t)qrow * q_ld + kk] : 0.f;
                     st[r][c + e] = (tb + r < row_end && kk < dim) ? t[(size_t)(tb + r) * t_ld + kk] : 0.f;
                 }
             }
@@ -163,6 +167,63 @@ l2_exact_top2_kernel(const float* __restrict__ q, int nq, size_t q_ld, const flo
         const int qi = q0 + ty * 4 + i;
         if (tx == 0 && qi < nq)
             reinterpret_cast<ulonglong2*>(partial)[(size_t)split * nq + qi] = make_ulonglong2(best0[i], best1[i]);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+l2_exact_top2_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float* __restrict__ t, int nt, size_t t_ld,
+                     int dim, int rows_per_split, long long train_offset, mpl_key64* __restrict__ partial)
+{
+    l2_exact_tile<MODE>(q, nq, nullptr, q_ld, t, nt, t_ld, dim, rows_per_split, train_offset, blockIdx.x, blockIdx.y, partial);
+}
+
+// List-driven persistent variant (queries the tensor-core path could not certify): *count positions in qlist.
+// The split count is chosen on the device so that even one 64-query block spreads over the whole grid.
+__device__ __forceinline__ int list_splits(int n, int nt, int grid)
+{
+    const int nblocks = (n + TQ - 1) / TQ;
+    int want = (grid + nblocks - 1) / nblocks;
+    const int max_splits = (nt + TT - 1) / TT;
+    if (want > max_splits) want = max_splits;
+    if (want < 1) want = 1;
+    int rps = (nt + want - 1) / want;
+    rps = ((rps + TT - 1) / TT) * TT;
+    return rps;                                   // rows per split
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+l2_exact_list_kernel(const float* __restrict__ q, const int* __restrict__ qlist, const unsigned* __restrict__ count, size_t q_ld,
+                     const float* __restrict__ t, int nt, size_t t_ld, int dim, long long train_offset, mpl_key64* __restrict__ partial)
+{
+    const int n = (int)*count;
+    if (n == 0) return;
+    const int rps = list_splits(n, nt, gridDim.x);
+    const int splits = (nt + rps - 1) / rps;
+    const int items = ((n + TQ - 1) / TQ) * splits;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+        l2_exact_tile<MODE>(q, n, qlist, q_ld, t, nt, t_ld, dim, rps, train_offset, w / splits, w % splits, partial);
+        __syncthreads();
+    }
+}
+
+__global__ void l2_list_merge_kernel(const int* __restrict__ qlist, const unsigned* __restrict__ count, int nt, int grid_of_scan,
+                                     const ulonglong2* __restrict__ partial, ulonglong2* __restrict__ keys_out)
+{
+    const int n = (int)*count;
+    if (n == 0) return;
+    const int rps = list_splits(n, nt, grid_of_scan);
+    const int splits = (nt + rps - 1) / rps;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
+        for (int s = 0; s < splits; ++s) {
+            const ulonglong2 v = partial[(size_t)s * n + p];
+            const mpl_key64 hi = max(b0, v.x);
+            b0 = min(b0, v.x);
+            b1 = min(min(b1, hi), v.y);
+        }
+        keys_out[qlist[p]] = make_ulonglong2(b0, b1);
     }
 }
 
@@ -270,6 +331,28 @@ int mpl_launch_l2_rerank(const float* q, int nq, size_t q_ld, const float* t, si
         l2_rerank_kernel<0><<<nq, threads, smem, st>>>(q, nq, q_ld, t, t_ld, dim, cand, n_cand, train_offset, out);
     else
         l2_rerank_kernel<1><<<nq, threads, smem, st>>>(q, nq, q_ld, t, t_ld, dim, cand, n_cand, train_offset, out);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}
+
+// Exact scan of the *count queries listed in qlist (device-side count: nothing is launched conditionally on the host).
+// partial needs mpl_l2_list_scratch_entries(nq, sm_count) 16-byte entries.
+size_t mpl_l2_list_scratch_entries(int nq, int sm_count) { return (size_t)2 * sm_count * TQ + 2 * (size_t)nq + TQ; }
+
+int mpl_launch_l2_exact_list(const float* q, const int* qlist, const unsigned* count, size_t q_ld, const float* t, int nt, size_t t_ld,
+                             int dim, int order_mode, long long train_offset, mpl_key64* partial, mpl_key64* keys_out, int sm_count,
+                             cudaStream_t st)
+{
+    const int grid = 2 * sm_count;
+    {
+        MplProfScope prof(MPL_PROF_L2_EXACT, st);
+        if (order_mode == 0) l2_exact_list_kernel<0><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial);
+        else                 l2_exact_list_kernel<1><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial);
+        MPL_CUDA_CHECK(cudaGetLastError());
+        mpl_count_launch();
+    }
+    l2_list_merge_kernel<<<8, 256, 0, st>>>(qlist, count, nt, grid, (const ulonglong2*)partial, (ulonglong2*)keys_out);
     MPL_CUDA_CHECK(cudaGetLastError());
     mpl_count_launch();
     return MPL_OK;

@@ -1,6 +1,639 @@
-// knn_l2_tc.cu -- placeholder until the tcgen05 ranking kernel lands (next commit).
+// knn_l2_tc.cu -- float-descriptor brute-force k-NN (k = 2) on the 5th-generation tensor cores, sm_100a.
+//
+// Replaces the hot loop of the reference's LINEAR matcher for CV_32F descriptors
+//   cvflann::Index<L2<float>>(LinearIndexParams).knnSearch      (matchers.cpp:634-664; OpenCV 4.2.0 flann/dist.h)
+// and of BRUTEFORCENMS (NMSLIB seq_search + l2, nmslib_matchers.h:159-424, distcomp_lp.cc:399-466).
+//
+// The reference evaluates d(q,t) = sum (q_i - t_i)^2 pair by pair in fp32.  Here the Q x T^T contraction runs
+// as a dense GEMM on tcgen05 and only RANKS: score(q,t) = |t|^2 - 2 q.t (the |q|^2 term is constant per
+// query).  Every distance that leaves the library is then recomputed in exact fp32, in the reference's own
+// accumulation order, for a short certified candidate list:
+//
+//   1. l2_prep_scan_kernel   |x|^2 per row, max |t|^2, and whether every value is exactly representable in
+//                            bf16 (true for OpenCV SIFT: integers 0..255).  No host round trip: the flag
+//                            lives in device memory and the later kernels branch on it.
+//   2. l2_prep_pack_kernel   operand copies: bf16 rows (exact data, kind::f16, full tensor rate, products and
+//                            fp32 accumulation exact for integer data) or fp32 rows read as tf32 (kind::tf32).
+//   3. l2_tc_rank_kernel     persistent, warp specialised: warp 0 = TMA producer (128B-swizzled K-major slabs,
+//                            cp.async.bulk.tensor), warp 1 = tcgen05.mma issuer (one elected thread),
+//                            warp 2 = TMEM allocator, warps 4-11 = epilogue.  CTA tile = 256 queries (two
+//                            UMMA M=128 blocks, resident in smem) x 128 train rows per step; accumulators
+//                            double-buffered in TMEM (2 x 2 x 128 columns = all 512).  Epilogue thread =
+//                            one query row: tcgen05.ld 32 columns at a time, score = fma(-2, acc, |t|^2),
+//                            register-resident sorted top-4 per thread (strict '<' keeps the lower train
+//                            index on ties).  Work = (query block, train tile) units split evenly over the
+//                            CTAs (grid = SM count), so a query block may be covered by several CTAs; each
+//                            writes its own candidate list ("slot").
+//   4. l2_certify_kernel     one warp per query: exact fp32 distances (cvflann / NMSLIB order) of the
+//                            candidates that can still be among the two nearest, top-2 by (dist, trainIdx),
+//                            and the certificate  d2 < tau + |q|^2 - eps  (tau = smallest "4th best" score
+//                            over the slots: every train row that is NOT a candidate scores >= tau; eps bounds
+//                            |score + |q|^2 - d|).  Certified queries are final and bit-exact.
+//   5. the rare uncertified query (near-duplicate clusters) goes through the exact fp32 scan
+//      (knn_l2_exact.cu, list-driven persistent kernel) -- still on the device, no host decision.
+//
+// Roofline: tensor pipe, 2*D flop per pair.
+#include "mpl_common.cuh"
 #include "mpl_ctx.h"
-bool   mpl_l2tc_supported(int, int, int) { return false; }
-size_t mpl_l2tc_scratch_bytes(int, int, int, int) { return 16; }
-int    mpl_l2tc_top2(const float*, int, size_t, const float*, int, size_t, int, int, long long, void*, size_t, mpl_key64*, int, cudaStream_t)
-{ mpl_set_error("tensor-core L2 path not built"); return MPL_ERR_BAD_ARG; }
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <math.h>
+
+namespace {
+
+// ---- geometry -------------------------------------------------------------------------------------
+constexpr int BM = 256;              // queries per CTA tile (2 x UMMA_M)
+constexpr int UM = 128;              // UMMA M
+constexpr int BN = 128;              // train rows per tile = UMMA N
+constexpr int SLAB_BYTES = 128;      // K extent of one smem slab in bytes (= swizzle width)
+constexpr int A_SLAB = BM * SLAB_BYTES;      // 32 KB
+constexpr int B_SLAB = BN * SLAB_BYTES;      // 16 KB
+constexpr int MAX_A_SLABS = 4;       // dim <= 128 floats (tf32) / 256 bf16
+constexpr int NSTAGES = 4;           // B slab ring
+constexpr int NORM_RING = 8;         // |t|^2 tiles in flight (>= NSTAGES + 2, see producer notes)
+constexpr int NC = 4;                // candidates kept per (thread, slot)
+constexpr int TC_THREADS = 384;      // warps 0..3 control, 4..11 epilogue
+constexpr int SMEM_A = MAX_A_SLABS * A_SLAB;                 // 128 KB
+constexpr int SMEM_B = NSTAGES * B_SLAB;                     //  64 KB
+constexpr int SMEM_NORM = NORM_RING * BN * 4;                //   4 KB
+constexpr int SMEM_BYTES = 1024 + SMEM_A + SMEM_B + SMEM_NORM + 256;
+
+struct TcHeader {                    // first 256 bytes of the scratch buffer (zeroed per call)
+    unsigned not_bf16_exact;         // 0 -> bf16 mode, else tf32 mode
+    unsigned max_tnorm_bits;         // max |t|^2 (float bits; non-negative floats order like uints)
+    unsigned fallback_count;         // queries that failed certification
+    unsigned pad[61];
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {   // arrives on bar when every MMA issued so far has completed
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 consecutive columns of 32-bit accumulators -> 32 registers per thread (thread = lane = row)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand slab, 128-byte swizzle: 8-row groups of 1024 bytes (SBO), descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor: D = f32, A/B format (1 = bf16, 2 = tf32), both K-major, N = 128, M = 128
+__host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt) {
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(UM >> 4) << 24);
+}
+
+// ---- 1. scan: row norms, max |t|^2, bf16-exactness -----------------------------------------------------
+// rows [0, nt) are train rows, [nt, nt + nq) query rows; one warp per row.  Norm buffers are padded to the
+// tile size with +inf (a pad row can then never enter a candidate list: inf < tau is false).
+__global__ void __launch_bounds__(256)
+l2_prep_scan_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld,
+                    int dim, float* __restrict__ tnorm, int nt_pad, float* __restrict__ qnorm, int nq_pad, TcHeader* hdr)
+{
+    const int lane = threadIdx.x & 31;
+    const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
+    const int total = nt_pad + nq_pad;
+    unsigned inexact = 0;
+    float tmax = 0.f;
+    for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < total; row += warps_per_grid) {
+        const bool is_t = row < nt_pad;
+        const int r = is_t ? row : row - nt_pad;
+        const int n = is_t ? nt : nq;
+        float* out = is_t ? tnorm : qnorm;
+        if (r >= n) { if (lane == 0) out[r] = INFINITY; continue; }
+        const float* x = (is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld);
+        float s = 0.f;
+        for (int i = lane; i < dim; i += 32) {
+            const float v = x[i];
+            inexact |= (__float_as_uint(v) & 0xFFFFu);
+            s = fmaf(v, v, s);
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) out[r] = s;
+        if (is_t) tmax = fmaxf(tmax, s);
+    }
+    inexact = __any_sync(0xffffffffu, inexact != 0);
+    if (lane == 0) {
+        if (inexact) atomicOr(&hdr->not_bf16_exact, 1u);
+        if (tmax > 0.f) atomicMax(&hdr->max_tnorm_bits, __float_as_uint(tmax));
+    }
+}
+
+// ---- 2. pack: operand rows in the MMA's element type ---------------------------------------------------
+// bf16 mode: rows of kp16 bf16 (kp16 = dim rounded up to 64); tf32 mode: rows of kp32 floats (dim rounded
+// up to 32).  Same destination buffer either way (sized for the fp32 case); zero padded columns.
+__global__ void __launch_bounds__(256)
+l2_prep_pack_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
+                    void* __restrict__ tp, void* __restrict__ qp, int kp16, int kp32, const TcHeader* __restrict__ hdr)
+{
+    const bool bf16_mode = hdr->not_bf16_exact == 0;
+    const int kp = bf16_mode ? kp16 : kp32;
+    const int groups = kp / 4;                                   // 4 elements per thread
+    const long long total = (long long)(nt + nq) * groups;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int row = (int)(i / groups), g = (int)(i - (long long)row * groups);
+        const bool is_t = row < nt;
+        const int r = is_t ? row : row - nt;
+        const float* x = is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld;
+        float v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = (4 * g + e < dim) ? x[4 * g + e] : 0.f;
+        char* dst = (char*)(is_t ? tp : qp);
+        if (bf16_mode) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+            uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst + ((size_t)r * kp + 4 * g) * 2) = o;
+        } else {
+            *reinterpret_cast<float4*>(dst + ((size_t)r * kp + 4 * g) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+    }
+}
+
+// ---- 3. tensor-core ranking kernel ----------------------------------------------------------------------
+struct TcParams {
+    int nq, nt, NT;                  // NT = train tiles of BN rows
+    long long U;                     // work units = query blocks x train tiles
+    int max_slots;                   // candidate slots per query block
+    int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
+    const float* tnorm;              // |t|^2 padded to NT * BN with +inf
+    uint4* cand;                     // [qblock][slot][BM rows][2 x uint4] = 4 scores + 4 train indices
+    const TcHeader* hdr;
+};
+
+// CTA c owns units [c*U/G, (c+1)*U/G); owner(u) = the CTA whose range holds unit u
+__host__ __device__ inline int tc_owner(long long u, long long U, int G) { return (int)(((u + 1) * G - 1) / U); }
+
+struct TopList {
+    float s0, s1, s2, s3; int i0, i1, i2, i3;
+    __device__ __forceinline__ void reset() { s0 = s1 = s2 = s3 = INFINITY; i0 = i1 = i2 = i3 = -1; }
+    __device__ __forceinline__ void insert(float s, int i) {     // caller checked s < s3
+        s3 = s; i3 = i;
+        if (s3 < s2) { float a = s2; s2 = s3; s3 = a; int b = i2; i2 = i3; i3 = b;
+            if (s2 < s1) { a = s1; s1 = s2; s2 = a; b = i1; i1 = i2; i2 = b;
+                if (s1 < s0) { a = s0; s0 = s1; s1 = a; b = i0; i0 = i1; i1 = b; } } }
+    }
+};
+
+__device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
+    // the loaded registers become valid here: tie them to the wait so no use can be scheduled above it
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                   "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :: "memory");
+}
+
+__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm, int col0, TopList& L)
+{
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+        const float4 n4 = *reinterpret_cast<const float4*>(nrm + 4 * g);          // LDS.128, warp-wide broadcast
+        const float a = fmaf(-2.f, __uint_as_float(r[4 * g + 0]), n4.x);
+        const float b = fmaf(-2.f, __uint_as_float(r[4 * g + 1]), n4.y);
+        const float c = fmaf(-2.f, __uint_as_float(r[4 * g + 2]), n4.z);
+        const float d = fmaf(-2.f, __uint_as_float(r[4 * g + 3]), n4.w);
+        if (fminf(fminf(a, b), fminf(c, d)) < L.s3) {
+            if (a < L.s3) L.insert(a, col0 + 4 * g + 0);
+            if (b < L.s3) L.insert(b, col0 + 4 * g + 1);
+            if (c < L.s3) L.insert(c, col0 + 4 * g + 2);
+            if (d < L.s3) L.insert(d, col0 + 4 * g + 3);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_constant__ CUtensorMap mapB16,
+                  const __grid_constant__ CUtensorMap mapA32, const __grid_constant__ CUtensorMap mapB32, const TcParams p)
+{
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);   // swizzle-128B atoms: 1024-byte aligned
+    unsigned char* sA = smem;
+    unsigned char* sB = smem + SMEM_A;
+    float* sN = reinterpret_cast<float*>(smem + SMEM_A + SMEM_B);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_A + SMEM_B + SMEM_NORM);
+    uint64_t* a_full = bars + 0; uint64_t* a_empty = bars + 1;
+    uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + NSTAGES;
+    uint64_t* t_full = bars + 2 + 2 * NSTAGES; uint64_t* t_empty = t_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool tf32 = p.hdr->not_bf16_exact != 0;
+    const int n_slabs = tf32 ? p.slabs32 : p.slabs16;
+    const int KS = tf32 ? 32 : 64;                               // elements per 128-byte slab row
+    const CUtensorMap* mapA = tf32 ? &mapA32 : &mapA16;
+    const CUtensorMap* mapB = tf32 ? &mapB32 : &mapB16;
+    const int G = gridDim.x;
+    const long long u0 = (long long)blockIdx.x * p.U / G, u1 = (long long)(blockIdx.x + 1) * p.U / G;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(mapA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(mapB) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(a_full, 1); mbar_init(a_empty, 1);
+        for (int s = 0; s < NSTAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {                                             // whole warp: allocate all 512 TMEM columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (one thread) =====
+        if (lane == 0) {
+            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned seq = 0;
+            for (long long u = u0; u < u1; ++u, ++seq) {
+                const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
+                if (qb != cur_qb) {
+                    mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));             // MMAs of the previous query block are done
+                    mbar_expect_tx(a_full, (uint32_t)(n_slabs * A_SLAB));
+                    for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * A_SLAB, mapA, s * KS, qb * BM, a_full);
+                    ++a_cnt; cur_qb = qb;
+                }
+                for (int s = 0; s < n_slabs; ++s) {
+                    mbar_wait(&b_empty[stage], sphase ^ 1);
+                    mbar_expect_tx(&b_full[stage], (uint32_t)(B_SLAB + (s == 0 ? BN * 4 : 0)));
+                    tma_load_2d(sB + stage * B_SLAB, mapB, s * KS, tile * BN, &b_full[stage]);
+                    // |t|^2 of the tile rides on the first slab's barrier.  Ring slot reuse is safe: the slab ring
+                    // keeps this thread at most NSTAGES tiles ahead of the MMA issuer, which is at most two tiles
+                    // ahead of the epilogue (TMEM double buffer), and NORM_RING >= NSTAGES + 2.
+                    if (s == 0) tma_bulk_g2s(sN + (seq % NORM_RING) * BN, p.tnorm + (size_t)tile * BN, BN * 4, &b_full[stage]);
+                    if (++stage == NSTAGES) { stage = 0; sphase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(tf32 ? 2u : 1u);
+            const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned it = 0;
+            for (long long u = u0; u < u1; ++u, ++it) {
+                const int qb = (int)(u / p.NT);
+                if (qb != cur_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; cur_qb = qb; }
+                const uint32_t b = it & 1;
+                mbar_wait(&t_empty[b], ((it >> 1) & 1) ^ 1);                     // epilogue drained this accumulator buffer
+                tc_fence_after();
+                for (int s = 0; s < n_slabs; ++s) {
+                    mbar_wait(&b_full[stage], sphase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int m = 0; m < 2; ++m)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {                            // 4 x 32 bytes of K per slab row
+                            const uint64_t ad = umma_desc(a_addr + s * A_SLAB + m * (UM * SLAB_BYTES) + k * 32);
+                            const uint64_t bd = umma_desc(b_addr + stage * B_SLAB + k * 32);
+                            const uint32_t d = tmem_base + b * 256 + m * 128;
+                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, (uint32_t)((s | k) != 0));
+                            else      tc_mma_f16(d, ad, bd, idesc, (uint32_t)((s | k) != 0));
+                        }
+                    tc_commit(&b_empty[stage]);                                  // slab free once these MMAs retire
+                    if (++stage == NSTAGES) { stage = 0; sphase ^= 1; }
+                }
+                tc_commit(&t_full[b]);
+                if (u + 1 < u1 && (int)((u + 1) / p.NT) != qb) tc_commit(a_empty);  // only when the producer will wait for it
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: thread = one query row of block m =====
+        const int m = (warp - 4) >> 2, quad = warp & 3, row = quad * 32 + lane;
+        TopList L; L.reset();
+        int cur_qb = -1; unsigned it = 0;
+        auto flush = [&](int qb) {
+            const int slot = (int)blockIdx.x - tc_owner((long long)qb * p.NT, p.U, G);
+            uint4* dst = p.cand + (((size_t)qb * p.max_slots + slot) * BM + m * UM + row) * 2;
+            dst[0] = make_uint4(__float_as_uint(L.s0), __float_as_uint(L.s1), __float_as_uint(L.s2), __float_as_uint(L.s3));
+            dst[1] = make_uint4((uint32_t)L.i0, (uint32_t)L.i1, (uint32_t)L.i2, (uint32_t)L.i3);
+        };
+        for (long long u = u0; u < u1; ++u, ++it) {
+            const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
+            if (qb != cur_qb) { if (cur_qb >= 0) flush(cur_qb); L.reset(); cur_qb = qb; }
+            const uint32_t b = it & 1;
+            mbar_wait(&t_full[b], (it >> 1) & 1);
+            tc_fence_after();
+            const float* nrm = sN + (it % NORM_RING) * BN;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128;
+            const int col0 = tile * BN;
+            uint32_t ra[32], rb[32];
+            tc_ld32(taddr, ra);
+            tc_wait_ld_regs(ra); tc_ld32(taddr + 32, rb); score_chunk(ra, nrm, col0, L);
+            tc_wait_ld_regs(rb); tc_ld32(taddr + 64, ra); score_chunk(rb, nrm + 32, col0 + 32, L);
+            tc_wait_ld_regs(ra); tc_ld32(taddr + 96, rb); score_chunk(ra, nrm + 64, col0 + 64, L);
+            tc_wait_ld_regs(rb);                          score_chunk(rb, nrm + 96, col0 + 96, L);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&t_empty[b]);
+        }
+        if (cur_qb >= 0) flush(cur_qb);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+}
+
+// ---- 4. exact re-rank + certificate --------------------------------------------------------------------
+// cvflann::L2<float> order (MODE 0): result += ((d0^2 + d1^2) + d2^2) + d3^2 per group of 4, scalar tail;
+// NMSLIB L2NormSIMD order (MODE 1): 4 lanes, ((l0 + l1) + l2) + l3, scalar tail, sqrtf.
+template <int MODE>
+__device__ __forceinline__ float exact_dist(const float* __restrict__ a /* train row */, const float* __restrict__ b /* query row */, int dim, float* sq_out)
+{
+    float r;
+    int i = 0;
+    if (MODE == 0) {
+        r = 0.f;
+        for (; i + 3 < dim; i += 4) {
+            const float d0 = __fsub_rn(a[i], b[i]), d1 = __fsub_rn(a[i + 1], b[i + 1]);
+            const float d2 = __fsub_rn(a[i + 2], b[i + 2]), d3 = __fsub_rn(a[i + 3], b[i + 3]);
+            float s = __fadd_rn(__fmul_rn(d0, d0), __fmul_rn(d1, d1));
+            s = __fadd_rn(s, __fmul_rn(d2, d2));
+            s = __fadd_rn(s, __fmul_rn(d3, d3));
+            r = __fadd_rn(r, s);
+        }
+    } else {
+        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+        for (; i + 3 < dim; i += 4) {
+            const float d0 = __fsub_rn(a[i], b[i]), d1 = __fsub_rn(a[i + 1], b[i + 1]);
+            const float d2 = __fsub_rn(a[i + 2], b[i + 2]), d3 = __fsub_rn(a[i + 3], b[i + 3]);
+            l0 = __fadd_rn(l0, __fmul_rn(d0, d0)); l1 = __fadd_rn(l1, __fmul_rn(d1, d1));
+            l2 = __fadd_rn(l2, __fmul_rn(d2, d2)); l3 = __fadd_rn(l3, __fmul_rn(d3, d3));
+        }
+        r = __fadd_rn(__fadd_rn(__fadd_rn(l0, l1), l2), l3);
+    }
+    for (; i < dim; ++i) { const float d = __fsub_rn(a[i], b[i]); r = __fadd_rn(r, __fmul_rn(d, d)); }
+    *sq_out = r;
+    return MODE == 1 ? sqrtf(r) : r;
+}
+
+__device__ __forceinline__ void warp_top2(mpl_key64& b0, mpl_key64& b1)
+{
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const mpl_key64 o0 = __shfl_xor_sync(0xffffffffu, b0, off), o1 = __shfl_xor_sync(0xffffffffu, b1, off);
+        const mpl_key64 hi = max(b0, o0);
+        b0 = min(b0, o0);
+        b1 = min(min(b1, o1), hi);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float* __restrict__ t, int nt, size_t t_ld, int dim,
+                  const float* __restrict__ qnorm, const uint4* __restrict__ cand, int NT, long long U, int G, int max_slots,
+                  long long train_offset, TcHeader* hdr, mpl_key64* __restrict__ keys_out, int* __restrict__ fallback_list)
+{
+    const int lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (qi >= nq) return;
+    const int qb = qi / BM, row = qi - qb * BM;
+    const int first = tc_owner((long long)qb * NT, U, G), last = tc_owner((long long)qb * NT + NT - 1, U, G);
+    const int n_cand = (last - first + 1) * NC;
+    const float qq = qnorm[qi];
+    const float tmax = __uint_as_float(hdr->max_tnorm_bits);
+    // eps >= |score + |q|^2 - d_ref|: operand quantisation (tf32 truncation, none in bf16-exact mode) plus a generous
+    // bound on fp32 accumulation error on both sides
+    const float sq = sqrtf(qq), st = sqrtf(tmax);
+    float eps = 1.2207031e-4f * (sq + st) * (sq + st);                            // 2^-13 (|q| + |t|max)^2
+    if (hdr->not_bf16_exact) eps += 3.90625e-3f * sq * st;                        // 2^-8 |q| |t|max
+    // pass A: the two smallest scores over all candidates, and tau = min over slots of the slot's 4th best
+    float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
+    for (int c = lane; c < n_cand; c += 32) {
+        const int slot = c / NC, e = c - slot * NC;
+        const uint4* rec = cand + (((size_t)qb * max_slots + slot) * BM + row) * 2;
+        const uint4 sc = rec[0];
+        const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
+        if (e == NC - 1) tau = fminf(tau, s);
+        const float hi = fmaxf(s_a, s); s_a = fminf(s_a, s); s_b = fminf(s_b, hi);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const float oa = __shfl_xor_sync(0xffffffffu, s_a, off), ob = __shfl_xor_sync(0xffffffffu, s_b, off);
+        const float hi = fmaxf(s_a, oa);
+        s_a = fminf(s_a, oa); s_b = fminf(fminf(s_b, ob), hi);
+        tau = fminf(tau, __shfl_xor_sync(0xffffffffu, tau, off));
+    }
+    // pass B: exact distance of every candidate that can still be one of the two nearest
+    const float cut = s_b + 2.f * eps;
+    mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
+    float sq2 = 0.f;                                                              // squared distance behind b1 (MODE 1)
+    const float* qrow = q + (size_t)qi * q_ld;
+    for (int c = lane; c < n_cand; c += 32) {
+        const int slot = c / NC, e = c - slot * NC;
+        const uint4* rec = cand + (((size_t)qb * max_slots + slot) * BM + row) * 2;
+        const uint4 sc = rec[0], id = rec[1];
+        const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
+        const int ti = (int)(e == 0 ? id.x : e == 1 ? id.y : e == 2 ? id.z : id.w);
+        if (ti < 0 || ti >= nt || !(s <= cut)) continue;
+        float sqv;
+        const float d = exact_dist<MODE>(t + (size_t)ti * t_ld, qrow, dim, &sqv);
+        const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
+        const mpl_key64 hi = max(b0, key);
+        b0 = min(b0, key); b1 = min(b1, hi);
+    }
+    warp_top2(b0, b1);
+    (void)sq2;
+    if (lane == 0) {
+        keys_out[2 * (size_t)qi] = b0; keys_out[2 * (size_t)qi + 1] = b1;
+        // certificate: every non-candidate has score >= tau, hence reference distance >= tau + |q|^2 - eps
+        bool ok;
+        if (b1 == MPL_KEY_INVALID) ok = (tau == INFINITY);                         // fewer than 2 train rows scanned in total
+        else {
+            float d2 = __uint_as_float((uint32_t)(b1 >> 32));
+            if (MODE == 1) d2 = __fmul_rn(d2, d2) * 1.000002f;                     // back to the squared domain, rounding margin
+            ok = d2 < tau + qq - eps;
+        }
+        if (!ok) fallback_list[atomicAdd(&hdr->fallback_count, 1u)] = qi;
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+struct TcPlan {
+    int NQB, NT, G, max_slots, kp16, kp32;
+    long long U;
+    size_t off_tnorm, off_qnorm, off_tp, off_qp, off_cand, off_list, off_part, total;
+};
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+TcPlan make_plan(int nq, int nt, int dim, int sm_count)
+{
+    TcPlan P;
+    P.NQB = (nq + BM - 1) / BM;
+    P.NT = (nt + BN - 1) / BN;
+    P.U = (long long)P.NQB * P.NT;
+    P.G = (int)(P.U < sm_count ? P.U : sm_count);
+    P.kp16 = ((dim + 63) / 64) * 64;
+    P.kp32 = ((dim + 31) / 32) * 32;
+    P.max_slots = 1;
+    for (int qb = 0; qb < P.NQB; ++qb) {
+        const int s = tc_owner((long long)qb * P.NT + P.NT - 1, P.U, P.G) - tc_owner((long long)qb * P.NT, P.U, P.G) + 1;
+        if (s > P.max_slots) P.max_slots = s;
+    }
+    size_t o = 256;
+    P.off_tnorm = o; o = align256(o + (size_t)P.NT * BN * 4);
+    P.off_qnorm = o; o = align256(o + (size_t)P.NQB * BM * 4);
+    P.off_tp = o;    o = align256(o + (size_t)nt * P.kp32 * 4);
+    P.off_qp = o;    o = align256(o + (size_t)nq * P.kp32 * 4);
+    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * BM * 32);
+    P.off_list = o;  o = align256(o + (size_t)nq * 4);
+    P.off_part = o;  o = align256(o + mpl_l2_list_scratch_entries(nq, sm_count) * 16);
+    P.total = o;
+    return P;
+}
+
+int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int elt_bytes, void* base, int kp, int rows, int box_k, int box_rows)
+{
+    cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)kp * elt_bytes};
+    cuuint32_t box[2] = {(cuuint32_t)box_k, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    // libcuda is reached through the runtime (no link-time dependency: the library must still load on a box
+    // without a driver so that it can fail loudly with MPL_ERR_NO_DEVICE instead of a dlopen error)
+    typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn_t encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        MPL_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess) { mpl_set_error("cuTensorMapEncodeTiled not available from the driver"); return MPL_ERR_CUDA; }
+        encode = (encode_fn_t)fn;
+    }
+    const CUresult r = encode(map, dt, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { mpl_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return MPL_ERR_CUDA; }
+    return MPL_OK;
+}
+
+}  // namespace
+
+bool mpl_l2tc_supported(int nq, int nt, int dim) { return nq >= 1 && nt >= 2 && dim >= 1 && dim <= 128; }
+
+size_t mpl_l2tc_scratch_bytes(int nq, int nt, int dim, int sm_count)
+{
+    if (!mpl_l2tc_supported(nq, nt, dim)) return 16;
+    return make_plan(nq, nt, dim, sm_count).total;
+}
+
+int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int nt, size_t t_ld, int dim, int sqrt_out,
+                  long long train_offset, void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st)
+{
+    if (!mpl_l2tc_supported(nq, nt, dim)) { mpl_set_error("l2 tensor-core path: unsupported shape (dim=%d)", dim); return MPL_ERR_BAD_ARG; }
+    const TcPlan P = make_plan(nq, nt, dim, sm_count);
+    if (!d_scratch || scratch_bytes < P.total) { mpl_set_error("l2 tensor-core path: scratch %zu < %zu bytes", scratch_bytes, P.total); return MPL_ERR_BAD_ARG; }
+    if (((uintptr_t)d_scratch & 255) != 0) { mpl_set_error("l2 tensor-core path: scratch must be 256-byte aligned"); return MPL_ERR_BAD_ARG; }
+    char* base = (char*)d_scratch;
+    TcHeader* hdr = (TcHeader*)base;
+    float* tnorm = (float*)(base + P.off_tnorm); float* qnorm = (float*)(base + P.off_qnorm);
+    void* tp = base + P.off_tp; void* qp = base + P.off_qp;
+    uint4* cand = (uint4*)(base + P.off_cand);
+    int* flist = (int*)(base + P.off_list);
+    mpl_key64* part = (mpl_key64*)(base + P.off_part);
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    alignas(64) CUtensorMap mA16, mB16, mA32, mB32;
+    int rc;
+    if ((rc = encode_map(&mA16, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, qp, P.kp16, nq, 64, BM))) return rc;
+    if ((rc = encode_map(&mB16, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tp, P.kp16, nt, 64, BN))) return rc;
+    if ((rc = encode_map(&mA32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, qp, P.kp32, nq, 32, BM))) return rc;
+    if ((rc = encode_map(&mB32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, tp, P.kp32, nt, 32, BN))) return rc;
+
+    MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
+    {
+        MplProfScope prof(MPL_PROF_L2_PREP, st);
+        const int rows = P.NT * BN + P.NQB * BM;
+        int blocks = (rows + 7) / 8; if (blocks > sm_count * 8) blocks = sm_count * 8;
+        l2_prep_scan_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tnorm, P.NT * BN, qnorm, P.NQB * BM, hdr);
+        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        l2_prep_pack_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, P.kp32, hdr);
+        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    }
+    {
+        MplProfScope prof(MPL_PROF_L2_TC, st);
+        TcParams prm;
+        prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots;
+        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.tnorm = tnorm; prm.cand = cand; prm.hdr = hdr;
+        l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(mA16, mB16, mA32, mB32, prm);
+        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    }
+    {
+        MplProfScope prof(MPL_PROF_L2_RERANK, st);
+        const int blocks = (nq + 7) / 8;
+        if (sqrt_out) l2_certify_kernel<1><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist);
+        else          l2_certify_kernel<0><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist);
+        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    }
+    return mpl_launch_l2_exact_list(d_q, flist, &hdr->fallback_count, q_ld, d_t, nt, t_ld, dim, sqrt_out ? 1 : 0, train_offset, part,
+                                    d_keys_out, sm_count, st);
+}
+
+// Number of queries of the last call on this scratch buffer that took the exact-scan fallback (diagnostics / tests).
+int mpl_l2tc_last_fallbacks(const void* d_scratch, unsigned* count, unsigned* tf32_mode, cudaStream_t st)
+{
+    TcHeader h;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(&h, d_scratch, sizeof(h), cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (count) *count = h.fallback_count;
+    if (tf32_mode) *tf32_mode = h.not_bf16_exact;
+    return MPL_OK;
+}

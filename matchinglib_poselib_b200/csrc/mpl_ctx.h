@@ -33,3 +33,4 @@ size_t mpl_l2tc_scratch_bytes(int nq, int nt, int dim, int sm_count);
 int    mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int nt, size_t t_ld, int dim, int sqrt_out,
                      long long train_offset, void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out,
                      int sm_count, cudaStream_t st);
+int    mpl_l2tc_last_fallbacks(const void* d_scratch, unsigned* count, unsigned* tf32_mode, cudaStream_t st);

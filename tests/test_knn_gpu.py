@@ -138,3 +138,62 @@ def test_get_matches_error_codes(m):
     assert m.getMatchesArray(kp1, kp2, d1.astype(np.float64), d2.astype(np.float64), None, "LINEAR")[0] == -1
     with pytest.raises(AssertionError):
         m.getMatchesArray(kp1, kp2, d1, d2.astype(np.float32), None, "LINEAR")
+
+
+# ---- tensor-core float path (knn_l2_tc.cu): ranking on tcgen05, exact re-rank, certificate, exact fallback ----
+def _tc(m, q, t, sqrt_out=False):
+    import ctypes
+    lib = m._lib.load()
+    lib.mpl_set_l2_path(2)
+    try:
+        idx, dist = m.knn2_l2(q, t, 2, sqrt_out)
+    finally:
+        lib.mpl_set_l2_path(0)
+    fb, mode = ctypes.c_uint(0), ctypes.c_uint(0)
+    m._lib.check(lib.mpl_knn_l2_last_stats_host(ctypes.byref(fb), ctypes.byref(mode)), "stats")
+    return idx, dist, fb.value, mode.value
+
+
+@pytest.mark.parametrize("nq,nt,d,kind", [(5, 2, 128, "sift"), (256, 128, 128, "sift"), (257, 129, 128, "sift"), (300, 40000, 128, "sift"),
+                                           (5000, 5000, 128, "sift"), (700, 9000, 64, "sift"), (640, 3000, 120, "signed"),
+                                           (1000, 20000, 128, "signed"), (513, 2050, 33, "signed"), (400, 1111, 7, "signed")])
+def test_l2_tc_path(m, nq, nt, d, kind):
+    q, t = datagen.sift_like(nq, nt, d, seed=nq + nt) if kind == "sift" else datagen.signed_float(nq, nt, d, seed=nq + nt)
+    idx, dist, fb, mode = _tc(m, q, t)
+    assert mode == (0 if kind == "sift" else 1)           # integer-valued SIFT -> bf16-exact operands, else tf32
+    oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)), (nq, nt, d)
+    assert np.array_equal(idx, oi)
+    assert fb <= max(4, nq // 20), "certificate failed for %d of %d queries" % (fb, nq)
+
+
+def test_l2_tc_sqrt_mode(m):
+    q, t = datagen.signed_float(600, 5000, 64, seed=5)
+    idx, dist, fb, mode = _tc(m, q, t, True)
+    oi, od = orc.knn_l2(q, t, 2, 1, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
+
+
+def test_l2_tc_duplicates_take_the_fallback(m):
+    """Ten identical train rows: the 4-deep candidate lists cannot certify -> exact scan, lowest indices win."""
+    q, t = datagen.sift_like(300, 3000, 128, seed=77)
+    t[100:110] = t[5]
+    q[0] = t[5]; q[1] = t[5]; q[1, 3] += 1
+    idx, dist, fb, mode = _tc(m, q, t)
+    oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
+    assert idx[0, 0] == 5 and idx[0, 1] == 100 and fb >= 1
+
+
+def test_l2_tc_equals_exact_scan_at_c2_size(m):
+    """BASELINE config C2 (20 000 x 20 000 x 128): tensor-core path == exact fp32 scan, bit for bit."""
+    lib = m._lib.load()
+    q, t = datagen.sift_like(20000, 20000, 128, seed=1002)
+    idx, dist, fb, mode = _tc(m, q, t)
+    lib.mpl_set_l2_path(1)
+    try:
+        ei, ed = m.knn2_l2(q, t, 2, False)
+    finally:
+        lib.mpl_set_l2_path(0)
+    assert np.array_equal(idx, ei) and np.array_equal(dist.view(np.int32), ed.view(np.int32))
+    assert mode == 0 and fb < 200
