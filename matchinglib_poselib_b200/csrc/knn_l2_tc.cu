@@ -233,8 +233,14 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
                  :: "memory");
 }
 
-__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm, int col0, TopList& L)
+// Fast path: 32 scores -> one bit per group of 4 columns whose minimum beats the list's 4th best.  The (rare) slow
+// path is ONE compact loop per call site: it re-reads the 4 accumulators of a flagged group from TMEM at a dynamic
+// column address (registers cannot be indexed dynamically) and runs the sorted insertions.  Keeping the insertion
+// code out of the unrolled fast path keeps the kernel inside the instruction cache.
+__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm, int col0, uint32_t taddr, TopList& L)
 {
+    unsigned mask = 0;
+    const float thr = L.s3;
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
         const float4 n4 = *reinterpret_cast<const float4*>(nrm + 4 * g);          // LDS.128, warp-wide broadcast
@@ -242,12 +248,25 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float
         const float b = fmaf(-2.f, __uint_as_float(r[4 * g + 1]), n4.y);
         const float c = fmaf(-2.f, __uint_as_float(r[4 * g + 2]), n4.z);
         const float d = fmaf(-2.f, __uint_as_float(r[4 * g + 3]), n4.w);
-        if (fminf(fminf(a, b), fminf(c, d)) < L.s3) {
-            if (a < L.s3) L.insert(a, col0 + 4 * g + 0);
-            if (b < L.s3) L.insert(b, col0 + 4 * g + 1);
-            if (c < L.s3) L.insert(c, col0 + 4 * g + 2);
-            if (d < L.s3) L.insert(d, col0 + 4 * g + 3);
-        }
+        if (fminf(fminf(a, b), fminf(c, d)) < thr) mask |= 1u << g;
+    }
+    mask = __reduce_or_sync(0xffffffffu, mask);                                   // warp-uniform: tcgen05.ld is .aligned
+#pragma unroll 1
+    while (mask) {
+        const int g = __ffs(mask) - 1;
+        mask &= mask - 1;
+        uint32_t v0, v1, v2, v3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(taddr + 4 * g) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v0), "+r"(v1), "+r"(v2), "+r"(v3) :: "memory");
+        const float4 n4 = *reinterpret_cast<const float4*>(nrm + 4 * g);
+        const float a = fmaf(-2.f, __uint_as_float(v0), n4.x), b = fmaf(-2.f, __uint_as_float(v1), n4.y);
+        const float c = fmaf(-2.f, __uint_as_float(v2), n4.z), d = fmaf(-2.f, __uint_as_float(v3), n4.w);
+        const int col = col0 + 4 * g;
+        if (a < L.s3) L.insert(a, col + 0);
+        if (b < L.s3) L.insert(b, col + 1);
+        if (c < L.s3) L.insert(c, col + 2);
+        if (d < L.s3) L.insert(d, col + 3);
     }
 }
 
@@ -372,10 +391,14 @@ l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_const
             const int col0 = tile * BN;
             uint32_t ra[32], rb[32];
             tc_ld32(taddr, ra);
-            tc_wait_ld_regs(ra); tc_ld32(taddr + 32, rb); score_chunk(ra, nrm, col0, L);
-            tc_wait_ld_regs(rb); tc_ld32(taddr + 64, ra); score_chunk(rb, nrm + 32, col0 + 32, L);
-            tc_wait_ld_regs(ra); tc_ld32(taddr + 96, rb); score_chunk(ra, nrm + 64, col0 + 64, L);
-            tc_wait_ld_regs(rb);                          score_chunk(rb, nrm + 96, col0 + 96, L);
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {                                        // two chunk pairs; one copy of the scoring code each
+                const int c0 = 64 * h;
+                tc_wait_ld_regs(ra); tc_ld32(taddr + c0 + 32, rb);
+                score_chunk(ra, nrm + c0, col0 + c0, taddr + c0, L);
+                tc_wait_ld_regs(rb); if (h == 0) tc_ld32(taddr + 64, ra);
+                score_chunk(rb, nrm + c0 + 32, col0 + c0 + 32, taddr + c0 + 32, L);
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&t_empty[b]);
