@@ -50,14 +50,16 @@ constexpr int SLAB_BYTES = 128;      // K extent of one smem slab in bytes (= sw
 constexpr int A_SLAB = BM * SLAB_BYTES;      // 32 KB
 constexpr int B_SLAB = BN * SLAB_BYTES;      // 16 KB
 constexpr int MAX_A_SLABS = 4;       // dim <= 128 floats (tf32) / 256 bf16
-constexpr int NSTAGES = 4;           // B slab ring
-constexpr int NORM_RING = 8;         // |t|^2 tiles in flight (>= NSTAGES + 2, see producer notes)
-constexpr int NC = 4;                // candidates kept per (thread, slot)
-constexpr int TC_THREADS = 384;      // warps 0..3 control, 4..11 epilogue
-constexpr int SMEM_A = MAX_A_SLABS * A_SLAB;                 // 128 KB
-constexpr int SMEM_B = NSTAGES * B_SLAB;                     //  64 KB
-constexpr int SMEM_NORM = NORM_RING * BN * 4;                //   4 KB
-constexpr int SMEM_BYTES = 1024 + SMEM_A + SMEM_B + SMEM_NORM + 256;
+constexpr int AUG_BYTES = 32;        // one extra K step per row: |t|^2 split in three exact pieces (B), ones (A)
+constexpr int A_AUG = BM * AUG_BYTES;                        //  8 KB
+constexpr int STAGE_BYTES = B_SLAB + BN * AUG_BYTES;         // 20 KB: one B slab (+ the tile's aug slab beside slab 0)
+constexpr int MAX_STAGES = 8;
+constexpr int SMEM_DATA = 216 * 1024;                        // A slabs | A aug | B ring (as many stages as fit)
+constexpr int NC = 4;                // candidates kept per list
+constexpr int LPS = 2;               // lists per (CTA, query block) slot: one per half of the tile's columns
+constexpr int EPI_WARPS = 16;        // 4 warpgroups: (query block half m) x (column half)
+constexpr int TC_THREADS = 128 + 32 * EPI_WARPS;             // warps 0..3 control, 4..19 epilogue
+constexpr int SMEM_BYTES = 1024 + SMEM_DATA + 256;
 
 struct TcHeader {                    // first 256 bytes of the scratch buffer (zeroed per call)
     unsigned not_bf16_exact;         // 0 -> bf16 mode, else tf32 mode
@@ -126,6 +128,10 @@ __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sy
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
+// K-major 32-byte rows, 32-byte swizzle: 8-row groups of 256 bytes (the aug slab)
+__device__ __forceinline__ uint64_t umma_desc_sw32(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);
+}
 // instruction descriptor: D = f32, A/B format (1 = bf16, 2 = tf32), both K-major, N = 128, M = 128
 __host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(UM >> 4) << 24);
@@ -171,22 +177,39 @@ l2_prep_scan_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
 // ---- 2. pack: operand rows in the MMA's element type ---------------------------------------------------
 // bf16 mode: rows of kp16 bf16 (kp16 = dim rounded up to 64); tf32 mode: rows of kp32 floats (dim rounded
 // up to 32).  Same destination buffer either way (sized for the fp32 case); zero padded columns.
+// Query rows are scaled by -2 (exact).  The "aug" K step folds |t|^2 into the contraction, so that the
+// accumulator IS the score |t|^2 - 2 q.t: train aug row = |t|^2 split into three pieces that are each exactly
+// representable in the operand type (3 x 8 bits bf16, 3 x 11 bits tf32 >= the 24-bit fp32 mantissa), query
+// aug row = (1, 1, 1, 0, ...).  Train pad rows (up to a whole tile) get +inf, so they never enter a list.
+__device__ __forceinline__ void split3(float n, unsigned keep_mask, float (&o)[3])
+{
+    if (!(n < INFINITY)) { o[0] = INFINITY; o[1] = 0.f; o[2] = 0.f; return; }
+    o[0] = __uint_as_float(__float_as_uint(n) & keep_mask);
+    const float r1 = n - o[0];                                   // exact
+    o[1] = __uint_as_float(__float_as_uint(r1) & keep_mask);
+    o[2] = r1 - o[1];                                            // exact, and fits the remaining bits
+}
+
 __global__ void __launch_bounds__(256)
 l2_prep_pack_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
-                    void* __restrict__ tp, void* __restrict__ qp, int kp16, int kp32, const TcHeader* __restrict__ hdr)
+                    void* __restrict__ tp, void* __restrict__ qp, int kp16, int kp32, const float* __restrict__ tnorm, int nt_pad,
+                    uint4* __restrict__ taug, uint4* __restrict__ qaug, const TcHeader* __restrict__ hdr)
 {
     const bool bf16_mode = hdr->not_bf16_exact == 0;
     const int kp = bf16_mode ? kp16 : kp32;
     const int groups = kp / 4;                                   // 4 elements per thread
     const long long total = (long long)(nt + nq) * groups;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long i = tid; i < total; i += stride) {
         const int row = (int)(i / groups), g = (int)(i - (long long)row * groups);
         const bool is_t = row < nt;
         const int r = is_t ? row : row - nt;
         const float* x = is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld;
+        const float sc = is_t ? 1.f : -2.f;
         float v[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = (4 * g + e < dim) ? x[4 * g + e] : 0.f;
+        for (int e = 0; e < 4; ++e) v[e] = (4 * g + e < dim) ? sc * x[4 * g + e] : 0.f;
         char* dst = (char*)(is_t ? tp : qp);
         if (bf16_mode) {
             __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
@@ -196,6 +219,22 @@ l2_prep_pack_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
             *reinterpret_cast<float4*>(dst + ((size_t)r * kp + 4 * g) * 4) = make_float4(v[0], v[1], v[2], v[3]);
         }
     }
+    // aug rows: 32 bytes each
+    for (long long i = tid; i < (long long)nt_pad + nq; i += stride) {
+        const bool is_t = i < nt_pad;
+        float o[3];
+        if (is_t) split3(tnorm[i], bf16_mode ? 0xFFFF0000u : 0xFFFFE000u, o);
+        else { o[0] = 1.f; o[1] = 1.f; o[2] = 1.f; }
+        uint4 w0 = make_uint4(0, 0, 0, 0);
+        if (bf16_mode) {
+            __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b2 = __floats2bfloat162_rn(o[2], 0.f);
+            w0.x = *reinterpret_cast<uint32_t*>(&a); w0.y = *reinterpret_cast<uint32_t*>(&b2);
+        } else {
+            w0.x = __float_as_uint(o[0]); w0.y = __float_as_uint(o[1]); w0.z = __float_as_uint(o[2]);
+        }
+        uint4* dst = is_t ? taug + 2 * i : qaug + 2 * (i - nt_pad);
+        dst[0] = w0; dst[1] = make_uint4(0, 0, 0, 0);
+    }
 }
 
 // ---- 3. tensor-core ranking kernel ----------------------------------------------------------------------
@@ -204,8 +243,7 @@ struct TcParams {
     long long U;                     // work units = query blocks x train tiles
     int max_slots;                   // candidate slots per query block
     int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
-    const float* tnorm;              // |t|^2 padded to NT * BN with +inf
-    uint4* cand;                     // [qblock][slot][BM rows][2 x uint4] = 4 scores + 4 train indices
+    uint4* cand;                     // [qblock][slot][LPS][BM rows][2 x uint4] = 4 scores + 4 train indices
     const TcHeader* hdr;
 };
 
@@ -213,15 +251,23 @@ struct TcParams {
 __host__ __device__ inline int tc_owner(long long u, long long U, int G) { return (int)(((u + 1) * G - 1) / U); }
 
 struct TopList {
-    float s0, s1, s2, s3; int i0, i1, i2, i3;
+    float s0, s1, s2, s3; int i0, i1, i2, i3;          // ascending scores; ties keep arrival (= train index) order
     __device__ __forceinline__ void reset() { s0 = s1 = s2 = s3 = INFINITY; i0 = i1 = i2 = i3 = -1; }
-    __device__ __forceinline__ void insert(float s, int i) {     // caller checked s < s3
-        s3 = s; i3 = i;
-        if (s3 < s2) { float a = s2; s2 = s3; s3 = a; int b = i2; i2 = i3; i3 = b;
-            if (s2 < s1) { a = s1; s1 = s2; s2 = a; b = i1; i1 = i2; i2 = b;
-                if (s1 < s0) { a = s0; s0 = s1; s1 = a; b = i0; i0 = i1; i1 = b; } } }
+    // branch-free sorted insertion, active only where p (p implies s < s3)
+    __device__ __forceinline__ void insert_if(bool p, float s, int i) {
+        const bool c2 = p && (s < s2), c1 = c2 && (s < s1), c0 = c1 && (s < s0);
+        s3 = p ? (c2 ? s2 : s) : s3;  i3 = p ? (c2 ? i2 : i) : i3;
+        s2 = c2 ? (c1 ? s1 : s) : s2; i2 = c2 ? (c1 ? i1 : i) : i2;
+        s1 = c1 ? (c0 ? s0 : s) : s1; i1 = c1 ? (c0 ? i0 : i) : i1;
+        s0 = c0 ? s : s0;             i0 = c0 ? i : i0;
     }
 };
+
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+    return v;
+}
 
 __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
     // the loaded registers become valid here: tie them to the wait so no use can be scheduled above it
@@ -233,22 +279,20 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
                  :: "memory");
 }
 
-// Fast path: 32 scores -> one bit per group of 4 columns whose minimum beats the list's 4th best.  The (rare) slow
-// path is ONE compact loop per call site: it re-reads the 4 accumulators of a flagged group from TMEM at a dynamic
-// column address (registers cannot be indexed dynamically) and runs the sorted insertions.  Keeping the insertion
-// code out of the unrolled fast path keeps the kernel inside the instruction cache.
-__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm, int col0, uint32_t taddr, TopList& L)
+// Fast path: 32 scores (the accumulators themselves) -> one bit per group of 4 columns whose minimum beats the
+// list's 4th best in any lane.  Slow path (rare): ONE compact loop per call site re-reads the 4 accumulators of a
+// flagged group from TMEM at a dynamic column address (registers cannot be indexed dynamically) and inserts the
+// group minimum branch-free; a second element of the same group beating the threshold in the same lane repeats the
+// round.  Keeping insertion code out of the unrolled fast path keeps the kernel inside the instruction cache.
+__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, uint32_t taddr, TopList& L)
 {
     unsigned mask = 0;
     const float thr = L.s3;
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
-        const float4 n4 = *reinterpret_cast<const float4*>(nrm + 4 * g);          // LDS.128, warp-wide broadcast
-        const float a = fmaf(-2.f, __uint_as_float(r[4 * g + 0]), n4.x);
-        const float b = fmaf(-2.f, __uint_as_float(r[4 * g + 1]), n4.y);
-        const float c = fmaf(-2.f, __uint_as_float(r[4 * g + 2]), n4.z);
-        const float d = fmaf(-2.f, __uint_as_float(r[4 * g + 3]), n4.w);
-        if (fminf(fminf(a, b), fminf(c, d)) < thr) mask |= 1u << g;
+        const float m = fminf(fminf(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1])),
+                              fminf(__uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3])));
+        if (m < thr) mask |= 1u << g;
     }
     mask = __reduce_or_sync(0xffffffffu, mask);                                   // warp-uniform: tcgen05.ld is .aligned
 #pragma unroll 1
@@ -259,49 +303,58 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], const float
         asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
                      : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(taddr + 4 * g) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v0), "+r"(v1), "+r"(v2), "+r"(v3) :: "memory");
-        const float4 n4 = *reinterpret_cast<const float4*>(nrm + 4 * g);
-        const float a = fmaf(-2.f, __uint_as_float(v0), n4.x), b = fmaf(-2.f, __uint_as_float(v1), n4.y);
-        const float c = fmaf(-2.f, __uint_as_float(v2), n4.z), d = fmaf(-2.f, __uint_as_float(v3), n4.w);
+        float a = __uint_as_float(v0), b = __uint_as_float(v1), c = __uint_as_float(v2), d = __uint_as_float(v3);
         const int col = col0 + 4 * g;
-        if (a < L.s3) L.insert(a, col + 0);
-        if (b < L.s3) L.insert(b, col + 1);
-        if (c < L.s3) L.insert(c, col + 2);
-        if (d < L.s3) L.insert(d, col + 3);
+        float x = fminf(fminf(a, b), fminf(c, d));
+#pragma unroll 1
+        do {
+            const int k = (a == x) ? 0 : (b == x) ? 1 : (c == x) ? 2 : 3;      // lowest column on equal scores
+            L.insert_if(x < L.s3, x, col + k);
+            a = (k == 0) ? INFINITY : a; b = (k == 1) ? INFINITY : b; c = (k == 2) ? INFINITY : c; d = (k == 3) ? INFINITY : d;
+            x = fminf(fminf(a, b), fminf(c, d));
+        } while (__any_sync(0xffffffffu, x < L.s3));
     }
 }
 
+struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
-l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_constant__ CUtensorMap mapB16,
-                  const __grid_constant__ CUtensorMap mapA32, const __grid_constant__ CUtensorMap mapB32, const TcParams p)
+l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
 {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);   // swizzle-128B atoms: 1024-byte aligned
-    unsigned char* sA = smem;
-    unsigned char* sB = smem + SMEM_A;
-    float* sN = reinterpret_cast<float*>(smem + SMEM_A + SMEM_B);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_A + SMEM_B + SMEM_NORM);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_DATA);
     uint64_t* a_full = bars + 0; uint64_t* a_empty = bars + 1;
-    uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + NSTAGES;
-    uint64_t* t_full = bars + 2 + 2 * NSTAGES; uint64_t* t_empty = t_full + 2;
+    uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + MAX_STAGES;
+    uint64_t* t_full = bars + 2 + 2 * MAX_STAGES; uint64_t* t_empty = t_full + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool tf32 = p.hdr->not_bf16_exact != 0;
     const int n_slabs = tf32 ? p.slabs32 : p.slabs16;
     const int KS = tf32 ? 32 : 64;                               // elements per 128-byte slab row
-    const CUtensorMap* mapA = tf32 ? &mapA32 : &mapA16;
-    const CUtensorMap* mapB = tf32 ? &mapB32 : &mapB16;
+    const CUtensorMap* mapA = tf32 ? &maps.a32 : &maps.a16;
+    const CUtensorMap* mapB = tf32 ? &maps.b32 : &maps.b16;
+    const CUtensorMap* mapAa = tf32 ? &maps.aa32 : &maps.aa16;
+    const CUtensorMap* mapBa = tf32 ? &maps.ba32 : &maps.ba16;
+    unsigned char* sA = smem;                                    // n_slabs x 32 KB
+    unsigned char* sAa = smem + n_slabs * A_SLAB;                // 8 KB
+    unsigned char* sB = sAa + A_AUG;                             // ring of n_stages x 20 KB
+    int n_stages = (SMEM_DATA - n_slabs * A_SLAB - A_AUG) / STAGE_BYTES;
+    if (n_stages > MAX_STAGES) n_stages = MAX_STAGES;
     const int G = gridDim.x;
     const long long u0 = (long long)blockIdx.x * p.U / G, u1 = (long long)(blockIdx.x + 1) * p.U / G;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(mapA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(mapB) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(mapAa) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(mapBa) : "memory");
     }
     if (warp == 1 && lane == 0) {
         mbar_init(a_full, 1); mbar_init(a_empty, 1);
-        for (int s = 0; s < NSTAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], 8); }
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {                                             // whole warp: allocate all 512 TMEM columns
@@ -316,24 +369,22 @@ l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_const
     if (warp == 0) {
         // ===== TMA producer (one thread) =====
         if (lane == 0) {
-            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned seq = 0;
-            for (long long u = u0; u < u1; ++u, ++seq) {
+            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1;
+            for (long long u = u0; u < u1; ++u) {
                 const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
                 if (qb != cur_qb) {
                     mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));             // MMAs of the previous query block are done
-                    mbar_expect_tx(a_full, (uint32_t)(n_slabs * A_SLAB));
+                    mbar_expect_tx(a_full, (uint32_t)(n_slabs * A_SLAB + A_AUG));
                     for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * A_SLAB, mapA, s * KS, qb * BM, a_full);
+                    tma_load_2d(sAa, mapAa, 0, qb * BM, a_full);
                     ++a_cnt; cur_qb = qb;
                 }
                 for (int s = 0; s < n_slabs; ++s) {
                     mbar_wait(&b_empty[stage], sphase ^ 1);
-                    mbar_expect_tx(&b_full[stage], (uint32_t)(B_SLAB + (s == 0 ? BN * 4 : 0)));
-                    tma_load_2d(sB + stage * B_SLAB, mapB, s * KS, tile * BN, &b_full[stage]);
-                    // |t|^2 of the tile rides on the first slab's barrier.  Ring slot reuse is safe: the slab ring
-                    // keeps this thread at most NSTAGES tiles ahead of the MMA issuer, which is at most two tiles
-                    // ahead of the epilogue (TMEM double buffer), and NORM_RING >= NSTAGES + 2.
-                    if (s == 0) tma_bulk_g2s(sN + (seq % NORM_RING) * BN, p.tnorm + (size_t)tile * BN, BN * 4, &b_full[stage]);
-                    if (++stage == NSTAGES) { stage = 0; sphase ^= 1; }
+                    mbar_expect_tx(&b_full[stage], (uint32_t)(B_SLAB + (s == 0 ? BN * AUG_BYTES : 0)));
+                    tma_load_2d(sB + stage * STAGE_BYTES, mapB, s * KS, tile * BN, &b_full[stage]);
+                    if (s == 0) tma_load_2d(sB + stage * STAGE_BYTES + B_SLAB, mapBa, 0, tile * BN, &b_full[stage]);
+                    if (++stage == n_stages) { stage = 0; sphase ^= 1; }
                 }
             }
         }
@@ -341,7 +392,7 @@ l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_const
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
             const uint32_t idesc = umma_idesc(tf32 ? 2u : 1u);
-            const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+            const uint32_t a_addr = smem_u32(sA), aa_addr = smem_u32(sAa), b_addr = smem_u32(sB);
             int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned it = 0;
             for (long long u = u0; u < u1; ++u, ++it) {
                 const int qb = (int)(u / p.NT);
@@ -352,31 +403,36 @@ l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_const
                 for (int s = 0; s < n_slabs; ++s) {
                     mbar_wait(&b_full[stage], sphase);
                     tc_fence_after();
+                    const uint32_t sb = b_addr + stage * STAGE_BYTES;
 #pragma unroll
-                    for (int m = 0; m < 2; ++m)
+                    for (int m = 0; m < 2; ++m) {
+                        const uint32_t d = tmem_base + b * 256 + m * 128;
+                        if (s == 0) {                                            // aug K step first: D = |t|^2 (overwrites)
+                            const uint64_t ad = umma_desc_sw32(aa_addr + m * (UM * AUG_BYTES)), bd = umma_desc_sw32(sb + B_SLAB);
+                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, 0u); else tc_mma_f16(d, ad, bd, idesc, 0u);
+                        }
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {                            // 4 x 32 bytes of K per slab row
                             const uint64_t ad = umma_desc(a_addr + s * A_SLAB + m * (UM * SLAB_BYTES) + k * 32);
-                            const uint64_t bd = umma_desc(b_addr + stage * B_SLAB + k * 32);
-                            const uint32_t d = tmem_base + b * 256 + m * 128;
-                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, (uint32_t)((s | k) != 0));
-                            else      tc_mma_f16(d, ad, bd, idesc, (uint32_t)((s | k) != 0));
+                            const uint64_t bd = umma_desc(sb + k * 32);
+                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, 1u); else tc_mma_f16(d, ad, bd, idesc, 1u);
                         }
+                    }
                     tc_commit(&b_empty[stage]);                                  // slab free once these MMAs retire
-                    if (++stage == NSTAGES) { stage = 0; sphase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; sphase ^= 1; }
                 }
                 tc_commit(&t_full[b]);
                 if (u + 1 < u1 && (int)((u + 1) / p.NT) != qb) tc_commit(a_empty);  // only when the producer will wait for it
             }
         }
     } else if (warp >= 4) {
-        // ===== epilogue: thread = one query row of block m =====
-        const int m = (warp - 4) >> 2, quad = warp & 3, row = quad * 32 + lane;
+        // ===== epilogue: thread = one query row of block m, one half of the tile's columns =====
+        const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
         TopList L; L.reset();
         int cur_qb = -1; unsigned it = 0;
         auto flush = [&](int qb) {
             const int slot = (int)blockIdx.x - tc_owner((long long)qb * p.NT, p.U, G);
-            uint4* dst = p.cand + (((size_t)qb * p.max_slots + slot) * BM + m * UM + row) * 2;
+            uint4* dst = p.cand + ((((size_t)qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2;
             dst[0] = make_uint4(__float_as_uint(L.s0), __float_as_uint(L.s1), __float_as_uint(L.s2), __float_as_uint(L.s3));
             dst[1] = make_uint4((uint32_t)L.i0, (uint32_t)L.i1, (uint32_t)L.i2, (uint32_t)L.i3);
         };
@@ -386,19 +442,14 @@ l2_tc_rank_kernel(const __grid_constant__ CUtensorMap mapA16, const __grid_const
             const uint32_t b = it & 1;
             mbar_wait(&t_full[b], (it >> 1) & 1);
             tc_fence_after();
-            const float* nrm = sN + (it % NORM_RING) * BN;
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128;
-            const int col0 = tile * BN;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128 + hf * 64;
+            const int col0 = tile * BN + hf * 64;
             uint32_t ra[32], rb[32];
             tc_ld32(taddr, ra);
-#pragma unroll 1
-            for (int h = 0; h < 2; ++h) {                                        // two chunk pairs; one copy of the scoring code each
-                const int c0 = 64 * h;
-                tc_wait_ld_regs(ra); tc_ld32(taddr + c0 + 32, rb);
-                score_chunk(ra, nrm + c0, col0 + c0, taddr + c0, L);
-                tc_wait_ld_regs(rb); if (h == 0) tc_ld32(taddr + 64, ra);
-                score_chunk(rb, nrm + c0 + 32, col0 + c0 + 32, taddr + c0 + 32, L);
-            }
+            tc_wait_ld_regs(ra); tc_ld32(taddr + 32, rb);
+            score_chunk(ra, col0, taddr, L);
+            tc_wait_ld_regs(rb);
+            score_chunk(rb, col0 + 32, taddr + 32, L);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&t_empty[b]);
@@ -465,7 +516,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     if (qi >= nq) return;
     const int qb = qi / BM, row = qi - qb * BM;
     const int first = tc_owner((long long)qb * NT, U, G), last = tc_owner((long long)qb * NT + NT - 1, U, G);
-    const int n_cand = (last - first + 1) * NC;
+    const int n_cand = (last - first + 1) * LPS * NC;          // lists of this query block are contiguous: (slot, half)
     const float qq = qnorm[qi];
     const float tmax = __uint_as_float(hdr->max_tnorm_bits);
     // eps >= |score + |q|^2 - d_ref|: operand quantisation (tf32 truncation, none in bf16-exact mode) plus a generous
@@ -477,7 +528,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
     for (int c = lane; c < n_cand; c += 32) {
         const int slot = c / NC, e = c - slot * NC;
-        const uint4* rec = cand + (((size_t)qb * max_slots + slot) * BM + row) * 2;
+        const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
         const uint4 sc = rec[0];
         const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
         if (e == NC - 1) tau = fminf(tau, s);
@@ -497,7 +548,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     const float* qrow = q + (size_t)qi * q_ld;
     for (int c = lane; c < n_cand; c += 32) {
         const int slot = c / NC, e = c - slot * NC;
-        const uint4* rec = cand + (((size_t)qb * max_slots + slot) * BM + row) * 2;
+        const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
         const uint4 sc = rec[0], id = rec[1];
         const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
         const int ti = (int)(e == 0 ? id.x : e == 1 ? id.y : e == 2 ? id.z : id.w);
@@ -528,7 +579,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
 struct TcPlan {
     int NQB, NT, G, max_slots, kp16, kp32;
     long long U;
-    size_t off_tnorm, off_qnorm, off_tp, off_qp, off_cand, off_list, off_part, total;
+    size_t off_tnorm, off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_list, off_part, total;
 };
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -552,14 +603,17 @@ TcPlan make_plan(int nq, int nt, int dim, int sm_count)
     P.off_qnorm = o; o = align256(o + (size_t)P.NQB * BM * 4);
     P.off_tp = o;    o = align256(o + (size_t)nt * P.kp32 * 4);
     P.off_qp = o;    o = align256(o + (size_t)nq * P.kp32 * 4);
-    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * BM * 32);
+    P.off_taug = o;  o = align256(o + (size_t)P.NT * BN * AUG_BYTES);
+    P.off_qaug = o;  o = align256(o + (size_t)nq * AUG_BYTES);
+    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * BM * 32);
     P.off_list = o;  o = align256(o + (size_t)nq * 4);
     P.off_part = o;  o = align256(o + mpl_l2_list_scratch_entries(nq, sm_count) * 16);
     P.total = o;
     return P;
 }
 
-int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int elt_bytes, void* base, int kp, int rows, int box_k, int box_rows)
+int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int elt_bytes, void* base, int kp, int rows, int box_k, int box_rows,
+               CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B)
 {
     cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)kp * elt_bytes};
@@ -579,7 +633,7 @@ int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int elt_bytes, void* ba
         encode = (encode_fn_t)fn;
     }
     const CUresult r = encode(map, dt, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                                              swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { mpl_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return MPL_ERR_CUDA; }
     return MPL_OK;
 }
@@ -614,12 +668,18 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_set = true;
     }
-    alignas(64) CUtensorMap mA16, mB16, mA32, mB32;
+    uint4* taug = (uint4*)(base + P.off_taug); uint4* qaug = (uint4*)(base + P.off_qaug);
+    alignas(64) TcMaps maps;
     int rc;
-    if ((rc = encode_map(&mA16, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, qp, P.kp16, nq, 64, BM))) return rc;
-    if ((rc = encode_map(&mB16, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tp, P.kp16, nt, 64, BN))) return rc;
-    if ((rc = encode_map(&mA32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, qp, P.kp32, nq, 32, BM))) return rc;
-    if ((rc = encode_map(&mB32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, tp, P.kp32, nt, 32, BN))) return rc;
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, F32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, BM))) return rc;
+    if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, nt, 64, BN))) return rc;
+    if ((rc = encode_map(&maps.a32, F32, 4, qp, P.kp32, nq, 32, BM))) return rc;
+    if ((rc = encode_map(&maps.b32, F32, 4, tp, P.kp32, nt, 32, BN))) return rc;
+    if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, P.NT * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_map(&maps.aa32, F32, 4, qaug, 8, nq, 8, BM, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_map(&maps.ba32, F32, 4, taug, 8, P.NT * BN, 8, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
 
     MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
     {
@@ -628,15 +688,15 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         int blocks = (rows + 7) / 8; if (blocks > sm_count * 8) blocks = sm_count * 8;
         l2_prep_scan_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tnorm, P.NT * BN, qnorm, P.NQB * BM, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        l2_prep_pack_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, P.kp32, hdr);
+        l2_prep_pack_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
     {
         MplProfScope prof(MPL_PROF_L2_TC, st);
         TcParams prm;
         prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots;
-        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.tnorm = tnorm; prm.cand = cand; prm.hdr = hdr;
-        l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(mA16, mB16, mA32, mB32, prm);
+        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.hdr = hdr;
+        l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
     {
