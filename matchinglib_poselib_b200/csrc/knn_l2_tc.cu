@@ -96,6 +96,13 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// one lane of a converged warp (keeps the surrounding code warp-uniform, so descriptors and addresses stay in
+// uniform registers instead of going through per-lane waterfall loops)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {   // arrives on bar when every MMA issued so far has completed
@@ -316,6 +323,53 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, u
     }
 }
 
+template <int MODE>   // 0 = bf16 (kind::f16), 1 = tf32
+__device__ __forceinline__ void mma_issue_loop(long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_addr, uint32_t aa_addr,
+                                               uint32_t b_addr, uint32_t tmem_base, uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full,
+                                               uint64_t* b_empty, uint64_t* t_full, uint64_t* t_empty)
+{
+    constexpr uint32_t idesc = umma_idesc(MODE == 1 ? 2u : 1u);
+    constexpr uint64_t hi128 = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);     // see umma_desc()
+    constexpr uint64_t hi32 = ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);       // see umma_desc_sw32()
+    int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned it = 0;
+    for (long long u = u0; u < u1; ++u, ++it) {
+        const int qb = (int)(u / NT);
+        if (qb != cur_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; cur_qb = qb; }
+        const uint32_t b = it & 1;
+        mbar_wait(&t_empty[b], ((it >> 1) & 1) ^ 1);                             // epilogue drained this accumulator buffer
+        tc_fence_after();
+        for (int s = 0; s < n_slabs; ++s) {
+            mbar_wait(&b_full[stage], sphase);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t sb = b_addr + stage * STAGE_BYTES;
+                const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    const uint32_t d = tmem_base + b * 256 + m * 128;
+                    if (s == 0) {                                                // aug K step first: D = |t|^2 (overwrites)
+                        const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
+                        const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
+                        if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
+                    }
+                    const uint64_t ad = hi128 | (uint64_t)((a_addr + s * A_SLAB + m * (UM * SLAB_BYTES)) >> 4);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {                                // 4 x 32 bytes of K per slab row
+                        if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                    }
+                }
+                tc_commit(&b_empty[stage]);                                      // slab free once these MMAs retire
+                if (s == n_slabs - 1) {
+                    tc_commit(&t_full[b]);
+                    if (u + 1 < u1 && (int)((u + 1) / NT) != qb) tc_commit(a_empty);   // only when the producer will wait for it
+                }
+            }
+            __syncwarp();
+            if (++stage == n_stages) { stage = 0; sphase ^= 1; }
+        }
+    }
+}
+
 struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -367,64 +421,37 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer (one thread) =====
-        if (lane == 0) {
-            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1;
-            for (long long u = u0; u < u1; ++u) {
-                const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
-                if (qb != cur_qb) {
-                    mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));             // MMAs of the previous query block are done
+        // ===== TMA producer: the whole warp runs the loop (uniform control flow), one elected lane issues =====
+        int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1;
+        for (long long u = u0; u < u1; ++u) {
+            const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
+            if (qb != cur_qb) {
+                mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));                 // MMAs of the previous query block are done
+                if (elect_one()) {
                     mbar_expect_tx(a_full, (uint32_t)(n_slabs * A_SLAB + A_AUG));
                     for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * A_SLAB, mapA, s * KS, qb * BM, a_full);
                     tma_load_2d(sAa, mapAa, 0, qb * BM, a_full);
-                    ++a_cnt; cur_qb = qb;
                 }
-                for (int s = 0; s < n_slabs; ++s) {
-                    mbar_wait(&b_empty[stage], sphase ^ 1);
+                __syncwarp();
+                ++a_cnt; cur_qb = qb;
+            }
+            for (int s = 0; s < n_slabs; ++s) {
+                mbar_wait(&b_empty[stage], sphase ^ 1);
+                if (elect_one()) {
                     mbar_expect_tx(&b_full[stage], (uint32_t)(B_SLAB + (s == 0 ? BN * AUG_BYTES : 0)));
                     tma_load_2d(sB + stage * STAGE_BYTES, mapB, s * KS, tile * BN, &b_full[stage]);
                     if (s == 0) tma_load_2d(sB + stage * STAGE_BYTES + B_SLAB, mapBa, 0, tile * BN, &b_full[stage]);
-                    if (++stage == n_stages) { stage = 0; sphase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == n_stages) { stage = 0; sphase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc(tf32 ? 2u : 1u);
-            const uint32_t a_addr = smem_u32(sA), aa_addr = smem_u32(sAa), b_addr = smem_u32(sB);
-            int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned it = 0;
-            for (long long u = u0; u < u1; ++u, ++it) {
-                const int qb = (int)(u / p.NT);
-                if (qb != cur_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; cur_qb = qb; }
-                const uint32_t b = it & 1;
-                mbar_wait(&t_empty[b], ((it >> 1) & 1) ^ 1);                     // epilogue drained this accumulator buffer
-                tc_fence_after();
-                for (int s = 0; s < n_slabs; ++s) {
-                    mbar_wait(&b_full[stage], sphase);
-                    tc_fence_after();
-                    const uint32_t sb = b_addr + stage * STAGE_BYTES;
-#pragma unroll
-                    for (int m = 0; m < 2; ++m) {
-                        const uint32_t d = tmem_base + b * 256 + m * 128;
-                        if (s == 0) {                                            // aug K step first: D = |t|^2 (overwrites)
-                            const uint64_t ad = umma_desc_sw32(aa_addr + m * (UM * AUG_BYTES)), bd = umma_desc_sw32(sb + B_SLAB);
-                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, 0u); else tc_mma_f16(d, ad, bd, idesc, 0u);
-                        }
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {                            // 4 x 32 bytes of K per slab row
-                            const uint64_t ad = umma_desc(a_addr + s * A_SLAB + m * (UM * SLAB_BYTES) + k * 32);
-                            const uint64_t bd = umma_desc(sb + k * 32);
-                            if (tf32) tc_mma_tf32(d, ad, bd, idesc, 1u); else tc_mma_f16(d, ad, bd, idesc, 1u);
-                        }
-                    }
-                    tc_commit(&b_empty[stage]);                                  // slab free once these MMAs retire
-                    if (++stage == n_stages) { stage = 0; sphase ^= 1; }
-                }
-                tc_commit(&t_full[b]);
-                if (u + 1 < u1 && (int)((u + 1) / p.NT) != qb) tc_commit(a_empty);  // only when the producer will wait for it
-            }
-        }
+        // ===== MMA issuer: uniform loop, one elected lane issues =====
+        if (tf32) mma_issue_loop<1>(u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
+                                    a_full, a_empty, b_full, b_empty, t_full, t_empty);
+        else      mma_issue_loop<0>(u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
+                                    a_full, a_empty, b_full, b_empty, t_full, t_empty);
     } else if (warp >= 4) {
         // ===== epilogue: thread = one query row of block m, one half of the tile's columns =====
         const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
