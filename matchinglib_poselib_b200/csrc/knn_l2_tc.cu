@@ -59,7 +59,8 @@ constexpr int NC = 4;                // candidates kept per list
 constexpr int LPS = 2;               // lists per (CTA, query block) slot: one per half of the tile's columns
 constexpr int EPI_WARPS = 16;        // 4 warpgroups: (query block half m) x (column half)
 constexpr int TC_THREADS = 128 + 32 * EPI_WARPS;             // warps 0..3 control, 4..19 epilogue
-constexpr int SMEM_BYTES = 1024 + SMEM_DATA + 256;
+constexpr int SMEM_TAIL = 256 + LPS * BM * 8;                  // barriers + TMEM slot | shared list thresholds (score, query block)
+constexpr int SMEM_BYTES = 1024 + SMEM_DATA + SMEM_TAIL;
 
 struct TcHeader {                    // first 256 bytes of the scratch buffer (zeroed per call)
     unsigned not_bf16_exact;         // 0 -> bf16 mode, else tf32 mode
@@ -291,10 +292,10 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
 // flagged group from TMEM at a dynamic column address (registers cannot be indexed dynamically) and inserts the
 // group minimum branch-free; a second element of the same group beating the threshold in the same lane repeats the
 // round.  Keeping insertion code out of the unrolled fast path keeps the kernel inside the instruction cache.
-__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, uint32_t taddr, TopList& L)
+__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, uint32_t taddr, TopList& L, float ext)
 {
     unsigned mask = 0;
-    const float thr = L.s3;
+    const float thr = fminf(L.s3, ext);
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
         const float m = fminf(fminf(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1])),
@@ -316,10 +317,10 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, u
 #pragma unroll 1
         do {
             const int k = (a == x) ? 0 : (b == x) ? 1 : (c == x) ? 2 : 3;      // lowest column on equal scores
-            L.insert_if(x < L.s3, x, col + k);
+            L.insert_if(x < fminf(L.s3, ext), x, col + k);
             a = (k == 0) ? INFINITY : a; b = (k == 1) ? INFINITY : b; c = (k == 2) ? INFINITY : c; d = (k == 3) ? INFINITY : d;
             x = fminf(fminf(a, b), fminf(c, d));
-        } while (__any_sync(0xffffffffu, x < L.s3));
+        } while (__any_sync(0xffffffffu, x < fminf(L.s3, ext)));
     }
 }
 
@@ -382,6 +383,7 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + MAX_STAGES;
     uint64_t* t_full = bars + 2 + 2 * MAX_STAGES; uint64_t* t_empty = t_full + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+    const uint32_t share_s = smem_u32(smem + SMEM_DATA + 256);       // [LPS][BM] x (4th best score, query block)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool tf32 = p.hdr->not_bf16_exact != 0;
@@ -415,6 +417,8 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    for (int i = threadIdx.x; i < LPS * BM; i += TC_THREADS)
+        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(share_s + 8 * i), "r"(0x7F800000u), "r"(-1) : "memory");
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -473,10 +477,18 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
             const int col0 = tile * BN + hf * 64;
             uint32_t ra[32], rb[32];
             tc_ld32(taddr, ra);
+            // The other column half keeps its own list for the same query: publish this list's 4th best and filter
+            // with the minimum of both.  Any threshold >= the final tau keeps the certificate valid (every rejected
+            // or evicted element scores >= a value that only decreases towards tau); the query-block tag guards
+            // against a stale value from the partner's previous segment.
+            float ox; int oq;
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(share_s + 8 * (hf * BM + m * UM + row)), "r"(__float_as_uint(L.s3)), "r"(qb) : "memory");
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(share_s + 8 * ((hf ^ 1) * BM + m * UM + row)) : "memory");
+            const float ext = (oq == qb) ? ox : INFINITY;
             tc_wait_ld_regs(ra); tc_ld32(taddr + 32, rb);
-            score_chunk(ra, col0, taddr, L);
+            score_chunk(ra, col0, taddr, L, ext);
             tc_wait_ld_regs(rb);
-            score_chunk(rb, col0 + 32, taddr + 32, L);
+            score_chunk(rb, col0 + 32, taddr + 32, L, ext);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&t_empty[b]);
