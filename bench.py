@@ -209,11 +209,12 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     l0 = g.launches()
     with ClockSampler(g.dev.index) as cs:
         ms = g.time_steps(step, steps, warmup, barrier)
+        launches = g.launches() - l0                              # warm-up + timed steps only
         t_end = time.time() + 1.0
         while len(cs.samples) < 8 and time.time() < t_end:       # very short runs: keep the GPU busy until sampled
             step()
         torch.cuda.synchronize()
-    launches = (g.launches() - l0)
+    launches = launches * steps // (steps + warmup)             # kernels launched inside the K timed steps
     # dominant kernel timed live with the library's own CUDA events (same stream), separate short pass
     lib.mpl_prof_enable(1)
     for _ in range(max(3, min(steps, 10))):
