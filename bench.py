@@ -201,7 +201,7 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
         m._lib.check(lib.mpl_knn2_l2f32_dev(d_q.data_ptr(), nq, dim, d_t.data_ptr(), nt, dim, dim, 0, rank * nt,
                                             d_scr.data_ptr(), scr_bytes, d_keys.data_ptr(), st), "knn2_l2f32_dev")
         if world > 1:
-            dist.all_gather_into_tensor(d_all, d_keys)           # NCCL over NVLink: 16 B x nq per rank
+            dist.all_gather_into_tensor(d_all.view(-1, 2), d_keys)   # NCCL over NVLink: 16 B x nq per rank
         m._lib.check(lib.mpl_merge_top2_dev(d_all.data_ptr(), world, nq, 2, 1, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
 
     lib.mpl_prof_enable(0)
