@@ -31,7 +31,7 @@ def test_hamming_train_sharded(env, world):
     m, torch, lib = env
     from matchinglib_poselib_b200.sharded import shard_rows
     q, t = datagen.binary_descriptors(777, 30011, 32, seed=world)
-    t[20000] = t[3]; q[5] = t[3]                                     # duplicate across shards -> lower global index first
+    t[20000] = t[7]; q[5] = t[7]                                     # duplicate across shards -> lower global index first
     dev = torch.device("cuda:0")
     d_q = torch.from_numpy(q).to(dev)
     nq = len(q)
@@ -47,7 +47,7 @@ def test_hamming_train_sharded(env, world):
     torch.cuda.synchronize()
     oi, od = orc.knn_hamming(q, t, 2, 0, threads=8)
     assert np.array_equal(idx.cpu().numpy(), oi) and np.array_equal(dist.cpu().numpy(), od)
-    assert idx[5].tolist() == [3, 20000]
+    assert idx[5].tolist() == [7, 20000]
 
 
 def test_sharded_index_class_single_rank(env):
