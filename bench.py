@@ -210,8 +210,12 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     with ClockSampler(g.dev.index) as cs:
         ms = g.time_steps(step, steps, warmup, barrier)
         launches = g.launches() - l0                              # warm-up + timed steps only
+        # the timed region lasts a few ms: keep the same work running until NVML has sampled it.  Every rank must issue
+        # the SAME number of steps (they contain a collective), so the padding is a fixed count, not a deadline.
+        for _ in range(600 if world > 1 else 0):
+            step()
         t_end = time.time() + 1.0
-        while len(cs.samples) < 8 and time.time() < t_end:       # very short runs: keep the GPU busy until sampled
+        while world == 1 and len(cs.samples) < 8 and time.time() < t_end:
             step()
         torch.cuda.synchronize()
     launches = launches * steps // (steps + warmup)             # kernels launched inside the K timed steps
