@@ -145,50 +145,11 @@ __host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(UM >> 4) << 24);
 }
 
-// ---- 1. scan: row norms, max |t|^2, bf16-exactness -----------------------------------------------------
-// rows [0, nt) are train rows, [nt, nt + nq) query rows; one warp per row.  Norm buffers are padded to the
-// tile size with +inf (a pad row can then never enter a candidate list: inf < tau is false).
-__global__ void __launch_bounds__(256)
-l2_prep_scan_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld,
-                    int dim, float* __restrict__ tnorm, int nt_pad, float* __restrict__ qnorm, int nq_pad, TcHeader* hdr)
-{
-    const int lane = threadIdx.x & 31;
-    const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
-    const int total = nt_pad + nq_pad;
-    unsigned inexact = 0;
-    float tmax = 0.f;
-    for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < total; row += warps_per_grid) {
-        const bool is_t = row < nt_pad;
-        const int r = is_t ? row : row - nt_pad;
-        const int n = is_t ? nt : nq;
-        float* out = is_t ? tnorm : qnorm;
-        if (r >= n) { if (lane == 0) out[r] = INFINITY; continue; }
-        const float* x = (is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld);
-        float s = 0.f;
-        for (int i = lane; i < dim; i += 32) {
-            const float v = x[i];
-            inexact |= (__float_as_uint(v) & 0xFFFFu);
-            s = fmaf(v, v, s);
-        }
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) out[r] = s;
-        if (is_t) tmax = fmaxf(tmax, s);
-    }
-    inexact = __any_sync(0xffffffffu, inexact != 0);
-    if (lane == 0) {
-        if (inexact) atomicOr(&hdr->not_bf16_exact, 1u);
-        if (tmax > 0.f) atomicMax(&hdr->max_tnorm_bits, __float_as_uint(tmax));
-    }
-}
-
-// ---- 2. pack: operand rows in the MMA's element type ---------------------------------------------------
-// bf16 mode: rows of kp16 bf16 (kp16 = dim rounded up to 64); tf32 mode: rows of kp32 floats (dim rounded
-// up to 32).  Same destination buffer either way (sized for the fp32 case); zero padded columns.
-// Query rows are scaled by -2 (exact).  The "aug" K step folds |t|^2 into the contraction, so that the
-// accumulator IS the score |t|^2 - 2 q.t: train aug row = |t|^2 split into three pieces that are each exactly
-// representable in the operand type (3 x 8 bits bf16, 3 x 11 bits tf32 >= the 24-bit fp32 mantissa), query
-// aug row = (1, 1, 1, 0, ...).  Train pad rows (up to a whole tile) get +inf, so they never enter a list.
+// ---- 1 + 2. operand preparation -------------------------------------------------------------------------
+// The "aug" K step folds |t|^2 into the contraction, so that the accumulator IS the score |t|^2 - 2 q.t: train
+// aug row = |t|^2 split into three pieces that are each exactly representable in the operand type (3 x 8 bits
+// bf16, 3 x 11 bits tf32 >= the 24-bit fp32 mantissa), query aug row = (1, 1, 1, 0, ...).  Train pad rows (up to a
+// whole tile) get +inf, so they never enter a list.  Query rows are scaled by -2 (exact).
 __device__ __forceinline__ void split3(float n, unsigned keep_mask, float (&o)[3])
 {
     if (!(n < INFINITY)) { o[0] = INFINITY; o[1] = 0.f; o[2] = 0.f; return; }
@@ -198,14 +159,94 @@ __device__ __forceinline__ void split3(float n, unsigned keep_mask, float (&o)[3
     o[2] = r1 - o[1];                                            // exact, and fits the remaining bits
 }
 
+__device__ __forceinline__ void write_aug(uint4* dst, bool is_t, float norm, bool bf16_mode)
+{
+    float o[3];
+    if (is_t) split3(norm, bf16_mode ? 0xFFFF0000u : 0xFFFFE000u, o);
+    else { o[0] = 1.f; o[1] = 1.f; o[2] = 1.f; }
+    uint4 w0 = make_uint4(0, 0, 0, 0);
+    if (bf16_mode) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b2 = __floats2bfloat162_rn(o[2], 0.f);
+        w0.x = *reinterpret_cast<uint32_t*>(&a); w0.y = *reinterpret_cast<uint32_t*>(&b2);
+    } else {
+        w0.x = __float_as_uint(o[0]); w0.y = __float_as_uint(o[1]); w0.z = __float_as_uint(o[2]);
+    }
+    dst[0] = w0; dst[1] = make_uint4(0, 0, 0, 0);
+}
+
+// One pass, one warp per row (rows [0, nt_pad) train, then [nt_pad, nt_pad + nq) queries): |x|^2, max |t|^2, whether
+// every value is exactly representable in bf16 (true for OpenCV SIFT: integers 0..255), and -- speculatively -- the
+// bf16 operand rows (kp16 = dim rounded up to 64, zero padded) and bf16 aug rows.  No host round trip: the flag lives
+// in device memory; if it ends up set, l2_prep_tf32_kernel overwrites the operands with fp32 rows read as tf32.
 __global__ void __launch_bounds__(256)
-l2_prep_pack_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
-                    void* __restrict__ tp, void* __restrict__ qp, int kp16, int kp32, const float* __restrict__ tnorm, int nt_pad,
+l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
+                    void* __restrict__ tp, void* __restrict__ qp, int kp16, float* __restrict__ tnorm, int nt_pad,
+                    float* __restrict__ qnorm, uint4* __restrict__ taug, uint4* __restrict__ qaug, TcHeader* hdr)
+{
+    const int lane = threadIdx.x & 31;
+    const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
+    const int total = nt_pad + nq;
+    const bool vec_ok = (((uintptr_t)q | (uintptr_t)t) & 15) == 0 && ((q_ld | t_ld) & 3) == 0;
+    unsigned inexact = 0;
+    float tmax = 0.f;
+    for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < total; row += warps_per_grid) {
+        const bool is_t = row < nt_pad;
+        const int r = is_t ? row : row - nt_pad;
+        if (is_t && r >= nt) {                                   // train pad row of the last tile
+            if (lane == 0) { tnorm[r] = INFINITY; write_aug(taug + 2 * (size_t)r, true, INFINITY, true); }
+            continue;
+        }
+        const float* x = is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld;
+        const float sc = is_t ? 1.f : -2.f;
+        char* dst = (char*)(is_t ? tp : qp) + (size_t)r * kp16 * 2;
+        float s = 0.f;
+        for (int i = 4 * lane; i < kp16; i += 128) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i + 3 < dim && vec_ok) v = *reinterpret_cast<const float4*>(x + i);
+            else {
+                if (i < dim) v.x = x[i];
+                if (i + 1 < dim) v.y = x[i + 1];
+                if (i + 2 < dim) v.z = x[i + 2];
+                if (i + 3 < dim) v.w = x[i + 3];
+            }
+            inexact |= (__float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w)) & 0xFFFFu;
+            s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+            __nv_bfloat162 lo = __floats2bfloat162_rn(sc * v.x, sc * v.y), hi = __floats2bfloat162_rn(sc * v.z, sc * v.w);
+            uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst + 2 * i) = o;
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) {
+            (is_t ? tnorm : qnorm)[r] = s;
+            write_aug((is_t ? taug : qaug) + 2 * (size_t)r, is_t, s, true);
+        }
+        if (is_t) tmax = fmaxf(tmax, s);
+    }
+    // one atomic per CTA (a same-address atomic per warp serialises in L2 and dominated this kernel)
+    __shared__ unsigned s_inexact, s_tmax;
+    if (threadIdx.x == 0) { s_inexact = 0; s_tmax = 0; }
+    __syncthreads();
+    inexact = __any_sync(0xffffffffu, inexact != 0);
+    if (lane == 0) {
+        if (inexact) atomicOr(&s_inexact, 1u);
+        if (tmax > 0.f) atomicMax(&s_tmax, __float_as_uint(tmax));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (s_inexact) atomicOr(&hdr->not_bf16_exact, 1u);
+        if (s_tmax) atomicMax(&hdr->max_tnorm_bits, s_tmax);
+    }
+}
+
+// Only when some value is not bf16-exact: fp32 operand rows (kp32 = dim rounded up to 32) and tf32 aug rows.
+__global__ void __launch_bounds__(256)
+l2_prep_tf32_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
+                    void* __restrict__ tp, void* __restrict__ qp, int kp32, const float* __restrict__ tnorm, int nt_pad,
                     uint4* __restrict__ taug, uint4* __restrict__ qaug, const TcHeader* __restrict__ hdr)
 {
-    const bool bf16_mode = hdr->not_bf16_exact == 0;
-    const int kp = bf16_mode ? kp16 : kp32;
-    const int groups = kp / 4;                                   // 4 elements per thread
+    if (hdr->not_bf16_exact == 0) return;
+    const int groups = kp32 / 4;
     const long long total = (long long)(nt + nq) * groups;
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -219,29 +260,11 @@ l2_prep_pack_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
 #pragma unroll
         for (int e = 0; e < 4; ++e) v[e] = (4 * g + e < dim) ? sc * x[4 * g + e] : 0.f;
         char* dst = (char*)(is_t ? tp : qp);
-        if (bf16_mode) {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
-            uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
-            *reinterpret_cast<uint2*>(dst + ((size_t)r * kp + 4 * g) * 2) = o;
-        } else {
-            *reinterpret_cast<float4*>(dst + ((size_t)r * kp + 4 * g) * 4) = make_float4(v[0], v[1], v[2], v[3]);
-        }
+        *reinterpret_cast<float4*>(dst + ((size_t)r * kp32 + 4 * g) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     }
-    // aug rows: 32 bytes each
     for (long long i = tid; i < (long long)nt_pad + nq; i += stride) {
         const bool is_t = i < nt_pad;
-        float o[3];
-        if (is_t) split3(tnorm[i], bf16_mode ? 0xFFFF0000u : 0xFFFFE000u, o);
-        else { o[0] = 1.f; o[1] = 1.f; o[2] = 1.f; }
-        uint4 w0 = make_uint4(0, 0, 0, 0);
-        if (bf16_mode) {
-            __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b2 = __floats2bfloat162_rn(o[2], 0.f);
-            w0.x = *reinterpret_cast<uint32_t*>(&a); w0.y = *reinterpret_cast<uint32_t*>(&b2);
-        } else {
-            w0.x = __float_as_uint(o[0]); w0.y = __float_as_uint(o[1]); w0.z = __float_as_uint(o[2]);
-        }
-        uint4* dst = is_t ? taug + 2 * i : qaug + 2 * (i - nt_pad);
-        dst[0] = w0; dst[1] = make_uint4(0, 0, 0, 0);
+        write_aug(is_t ? taug + 2 * i : qaug + 2 * (i - nt_pad), is_t, is_t ? tnorm[i] : 0.f, false);
     }
 }
 
@@ -503,33 +526,38 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
 // ---- 4. exact re-rank + certificate --------------------------------------------------------------------
 // cvflann::L2<float> order (MODE 0): result += ((d0^2 + d1^2) + d2^2) + d3^2 per group of 4, scalar tail;
 // NMSLIB L2NormSIMD order (MODE 1): 4 lanes, ((l0 + l1) + l2) + l3, scalar tail, sqrtf.
+// The whole warp evaluates ONE pair: lane l owns the group of four dims 4l..4l+3 of each 128-dim round (coalesced
+// 512-byte row reads), then every lane replays the reference's sequential accumulation over the groups in ascending
+// order with warp shuffles -- same operations, same order, same roundings as the reference's scalar loop.
 template <int MODE>
-__device__ __forceinline__ float exact_dist(const float* __restrict__ a /* train row */, const float* __restrict__ b /* query row */, int dim, float* sq_out)
+__device__ __forceinline__ float warp_exact_dist(const float* __restrict__ a /* train row */, const float* __restrict__ b /* query row */,
+                                                 int dim, int lane, bool vec_ok)
 {
-    float r;
-    int i = 0;
-    if (MODE == 0) {
-        r = 0.f;
-        for (; i + 3 < dim; i += 4) {
-            const float d0 = __fsub_rn(a[i], b[i]), d1 = __fsub_rn(a[i + 1], b[i + 1]);
-            const float d2 = __fsub_rn(a[i + 2], b[i + 2]), d3 = __fsub_rn(a[i + 3], b[i + 3]);
-            float s = __fadd_rn(__fmul_rn(d0, d0), __fmul_rn(d1, d1));
-            s = __fadd_rn(s, __fmul_rn(d2, d2));
-            s = __fadd_rn(s, __fmul_rn(d3, d3));
-            r = __fadd_rn(r, s);
+    const int dim4 = dim & ~3;
+    float r = 0.f, l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+    for (int base = 0; base < dim4; base += 128) {
+        const int i = base + 4 * lane;
+        float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
+        if (i < dim4) {
+            float4 x, y;
+            if (vec_ok) { x = *reinterpret_cast<const float4*>(a + i); y = *reinterpret_cast<const float4*>(b + i); }
+            else { x = make_float4(a[i], a[i + 1], a[i + 2], a[i + 3]); y = make_float4(b[i], b[i + 1], b[i + 2], b[i + 3]); }
+            const float d0 = __fsub_rn(x.x, y.x), d1 = __fsub_rn(x.y, y.y), d2 = __fsub_rn(x.z, y.z), d3 = __fsub_rn(x.w, y.w);
+            p0 = __fmul_rn(d0, d0); p1 = __fmul_rn(d1, d1); p2 = __fmul_rn(d2, d2); p3 = __fmul_rn(d3, d3);
         }
-    } else {
-        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-        for (; i + 3 < dim; i += 4) {
-            const float d0 = __fsub_rn(a[i], b[i]), d1 = __fsub_rn(a[i + 1], b[i + 1]);
-            const float d2 = __fsub_rn(a[i + 2], b[i + 2]), d3 = __fsub_rn(a[i + 3], b[i + 3]);
-            l0 = __fadd_rn(l0, __fmul_rn(d0, d0)); l1 = __fadd_rn(l1, __fmul_rn(d1, d1));
-            l2 = __fadd_rn(l2, __fmul_rn(d2, d2)); l3 = __fadd_rn(l3, __fmul_rn(d3, d3));
+        const int groups = min(32, (dim4 - base) >> 2);
+        if (MODE == 0) {
+            const float s = __fadd_rn(__fadd_rn(__fadd_rn(p0, p1), p2), p3);
+            for (int g = 0; g < groups; ++g) r = __fadd_rn(r, __shfl_sync(0xffffffffu, s, g));
+        } else {
+            for (int g = 0; g < groups; ++g) {
+                l0 = __fadd_rn(l0, __shfl_sync(0xffffffffu, p0, g)); l1 = __fadd_rn(l1, __shfl_sync(0xffffffffu, p1, g));
+                l2 = __fadd_rn(l2, __shfl_sync(0xffffffffu, p2, g)); l3 = __fadd_rn(l3, __shfl_sync(0xffffffffu, p3, g));
+            }
         }
-        r = __fadd_rn(__fadd_rn(__fadd_rn(l0, l1), l2), l3);
     }
-    for (; i < dim; ++i) { const float d = __fsub_rn(a[i], b[i]); r = __fadd_rn(r, __fmul_rn(d, d)); }
-    *sq_out = r;
+    if (MODE == 1) r = __fadd_rn(__fadd_rn(__fadd_rn(l0, l1), l2), l3);
+    for (int i = dim4; i < dim; ++i) { const float d = __fsub_rn(a[i], b[i]); r = __fadd_rn(r, __fmul_rn(d, d)); }
     return MODE == 1 ? sqrtf(r) : r;
 }
 
@@ -583,23 +611,29 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     // pass B: exact distance of every candidate that can still be one of the two nearest
     const float cut = s_b + 2.f * eps;
     mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
-    float sq2 = 0.f;                                                              // squared distance behind b1 (MODE 1)
     const float* qrow = q + (size_t)qi * q_ld;
-    for (int c = lane; c < n_cand; c += 32) {
-        const int slot = c / NC, e = c - slot * NC;
-        const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
-        const uint4 sc = rec[0], id = rec[1];
-        const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
-        const int ti = (int)(e == 0 ? id.x : e == 1 ? id.y : e == 2 ? id.z : id.w);
-        if (ti < 0 || ti >= nt || !(s <= cut)) continue;
-        float sqv;
-        const float d = exact_dist<MODE>(t + (size_t)ti * t_ld, qrow, dim, &sqv);
-        const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
-        const mpl_key64 hi = max(b0, key);
-        b0 = min(b0, key); b1 = min(b1, hi);
+    const bool vec_ok = (((uintptr_t)q | (uintptr_t)t) & 15) == 0 && ((q_ld | t_ld) & 3) == 0;
+    for (int c0 = 0; c0 < n_cand; c0 += 32) {
+        const int c = c0 + lane;
+        int ti = -1; float s = INFINITY;
+        if (c < n_cand) {
+            const int slot = c / NC, e = c - slot * NC;
+            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
+            const uint4 sc = rec[0], id = rec[1];
+            s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
+            ti = (int)(e == 0 ? id.x : e == 1 ? id.y : e == 2 ? id.z : id.w);
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, ti >= 0 && ti < nt && s <= cut);
+        while (todo) {                                                            // warp-uniform: one pair at a time
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int tj = __shfl_sync(0xffffffffu, ti, src);
+            const float d = warp_exact_dist<MODE>(t + (size_t)tj * t_ld, qrow, dim, lane, vec_ok);
+            const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + tj);
+            const mpl_key64 hi = max(b0, key);
+            b0 = min(b0, key); b1 = min(b1, hi);                                  // identical in every lane
+        }
     }
-    warp_top2(b0, b1);
-    (void)sq2;
     if (lane == 0) {
         keys_out[2 * (size_t)qi] = b0; keys_out[2 * (size_t)qi + 1] = b1;
         // certificate: every non-candidate has score >= tau, hence reference distance >= tau + |q|^2 - eps
@@ -723,11 +757,11 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
     {
         MplProfScope prof(MPL_PROF_L2_PREP, st);
-        const int rows = P.NT * BN + P.NQB * BM;
-        int blocks = (rows + 7) / 8; if (blocks > sm_count * 8) blocks = sm_count * 8;
-        l2_prep_scan_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tnorm, P.NT * BN, qnorm, P.NQB * BM, hdr);
+        const int rows = P.NT * BN + nq;
+        int blocks = (rows + 7) / 8; if (blocks > sm_count * 16) blocks = sm_count * 16;
+        l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        l2_prep_pack_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
+        l2_prep_tf32_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
     {
