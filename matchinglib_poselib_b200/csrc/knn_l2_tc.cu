@@ -54,13 +54,18 @@ constexpr int AUG_BYTES = 32;        // one extra K step per row: |t|^2 split in
 constexpr int A_AUG = BM * AUG_BYTES;                        //  8 KB
 constexpr int STAGE_BYTES = B_SLAB + BN * AUG_BYTES;         // 20 KB: one B slab (+ the tile's aug slab beside slab 0)
 constexpr int MAX_STAGES = 8;
-constexpr int SMEM_DATA = 216 * 1024;                        // A slabs | A aug | B ring (as many stages as fit)
+constexpr int SMEM_DATA = 197 * 1024;                        // A slabs | A aug | B ring (as many stages as fit)
 constexpr int NC = 4;                // candidates kept per list
 constexpr int LPS = 2;               // lists per (CTA, query block) slot: one per half of the tile's columns
-constexpr int EPI_WARPS = 16;        // 4 warpgroups: (query block half m) x (column half)
+constexpr int EPI_WARPS = 16;        // 4 warpgroups: (UMMA M block m) x (column half); thread = one query row x 64 columns
 constexpr int TC_THREADS = 128 + 32 * EPI_WARPS;             // warps 0..3 control, 4..19 epilogue
-constexpr int SMEM_TAIL = 256 + LPS * BM * 8;                  // barriers + TMEM slot | shared list thresholds (score, query block)
+constexpr int PEND_CAP = 6;          // pending (score, train index) entries per epilogue thread, drained into the sorted list
+constexpr int PEND_STRIDE = 32 * EPI_WARPS * 8;              // bytes between consecutive entries of one thread (lane-interleaved)
+constexpr int SMEM_SHARE = LPS * BM * 8;                     // published list thresholds: (NC-th best score, query block)
+constexpr int SMEM_TAIL = 256 + SMEM_SHARE + PEND_CAP * PEND_STRIDE;      // barriers + TMEM slot | thresholds | pending buffers
 constexpr int SMEM_BYTES = 1024 + SMEM_DATA + SMEM_TAIL;
+static_assert(SMEM_BYTES <= 227 * 1024, "dynamic shared memory limit of sm_100");
+static_assert((SMEM_DATA - MAX_A_SLABS * A_SLAB - A_AUG) / STAGE_BYTES >= 3, "B ring needs at least 3 stages in tf32 mode");
 
 struct TcHeader {                    // first 256 bytes of the scratch buffer (zeroed per call)
     unsigned not_bf16_exact;         // 0 -> bf16 mode, else tf32 mode
@@ -310,40 +315,95 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
                  :: "memory");
 }
 
-// Fast path: 32 scores (the accumulators themselves) -> one bit per group of 4 columns whose minimum beats the
-// list's 4th best in any lane.  Slow path (rare): ONE compact loop per call site re-reads the 4 accumulators of a
-// flagged group from TMEM at a dynamic column address (registers cannot be indexed dynamically) and inserts the
-// group minimum branch-free; a second element of the same group beating the threshold in the same lane repeats the
-// round.  Keeping insertion code out of the unrolled fast path keeps the kernel inside the instruction cache.
-__device__ __forceinline__ void score_chunk(const uint32_t (&r)[32], int col0, uint32_t taddr, TopList& L, float ext)
+// Epilogue state of one thread (= one query row): the sorted top-NC list in registers, a stale copy of its NC-th
+// best score (thr) used as the filter, and a small pending buffer in shared memory.
+//
+// Fast path (per 32-column chunk): minimum of every group of 4 accumulators, one sign bit per group from
+// (min - thr) (FADD on the fma pipe + one funnel shift; the alu pipe, which FMNMX/SEL/ISETP share, is what bounds this
+// kernel), OR over the warp.  Slow path: ONE compact loop per call site handles a flagged group for the whole warp:
+// re-read its 4 accumulators from TMEM at a dynamic column (registers cannot be indexed dynamically) and APPEND the
+// elements below thr to the thread's pending buffer -- no sorted insertion here.  Pending entries are drained into the
+// sorted list, lane-parallel, only when some lane's buffer could overflow on the next group (and at the end of the
+// segment); thr is refreshed then.  A stale thr is >= the final NC-th best, so every element that is rejected by the
+// filter or evicted by the drain scores >= the list's final NC-th best: the certificate's tau stays valid.  Entries are
+// drained in arrival (= ascending train index) order with strict '<', i.e. the list is exactly what one-by-one
+// insertion would have produced (lower train index wins ties).
+struct EpiState {
+    TopList L;
+    float thr;                       // filter threshold: min(own NC-th best, partner list's published NC-th best), possibly stale
+    float ext;                       // the partner's published value as read at the start of the tile
+    uint32_t pbase, pptr;            // shared-memory byte addresses: first entry of this thread / next free entry
+    uint32_t pub;                    // shared-memory address where this list's threshold is published
+    int qb;                          // query block of the current segment (tag of the published threshold)
+};
+
+__device__ __forceinline__ void epi_drain(EpiState& S)
 {
-    unsigned mask = 0;
-    const float thr = fminf(L.s3, ext);
-#pragma unroll
-    for (int g = 0; g < 8; ++g) {
-        const float m = fminf(fminf(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1])),
-                              fminf(__uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3])));
-        if (m < thr) mask |= 1u << g;
+    const int cnt = (int)((S.pptr - S.pbase) / PEND_STRIDE);
+    const int n = __reduce_max_sync(0xffffffffu, cnt);
+#pragma unroll 1
+    for (int i = 0; i < n; ++i) {
+        float sc = INFINITY; int id = -1;
+        if (i < cnt) asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(sc), "=r"(id) : "r"(S.pbase + i * PEND_STRIDE) : "memory");
+        S.L.insert_if(sc < S.L.s3, sc, id);
     }
-    mask = __reduce_or_sync(0xffffffffu, mask);                                   // warp-uniform: tcgen05.ld is .aligned
+    S.pptr = S.pbase;
+    S.thr = fminf(S.L.s3, S.ext);
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pub), "r"(__float_as_uint(S.L.s3)), "r"(S.qb) : "memory");
+}
+
+// one bit per group of 4 columns whose minimum is below thr: sign(min - thr) (FADD on the fma pipe) funnelled into the mask
+__device__ __forceinline__ unsigned group_mask(const uint32_t (&r)[32], float thr)
+{
+    unsigned lo = 0, hi = 0;                                                      // two independent chains of 4
+#pragma unroll
+    for (int g = 3; g >= 0; --g) {
+        const float m0 = fminf(fminf(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1])),
+                               fminf(__uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3])));
+        const float m1 = fminf(fminf(__uint_as_float(r[16 + 4 * g]), __uint_as_float(r[16 + 4 * g + 1])),
+                               fminf(__uint_as_float(r[16 + 4 * g + 2]), __uint_as_float(r[16 + 4 * g + 3])));
+        // the sign of (m - thr) is set iff m < thr (inf - inf gives the positive canonical NaN: pad rows never flag)
+        lo = __funnelshift_l(__float_as_uint(__fsub_rn(m0, thr)), lo, 1);
+        hi = __funnelshift_l(__float_as_uint(__fsub_rn(m1, thr)), hi, 1);
+    }
+    return (lo & 0xFu) | ((hi & 0xFu) << 4);
+}
+
+__device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&v)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr) : "memory");
+}
+
+// Slow path: the flagged groups of a tile half (bit g of mask = columns 4g..4g+3 from col0 / taddr), one at a time for the
+// whole warp.  The TMEM re-read of the next flagged group is in flight while the current one is appended.
+__device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t taddr, EpiState& S)
+{
+    if (mask == 0) return;
+    uint32_t v[4];
+    int g = __ffs(mask) - 1;
+    mask &= mask - 1;
+    tc_ld4(taddr + 4 * g, v);
 #pragma unroll 1
-    while (mask) {
-        const int g = __ffs(mask) - 1;
-        mask &= mask - 1;
-        uint32_t v0, v1, v2, v3;
-        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(taddr + 4 * g) : "memory");
-        asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v0), "+r"(v1), "+r"(v2), "+r"(v3) :: "memory");
-        float a = __uint_as_float(v0), b = __uint_as_float(v1), c = __uint_as_float(v2), d = __uint_as_float(v3);
+    while (true) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]) :: "memory");
+        const uint32_t w0 = v[0], w1 = v[1], w2 = v[2], w3 = v[3];
         const int col = col0 + 4 * g;
-        float x = fminf(fminf(a, b), fminf(c, d));
-#pragma unroll 1
-        do {
-            const int k = (a == x) ? 0 : (b == x) ? 1 : (c == x) ? 2 : 3;      // lowest column on equal scores
-            L.insert_if(x < fminf(L.s3, ext), x, col + k);
-            a = (k == 0) ? INFINITY : a; b = (k == 1) ? INFINITY : b; c = (k == 2) ? INFINITY : c; d = (k == 3) ? INFINITY : d;
-            x = fminf(fminf(a, b), fminf(c, d));
-        } while (__any_sync(0xffffffffu, x < fminf(L.s3, ext)));
+        const bool more = mask != 0;
+        if (more) {
+            g = __ffs(mask) - 1;
+            mask &= mask - 1;
+            tc_ld4(taddr + 4 * g, v);
+        }
+        const uint32_t w[4] = {w0, w1, w2, w3};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (__uint_as_float(w[e]) < S.thr) {
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pptr), "r"(w[e]), "r"(col + e) : "memory");
+                S.pptr += PEND_STRIDE;
+            }
+        }
+        if (__any_sync(0xffffffffu, S.pptr > S.pbase + (PEND_CAP - 4) * PEND_STRIDE)) epi_drain(S);
+        if (!more) break;
     }
 }
 
@@ -355,10 +415,13 @@ __device__ __forceinline__ void mma_issue_loop(long long u0, long long u1, int N
     constexpr uint32_t idesc = umma_idesc(MODE == 1 ? 2u : 1u);
     constexpr uint64_t hi128 = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);     // see umma_desc()
     constexpr uint64_t hi32 = ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);       // see umma_desc_sw32()
-    int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1; unsigned it = 0;
+    int stage = 0; uint32_t sphase = 0; int a_cnt = 0; unsigned it = 0;
+    int tile = (int)(u0 - (u0 / NT) * NT);                                       // tile index inside the current query block
+    bool new_qb = true;
     for (long long u = u0; u < u1; ++u, ++it) {
-        const int qb = (int)(u / NT);
-        if (qb != cur_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; cur_qb = qb; }
+        if (new_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; new_qb = false; }
+        const bool last_of_qb = (++tile == NT);
+        if (last_of_qb) { tile = 0; new_qb = true; }
         const uint32_t b = it & 1;
         mbar_wait(&t_empty[b], ((it >> 1) & 1) ^ 1);                             // epilogue drained this accumulator buffer
         tc_fence_after();
@@ -385,7 +448,7 @@ __device__ __forceinline__ void mma_issue_loop(long long u0, long long u1, int N
                 tc_commit(&b_empty[stage]);                                      // slab free once these MMAs retire
                 if (s == n_slabs - 1) {
                     tc_commit(&t_full[b]);
-                    if (u + 1 < u1 && (int)((u + 1) / NT) != qb) tc_commit(a_empty);   // only when the producer will wait for it
+                    if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);                  // only when the producer will wait for it
                 }
             }
             __syncwarp();
@@ -406,7 +469,8 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + MAX_STAGES;
     uint64_t* t_full = bars + 2 + 2 * MAX_STAGES; uint64_t* t_empty = t_full + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
-    const uint32_t share_s = smem_u32(smem + SMEM_DATA + 256);       // [LPS][BM] x (4th best score, query block)
+    const uint32_t share_s = smem_u32(smem + SMEM_DATA + 256);       // [LPS][BM] x (NC-th best score, query block)
+    const uint32_t pend_s = share_s + SMEM_SHARE;                    // [PEND_CAP][epilogue threads] x (score, train index)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool tf32 = p.hdr->not_bf16_exact != 0;
@@ -450,8 +514,9 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     if (warp == 0) {
         // ===== TMA producer: the whole warp runs the loop (uniform control flow), one elected lane issues =====
         int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1;
+        int qb = (int)(u0 / p.NT), tile = (int)(u0 - (long long)qb * p.NT) - 1;
         for (long long u = u0; u < u1; ++u) {
-            const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
+            if (++tile == p.NT) { tile = 0; ++qb; }
             if (qb != cur_qb) {
                 mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));                 // MMAs of the previous query block are done
                 if (elect_one()) {
@@ -480,19 +545,25 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
         else      mma_issue_loop<0>(u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
                                     a_full, a_empty, b_full, b_empty, t_full, t_empty);
     } else if (warp >= 4) {
-        // ===== epilogue: thread = one query row of block m, one half of the tile's columns =====
+        // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile =====
         const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
-        TopList L; L.reset();
-        int cur_qb = -1; unsigned it = 0;
-        auto flush = [&](int qb) {
-            const int slot = (int)blockIdx.x - tc_owner((long long)qb * p.NT, p.U, G);
-            uint4* dst = p.cand + ((((size_t)qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2;
-            dst[0] = make_uint4(__float_as_uint(L.s0), __float_as_uint(L.s1), __float_as_uint(L.s2), __float_as_uint(L.s3));
-            dst[1] = make_uint4((uint32_t)L.i0, (uint32_t)L.i1, (uint32_t)L.i2, (uint32_t)L.i3);
+        EpiState S;
+        S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
+        S.pbase = S.pptr = pend_s + (uint32_t)(threadIdx.x - 128) * 8u;
+        S.pub = share_s + 8u * (uint32_t)(hf * BM + m * UM + row);
+        const uint32_t partner = share_s + 8u * (uint32_t)((hf ^ 1) * BM + m * UM + row);
+        int tile = (int)(u0 - (u0 / p.NT) * p.NT);
+        S.qb = (int)(u0 / p.NT);
+        unsigned it = 0;
+        auto flush = [&]() {
+            epi_drain(S);
+            const int slot = (int)blockIdx.x - tc_owner((long long)S.qb * p.NT, p.U, G);
+            uint4* dst = p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2;
+            dst[0] = make_uint4(__float_as_uint(S.L.s0), __float_as_uint(S.L.s1), __float_as_uint(S.L.s2), __float_as_uint(S.L.s3));
+            dst[1] = make_uint4((uint32_t)S.L.i0, (uint32_t)S.L.i1, (uint32_t)S.L.i2, (uint32_t)S.L.i3);
+            S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
         };
         for (long long u = u0; u < u1; ++u, ++it) {
-            const int qb = (int)(u / p.NT), tile = (int)(u - (long long)qb * p.NT);
-            if (qb != cur_qb) { if (cur_qb >= 0) flush(cur_qb); L.reset(); cur_qb = qb; }
             const uint32_t b = it & 1;
             mbar_wait(&t_full[b], (it >> 1) & 1);
             tc_fence_after();
@@ -500,23 +571,24 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
             const int col0 = tile * BN + hf * 64;
             uint32_t ra[32], rb[32];
             tc_ld32(taddr, ra);
-            // The other column half keeps its own list for the same query: publish this list's 4th best and filter
-            // with the minimum of both.  Any threshold >= the final tau keeps the certificate valid (every rejected
-            // or evicted element scores >= a value that only decreases towards tau); the query-block tag guards
-            // against a stale value from the partner's previous segment.
+            tc_ld32(taddr + 32, rb);
+            // The other column half keeps its own list for the same query: filter with the minimum of both lists' NC-th
+            // best.  Any threshold >= the final tau keeps the certificate valid; the query-block tag guards against a
+            // stale value from the partner's previous segment.
             float ox; int oq;
-            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(share_s + 8 * (hf * BM + m * UM + row)), "r"(__float_as_uint(L.s3)), "r"(qb) : "memory");
-            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(share_s + 8 * ((hf ^ 1) * BM + m * UM + row)) : "memory");
-            const float ext = (oq == qb) ? ox : INFINITY;
-            tc_wait_ld_regs(ra); tc_ld32(taddr + 32, rb);
-            score_chunk(ra, col0, taddr, L, ext);
-            tc_wait_ld_regs(rb);
-            score_chunk(rb, col0 + 32, taddr + 32, L, ext);
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(partner) : "memory");
+            S.ext = (oq == S.qb) ? ox : INFINITY;
+            S.thr = fminf(S.thr, S.ext);
+            tc_wait_ld_regs(ra); tc_wait_ld_regs(rb);
+            unsigned mask = group_mask(ra, S.thr) | (group_mask(rb, S.thr) << 8);
+            mask = __reduce_or_sync(0xffffffffu, mask);                           // warp-uniform: tcgen05.ld is .aligned
+            epi_events(mask, col0, taddr, S);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&t_empty[b]);
+            if (++tile == p.NT) { flush(); tile = 0; ++S.qb; }
         }
-        if (cur_qb >= 0) flush(cur_qb);
+        if (tile != 0) flush();
     }
     tc_fence_before();
     __syncthreads();
