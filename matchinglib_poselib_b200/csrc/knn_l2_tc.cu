@@ -71,7 +71,8 @@ struct TcHeader {                    // first 256 bytes of the scratch buffer (z
     unsigned not_bf16_exact;         // 0 -> bf16 mode, else tf32 mode
     unsigned max_tnorm_bits;         // max |t|^2 (float bits; non-negative floats order like uints)
     unsigned fallback_count;         // queries that failed certification
-    unsigned pad[61];
+    unsigned not_integer;            // some value is not an integer: the exact-integer mode (top-2 lists, no certificate) is off
+    unsigned pad[60];
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------
@@ -193,6 +194,7 @@ l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
     const int total = nt_pad + nq;
     const bool vec_ok = (((uintptr_t)q | (uintptr_t)t) & 15) == 0 && ((q_ld | t_ld) & 3) == 0;
     unsigned inexact = 0;
+    bool nonint = false;
     float tmax = 0.f;
     for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < total; row += warps_per_grid) {
         const bool is_t = row < nt_pad;
@@ -215,6 +217,7 @@ l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
                 if (i + 3 < dim) v.w = x[i + 3];
             }
             inexact |= (__float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w)) & 0xFFFFu;
+            nonint |= (v.x != truncf(v.x)) | (v.y != truncf(v.y)) | (v.z != truncf(v.z)) | (v.w != truncf(v.w));   // NaN/inf: true
             s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
             __nv_bfloat162 lo = __floats2bfloat162_rn(sc * v.x, sc * v.y), hi = __floats2bfloat162_rn(sc * v.z, sc * v.w);
             uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
@@ -232,14 +235,15 @@ l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
     __shared__ unsigned s_inexact, s_tmax;
     if (threadIdx.x == 0) { s_inexact = 0; s_tmax = 0; }
     __syncthreads();
-    inexact = __any_sync(0xffffffffu, inexact != 0);
+    inexact = (__any_sync(0xffffffffu, inexact != 0) ? 1u : 0u) | (__any_sync(0xffffffffu, nonint) ? 2u : 0u);
     if (lane == 0) {
-        if (inexact) atomicOr(&s_inexact, 1u);
+        if (inexact) atomicOr(&s_inexact, inexact);
         if (tmax > 0.f) atomicMax(&s_tmax, __float_as_uint(tmax));
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        if (s_inexact) atomicOr(&hdr->not_bf16_exact, 1u);
+        if (s_inexact & 1u) atomicOr(&hdr->not_bf16_exact, 1u);
+        if (s_inexact & 2u) atomicOr(&hdr->not_integer, 1u);
         if (s_tmax) atomicMax(&hdr->max_tnorm_bits, s_tmax);
     }
 }
@@ -286,16 +290,37 @@ struct TcParams {
 // CTA c owns units [c*U/G, (c+1)*U/G); owner(u) = the CTA whose range holds unit u
 __host__ __device__ inline int tc_owner(long long u, long long U, int G) { return (int)(((u + 1) * G - 1) / U); }
 
-struct TopList {
-    float s0, s1, s2, s3; int i0, i1, i2, i3;          // ascending scores; ties keep arrival (= train index) order
+// Sorted candidate lists in registers (ascending scores; ties keep arrival = train index order).  TopList4 serves the
+// general case (the certificate needs the 4th best as tau); TopList2 the exact-integer mode (see l2_certify_kernel).
+struct TopList4 {
+    float s0, s1, s2, s3; int i0, i1, i2, i3;
     __device__ __forceinline__ void reset() { s0 = s1 = s2 = s3 = INFINITY; i0 = i1 = i2 = i3 = -1; }
-    // branch-free sorted insertion, active only where p (p implies s < s3)
+    __device__ __forceinline__ float last() const { return s3; }
+    // branch-free sorted insertion, active only where p (p implies s < last())
     __device__ __forceinline__ void insert_if(bool p, float s, int i) {
         const bool c2 = p && (s < s2), c1 = c2 && (s < s1), c0 = c1 && (s < s0);
         s3 = p ? (c2 ? s2 : s) : s3;  i3 = p ? (c2 ? i2 : i) : i3;
         s2 = c2 ? (c1 ? s1 : s) : s2; i2 = c2 ? (c1 ? i1 : i) : i2;
         s1 = c1 ? (c0 ? s0 : s) : s1; i1 = c1 ? (c0 ? i0 : i) : i1;
         s0 = c0 ? s : s0;             i0 = c0 ? i : i0;
+    }
+    __device__ __forceinline__ void store(uint4* dst) const {
+        dst[0] = make_uint4(__float_as_uint(s0), __float_as_uint(s1), __float_as_uint(s2), __float_as_uint(s3));
+        dst[1] = make_uint4((uint32_t)i0, (uint32_t)i1, (uint32_t)i2, (uint32_t)i3);
+    }
+};
+struct TopList2 {
+    float s0, s1; int i0, i1;
+    __device__ __forceinline__ void reset() { s0 = s1 = INFINITY; i0 = i1 = -1; }
+    __device__ __forceinline__ float last() const { return s1; }
+    __device__ __forceinline__ void insert_if(bool p, float s, int i) {
+        const bool c0 = p && (s < s0);
+        s1 = p ? (c0 ? s0 : s) : s1;  i1 = p ? (c0 ? i0 : i) : i1;
+        s0 = c0 ? s : s0;             i0 = c0 ? i : i0;
+    }
+    __device__ __forceinline__ void store(uint4* dst) const {
+        dst[0] = make_uint4(__float_as_uint(s0), __float_as_uint(s1), 0x7F800000u, 0x7F800000u);
+        dst[1] = make_uint4((uint32_t)i0, (uint32_t)i1, 0xFFFFFFFFu, 0xFFFFFFFFu);
     }
 };
 
@@ -328,8 +353,9 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
 // filter or evicted by the drain scores >= the list's final NC-th best: the certificate's tau stays valid.  Entries are
 // drained in arrival (= ascending train index) order with strict '<', i.e. the list is exactly what one-by-one
 // insertion would have produced (lower train index wins ties).
+template <class List>
 struct EpiState {
-    TopList L;
+    List L;
     float thr;                       // filter threshold: min(own NC-th best, partner list's published NC-th best), possibly stale
     float ext;                       // the partner's published value as read at the start of the tile
     uint32_t pbase, pptr;            // shared-memory byte addresses: first entry of this thread / next free entry
@@ -337,7 +363,8 @@ struct EpiState {
     int qb;                          // query block of the current segment (tag of the published threshold)
 };
 
-__device__ __forceinline__ void epi_drain(EpiState& S)
+template <class List>
+__device__ __forceinline__ void epi_drain(EpiState<List>& S)
 {
     const int cnt = (int)((S.pptr - S.pbase) / PEND_STRIDE);
     const int n = __reduce_max_sync(0xffffffffu, cnt);
@@ -345,11 +372,11 @@ __device__ __forceinline__ void epi_drain(EpiState& S)
     for (int i = 0; i < n; ++i) {
         float sc = INFINITY; int id = -1;
         if (i < cnt) asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(sc), "=r"(id) : "r"(S.pbase + i * PEND_STRIDE) : "memory");
-        S.L.insert_if(sc < S.L.s3, sc, id);
+        S.L.insert_if(sc < S.L.last(), sc, id);
     }
     S.pptr = S.pbase;
-    S.thr = fminf(S.L.s3, S.ext);
-    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pub), "r"(__float_as_uint(S.L.s3)), "r"(S.qb) : "memory");
+    S.thr = fminf(S.L.last(), S.ext);
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pub), "r"(__float_as_uint(S.L.last())), "r"(S.qb) : "memory");
 }
 
 // one bit per group of 4 columns whose minimum is below thr: sign(min - thr) (FADD on the fma pipe) funnelled into the mask
@@ -376,7 +403,8 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&v)[4]) {
 
 // Slow path: the flagged groups of a tile half (bit g of mask = columns 4g..4g+3 from col0 / taddr), one at a time for the
 // whole warp.  The TMEM re-read of the next flagged group is in flight while the current one is appended.
-__device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t taddr, EpiState& S)
+template <class List>
+__device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t taddr, EpiState<List>& S)
 {
     if (mask == 0) return;
     uint32_t v[4];
@@ -418,43 +446,125 @@ __device__ __forceinline__ void mma_issue_loop(long long u0, long long u1, int N
     int stage = 0; uint32_t sphase = 0; int a_cnt = 0; unsigned it = 0;
     int tile = (int)(u0 - (u0 / NT) * NT);                                       // tile index inside the current query block
     bool new_qb = true;
+    // one K slab (+ the aug step with slab 0) of one UMMA M block
+    auto issue = [&](int s, int m, uint32_t sb, uint32_t d) {
+        const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
+        if (s == 0) {                                                            // aug K step first: D = |t|^2 (overwrites)
+            const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
+            const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
+            if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
+        }
+        const uint64_t ad = hi128 | (uint64_t)((a_addr + s * A_SLAB + m * (UM * SLAB_BYTES)) >> 4);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {                                            // 4 x 32 bytes of K per slab row
+            if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+        }
+    };
+    // Accumulator buffers are handed over per UMMA M block: t_full / t_empty index = buffer * 2 + m.  When a whole tile's
+    // slabs fit the ring (bf16 mode) the M blocks are issued one after the other, so the epilogue warps of block 0 start
+    // while block 1 is still being multiplied and the two groups of epilogue warps never wait for each other.
+    const bool m_major = n_slabs <= n_stages - 1;
     for (long long u = u0; u < u1; ++u, ++it) {
         if (new_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; new_qb = false; }
         const bool last_of_qb = (++tile == NT);
         if (last_of_qb) { tile = 0; new_qb = true; }
-        const uint32_t b = it & 1;
-        mbar_wait(&t_empty[b], ((it >> 1) & 1) ^ 1);                             // epilogue drained this accumulator buffer
-        tc_fence_after();
-        for (int s = 0; s < n_slabs; ++s) {
-            mbar_wait(&b_full[stage], sphase);
-            tc_fence_after();
-            if (elect_one()) {
-                const uint32_t sb = b_addr + stage * STAGE_BYTES;
-                const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
+        const uint32_t b = it & 1, eparity = ((it >> 1) & 1) ^ 1;
+        if (m_major) {
 #pragma unroll
-                for (int m = 0; m < 2; ++m) {
-                    const uint32_t d = tmem_base + b * 256 + m * 128;
-                    if (s == 0) {                                                // aug K step first: D = |t|^2 (overwrites)
-                        const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
-                        const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
-                        if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
+            for (int m = 0; m < 2; ++m) {
+                mbar_wait(&t_empty[b * 2 + m], eparity);                         // epilogue drained this accumulator block
+                tc_fence_after();
+                int st = stage; uint32_t ph = sphase;
+                for (int s = 0; s < n_slabs; ++s) {
+                    if (m == 0) { mbar_wait(&b_full[st], ph); tc_fence_after(); }
+                    if (elect_one()) {
+                        issue(s, m, b_addr + st * STAGE_BYTES, tmem_base + b * 256 + m * 128);
+                        if (m == 1) tc_commit(&b_empty[st]);                     // slab free once these MMAs retire
+                        if (s == n_slabs - 1) {
+                            tc_commit(&t_full[b * 2 + m]);
+                            if (m == 1 && u + 1 < u1 && last_of_qb) tc_commit(a_empty);   // only when the producer will wait for it
+                        }
                     }
-                    const uint64_t ad = hi128 | (uint64_t)((a_addr + s * A_SLAB + m * (UM * SLAB_BYTES)) >> 4);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {                                // 4 x 32 bytes of K per slab row
-                        if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
-                    }
+                    __syncwarp();
+                    if (++st == n_stages) { st = 0; ph ^= 1; }
                 }
-                tc_commit(&b_empty[stage]);                                      // slab free once these MMAs retire
-                if (s == n_slabs - 1) {
-                    tc_commit(&t_full[b]);
-                    if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);                  // only when the producer will wait for it
-                }
+                if (m == 1) { stage = st; sphase = ph; }
             }
-            __syncwarp();
-            if (++stage == n_stages) { stage = 0; sphase ^= 1; }
+        } else {
+            mbar_wait(&t_empty[b * 2], eparity);
+            mbar_wait(&t_empty[b * 2 + 1], eparity);
+            tc_fence_after();
+            for (int s = 0; s < n_slabs; ++s) {
+                mbar_wait(&b_full[stage], sphase);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t sb = b_addr + stage * STAGE_BYTES;
+                    issue(s, 0, sb, tmem_base + b * 256);
+                    issue(s, 1, sb, tmem_base + b * 256 + 128);
+                    tc_commit(&b_empty[stage]);
+                    if (s == n_slabs - 1) {
+                        tc_commit(&t_full[b * 2]);
+                        tc_commit(&t_full[b * 2 + 1]);
+                        if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);
+                    }
+                }
+                __syncwarp();
+                if (++stage == n_stages) { stage = 0; sphase ^= 1; }
+            }
         }
     }
+}
+
+// Epilogue warps 4..19: thread = one query row of UMMA block m, one half (64 columns) of the tile.
+template <class List, bool EXACT>
+__device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, long long u1, int G, uint32_t tmem_base,
+                                              uint32_t share_s, uint32_t pend_s, uint64_t* t_full, uint64_t* t_empty)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
+    EpiState<List> S;
+    S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
+    S.pbase = S.pptr = pend_s + (uint32_t)(threadIdx.x - 128) * 8u;
+    S.pub = share_s + 8u * (uint32_t)(hf * BM + m * UM + row);
+    const uint32_t partner = share_s + 8u * (uint32_t)((hf ^ 1) * BM + m * UM + row);
+    int tile = (int)(u0 - (u0 / p.NT) * p.NT);
+    S.qb = (int)(u0 / p.NT);
+    unsigned it = 0;
+    auto flush = [&]() {
+        epi_drain(S);
+        const int slot = (int)blockIdx.x - tc_owner((long long)S.qb * p.NT, p.U, G);
+        S.L.store(p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2);
+        S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
+    };
+    for (long long u = u0; u < u1; ++u, ++it) {
+        const uint32_t b = it & 1;
+        mbar_wait(&t_full[b * 2 + m], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128 + hf * 64;
+        const int col0 = tile * BN + hf * 64;
+        uint32_t ra[32], rb[32];
+        tc_ld32(taddr, ra);
+        tc_ld32(taddr + 32, rb);
+        // The other column half keeps its own list for the same query: filter with the minimum of both lists' last
+        // entries.  General mode: any threshold >= the final tau keeps the certificate valid.  Exact mode: an element
+        // may only be dropped if two others are STRICTLY better or equal with a lower train index; the partner's
+        // columns are not ordered against ours, so its threshold is relaxed by one (scores are integers there).  The
+        // query-block tag guards against a stale value from the partner's previous segment.
+        float ox; int oq;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(partner) : "memory");
+        if (EXACT) ox = __fadd_rn(ox, 1.0f);
+        S.ext = (oq == S.qb) ? ox : INFINITY;
+        S.thr = fminf(S.thr, S.ext);
+        tc_wait_ld_regs(ra); tc_wait_ld_regs(rb);
+        unsigned mask = group_mask(ra, S.thr) | (group_mask(rb, S.thr) << 8);
+        mask = __reduce_or_sync(0xffffffffu, mask);                               // warp-uniform: tcgen05.ld is .aligned
+        epi_events(mask, col0, taddr, S);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[b * 2 + m]);
+        if (++tile == p.NT) { flush(); tile = 0; ++S.qb; }
+    }
+    if (tile != 0) flush();
 }
 
 struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
@@ -467,8 +577,8 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_DATA);
     uint64_t* a_full = bars + 0; uint64_t* a_empty = bars + 1;
     uint64_t* b_full = bars + 2; uint64_t* b_empty = bars + 2 + MAX_STAGES;
-    uint64_t* t_full = bars + 2 + 2 * MAX_STAGES; uint64_t* t_empty = t_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+    uint64_t* t_full = bars + 2 + 2 * MAX_STAGES; uint64_t* t_empty = t_full + 4;      // [accumulator buffer][UMMA M block]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 4);
     const uint32_t share_s = smem_u32(smem + SMEM_DATA + 256);       // [LPS][BM] x (NC-th best score, query block)
     const uint32_t pend_s = share_s + SMEM_SHARE;                    // [PEND_CAP][epilogue threads] x (score, train index)
 
@@ -497,7 +607,7 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     if (warp == 1 && lane == 0) {
         mbar_init(a_full, 1); mbar_init(a_empty, 1);
         for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], EPI_WARPS); }
+        for (int b = 0; b < 4; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], EPI_WARPS / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {                                             // whole warp: allocate all 512 TMEM columns
@@ -546,49 +656,12 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
                                     a_full, a_empty, b_full, b_empty, t_full, t_empty);
     } else if (warp >= 4) {
         // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile =====
-        const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
-        EpiState S;
-        S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
-        S.pbase = S.pptr = pend_s + (uint32_t)(threadIdx.x - 128) * 8u;
-        S.pub = share_s + 8u * (uint32_t)(hf * BM + m * UM + row);
-        const uint32_t partner = share_s + 8u * (uint32_t)((hf ^ 1) * BM + m * UM + row);
-        int tile = (int)(u0 - (u0 / p.NT) * p.NT);
-        S.qb = (int)(u0 / p.NT);
-        unsigned it = 0;
-        auto flush = [&]() {
-            epi_drain(S);
-            const int slot = (int)blockIdx.x - tc_owner((long long)S.qb * p.NT, p.U, G);
-            uint4* dst = p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2;
-            dst[0] = make_uint4(__float_as_uint(S.L.s0), __float_as_uint(S.L.s1), __float_as_uint(S.L.s2), __float_as_uint(S.L.s3));
-            dst[1] = make_uint4((uint32_t)S.L.i0, (uint32_t)S.L.i1, (uint32_t)S.L.i2, (uint32_t)S.L.i3);
-            S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
-        };
-        for (long long u = u0; u < u1; ++u, ++it) {
-            const uint32_t b = it & 1;
-            mbar_wait(&t_full[b], (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128 + hf * 64;
-            const int col0 = tile * BN + hf * 64;
-            uint32_t ra[32], rb[32];
-            tc_ld32(taddr, ra);
-            tc_ld32(taddr + 32, rb);
-            // The other column half keeps its own list for the same query: filter with the minimum of both lists' NC-th
-            // best.  Any threshold >= the final tau keeps the certificate valid; the query-block tag guards against a
-            // stale value from the partner's previous segment.
-            float ox; int oq;
-            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(partner) : "memory");
-            S.ext = (oq == S.qb) ? ox : INFINITY;
-            S.thr = fminf(S.thr, S.ext);
-            tc_wait_ld_regs(ra); tc_wait_ld_regs(rb);
-            unsigned mask = group_mask(ra, S.thr) | (group_mask(rb, S.thr) << 8);
-            mask = __reduce_or_sync(0xffffffffu, mask);                           // warp-uniform: tcgen05.ld is .aligned
-            epi_events(mask, col0, taddr, S);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&t_empty[b]);
-            if (++tile == p.NT) { flush(); tile = 0; ++S.qb; }
-        }
-        if (tile != 0) flush();
+        // Exact-integer mode (bf16-exact integer data, e.g. OpenCV SIFT): the scores are exact, so sorted top-2 lists give
+        // the exact answer and no certificate margin is needed -- half as many insertions as the general top-4 lists.
+        if (!tf32 && p.hdr->not_integer == 0)
+            epilogue_loop<TopList2, true>(p, u0, u1, G, tmem_base, share_s, pend_s, t_full, t_empty);
+        else
+            epilogue_loop<TopList4, false>(p, u0, u1, G, tmem_base, share_s, pend_s, t_full, t_empty);
     }
     tc_fence_before();
     __syncthreads();
@@ -663,6 +736,15 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     const float sq = sqrtf(qq), st = sqrtf(tmax);
     float eps = 1.2207031e-4f * (sq + st) * (sq + st);                            // 2^-13 (|q| + |t|max)^2
     if (hdr->not_bf16_exact) eps += 3.90625e-3f * sq * st;                        // 2^-8 |q| |t|max
+    // Exact-integer mode (the ranking kernel kept top-2 lists): every value is an integer that bf16 holds exactly.  If
+    // (|q| + |t|max)^2 < 2^24 as well, every product, partial sum and distance on both sides is an integer below 2^24,
+    // i.e. exact in fp32 in any order: score + |q|^2 IS the reference distance, the union of the lists' top-2 (ties kept
+    // by lowest train index) contains the two nearest, and no margin is needed.  Beyond that bound the top-2 lists
+    // cannot be certified and the query takes the exact scan.
+    const bool lists2 = hdr->not_bf16_exact == 0 && hdr->not_integer == 0;
+    const bool exact_ok = lists2 && (sq + st) * (sq + st) < 16777216.f * 0.999f;
+    if (exact_ok) eps = 0.f;
+    const int nc = lists2 ? 2 : NC;
     // pass A: the two smallest scores over all candidates, and tau = min over slots of the slot's 4th best
     float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
     for (int c = lane; c < n_cand; c += 32) {
@@ -670,7 +752,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
         const uint4 sc = rec[0];
         const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
-        if (e == NC - 1) tau = fminf(tau, s);
+        if (e == nc - 1) tau = fminf(tau, s);
         const float hi = fmaxf(s_a, s); s_a = fminf(s_a, s); s_b = fminf(s_b, hi);
     }
 #pragma unroll
@@ -711,6 +793,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         // certificate: every non-candidate has score >= tau, hence reference distance >= tau + |q|^2 - eps
         bool ok;
         if (b1 == MPL_KEY_INVALID) ok = (tau == INFINITY);                         // fewer than 2 train rows scanned in total
+        else if (lists2) ok = exact_ok;
         else {
             float d2 = __uint_as_float((uint32_t)(b1 >> 32));
             if (MODE == 1) d2 = __fmul_rn(d2, d2) * 1.000002f;                     // back to the squared domain, rounding margin

@@ -174,15 +174,40 @@ def test_l2_tc_sqrt_mode(m):
     assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
 
 
-def test_l2_tc_duplicates_take_the_fallback(m):
-    """Ten identical train rows: the 4-deep candidate lists cannot certify -> exact scan, lowest indices win."""
+def test_l2_tc_duplicates_integer_mode_needs_no_fallback(m):
+    """Ten identical train rows, integer-valued (SIFT) data: scores are exact, the top-2 lists keep the lowest train
+    indices on ties and no query needs the exact scan."""
     q, t = datagen.sift_like(300, 3000, 128, seed=77)
     t[100:110] = t[5]
     q[0] = t[5]; q[1] = t[5]; q[1, 3] += 1
+    t[2000] = t[5]; t[2999] = t[5]                       # duplicates in other tiles / the other column half too
     idx, dist, fb, mode = _tc(m, q, t)
     oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
     assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
-    assert idx[0, 0] == 5 and idx[0, 1] == 100 and fb >= 1
+    assert idx[0, 0] == 5 and idx[0, 1] == 100 and mode == 0 and fb == 0
+
+
+def test_l2_tc_duplicates_take_the_fallback(m):
+    """Ten identical train rows, non-integer data (tf32 ranking): the 4-deep candidate lists cannot certify -> exact
+    scan, lowest indices win."""
+    q, t = datagen.signed_float(300, 3000, 128, seed=77)
+    t[100:110] = t[5]
+    q[0] = t[5]; q[1] = t[5]; q[1, 3] += 0.25
+    idx, dist, fb, mode = _tc(m, q, t)
+    oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
+    assert idx[0, 0] == 5 and idx[0, 1] == 100 and mode == 1 and fb >= 1
+
+
+def test_l2_tc_large_integers_leave_exact_mode(m):
+    """Integer data whose distances exceed 2^24 are not exact in fp32: the top-2 lists cannot be certified and every
+    query must come back through the exact scan, still bit-identical to the reference."""
+    q, t = datagen.sift_like(64, 600, 128, seed=5)
+    q *= 16; t *= 16                                     # still bf16-exact integers, norms ~ 8192
+    idx, dist, fb, mode = _tc(m, q, t)
+    oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
+    assert mode == 0 and fb == 64
 
 
 def test_l2_tc_equals_exact_scan_at_c2_size(m):
