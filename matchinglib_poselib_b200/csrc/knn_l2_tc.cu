@@ -95,6 +95,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// non-blocking: has the phase with this parity completed?
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
@@ -401,118 +408,113 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&v)[4]) {
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr) : "memory");
 }
 
-// Slow path: the flagged groups of a tile half (bit g of mask = columns 4g..4g+3 from col0 / taddr), one at a time for the
-// whole warp.  The TMEM re-read of the next flagged group is in flight while the current one is appended.
+// Slow path: the flagged groups of a tile half (bit g of mask = columns 4g..4g+3 from col0 / taddr), for the whole warp.
+// Up to EVB groups are re-read from TMEM with one round trip, then appended one after the other.
+constexpr int EVB = 2;
 template <class List>
 __device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t taddr, EpiState<List>& S)
 {
-    if (mask == 0) return;
-    uint32_t v[4];
-    int g = __ffs(mask) - 1;
-    mask &= mask - 1;
-    tc_ld4(taddr + 4 * g, v);
 #pragma unroll 1
-    while (true) {
-        asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]) :: "memory");
-        const uint32_t w0 = v[0], w1 = v[1], w2 = v[2], w3 = v[3];
-        const int col = col0 + 4 * g;
-        const bool more = mask != 0;
-        if (more) {
-            g = __ffs(mask) - 1;
-            mask &= mask - 1;
-            tc_ld4(taddr + 4 * g, v);
-        }
-        const uint32_t w[4] = {w0, w1, w2, w3};
+    while (mask) {
+        uint32_t v[EVB][4]; int g[EVB];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            if (__uint_as_float(w[e]) < S.thr) {
-                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pptr), "r"(w[e]), "r"(col + e) : "memory");
-                S.pptr += PEND_STRIDE;
+        for (int j = 0; j < EVB; ++j) {
+            g[j] = -1;
+            if (mask) {                                                          // warp-uniform
+                g[j] = __ffs(mask) - 1;
+                mask &= mask - 1;
+                tc_ld4(taddr + 4 * g[j], v[j]);
             }
         }
-        if (__any_sync(0xffffffffu, S.pptr > S.pbase + (PEND_CAP - 4) * PEND_STRIDE)) epi_drain(S);
-        if (!more) break;
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < EVB; ++j) {
+            if (g[j] >= 0) {
+                // the loaded registers become valid at the wait above: tie them to this point
+                asm volatile("" : "+r"(v[j][0]), "+r"(v[j][1]), "+r"(v[j][2]), "+r"(v[j][3]) :: "memory");
+                const int col = col0 + 4 * g[j];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (__uint_as_float(v[j][e]) < S.thr) {
+                        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pptr), "r"(v[j][e]), "r"(col + e) : "memory");
+                        S.pptr += PEND_STRIDE;
+                    }
+                }
+                if (__any_sync(0xffffffffu, S.pptr > S.pbase + (PEND_CAP - 4) * PEND_STRIDE)) epi_drain(S);
+            }
+        }
     }
 }
 
+// MMA issuer of ONE UMMA M block (two issuer warps per CTA, m = 0 and m = 1: the scalar work between two tcgen05.mma --
+// barrier waits, descriptor arithmetic, commits -- costs a single warp more time per tile than the tensor pipe needs for
+// the tile's MMAs, so it is split).  The whole warp runs the loop (uniform control flow), one elected lane issues.
+// Accumulators are handed over per M block: t_full / t_empty index = accumulator buffer * 2 + m; a B slab is released
+// when BOTH issuers' MMAs on it have retired (b_empty counts 2 commits), likewise the resident A block (a_empty).
 template <int MODE>   // 0 = bf16 (kind::f16), 1 = tf32
-__device__ __forceinline__ void mma_issue_loop(long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_addr, uint32_t aa_addr,
+__device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_addr, uint32_t aa_addr,
                                                uint32_t b_addr, uint32_t tmem_base, uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full,
                                                uint64_t* b_empty, uint64_t* t_full, uint64_t* t_empty)
 {
     constexpr uint32_t idesc = umma_idesc(MODE == 1 ? 2u : 1u);
     constexpr uint64_t hi128 = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);     // see umma_desc()
     constexpr uint64_t hi32 = ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);       // see umma_desc_sw32()
-    int stage = 0; uint32_t sphase = 0; int a_cnt = 0; unsigned it = 0;
+    const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
+    const uint64_t ad0 = hi128 | (uint64_t)((a_addr + m * (UM * SLAB_BYTES)) >> 4);
+    int stage = 0; uint32_t sphase = 0, a_phase = 0; unsigned it = 0;
     int tile = (int)(u0 - (u0 / NT) * NT);                                       // tile index inside the current query block
     bool new_qb = true;
-    // one K slab (+ the aug step with slab 0) of one UMMA M block
-    auto issue = [&](int s, int m, uint32_t sb, uint32_t d) {
-        const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
-        if (s == 0) {                                                            // aug K step first: D = |t|^2 (overwrites)
-            const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
-            const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
-            if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
-        }
-        const uint64_t ad = hi128 | (uint64_t)((a_addr + s * A_SLAB + m * (UM * SLAB_BYTES)) >> 4);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {                                            // 4 x 32 bytes of K per slab row
-            if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
-        }
-    };
-    // Accumulator buffers are handed over per UMMA M block: t_full / t_empty index = buffer * 2 + m.  When a whole tile's
-    // slabs fit the ring (bf16 mode) the M blocks are issued one after the other, so the epilogue warps of block 0 start
-    // while block 1 is still being multiplied and the two groups of epilogue warps never wait for each other.
-    const bool m_major = n_slabs <= n_stages - 1;
+#ifdef MPL_TC_TRACE
+    long long w_te = 0, w_bf = 0, w_af = 0, w_is = 0, t_start = clock64(), tq;
+#define MPL_TWAIT(acc, stmt) do { tq = clock64(); stmt; acc += clock64() - tq; } while (0)
+#else
+#define MPL_TWAIT(acc, stmt) stmt
+#endif
     for (long long u = u0; u < u1; ++u, ++it) {
-        if (new_qb) { mbar_wait(a_full, (uint32_t)(a_cnt & 1)); ++a_cnt; new_qb = false; }
+        if (new_qb) { MPL_TWAIT(w_af, mbar_wait(a_full, a_phase)); a_phase ^= 1; new_qb = false; }
         const bool last_of_qb = (++tile == NT);
         if (last_of_qb) { tile = 0; new_qb = true; }
-        const uint32_t b = it & 1, eparity = ((it >> 1) & 1) ^ 1;
-        if (m_major) {
-#pragma unroll
-            for (int m = 0; m < 2; ++m) {
-                mbar_wait(&t_empty[b * 2 + m], eparity);                         // epilogue drained this accumulator block
-                tc_fence_after();
-                int st = stage; uint32_t ph = sphase;
-                for (int s = 0; s < n_slabs; ++s) {
-                    if (m == 0) { mbar_wait(&b_full[st], ph); tc_fence_after(); }
-                    if (elect_one()) {
-                        issue(s, m, b_addr + st * STAGE_BYTES, tmem_base + b * 256 + m * 128);
-                        if (m == 1) tc_commit(&b_empty[st]);                     // slab free once these MMAs retire
-                        if (s == n_slabs - 1) {
-                            tc_commit(&t_full[b * 2 + m]);
-                            if (m == 1 && u + 1 < u1 && last_of_qb) tc_commit(a_empty);   // only when the producer will wait for it
-                        }
-                    }
-                    __syncwarp();
-                    if (++st == n_stages) { st = 0; ph ^= 1; }
-                }
-                if (m == 1) { stage = st; sphase = ph; }
-            }
-        } else {
-            mbar_wait(&t_empty[b * 2], eparity);
-            mbar_wait(&t_empty[b * 2 + 1], eparity);
+        const uint32_t b = it & 1;
+        const uint32_t d = tmem_base + b * 256 + m * 128;
+        MPL_TWAIT(w_te, mbar_wait(&t_empty[b * 2 + m], ((it >> 1) & 1) ^ 1));    // epilogue drained this accumulator block
+        tc_fence_after();
+        for (int s = 0; s < n_slabs; ++s) {
+            MPL_TWAIT(w_bf, mbar_wait(&b_full[stage], sphase));
             tc_fence_after();
-            for (int s = 0; s < n_slabs; ++s) {
-                mbar_wait(&b_full[stage], sphase);
-                tc_fence_after();
-                if (elect_one()) {
-                    const uint32_t sb = b_addr + stage * STAGE_BYTES;
-                    issue(s, 0, sb, tmem_base + b * 256);
-                    issue(s, 1, sb, tmem_base + b * 256 + 128);
-                    tc_commit(&b_empty[stage]);
-                    if (s == n_slabs - 1) {
-                        tc_commit(&t_full[b * 2]);
-                        tc_commit(&t_full[b * 2 + 1]);
-                        if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);
-                    }
+#ifdef MPL_TC_TRACE
+            tq = clock64();
+#endif
+            if (elect_one()) {
+                const uint32_t sb = b_addr + stage * STAGE_BYTES;
+                const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
+                const uint64_t ad = ad0 + (uint64_t)(s * (A_SLAB >> 4));
+                if (s == 0) {                                                    // aug K step first: D = |t|^2 (overwrites)
+                    const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
+                    if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
                 }
-                __syncwarp();
-                if (++stage == n_stages) { stage = 0; sphase ^= 1; }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {                                    // 4 x 32 bytes of K per slab row
+                    if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                }
+                tc_commit(&b_empty[stage]);                                      // slab free once both issuers' MMAs retire
+                if (s == n_slabs - 1) {
+                    tc_commit(&t_full[b * 2 + m]);
+                    if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);            // only when the producer will wait for it
+                }
             }
+            __syncwarp();
+#ifdef MPL_TC_TRACE
+            w_is += clock64() - tq;
+#endif
+            if (++stage == n_stages) { stage = 0; sphase ^= 1; }
         }
     }
+#ifdef MPL_TC_TRACE
+    if (blockIdx.x == 3 && (threadIdx.x & 31) == 0)
+        printf("mma warp m=%d: total %lld cycles for %lld tiles; waits: t_empty %lld  b_full %lld  a_full %lld; issue sections %lld\n",
+               m, clock64() - t_start, u1 - u0, w_te, w_bf, w_af, w_is);
+#endif
+#undef MPL_TWAIT
 }
 
 // Epilogue warps 4..19: thread = one query row of UMMA block m, one half (64 columns) of the tile.
@@ -536,15 +538,16 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         S.L.store(p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2);
         S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
     };
+    const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + m * 128 + hf * 64;
     for (long long u = u0; u < u1; ++u, ++it) {
         const uint32_t b = it & 1;
+        const uint32_t taddr = tbase + b * 256;
         mbar_wait(&t_full[b * 2 + m], (it >> 1) & 1);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * 256 + m * 128 + hf * 64;
-        const int col0 = tile * BN + hf * 64;
         uint32_t ra[32], rb[32];
         tc_ld32(taddr, ra);
         tc_ld32(taddr + 32, rb);
+        const int col0 = tile * BN + hf * 64;
         // The other column half keeps its own list for the same query: filter with the minimum of both lists' last
         // entries.  General mode: any threshold >= the final tau keeps the certificate valid.  Exact mode: an element
         // may only be dropped if two others are STRICTLY better or equal with a lower train index; the partner's
@@ -605,8 +608,8 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
         asm volatile("prefetch.tensormap [%0];" ::"l"(mapBa) : "memory");
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(a_full, 1); mbar_init(a_empty, 1);
-        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        mbar_init(a_full, 1); mbar_init(a_empty, 2);                 // *_empty: one commit per MMA issuer warp
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 2); }
         for (int b = 0; b < 4; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], EPI_WARPS / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -648,11 +651,12 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
                 if (++stage == n_stages) { stage = 0; sphase ^= 1; }
             }
         }
-    } else if (warp == 1) {
-        // ===== MMA issuer: uniform loop, one elected lane issues =====
-        if (tf32) mma_issue_loop<1>(u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
+    } else if (warp == 1 || warp == 3) {
+        // ===== MMA issuers: warp 1 -> UMMA M block 0, warp 3 -> M block 1 =====
+        const int m = warp >> 1;
+        if (tf32) mma_issue_loop<1>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
                                     a_full, a_empty, b_full, b_empty, t_full, t_empty);
-        else      mma_issue_loop<0>(u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
+        else      mma_issue_loop<0>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
                                     a_full, a_empty, b_full, b_empty, t_full, t_empty);
     } else if (warp >= 4) {
         // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile =====

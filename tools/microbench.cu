@@ -115,6 +115,63 @@ __global__ void k_ldtm(uint32_t* out, int iters)
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(slot), "r"(512) : "memory");
 }
 
+// tcgen05.mma issue rate: one thread issues `n` back-to-back MMAs (kind::f16, bf16 operands, M = 128, K = 16) on zeroed
+// shared-memory operands (K-major, 128-byte swizzle), `chains` accumulators used round-robin, then one commit.
+__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0)
+{
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar, bar2;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (16384 + 32768) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0;
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bar)) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1000000;" ::"r"((uint32_t)__cvta_generic_to_shared(&bar2)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = slot;
+    if (warp == 0) {                                   // whole warp runs the loop (uniform), one elected lane issues
+        const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem), b = a + 16384;
+        const uint64_t hi = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        const uint64_t ad = hi | (uint64_t)((a >> 4) & 0x3FFF), bd = hi | (uint64_t)((b >> 4) & 0x3FFF);
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t d1 = tmem + (chains > 1 ? (uint32_t)N : 0u);
+        const long long t0 = clock64();
+        for (int i = 0; i < n; i += 4) {
+            uint32_t pred;
+            asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+            if (pred) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                                 ::"r"((k & 1) ? d1 : tmem), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(1u) : "memory");
+                if (commit_every && ((i >> 2) % commit_every) == 0)
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(&bar2)) : "memory");
+            }
+            __syncwarp();
+        }
+        if (threadIdx.x == 0) {
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(&bar)) : "memory");
+            asm volatile("{\n\t.reg .pred p;\n\tW: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t@p bra D;\n\tbra W;\n\tD:\n\t}"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(&bar)) : "memory");
+            cycles[blockIdx.x] = clock64() - t0;
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+}
+
 template <typename F>
 static float time_ms(F launch)
 {
@@ -165,6 +222,26 @@ int main()
         // bytes per SM per clock at the max clock (32 lanes x 32 columns x 4 B per warp-load)
         const double bytes = (double)warps * iters * 4 * 4096;
         printf(", \"ldtm_x32_%dwarps_B_per_clk_per_sm\": %.1f", warps, bytes / (ms * 1e-3 * clk_khz * 1e3));
+    }
+    cudaFuncSetAttribute(k_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    for (int N : {64, 128, 256}) {
+        for (int chains : {1, 2}) {
+            if (N * chains > 512) continue;
+            const int n = 2000;
+            long long* cyc = (long long*)buf;
+            k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, N, chains);
+            if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
+            long long h[148]; cudaMemcpy(h, cyc, sizeof(long long) * (sms < 148 ? sms : 148), cudaMemcpyDeviceToHost);
+            printf(", \"umma_m128_n%d_k16_bf16_chains%d_cycles_per_mma\": %.1f", N, chains, (double)h[0] / n);
+        }
+    }
+    for (int ce : {1, 2}) {
+        const int n = 2000;
+        long long* cyc = (long long*)buf;
+        k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, 128, 2, ce);
+        if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
+        long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
+        printf(", \"umma_m128_n128_commit_every_%d_mma_cycles_per_mma\": %.1f", 4 * ce, (double)h[0] / n);
     }
     printf("}\n");
     return 0;
