@@ -48,6 +48,27 @@ def peaks():
     return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, sm_max_mhz=1965.0, _src="fallback")
 
 
+def pipe_peaks():
+    """Per-pipe issue rates measured on a B200 of this pool with tools/microbench.cu (profiles/r1_microbench.json):
+    roofline denominators where MEASURED_PEAKS.json has none (integer POPC, fp64)."""
+    p = os.path.join(ROOT, "profiles", "r1_microbench.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        d["_src"] = "measured: tools/microbench.cu -> profiles/r1_microbench.json"
+        return d
+    # CUDA programming guide throughput table x 148 SMs x 1.965 GHz
+    return dict(popc_gops=4650.0, dfma_ginst=18600.0, ddiv_rn_gops=1300.0, _src="fallback: programming-guide rates")
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
+    bench command (profiles/r1_ncu_traffic.json); None when there is no capture for the kernel."""
+    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(kernel, {}).get("dram_bytes_per_launch")
+    return None
+
+
 # ------------------------------------------------------------------------------------------------
 # clocks during the timed region (NVML; same fields as the profiling guide's nvidia-smi line)
 # ------------------------------------------------------------------------------------------------
@@ -296,16 +317,18 @@ def bench_hamming(g, steps, warmup):
     step_ms = float(np.mean(ms))
     kern_ms = k_ms / max(k_n, 1)
     pk = peaks()
+    pp = pipe_peaks()
     bytes_alg = (nq + nt) * nb + nq * 16
     popc = pairs * (nb // 4)
     return dict(
         workload="C1: ORB 8192x8192x32B Hamming k=2 + ratio (LINEAR)", value=pairs / (step_ms * 1e-3), unit="pairs/s", ms_per_step=step_ms,
         dtype="u32 popc",
         roofline=dict(bound="hbm", achieved=bytes_alg / (kern_ms * 1e-3) / 1e9, peak=pk["hbm_gbs"], unit="GB/s",
-                      frac=bytes_alg / (kern_ms * 1e-3) / 1e9 / pk["hbm_gbs"], traffic=None, peak_src=pk["_src"],
+                      frac=bytes_alg / (kern_ms * 1e-3) / 1e9 / pk["hbm_gbs"], traffic=ncu_traffic("hamming_top2_kernel"), peak_src=pk["_src"],
                       kernel="hamming_top2_kernel", kernel_ms=kern_ms,
                       note="compute-bound on the integer pipe, not HBM (algorithmic bytes are 0.65 MB): see alu"),
-        alu=dict(achieved_gpopc_s=popc / (kern_ms * 1e-3) / 1e9, popc_per_pair=nb // 4),
+        alu=dict(bound="int popc issue", achieved_gpopc_s=popc / (kern_ms * 1e-3) / 1e9, peak_gpopc_s=pp["popc_gops"],
+                 frac=popc / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], popc_per_pair=nb // 4, peak_src=pp["_src"]),
         e2e=dict(value=pairs / float(np.median(ts)), unit="pairs/s", h2d_bytes_per_step=int(hq.nbytes + ht.nbytes), d2h_bytes_per_step=int(nq * 16),
                  matches=int(len(mt))))
 
@@ -370,7 +393,15 @@ def bench_ransac(g, steps, warmup):
     evals = float(n_models) * n
     step_ms = float(np.mean(ms))
     score_ms = sc_ms / max(sc_n, 1)
+    # fp64 issue bound of one Sampson evaluation in the reference's operation order (no FMA contraction): 16 DMUL +
+    # 14 DADD + one IEEE divide; the divide is costed at the measured DFMA-rate / DDIV-rate ratio
+    pp = pipe_peaks()
+    dp_slots = 30.0 + pp["dfma_ginst"] / pp["ddiv_rn_gops"]
+    evals_peak = pp["dfma_ginst"] * 1e9 / dp_slots
     return dict(
+        roofline=dict(bound="fp64 issue", achieved=evals / (score_ms * 1e-3), peak=evals_peak, unit="Sampson evaluations/s",
+                      frac=evals / (score_ms * 1e-3) / evals_peak, dp_issue_slots_per_eval=dp_slots, traffic=ncu_traffic("sampson_score_kernel"),
+                      kernel="sampson_score_kernel", kernel_ms=score_ms, peak_src=pp["_src"]),
         workload="C3: RANSAC 5pt, 10000 correspondences x 100000 pre-drawn samples (%d real models)" % n_models,
         value=evals / (step_ms * 1e-3), unit="model*correspondence Sampson evaluations/s", ms_per_step=step_ms, dtype="f64",
         hypotheses_per_ms=h / step_ms, models_per_ms=n_models / step_ms,
@@ -498,7 +529,8 @@ def main():
             "data": "synthetic",
             "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else "train rows sharded over %d ranks, NCCL all-gather of top-2 keys + merge" % world),
             "clocks": r["clocks"],
-            "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=None, kernel=kname, kernel_ms=k_ms,
+            "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=ncu_traffic("l2_tc_rank_kernel"),
+                             kernel=kname, kernel_ms=k_ms,
                              peak_src="%s: %s" % (pk["_src"], peak_name), flops_per_launch=flops,
                              step_share={k: (v[0] / max(v[1], 1)) for k, v in kern.items() if v[1]}),
             "e2e": dict(value=float(r["nq"]) * r["nt"] / e2e_s, unit="pairs/s", h2d_bytes_per_step=int(bi), d2h_bytes_per_step=int(bo), ms=e2e_s * 1e3,
