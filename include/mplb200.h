@@ -148,6 +148,15 @@ int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samp
                   double* models, int32_t* n_models, int32_t* counts, double* errsums);
 int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const char* method, double threshold,
                                int refine, double* E_out, int* n_E, uint8_t* mask);
+/* mpl_get_pose_triang_pts_api mirrors poselib::getPoseTriangPts(E, p1, p2, R, t, Q, mask, dist, translatE)
+ *   (MP/poselib/source/pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338, decomposeEssentialMat :340-352):
+ *   E 3x3 row-major, p1/p2 n x 2 doubles (camera-normalised).  mask (may be NULL): n bytes; mask_given != 0 -> its
+ *   content restricts the points that count (the RANSAC inlier mask) and is AND-ed in place, mask_given == 0 -> treated
+ *   as all ones and overwritten.  Outputs R[9], t[3], Q[n*3] (triangulated points of the chosen combination, all n).
+ *   Returns the number of valid 3-D points (>= 0), -1 if R, t or Q is missing (the reference's code), or MPL_ERR_*.
+ *   The per-point triangulation / cheirality / distance tests of all four (R, +-t) combinations run on the device. */
+int mpl_get_pose_triang_pts_api(const double* E, const double* p1, const double* p2, int n, uint8_t* mask, int mask_given,
+                                double dist, int translatE, double* R, double* t, double* Q);
 /* device-pointer stages (enqueue only): corr = n x 32-byte records (x1,y1,x2,y2); models h x 90 doubles;
  * offsets h+1 int32 (offsets[h] = number of dense models); dense up to 10h x 9 doubles. */
 int mpl_ransac_pack_corr_dev(const void* d_p1, const void* d_p2, int n, void* d_corr, void* stream);
