@@ -24,6 +24,7 @@
 #include <cstdlib>
 #include <iostream>
 #include <string>
+#include <cstring>
 #include <vector>
 
 #include "mplb200.h"
@@ -95,6 +96,41 @@ inline bool estimateEssentialMat(cv::OutputArray E, cv::InputArray p1, cv::Input
     cv::Mat(3 * (npoints == 5 ? n_E : 1), 3, CV_64F, e_buf).copyTo(E);
     if (mask.needed()) cv::Mat(1, npoints, CV_8U, m.data()).copyTo(mask);        // :130-135
     return rc == 1;
+}
+
+// poselib::getPoseTriangPts (pose_estim.h:192-200; pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338)
+inline int getPoseTriangPts(cv::InputArray E, cv::InputArray p1, cv::InputArray p2, cv::OutputArray R, cv::OutputArray t, cv::OutputArray Q,
+                            cv::InputOutputArray mask = cv::noArray(), const double dist = 50.0, bool translatE = false)
+{
+    if (!R.needed() || !t.needed() || !Q.needed()) return -1;                    // :925-926
+    cv::Mat Em, points1, points2;
+    E.getMat().convertTo(Em, CV_64F);
+    p1.getMat().copyTo(points1);                                                 // five-point.cpp:154-156 deep copies
+    p2.getMat().copyTo(points2);
+    const int npoints = points1.checkVector(2);
+    CV_Assert(npoints >= 0 && points2.checkVector(2) == npoints && points1.type() == points2.type());   // :157-159
+    points1.convertTo(points1, CV_64F);
+    points2.convertTo(points2, CV_64F);
+    points1 = points1.reshape(1, npoints);
+    points2 = points2.reshape(1, npoints);
+    Em = Em.clone();
+    bool given = false;
+    std::vector<uchar> m((size_t)npoints, 1);
+    if (mask.needed()) {
+        cv::Mat mm = mask.getMat();
+        if (!mm.empty()) { CV_Assert((int)mm.total() == npoints && mm.type() == CV_8U); std::memcpy(m.data(), mm.clone().data, (size_t)npoints); given = true; }
+    }
+    double r_buf[9], t_buf[3];
+    std::vector<double> q((size_t)npoints * 3 + 3);
+    const int rc = mpl_get_pose_triang_pts_api(Em.ptr<double>(), points1.ptr<double>(), points2.ptr<double>(), npoints,
+                                               mask.needed() ? m.data() : nullptr, given ? 1 : 0, dist, translatE ? 1 : 0, r_buf, t_buf, q.data());
+    if (rc == MPL_ERR_ASSERT) CV_Error(cv::Error::StsAssert, mpl_last_error());
+    if (rc < -1) CV_Error(cv::Error::StsError, mpl_last_error());
+    cv::Mat(3, 3, CV_64F, r_buf).copyTo(R);                                      // :930-940
+    cv::Mat(3, 1, CV_64F, t_buf).copyTo(t);
+    cv::Mat(npoints, 3, CV_64F, q.data()).copyTo(Q);
+    if (mask.needed()) cv::Mat(1, npoints, CV_8U, m.data()).copyTo(mask);        // five-point.cpp:284-301
+    return rc;
 }
 
 }  // namespace poselib

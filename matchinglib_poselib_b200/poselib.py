@@ -69,6 +69,31 @@ def estimateEssentialMat(p1, p2, method="ARRSAC", threshold=1.6, refine=True, wa
     return bool(rc), E[0].reshape(3, 3), (mask.reshape(1, -1) if want_mask else None)
 
 
+def getPoseTriangPts(E, p1, p2, mask=None, dist=50.0, translatE=False):
+    """poselib::getPoseTriangPts (pose_estim.h:192-200, pose_estim.cpp:913-946 -> recoverPose, five-point.cpp:150-338).
+    Returns (n_valid, R 3x3, t 3x1, Q n x 3, mask 1 x n uint8).  `mask` (optional, 1 x n or n) is the inlier mask
+    of estimateEssentialMat: only its non-zero entries count and the returned mask is its AND with the cheirality /
+    distance tests; without it every correspondence counts.  The per-point work runs on the GPU."""
+    lib = _lib.load()
+    E = np.ascontiguousarray(np.asarray(E, np.float64).reshape(3, 3))
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if p2.shape[0] != n:
+        raise AssertionError("CV_Assert(npoints >= 0 && points2.checkVector(2) == npoints)")
+    given = mask is not None
+    m = np.ascontiguousarray(np.asarray(mask, np.uint8).reshape(-1)).copy() if given else np.zeros(n, np.uint8)
+    if m.shape[0] != n:
+        raise AssertionError("mask must hold one byte per correspondence")
+    R = np.zeros((3, 3)); t = np.zeros((3, 1)); Q = np.zeros((max(n, 1), 3))
+    rc = lib.mpl_get_pose_triang_pts_api(_lib.ptr(E), _lib.ptr(p1), _lib.ptr(p2), n, _lib.ptr(m), int(given), float(dist),
+                                         int(bool(translatE)), _lib.ptr(R), _lib.ptr(t), _lib.ptr(Q))
+    if rc == -103:
+        raise AssertionError(_lib.last_error())
+    if rc < 0:
+        raise _lib.MplError("getPoseTriangPts failed (%d): %s" % (rc, _lib.last_error()))
+    return rc, R, t, Q[:n], m.reshape(1, -1)
+
+
 def _smoke():
     """One small RANSAC run on cuda:0, checked against the oracle (called by __graft_entry__.smoke)."""
     import os

@@ -12,7 +12,7 @@ typedef unsigned char uchar;
 #define CV_Assert(expr) do { if (!(expr)) throw std::runtime_error(#expr); } while (0)
 #define CV_Error(code, msg) throw std::runtime_error(msg)
 namespace cv {
-namespace Error { enum { StsAssert = -215 }; }
+namespace Error { enum { StsAssert = -215, StsError = -2 }; }
 struct Size { int width, height; };
 struct Point2f { float x, y; };
 struct KeyPoint { Point2f pt; float size, angle, response; int octave, class_id; };
@@ -28,10 +28,14 @@ public:
     void convertTo(Mat& dst, int type) const; Mat reshape(int cn, int rows) const;
     template <class T> T* ptr(int r = 0);
     void copyTo(const _OutputArray& dst) const;
+    void copyTo(Mat& dst) const;
+    bool empty() const; size_t total() const;
 };
 class _InputArray { public: Mat getMat() const; };
 class _OutputArray : public _InputArray { public: bool needed() const; };
+class _InputOutputArray : public _OutputArray {};
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
-const _OutputArray& noArray();
+typedef const _InputOutputArray& InputOutputArray;
+const _InputOutputArray& noArray();
 }

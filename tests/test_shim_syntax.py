@@ -11,7 +11,9 @@ def test_shim_compiles(tmp_path):
     src.write_text('#include "matchinglib_poselib_b200.hpp"\n'
                    'int f(const std::vector<cv::KeyPoint>& k, const cv::Mat& d, std::vector<cv::DMatch>& m) {\n'
                    '  return matchinglib::getMatches(k, k, d, d, cv::Size(), m, "LINEAR"); }\n'
-                   'bool g(cv::OutputArray E, cv::InputArray p) { return poselib::estimateEssentialMat(E, p, p, "RANSAC", 0.001, true); }\n')
+                   'bool g(cv::OutputArray E, cv::InputArray p) { return poselib::estimateEssentialMat(E, p, p, "RANSAC", 0.001, true); }\n'
+                   'int h(cv::InputArray E, cv::InputArray p, cv::OutputArray R, cv::OutputArray t, cv::OutputArray Q, cv::InputOutputArray m) {\n'
+                   '  return poselib::getPoseTriangPts(E, p, p, R, t, Q, m, 130.0); }\n')
     r = subprocess.run(["g++", "-std=c++14", "-fsyntax-only", "-Wall", "-I", os.path.join(ROOT, "include"),
                         "-I", os.path.join(ROOT, "tests", "cv_mock"), str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
