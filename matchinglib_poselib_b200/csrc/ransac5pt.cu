@@ -80,36 +80,32 @@ __global__ void fivept_from_basis_kernel(const double* __restrict__ basis /* [4]
     n_models[0] = fivept::solve_from_basis(ee, models);
 }
 
-// single-block exclusive scan of n_models -> offsets[h+1]
+// single-block exclusive scan of n_models -> offsets[h+1]: each thread owns a contiguous chunk (local sum, one block
+// scan of the 1024 partial sums, then the chunk's running prefix) -- two barriers in total instead of four per 1024
+// elements
 __global__ void __launch_bounds__(1024) scan_counts_kernel(const int32_t* __restrict__ counts, int h, int32_t* __restrict__ offsets)
 {
     __shared__ int warp_sums[32];
-    __shared__ int carry;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) carry = 0;
+    const int per = (h + 1023) / 1024;
+    const int start = min(h, tid * per), end = min(h, start + per);
+    int sum = 0;
+    for (int i = start; i < end; ++i) sum += counts[i];
+    int x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_sums[wid] = x;
     __syncthreads();
-    for (int base = 0; base < h; base += 1024) {
-        const int i = base + tid;
-        const int v = i < h ? counts[i] : 0;
-        int x = v;
+    if (wid == 0) {
+        int w = warp_sums[lane];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-        if (lane == 31) warp_sums[wid] = x;
-        __syncthreads();
-        if (wid == 0) {
-            int w = warp_sums[lane];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
-            warp_sums[lane] = w;
-        }
-        __syncthreads();
-        const int prefix = carry + (wid ? warp_sums[wid - 1] : 0) + x - v;
-        if (i < h) offsets[i] = prefix;
-        __syncthreads();
-        if (tid == 1023) carry = prefix + v;
-        __syncthreads();
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+        warp_sums[lane] = w;
     }
-    if (tid == 0) offsets[h] = carry;
+    __syncthreads();
+    int running = (wid ? warp_sums[wid - 1] : 0) + x - sum;
+    for (int i = start; i < end; ++i) { offsets[i] = running; running += counts[i]; }
+    if (tid == 1023) offsets[h] = running;
 }
 
 __global__ void gather_models_kernel(const double* __restrict__ models, const int32_t* __restrict__ n_models,
