@@ -157,6 +157,19 @@ int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const 
  *   The per-point triangulation / cheirality / distance tests of all four (R, +-t) combinations run on the device. */
 int mpl_get_pose_triang_pts_api(const double* E, const double* p1, const double* p2, int n, uint8_t* mask, int mask_given,
                                 double dist, int translatE, double* R, double* t, double* Q);
+/* mpl_match_pose_pair: both halves of the hot path for ONE image pair with the matches staying on the device in
+ *   between (the reference driver's sequence tests/poselib-test/main.cpp:1522-1599 with host vectors
+ *   between the steps): binary descriptors (nbytes per row) -> brute-force k=2 (matcher_name "LINEAR" or
+ *   "BRUTEFORCENMS") -> ratio test + cv::DMatch list in ascending queryIdx (matchers.cpp:601-625) -> correspondences
+ *   (pts1[queryIdx], pts2[trainIdx]; pts are n x 2 camera-normalised doubles) -> h minimal samples drawn on the device
+ *   with getSubset/checkSubset's rules (modelest.cpp:567-650; counter-based generator from `seed`) -> 5-point RANSAC as
+ *   in mpl_ransac5pt with max_iters = h.  Outputs: matches[<= n1] / *n_matches, samples_out[h x 5] (optional) /
+ *   *n_samples (samples usable before getSubset failed), E[9], mask[*n_matches] over the match list, *n_inl, *iters_run. */
+int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, const uint8_t* desc2, int n2, size_t step2, int nbytes,
+                        const double* pts1, const double* pts2, const char* matcher_name, int ratio_test,
+                        double th, int h, double conf, int refine, unsigned long long seed,
+                        mpl_dmatch* matches, int* n_matches, int32_t* samples_out, int* n_samples,
+                        double* E, uint8_t* mask, int* n_inl, int* iters_run);
 /* device-pointer stages (enqueue only): corr = n x 32-byte records (x1,y1,x2,y2); models h x 90 doubles;
  * offsets h+1 int32 (offsets[h] = number of dense models); dense up to 10h x 9 doubles. */
 int mpl_ransac_pack_corr_dev(const void* d_p1, const void* d_p2, int n, void* d_corr, void* stream);

@@ -54,6 +54,9 @@ SIGNATURES = {
     "mpl_ransac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_double, c_int,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_estimate_essential_api": (c_int, [c_void_p, c_void_p, c_int, c_char_p, c_double, c_int, c_void_p, c_void_p, c_void_p]),
+    "mpl_match_pose_pair": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_void_p, c_void_p, c_char_p, c_int,
+                                    c_double, c_int, c_double, c_int, ctypes.c_ulonglong, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_get_pose_triang_pts_api": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p]),
     "mpl_ransac_pack_corr_dev": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "mpl_ransac_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

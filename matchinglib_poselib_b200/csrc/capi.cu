@@ -223,6 +223,45 @@ static int upload_rows(MplBuf& buf, const void* h, int rows, size_t row_bytes, s
     return MPL_OK;
 }
 
+// Upload both descriptor sets, scan, and leave the merged per-query top-2 keys on the device (context buffer KEYS).
+// Caller holds the context mutex; nq, nt > 0.
+int mpl_hamming_keys_locked(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step, int nbytes,
+                            int ignore_tail_bytes, mpl_key64** d_keys)
+{
+    int rc;
+    cudaStream_t st = g_ctx.stream;
+    const int used = nbytes - ignore_tail_bytes;
+    const int w16 = round_w16(used);
+    const size_t rowb = (size_t)w16 * 16;
+    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T], &braw = g_ctx.bufs[MPL_BUF_RAW];
+    // queries and train rows -> packed device layout
+    const uint8_t* src[2] = {q, t}; const int n[2] = {nq, nt}; const size_t stp[2] = {q_step, t_step};
+    MplBuf* dst[2] = {&bq, &bt};
+    for (int s = 0; s < 2; ++s) {
+        if ((size_t)used == rowb) {                       // already in device layout: strided copy only
+            rc = upload_rows(*dst[s], src[s], n[s], rowb, stp[s], rowb, st);
+            if (rc) return rc;
+        } else {
+            rc = upload_rows(braw, src[s], n[s], (size_t)nbytes, stp[s], (size_t)nbytes, st);
+            if (rc) return rc;
+            rc = dst[s]->ensure((size_t)n[s] * rowb);
+            if (rc) return rc;
+            rc = mpl_launch_pack_rows_u8((const uint8_t*)braw.ptr, n[s], (size_t)nbytes, used, (uint8_t*)dst[s]->ptr, w16, st);
+            if (rc) return rc;
+        }
+    }
+    const int splits = mpl_hamming_pick_splits(nq, nt, w16, g_ctx.sm_count);
+    MplBuf &bpart = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS];
+    if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
+    if ((rc = bpart.ensure((size_t)splits * nq * 2 * sizeof(mpl_key64)))) return rc;
+    rc = mpl_launch_hamming_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, splits, 1, 0, (mpl_key64*)bpart.ptr, st);
+    if (rc) return rc;
+    rc = mpl_launch_merge_top2((const mpl_key64*)bpart.ptr, splits, nq, 2, nullptr, nullptr, -1, (mpl_key64*)bkeys.ptr, st);
+    if (rc) return rc;
+    *d_keys = (mpl_key64*)bkeys.ptr;
+    return MPL_OK;
+}
+
 extern "C" int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step,
                                 int nbytes, int ignore_tail_bytes, int k, int32_t* idx, int32_t* dist)
 {

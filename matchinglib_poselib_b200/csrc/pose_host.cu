@@ -145,6 +145,48 @@ extern "C" int mpl_ransac_score_dev(const void* d_dense, int m, const void* d_co
 }
 
 // ---- runRANSAC ---------------------------------------------------------------------------------------
+// Scratch layout of one RANSAC run inside the context's buffers (n correspondences, h samples).
+struct RansacBufs {
+    double *d_p1, *d_p2; void* d_corr; int32_t *d_samples, *d_nm, *d_off; double *d_models, *d_dense, *d_errsums;
+    int32_t* d_counts; double* d_misc; uint8_t* d_mask;
+};
+static int ransac_bufs_locked(MplCtx* ctx, int n, int h_use, RansacBufs& R)
+{
+    int rc;
+    MplBuf* B = ctx->bufs;
+    if ((rc = B[MPL_BUF_R0].ensure((size_t)n * 32 + (size_t)n * 32))) return rc;     // p1|p2 staging
+    if ((rc = B[MPL_BUF_R1].ensure((size_t)n * 32))) return rc;                      // corr
+    if ((rc = B[MPL_BUF_R2].ensure((size_t)h_use * 20 + (size_t)(h_use + 1) * 8))) return rc;   // samples | n_models | offsets
+    if ((rc = B[MPL_BUF_R3].ensure((size_t)h_use * 90 * 8))) return rc;              // models [h][10][9]
+    if ((rc = B[MPL_BUF_R4].ensure((size_t)h_use * 90 * 8))) return rc;              // dense models
+    if ((rc = B[MPL_BUF_R5].ensure((size_t)h_use * 10 * 12 + (size_t)n * 8 + 4096 + 148 * 45 * 8))) return rc;   // counts | errsums | mask | misc
+    R.d_p1 = (double*)B[MPL_BUF_R0].ptr; R.d_p2 = R.d_p1 + 2 * (size_t)n;
+    R.d_corr = B[MPL_BUF_R1].ptr;
+    R.d_samples = (int32_t*)B[MPL_BUF_R2].ptr;
+    R.d_nm = R.d_samples + 5 * (size_t)h_use;
+    R.d_off = R.d_nm + h_use;
+    R.d_models = (double*)B[MPL_BUF_R3].ptr;
+    R.d_dense = (double*)B[MPL_BUF_R4].ptr;
+    R.d_errsums = (double*)B[MPL_BUF_R5].ptr;
+    R.d_counts = (int32_t*)(R.d_errsums + (size_t)h_use * 10);
+    R.d_misc = (double*)(((uintptr_t)(R.d_counts + (size_t)h_use * 10) + 63) & ~(uintptr_t)63);  // 64-byte aligned: basis[36] models[90] nm gram[...]
+    R.d_mask = (uint8_t*)(R.d_misc + 36 + 90 + 8 + 148 * 45);
+    return MPL_OK;
+}
+
+// runRANSAC from the solve on: correspondences (R.d_corr) and samples (R.d_samples) are already on the device.
+int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iters, double conf, int refine, double* E, uint8_t* mask,
+                          int* n_inl, int* iters_run, double* models_out, int32_t* n_models_out, int32_t* counts_out, double* errsums_out);
+
+int mpl_ransac_device_inputs_locked(MplCtx* ctx, int n, int h_use, void** d_corr, int32_t** d_samples)
+{
+    RansacBufs R;
+    const int rc = ransac_bufs_locked(ctx, n, h_use, R);
+    if (rc) return rc;
+    *d_corr = R.d_corr; *d_samples = R.d_samples;
+    return MPL_OK;
+}
+
 extern "C" int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double th,
                              int max_iters, double conf, int refine, double* E, uint8_t* mask, int* n_inl, int* iters_run,
                              double* models_out, int32_t* n_models_out, int32_t* counts_out, double* errsums_out)
@@ -168,30 +210,27 @@ extern "C" int mpl_ransac5pt(const double* p1, const double* p2, int n, const in
     const bool want_all = models_out || n_models_out || counts_out || errsums_out;
     const int h_use = want_all ? h : std::min(h, max_iters);   // later samples can never be reached by the loop
     if (h_use == 0) return MPL_OK;
-    MplBuf* B = ctx->bufs;
-    if ((rc = B[MPL_BUF_R0].ensure((size_t)n * 32 + (size_t)n * 32))) return rc;     // p1|p2 staging then corr
-    if ((rc = B[MPL_BUF_R1].ensure((size_t)n * 32))) return rc;
-    if ((rc = B[MPL_BUF_R2].ensure((size_t)h_use * 20 + (size_t)(h_use + 1) * 8))) return rc;   // samples | n_models | offsets
-    if ((rc = B[MPL_BUF_R3].ensure((size_t)h_use * 90 * 8))) return rc;              // models [h][10][9]
-    if ((rc = B[MPL_BUF_R4].ensure((size_t)h_use * 90 * 8))) return rc;              // dense models
-    if ((rc = B[MPL_BUF_R5].ensure((size_t)h_use * 10 * 12 + (size_t)n * 8 + 4096 + 148 * 45 * 8))) return rc;   // counts | errsums | mask | misc
-    double* d_p1 = (double*)B[MPL_BUF_R0].ptr; double* d_p2 = d_p1 + 2 * (size_t)n;
-    void* d_corr = B[MPL_BUF_R1].ptr;
-    int32_t* d_samples = (int32_t*)B[MPL_BUF_R2].ptr;
-    int32_t* d_nm = d_samples + 5 * (size_t)h_use;
-    int32_t* d_off = d_nm + h_use;
-    double* d_models = (double*)B[MPL_BUF_R3].ptr;
-    double* d_dense = (double*)B[MPL_BUF_R4].ptr;
-    double* d_errsums = (double*)B[MPL_BUF_R5].ptr;
-    int32_t* d_counts = (int32_t*)(d_errsums + (size_t)h_use * 10);
-    double* d_misc;
-    d_misc = (double*)(((uintptr_t)(d_counts + (size_t)h_use * 10) + 63) & ~(uintptr_t)63);      // 64-byte aligned: basis[36] models[90] nm gram[...]
-    uint8_t* d_mask = (uint8_t*)(d_misc + 36 + 90 + 8 + 148 * 45);
+    RansacBufs R;
+    if ((rc = ransac_bufs_locked(ctx, n, h_use, R))) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_p1, p1, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_p2, p2, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_samples, samples, (size_t)h_use * 20, cudaMemcpyHostToDevice, st));
+    if ((rc = mpl_launch_pack_corr(R.d_p1, R.d_p2, n, R.d_corr, st))) return rc;
+    return mpl_ransac_run_locked(ctx, n, h_use, th, max_iters, conf, refine, E, mask, n_inl, iters_run, models_out, n_models_out, counts_out, errsums_out);
+}
 
-    MPL_CUDA_CHECK(cudaMemcpyAsync(d_p1, p1, (size_t)n * 16, cudaMemcpyHostToDevice, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(d_p2, p2, (size_t)n * 16, cudaMemcpyHostToDevice, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(d_samples, samples, (size_t)h_use * 20, cudaMemcpyHostToDevice, st));
-    if ((rc = mpl_launch_pack_corr(d_p1, d_p2, n, d_corr, st))) return rc;
+int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iters, double conf, int refine, double* E, uint8_t* mask,
+                          int* n_inl, int* iters_run, double* models_out, int32_t* n_models_out, int32_t* counts_out, double* errsums_out)
+{
+    int rc;
+    cudaStream_t st = ctx->stream;
+    RansacBufs R;
+    if ((rc = ransac_bufs_locked(ctx, n, h_use, R))) return rc;                      // no growth here: same sizes as the caller's
+    void* d_corr = R.d_corr; int32_t* d_samples = R.d_samples; int32_t* d_nm = R.d_nm; int32_t* d_off = R.d_off;
+    double* d_models = R.d_models; double* d_dense = R.d_dense; double* d_errsums = R.d_errsums; int32_t* d_counts = R.d_counts;
+    double* d_misc = R.d_misc; uint8_t* d_mask = R.d_mask;
+    *n_inl = 0;
+    if (iters_run) *iters_run = 0;
     if ((rc = mpl_launch_fivept_solve(d_corr, n, d_samples, h_use, d_models, d_nm, st))) return rc;
     if ((rc = mpl_launch_compact_models(d_models, d_nm, h_use, d_off, d_dense, st))) return rc;
     std::vector<int32_t> off((size_t)h_use + 1);

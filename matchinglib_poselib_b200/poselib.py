@@ -94,6 +94,33 @@ def getPoseTriangPts(E, p1, p2, mask=None, dist=50.0, translatE=False):
     return rc, R, t, Q[:n], m.reshape(1, -1)
 
 
+DMATCH = np.dtype([("queryIdx", "<i4"), ("trainIdx", "<i4"), ("imgIdx", "<i4"), ("distance", "<f4")])
+
+
+def matchAndEstimatePose(desc1, desc2, pts1, pts2, matcher_name="LINEAR", ratioTest=True, threshold=1.6, n_samples=1000,
+                         confidence=0.999, refine=True, seed=1):
+    """Both halves of the hot path for one image pair with the matches kept on the GPU in between
+    (mpl_match_pose_pair; the reference driver's getCorrespondences -> estimateEssentialMat sequence,
+    tests/poselib-test/main.cpp:1522-1599).  desc: uint8 [n, nbytes]; pts: [n, 2] camera-normalised keypoint coordinates.
+    Returns dict(matches (cv::DMatch records), samples [h, 5] drawn on the device, ok, E, mask (over matches), count, iters)."""
+    lib = _lib.load()
+    d1 = np.ascontiguousarray(desc1, np.uint8); d2 = np.ascontiguousarray(desc2, np.uint8)
+    p1, p2 = _pts(pts1), _pts(pts2)
+    if d1.ndim != 2 or d2.ndim != 2 or d1.shape[1] != d2.shape[1] or p1.shape[0] != d1.shape[0] or p2.shape[0] != d2.shape[0]:
+        raise AssertionError("descriptor / keypoint shapes do not agree")
+    n1 = d1.shape[0]
+    matches = np.zeros(max(n1, 1), DMATCH); samples = np.zeros((max(n_samples, 1), 5), np.int32)
+    E = np.zeros(9); mask = np.zeros(max(n1, 1), np.uint8)
+    nm, ns, cnt, iters = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+    _lib.check(lib.mpl_match_pose_pair(_lib.ptr(d1), n1, d1.strides[0], _lib.ptr(d2), d2.shape[0], d2.strides[0], d1.shape[1],
+                                       _lib.ptr(p1), _lib.ptr(p2), matcher_name.encode(), int(bool(ratioTest)), float(threshold),
+                                       int(n_samples), float(confidence), int(bool(refine)), int(seed), _lib.ptr(matches),
+                                       ctypes.byref(nm), _lib.ptr(samples), ctypes.byref(ns), _lib.ptr(E), _lib.ptr(mask),
+                                       ctypes.byref(cnt), ctypes.byref(iters)), "mpl_match_pose_pair")
+    return dict(matches=matches[: nm.value], samples=samples[: ns.value], ok=cnt.value > 0, E=E.reshape(3, 3),
+                mask=mask[: nm.value], count=cnt.value, iters=iters.value)
+
+
 def _smoke():
     """One small RANSAC run on cuda:0, checked against the oracle (called by __graft_entry__.smoke)."""
     import os

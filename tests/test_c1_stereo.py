@@ -69,3 +69,31 @@ def test_gpu_chain_equals_oracle_chain(oracle_chain):
     assert ang < 1e-2 and np.allclose(t, et, atol=1e-3)                           # same conditioning as E above
     ang, dot = _pose_error(R, t)
     assert ang < 1.0 and dot > 0.998
+
+
+@pytest.mark.gpu
+def test_gpu_device_resident_pipeline(oracle_chain):
+    """mpl_match_pose_pair (matches stay on the device between the scan and the scoring): the match list equals the
+    oracle's, the device-drawn samples obey getSubset's rules, and RANSAC on exactly those samples equals the oracle's."""
+    import __graft_entry__ as g
+    g.build()
+    from matchinglib_poselib_b200 import poselib, _lib
+    _lib.check(_lib.load().mpl_init(0), "mpl_init")
+    c = oracle_chain
+    r = poselib.matchAndEstimatePose(G["l_desc"], G["r_desc"], G["l_norm"], G["r_norm"], "LINEAR", True, _threshold(), 1000, 0.999, True, seed=7)
+    assert np.array_equal(r["matches"], c["mt"])
+    s = r["samples"]
+    n = len(c["mt"])
+    assert s.shape == (1000, 5) and s.min() >= 0 and s.max() < n
+    assert all(len(set(row)) == 5 for row in s.tolist())
+    for row in s[:200]:                                           # checkSubset on every prefix, both images
+        for k in range(3, 6):
+            assert datagen_pose._subset_ok(c["p1"][row[:k]]) and datagen_pose._subset_ok(c["p2"][row[:k]])
+    assert len(np.unique(s, axis=0)) > 990                        # independent streams per sample
+    exp = oransac.ransac5pt(c["p1"], c["p2"], s, _threshold(), refine=True)
+    assert r["count"] == exp["count"] and r["iters"] == exp["iters"] and np.array_equal(r["mask"], exp["mask"])
+    assert min(np.linalg.norm(r["E"] - exp["E"]), np.linalg.norm(r["E"] + exp["E"])) < 1e-3
+    r2 = poselib.matchAndEstimatePose(G["l_desc"], G["r_desc"], G["l_norm"], G["r_norm"], "LINEAR", True, _threshold(), 1000, 0.999, True, seed=7)
+    assert np.array_equal(r2["samples"], s) and np.array_equal(r2["mask"], r["mask"])       # deterministic for a given seed
+    r3 = poselib.matchAndEstimatePose(G["l_desc"][:3], G["r_desc"], G["l_norm"][:3], G["r_norm"], "LINEAR", False, _threshold(), 50)
+    assert len(r3["matches"]) == 3 and r3["count"] == 0 and len(r3["samples"]) == 0         # fewer than 5 correspondences
