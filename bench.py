@@ -334,6 +334,37 @@ def bench_hamming(g, steps, warmup):
 
 
 # ------------------------------------------------------------------------------------------------
+# C4 unit: ONE image pair, AKAZE-like 61-byte descriptors 5000 x 5000 + per-pair RANSAC (1000 samples), end to end through
+# mpl_match_pose_pair (host buffers in, matches / E / mask out; matches stay on the device between the two halves)
+# ------------------------------------------------------------------------------------------------
+def bench_pair_pipeline(g, reps):
+    import datagen, datagen_pose
+    from matchinglib_poselib_b200 import poselib
+    n, nb = 5000, 61
+    sc = datagen_pose.make_scene(n, 0.0, seed=1004)
+    rng = np.random.default_rng(1004)
+    t = rng.integers(0, 256, (n, nb), dtype=np.uint8)
+    q = rng.integers(0, 256, (n, nb), dtype=np.uint8)
+    good = rng.random(n) < 0.5                                   # half of the queries are noisy copies of "their" train row
+    flips = np.packbits(rng.random((n, nb * 8)) < 0.08, axis=1)
+    q[good] = t[good] ^ flips[good]
+    th = sc["th"]
+    r = None
+    ts = []
+    for i in range(reps + 2):
+        g.torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r = poselib.matchAndEstimatePose(q, t, sc["p1"], sc["p2"], "LINEAR", True, th, 1000, 0.999, True, seed=5)
+        if i >= 2:
+            ts.append(time.perf_counter() - t0)
+    dt = float(np.median(ts))
+    return dict(workload="C4 unit: one pair, AKAZE-like 61 B x 5000 x 5000 Hamming k=2 + ratio, then RANSAC 5pt (1000 device-drawn samples, refit), "
+                         "mpl_match_pose_pair end to end from host buffers",
+                value=1.0 / dt, unit="image pairs/s", ms_per_pair=dt * 1e3, matches=int(len(r["matches"])), inliers=int(r["count"]),
+                ransac_iterations=int(r["iters"]), h2d_bytes_per_pair=int(q.nbytes + t.nbytes + 2 * n * 16), d2h_bytes_per_pair=int(len(r["matches"]) * 17 + 72))
+
+
+# ------------------------------------------------------------------------------------------------
 # C3: RANSAC 5-point, 10 000 correspondences x 100 000 pre-drawn samples
 # ------------------------------------------------------------------------------------------------
 def bench_ransac(g, steps, warmup):
@@ -544,7 +575,8 @@ def main():
             cb["nn_agreement_with_gpu"] = agree
             out["cpu_baseline"] = cb
         if not args.no_parts and world == 1:
-            out["parts"] = dict(hamming_c1=bench_hamming(g, args.steps, args.warmup), ransac_c3=bench_ransac(g, max(3, args.steps // 4), 3))
+            out["parts"] = dict(hamming_c1=bench_hamming(g, args.steps, args.warmup), ransac_c3=bench_ransac(g, max(3, args.steps // 4), 3),
+                                pair_pipeline_c4=bench_pair_pipeline(g, 10))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

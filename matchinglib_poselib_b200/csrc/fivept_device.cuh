@@ -263,6 +263,66 @@ __device__ inline int durand_kerner10(const double* c, double* re, double* im)
     return n;
 }
 
+// Same iteration for the full degree (the common case), every index a compile-time constant: the ten iterates and the
+// coefficients stay in registers instead of dynamically indexed local memory.  300 sweeps are the reference's: the
+// iteration practically never becomes bit-stationary (measured on the oracle: 99.5 % of the samples use all sweeps).
+__device__ __forceinline__ void durand_kerner_deg10(const double (&c)[11], double (&re)[10], double (&im)[10])
+{
+    {
+        double pr = 1, pi = 0;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) { re[i] = pr; im[i] = pi; const double t = pr - pi; pi = pr + pi; pr = t; }
+    }
+#pragma unroll 1
+    for (int iter = 0; iter < 300; ++iter) {
+        bool changed = false;
+        double max_diff = 0;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+            const double pr = re[i], pi = im[i];
+            double nr = c[10], ni = 0, dr = c[10], di = 0;
+            int same = 1;
+#pragma unroll
+            for (int j = 0; j < 10; ++j) {
+                const double t = __dadd_rn(__dsub_rn(__dmul_rn(nr, pr), __dmul_rn(ni, pi)), c[10 - j - 1]);
+                ni = __dadd_rn(__dmul_rn(nr, pi), __dmul_rn(ni, pr));
+                nr = t;
+                if (j != i) {
+                    const double er = __dsub_rn(pr, re[j]), ei = __dsub_rn(pi, im[j]);
+                    if (er != 0 || ei != 0) {
+                        const double t2 = __dsub_rn(__dmul_rn(dr, er), __dmul_rn(di, ei));
+                        di = __dadd_rn(__dmul_rn(dr, ei), __dmul_rn(di, er));
+                        dr = t2;
+                    } else ++same;
+                }
+            }
+            const double tt = __ddiv_rn(1.0, __dadd_rn(__dmul_rn(dr, dr), __dmul_rn(di, di)));
+            double qr = __dmul_rn(__dadd_rn(__dmul_rn(nr, dr), __dmul_rn(ni, di)), tt);
+            double qi = __dmul_rn(__dadd_rn(__dmul_rn(-nr, di), __dmul_rn(ni, dr)), tt);
+            if (same > 1) {              // coincident iterates (cv::solvePoly's multiple-root branch)
+                const double old_re = qr, old_im = qi;
+                const int sq = (same % 2 == 0) ? same / 2 : same / 2 - 1;
+                for (int k = 0; k < sq; ++k) {
+                    qr = old_re * old_re + old_im * old_im; qr = sqrt(qr); qr += old_re;
+                    qi = qr - old_re; qr /= 2; qr = sqrt(qr); qi /= 2; qi = sqrt(qi);
+                    if (old_re < 0) qi = -qi;
+                }
+                if (same % 2 != 0) {
+                    const double m = pow(sqrt(qr * qr + qi * qi), 1.0 / 3), ang = atan2(qi, qr) / 3;
+                    qr = m * cos(ang); qi = m * sin(ang);
+                }
+            }
+            const double nre = __dsub_rn(pr, qr), nim = __dsub_rn(pi, qi);
+            changed |= (nre != pr) || (nim != pi);
+            re[i] = nre; im[i] = nim;
+            max_diff = fmax(max_diff, fabs(qr) + fabs(qi));
+        }
+        if (!changed || !(max_diff > 0)) break;
+    }
+#pragma unroll
+    for (int i = 0; i < 10; ++i) if (fabs(im[i]) < 1e-100) im[i] = 0;
+}
+
 // ---- steps 3-6 from a given null-space basis -------------------------------------------------------
 // models: up to 10 x 9 doubles; returns the count.
 __device__ inline int solve_from_basis(const double ee[4][9], double* models)
@@ -300,7 +360,8 @@ __device__ inline int solve_from_basis(const double ee[4][9], double* models)
             for (int j = 0; j < 5; ++j) c[i + j] = fma((double)perm[s][3] * t2[i], bw[perm[s][2]][j], c[i + j]);
     }
     double re[10], im[10];
-    durand_kerner10(c, re, im);
+    if (fabs(c[10]) > 2.220446049250313e-16) durand_kerner_deg10(c, re, im);
+    else durand_kerner10(c, re, im);
     int count = 0;
     for (int i = 0; i < 10; ++i) {
         if (fabs(im[i]) > 1e-10) continue;
