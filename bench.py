@@ -227,9 +227,28 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
 
     lib.mpl_prof_enable(0)
     barrier = (lambda: dist.barrier()) if world > 1 else None
+    # Single GPU: the step (memset + 7 kernels of the library, all enqueued on the caller's stream) is captured once
+    # into a CUDA graph and replayed -- same kernels, same arguments, no per-launch host gaps.
+    run = step
+    graphed = False
+    if world == 1 and os.environ.get("MPL_BENCH_NO_GRAPH") is None:
+        try:
+            step()
+            lc = g.launches()
+            step()
+            per_step = g.launches() - lc                           # replays do not pass through the library's counter
+            torch.cuda.synchronize()
+            cg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(cg):
+                step()
+            torch.cuda.synchronize()
+            run, graphed = cg.replay, True
+        except Exception as e:                                     # capture not possible: time the plain launches
+            sys.stderr.write("bench: CUDA graph capture failed (%s); timing plain launches\n" % e)
+            run, graphed = step, False
     l0 = g.launches()
     with ClockSampler(g.dev.index) as cs:
-        ms = g.time_steps(step, steps, warmup, barrier)
+        ms = g.time_steps(run, steps, warmup, barrier)
         launches = g.launches() - l0                              # warm-up + timed steps only
         # the timed region lasts a few ms: keep the same work running until NVML has sampled it.  Every rank must issue
         # the SAME number of steps (they contain a collective), so the padding is a fixed count, not a deadline.
@@ -237,9 +256,11 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
             step()
         t_end = time.time() + 1.0
         while world == 1 and len(cs.samples) < 8 and time.time() < t_end:
-            step()
+            run()
         torch.cuda.synchronize()
     launches = launches * steps // (steps + warmup)             # kernels launched inside the K timed steps
+    if graphed:
+        launches = per_step * steps
     # dominant kernel timed live with the library's own CUDA events (same stream), separate short pass
     lib.mpl_prof_enable(1)
     for _ in range(max(3, min(steps, 10))):
@@ -251,6 +272,7 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     res = dict(ms=ms, launches_per_step=None, kern=kern, clocks=cs.summary(), nq=nq, nt=nt, dim=dim,
                idx=d_idx.cpu().numpy(), dist=d_dist.cpu().numpy(), q=q, t=t)
     res["launches_timed"] = launches
+    res["graphed"] = graphed
     return res
 
 
