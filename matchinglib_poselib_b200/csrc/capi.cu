@@ -87,6 +87,21 @@ int MplBuf::ensure(size_t bytes)
 }
 void MplBuf::release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
 
+// Pinned host staging for results: device -> host copies land here at full PCIe rate (a copy into pageable memory is
+// staged by the driver in small synchronous pieces), then one memcpy hands them to the caller's buffer.
+static void*  g_stage = nullptr;
+static size_t g_stage_cap = 0;
+static int stage_ensure(size_t bytes)
+{
+    if (bytes <= g_stage_cap) return MPL_OK;
+    if (g_stage) { cudaFreeHost(g_stage); g_stage = nullptr; g_stage_cap = 0; }
+    const size_t want = bytes + bytes / 4 + 4096;
+    MPL_CUDA_CHECK(cudaHostAlloc(&g_stage, want, cudaHostAllocDefault));
+    g_stage_cap = want;
+    return MPL_OK;
+}
+static void stage_release() { if (g_stage) cudaFreeHost(g_stage); g_stage = nullptr; g_stage_cap = 0; }
+
 static int init_locked(int device)
 {
     if (g_ctx.ready && g_ctx.device == device) return MPL_OK;
@@ -98,7 +113,7 @@ static int init_locked(int device)
         return MPL_ERR_NO_DEVICE;
     }
     if (device < 0 || device >= n) { mpl_set_error("device %d out of range (0..%d)", device, n - 1); return MPL_ERR_BAD_ARG; }
-    if (g_ctx.ready) { for (auto& b : g_ctx.bufs) b.release(); cudaStreamDestroy(g_ctx.stream); g_ctx.ready = false; }
+    if (g_ctx.ready) { for (auto& b : g_ctx.bufs) b.release(); stage_release(); cudaStreamDestroy(g_ctx.stream); g_ctx.ready = false; }
     MPL_CUDA_CHECK(cudaSetDevice(device));
     cudaDeviceProp p;
     MPL_CUDA_CHECK(cudaGetDeviceProperties(&p, device));
@@ -128,6 +143,7 @@ extern "C" int mpl_shutdown(void)
     cudaSetDevice(g_ctx.device);
     cudaStreamSynchronize(g_ctx.stream);
     for (auto& b : g_ctx.bufs) b.release();
+    stage_release();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.ready = false;
     return MPL_OK;
@@ -262,6 +278,26 @@ int mpl_hamming_keys_locked(const uint8_t* q, int nq, size_t q_step, const uint8
     return MPL_OK;
 }
 
+// idx/dist columns of merged device keys -> caller's host arrays through the pinned staging buffer
+static int keys_to_host_locked(const mpl_key64* d_keys, int nq, int k, int float_mode, int32_t* idx, void* dist)
+{
+    int rc;
+    cudaStream_t st = g_ctx.stream;
+    MplBuf &bidx = g_ctx.bufs[MPL_BUF_IDX], &bdist = g_ctx.bufs[MPL_BUF_DIST];
+    const size_t bytes = (size_t)nq * k * 4;
+    if ((rc = bidx.ensure(bytes))) return rc;
+    if ((rc = bdist.ensure(bytes))) return rc;
+    if ((rc = stage_ensure(2 * bytes))) return rc;
+    rc = mpl_launch_merge_top2(d_keys, 1, nq, k, (int32_t*)bidx.ptr, bdist.ptr, float_mode, nullptr, st);
+    if (rc) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(g_stage, bidx.ptr, bytes, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync((char*)g_stage + bytes, bdist.ptr, bytes, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    memcpy(idx, g_stage, bytes);
+    memcpy(dist, (char*)g_stage + bytes, bytes);
+    return MPL_OK;
+}
+
 extern "C" int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step,
                                 int nbytes, int ignore_tail_bytes, int k, int32_t* idx, int32_t* dist)
 {
@@ -275,40 +311,9 @@ extern "C" int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const u
     if (rc) return rc;
     if (nq == 0) return MPL_OK;
     if (nt == 0) { for (int i = 0; i < nq * k; ++i) { idx[i] = -1; dist[i] = INT_MAX; } return MPL_OK; }
-    cudaStream_t st = g_ctx.stream;
-    const int used = nbytes - ignore_tail_bytes;
-    const int w16 = round_w16(used);
-    const size_t rowb = (size_t)w16 * 16;
-    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T], &braw = g_ctx.bufs[MPL_BUF_RAW];
-    // queries and train rows -> packed device layout
-    const uint8_t* src[2] = {q, t}; const int n[2] = {nq, nt}; const size_t stp[2] = {q_step, t_step};
-    MplBuf* dst[2] = {&bq, &bt};
-    for (int s = 0; s < 2; ++s) {
-        if ((size_t)used == rowb) {                       // already in device layout: strided copy only
-            rc = upload_rows(*dst[s], src[s], n[s], rowb, stp[s], rowb, st);
-            if (rc) return rc;
-        } else {
-            rc = upload_rows(braw, src[s], n[s], (size_t)nbytes, stp[s], (size_t)nbytes, st);
-            if (rc) return rc;
-            rc = dst[s]->ensure((size_t)n[s] * rowb);
-            if (rc) return rc;
-            rc = mpl_launch_pack_rows_u8((const uint8_t*)braw.ptr, n[s], (size_t)nbytes, used, (uint8_t*)dst[s]->ptr, w16, st);
-            if (rc) return rc;
-        }
-    }
-    const int splits = mpl_hamming_pick_splits(nq, nt, w16, g_ctx.sm_count);
-    MplBuf &bpart = g_ctx.bufs[MPL_BUF_PART], &bidx = g_ctx.bufs[MPL_BUF_IDX], &bdist = g_ctx.bufs[MPL_BUF_DIST];
-    if ((rc = bpart.ensure((size_t)splits * nq * 2 * sizeof(mpl_key64)))) return rc;
-    if ((rc = bidx.ensure((size_t)nq * k * 4))) return rc;
-    if ((rc = bdist.ensure((size_t)nq * k * 4))) return rc;
-    rc = mpl_launch_hamming_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, splits, 1, 0, (mpl_key64*)bpart.ptr, st);
-    if (rc) return rc;
-    rc = mpl_launch_merge_top2((const mpl_key64*)bpart.ptr, splits, nq, k, (int32_t*)bidx.ptr, bdist.ptr, -1, nullptr, st);
-    if (rc) return rc;
-    MPL_CUDA_CHECK(cudaMemcpyAsync(idx, bidx.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(dist, bdist.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-    return MPL_OK;
+    mpl_key64* d_keys = nullptr;
+    if ((rc = mpl_hamming_keys_locked(q, nq, q_step, t, nt, t_step, nbytes, ignore_tail_bytes, &d_keys))) return rc;
+    return keys_to_host_locked(d_keys, nq, k, -1, idx, dist);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -369,6 +374,33 @@ extern "C" int mpl_knn_l2_last_stats_host(unsigned* fallbacks, unsigned* tf32_mo
     return mpl_l2tc_last_fallbacks(g_ctx.bufs[MPL_BUF_PART].ptr, fallbacks, tf32_mode, g_ctx.stream);
 }
 
+// Upload both float descriptor sets, scan, and leave the per-query top-2 keys on the device (context buffer KEYS).
+// Caller holds the context mutex; nq, nt > 0.
+static int l2_keys_locked(const float* q, int nq, size_t q_step, const float* t, int nt, size_t t_step, int dim, int sqrt_out,
+                          mpl_key64** d_keys)
+{
+    int rc;
+    cudaStream_t st = g_ctx.stream;
+    const size_t ld = (size_t)((dim + 3) / 4) * 4;           // device row pitch in floats (16-byte aligned rows)
+    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T];
+    if (ld != (size_t)dim) {                                  // pad columns are never read as payload, but keep them clean
+        if ((rc = bq.ensure((size_t)nq * ld * 4 + 16))) return rc;
+        if ((rc = bt.ensure((size_t)nt * ld * 4 + 16))) return rc;
+        MPL_CUDA_CHECK(cudaMemsetAsync(bq.ptr, 0, (size_t)nq * ld * 4, st));
+        MPL_CUDA_CHECK(cudaMemsetAsync(bt.ptr, 0, (size_t)nt * ld * 4, st));
+    }
+    if ((rc = upload_rows(bq, q, nq, (size_t)dim * 4, q_step, ld * 4, st))) return rc;
+    if ((rc = upload_rows(bt, t, nt, (size_t)dim * 4, t_step, ld * 4, st))) return rc;
+    MplBuf &bscr = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS];
+    const size_t scr = mpl_knn_l2_scratch_bytes(nq, nt, dim);
+    if ((rc = bscr.ensure(scr))) return rc;
+    if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
+    rc = mpl_knn2_l2f32_dev(bq.ptr, nq, ld, bt.ptr, nt, ld, dim, sqrt_out, 0, bscr.ptr, scr, bkeys.ptr, (void*)st);
+    if (rc) return rc;
+    *d_keys = (mpl_key64*)bkeys.ptr;
+    return MPL_OK;
+}
+
 extern "C" int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt, size_t t_step,
                               int dim, int sqrt_out, int k, int32_t* idx, float* dist)
 {
@@ -381,31 +413,9 @@ extern "C" int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float
     if (rc) return rc;
     if (nq == 0) return MPL_OK;
     if (nt == 0) { for (int i = 0; i < nq * k; ++i) { idx[i] = -1; dist[i] = FLT_MAX; } return MPL_OK; }
-    cudaStream_t st = g_ctx.stream;
-    const size_t ld = (size_t)((dim + 3) / 4) * 4;           // device row pitch in floats (16-byte aligned rows)
-    MplBuf &bq = g_ctx.bufs[MPL_BUF_Q], &bt = g_ctx.bufs[MPL_BUF_T];
-    if (ld != (size_t)dim) {                                  // pad columns are never read as payload, but keep them clean
-        if ((rc = bq.ensure((size_t)nq * ld * 4 + 16))) return rc;
-        if ((rc = bt.ensure((size_t)nt * ld * 4 + 16))) return rc;
-        MPL_CUDA_CHECK(cudaMemsetAsync(bq.ptr, 0, (size_t)nq * ld * 4, st));
-        MPL_CUDA_CHECK(cudaMemsetAsync(bt.ptr, 0, (size_t)nt * ld * 4, st));
-    }
-    if ((rc = upload_rows(bq, q, nq, (size_t)dim * 4, q_step, ld * 4, st))) return rc;
-    if ((rc = upload_rows(bt, t, nt, (size_t)dim * 4, t_step, ld * 4, st))) return rc;
-    MplBuf &bscr = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS], &bidx = g_ctx.bufs[MPL_BUF_IDX], &bdist = g_ctx.bufs[MPL_BUF_DIST];
-    const size_t scr = mpl_knn_l2_scratch_bytes(nq, nt, dim);
-    if ((rc = bscr.ensure(scr))) return rc;
-    if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
-    if ((rc = bidx.ensure((size_t)nq * k * 4))) return rc;
-    if ((rc = bdist.ensure((size_t)nq * k * 4))) return rc;
-    rc = mpl_knn2_l2f32_dev(bq.ptr, nq, ld, bt.ptr, nt, ld, dim, sqrt_out, 0, bscr.ptr, scr, bkeys.ptr, (void*)st);
-    if (rc) return rc;
-    rc = mpl_launch_merge_top2((const mpl_key64*)bkeys.ptr, 1, nq, k, (int32_t*)bidx.ptr, bdist.ptr, 0, nullptr, st);
-    if (rc) return rc;
-    MPL_CUDA_CHECK(cudaMemcpyAsync(idx, bidx.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(dist, bdist.ptr, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-    return MPL_OK;
+    mpl_key64* d_keys = nullptr;
+    if ((rc = l2_keys_locked(q, nq, q_step, t, nt, t_step, dim, sqrt_out, &d_keys))) return rc;
+    return keys_to_host_locked(d_keys, nq, k, 0, idx, dist);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -466,21 +476,39 @@ extern "C" int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
         mpl_set_error("Format of descriptors not supported!"); return -1;
     }
     if (cols1 != cols2) { mpl_set_error("descriptor lengths differ (%d vs %d)", cols1, cols2); return -1; }
-    const int k = linear ? (ratio_test ? 2 : 1) : 2;       // :529-538 nn = ratioTest ? 2 : 1; nmslib_matchers.h:180 K = 2
-    std::vector<int32_t> idx((size_t)rows1 * k);
-    int rc;
-    if (cv_type1 == CV_8U_) {
-        std::vector<int32_t> d((size_t)rows1 * k);
-        const int ignore = nms ? ((cols1 & 1) ? 1 : 2) : 0;  // last packed 16-bit word never compared
-        if (nms && cols1 - ignore <= 0) { for (auto& v : d) v = 0; for (int qi = 0; qi < rows1; ++qi) for (int c = 0; c < k; ++c) idx[(size_t)qi * k + c] = c; rc = 0; }
-        else rc = mpl_knn2_hamming((const uint8_t*)desc1, rows1, step1, (const uint8_t*)desc2, rows2, step2, cols1, ignore, k, idx.data(), d.data());
-        if (rc) return -3;
-        mpl_ratio_matches_i32(idx.data(), d.data(), rows1, k, ratio_test, out, n_out);
+    // :529-538 nn = ratioTest ? 2 : 1 (LINEAR); nmslib_matchers.h:180 K = 2: the scan always keeps two, the emission below
+    // applies the ratio test (or not) on the device and the compacted cv::DMatch list comes back in one copy.
+    const int ignore = (cv_type1 == CV_8U_ && nms) ? ((cols1 & 1) ? 1 : 2) : 0;   // last packed 16-bit word never compared
+    if (cv_type1 == CV_8U_ && cols1 - ignore <= 0) {        // nothing to compare: every distance 0, neighbours 0 and 1
+        int n = 0;
+        for (int qi = 0; qi < rows1; ++qi) {
+            if (ratio_test) continue;                       // 0 < 0.75 * 0 never holds
+            out[n].queryIdx = qi; out[n].trainIdx = 0; out[n].imgIdx = -1; out[n].distance = 0.f; ++n;
+        }
+        *n_out = n;
     } else {
-        std::vector<float> d((size_t)rows1 * k);
-        rc = mpl_knn2_l2f32((const float*)desc1, rows1, step1, (const float*)desc2, rows2, step2, cols1, nms ? 1 : 0, k, idx.data(), d.data());
+        if (cv_type1 == CV_8U_ && cols1 - ignore > 256) { mpl_set_error("descriptors longer than 256 bytes are not supported"); return -3; }
+        if (!desc1 || !desc2 || !out || step1 < (size_t)cols1 * (cv_type1 == CV_8U_ ? 1 : 4) || step2 < (size_t)cols2 * (cv_type1 == CV_8U_ ? 1 : 4)) {
+            mpl_set_error("getMatches: bad descriptor matrix"); return -3;
+        }
+        std::lock_guard<std::mutex> g(g_mu);
+        if (mpl_ensure_ctx_locked()) return -3;
+        cudaStream_t st = g_ctx.stream;
+        mpl_key64* d_keys = nullptr;
+        int rc;
+        if (cv_type1 == CV_8U_) rc = mpl_hamming_keys_locked((const uint8_t*)desc1, rows1, step1, (const uint8_t*)desc2, rows2, step2, cols1, ignore, &d_keys);
+        else                    rc = l2_keys_locked((const float*)desc1, rows1, step1, (const float*)desc2, rows2, step2, cols1, nms ? 1 : 0, &d_keys);
         if (rc) return -3;
-        mpl_ratio_matches_f32(idx.data(), d.data(), rows1, k, ratio_test, out, n_out);
+        MplBuf& bm = g_ctx.bufs[MPL_BUF_IDX];
+        const size_t bytes = 16 + (size_t)rows1 * sizeof(mpl_dmatch);
+        if (bm.ensure(bytes) || stage_ensure(bytes)) return -3;
+        if (mpl_launch_ratio_dmatch(d_keys, rows1, ratio_test, cv_type1 == CV_32F_, bm.ptr, st)) return -3;
+        if (cudaMemcpyAsync(g_stage, bm.ptr, bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+            mpl_set_error("getMatches: device copy failed (%s)", cudaGetErrorString(cudaGetLastError())); return -3;
+        }
+        const int n = *(const int*)g_stage;
+        memcpy(out, (const char*)g_stage + 16, (size_t)n * sizeof(mpl_dmatch));
+        *n_out = n;
     }
     if (linear && *n_out < 2) { mpl_set_error("Too less remaining matches using the LINEAR matcher."); return -3; }  // :709-713
     return 0;

@@ -213,6 +213,48 @@ __global__ void merge_top2_kernel(const ulonglong2* __restrict__ partial, int n_
     }
 }
 
+// Lowe ratio test + cv::DMatch emission on merged keys (matchers.cpp:601-625; nmslib_matchers.h:399-421), order-preserving:
+// one CTA, every thread owns a contiguous chunk of queries (count, block scan, write).  out = 16-byte header (count) followed
+// by the matches in ascending queryIdx, so one D2H copy brings back both.  ratio_test == 0: every query emits its nearest.
+// An absent second neighbour compares as FLT_MAX / INT_MAX, like the idx/dist arrays of merge_top2_kernel would.
+__global__ void __launch_bounds__(1024)
+ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test, int is_float, int4* __restrict__ out)
+{
+    __shared__ int warp_sums[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (nq + 1023) / 1024;
+    const int start = min(nq, tid * per), end = min(nq, start + per);
+    auto dist_f = [&](mpl_key64 k) {
+        if (k == MPL_KEY_INVALID) return is_float ? 3.402823466e+38f : (float)0x7FFFFFFF;
+        const uint32_t d = (uint32_t)(k >> 32);
+        return is_float ? __uint_as_float(d) : (float)(int32_t)d;
+    };
+    auto passes = [&](const ulonglong2 k) { return !ratio_test || dist_f(k.x) < 0.75f * dist_f(k.y); };
+    int sum = 0;
+    for (int i = start; i < end; ++i) sum += passes(keys[i]) ? 1 : 0;
+    int x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        int w = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+        warp_sums[lane] = w;
+    }
+    __syncthreads();
+    int pos = (wid ? warp_sums[wid - 1] : 0) + x - sum;
+    for (int i = start; i < end; ++i) {
+        const ulonglong2 k = keys[i];
+        if (!passes(k)) continue;
+        const int ti = k.x == MPL_KEY_INVALID ? -1 : (int)(uint32_t)(k.x & 0xFFFFFFFFull);
+        out[1 + pos] = make_int4(i, ti, -1, __float_as_int(dist_f(k.x)));      // queryIdx, trainIdx, imgIdx = -1, distance
+        ++pos;
+    }
+    if (tid == 1023) out[0] = make_int4(pos, 0, 0, 0);
+}
+
 template <int W16>
 int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, int n_pairs, long long train_offset,
              mpl_key64* partial, cudaStream_t st)
@@ -290,6 +332,15 @@ int mpl_launch_merge_top2(const mpl_key64* partial, int n_parts, int nq, int k, 
     MplProfScope prof(MPL_PROF_MERGE, st);
     merge_top2_kernel<<<(nq + 127) / 128, 128, 0, st>>>((const ulonglong2*)partial, n_parts, nq, k, idx,
                                                         (uint32_t*)dist, float_sqrt, (ulonglong2*)merged_keys);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_ratio_dmatch(const mpl_key64* keys, int nq, int ratio_test, int is_float, void* out, cudaStream_t st)
+{
+    MplProfScope prof(MPL_PROF_MERGE, st);
+    ratio_dmatch_kernel<<<1, 1024, 0, st>>>((const ulonglong2*)keys, nq, ratio_test, is_float, (int4*)out);
     MPL_CUDA_CHECK(cudaGetLastError());
     mpl_count_launch();
     return MPL_OK;

@@ -49,14 +49,14 @@ def getMatchesArray(keypoints1, keypoints2, descriptors1, descriptors2, imgSi=No
         raise NotImplementedError("VFCrefine is outside the B200 hot path")
     a1, r1, c1, s1, t1 = _mat_fields(descriptors1)
     a2, r2, c2, s2, t2 = _mat_fields(descriptors2)
-    out = np.zeros(max(r1, 1), dtype=DMATCH_DTYPE)
+    out = np.empty(max(r1, 1), dtype=DMATCH_DTYPE)        # the library fills the first n_out records
     n_out = ctypes.c_int(0)
     err = lib.mpl_get_matches_api(len(keypoints1), len(keypoints2), _lib.ptr(a1), r1, c1, s1, t1,
                                   _lib.ptr(a2), r2, c2, s2, t2, matcher_name.encode(), int(bool(ratioTest)),
                                   int(nr_threads), _lib.ptr(out), ctypes.byref(n_out))
     if err == -103:
         raise AssertionError(_lib.last_error())          # cv::Exception from CV_Assert in the reference
-    return err, out[: n_out.value].copy()
+    return err, out[: n_out.value]
 
 
 def getMatches(keypoints1, keypoints2, descriptors1, descriptors2, imgSi, finalMatches, matcher_name="GMBSOF",
