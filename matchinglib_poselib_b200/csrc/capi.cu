@@ -8,6 +8,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstring>
+#include <cstdlib>
 #include <climits>
 #include <cfloat>
 #include <mutex>
@@ -144,6 +145,7 @@ extern "C" int mpl_shutdown(void)
     cudaStreamSynchronize(g_ctx.stream);
     for (auto& b : g_ctx.bufs) b.release();
     stage_release();
+   
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.ready = false;
     return MPL_OK;
@@ -389,12 +391,12 @@ static int l2_keys_locked(const float* q, int nq, size_t q_step, const float* t,
         MPL_CUDA_CHECK(cudaMemsetAsync(bq.ptr, 0, (size_t)nq * ld * 4, st));
         MPL_CUDA_CHECK(cudaMemsetAsync(bt.ptr, 0, (size_t)nt * ld * 4, st));
     }
-    if ((rc = upload_rows(bq, q, nq, (size_t)dim * 4, q_step, ld * 4, st))) return rc;
-    if ((rc = upload_rows(bt, t, nt, (size_t)dim * 4, t_step, ld * 4, st))) return rc;
     MplBuf &bscr = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS];
     const size_t scr = mpl_knn_l2_scratch_bytes(nq, nt, dim);
     if ((rc = bscr.ensure(scr))) return rc;
     if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
+    if ((rc = upload_rows(bq, q, nq, (size_t)dim * 4, q_step, ld * 4, st))) return rc;
+    if ((rc = upload_rows(bt, t, nt, (size_t)dim * 4, t_step, ld * 4, st))) return rc;
     rc = mpl_knn2_l2f32_dev(bq.ptr, nq, ld, bt.ptr, nt, ld, dim, sqrt_out, 0, bscr.ptr, scr, bkeys.ptr, (void*)st);
     if (rc) return rc;
     *d_keys = (mpl_key64*)bkeys.ptr;

@@ -749,6 +749,27 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     const bool exact_ok = lists2 && (sq + st) * (sq + st) < 16777216.f * 0.999f;
     if (exact_ok) eps = 0.f;
     const int nc = lists2 ? 2 : NC;
+    if (exact_ok) {
+        // score + |q|^2 is the reference distance bit for bit: no row is read again.  Lane-local top-2 of the keys
+        // (dist, trainIdx), then a butterfly merge over the warp.
+        mpl_key64 k0 = MPL_KEY_INVALID, k1 = MPL_KEY_INVALID;
+        for (int c = lane; c < n_cand; c += 32) {
+            const int slot = c / NC, e = c - slot * NC;
+            if (e >= 2) continue;
+            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
+            const uint4 sc = rec[0], id = rec[1];
+            const int ti = (int)(e == 0 ? id.x : id.y);
+            if (ti < 0 || ti >= nt) continue;
+            float d = __fadd_rn(__uint_as_float(e == 0 ? sc.x : sc.y), qq);
+            if (MODE == 1) d = sqrtf(d);
+            const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
+            const mpl_key64 hi = max(k0, key);
+            k0 = min(k0, key); k1 = min(k1, hi);
+        }
+        warp_top2(k0, k1);
+        if (lane == 0) { keys_out[2 * (size_t)qi] = k0; keys_out[2 * (size_t)qi + 1] = k1; }
+        return;                                    // k1 invalid only if fewer than two train rows exist: nothing to certify
+    }
     // pass A: the two smallest scores over all candidates, and tau = min over slots of the slot's 4th best
     float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
     for (int c = lane; c < n_cand; c += 32) {
