@@ -72,6 +72,76 @@ def getMatches(keypoints1, keypoints2, descriptors1, descriptors2, imgSi, finalM
     return err
 
 
+# ---- getCorrespondences (correspondences.cpp:148-519): the orchestrator around getMatches --------------------------
+# Keypoint detection and descriptor extraction are OpenCV calls on the host in the reference too (features.cpp:145-244,
+# 397-520; SURVEY section 2: outside the hot path); only the matching step runs through libmplb200.  Detector /
+# extractor names follow features.cpp:987-1056 for the types the installed cv2 build provides.
+def _cv2_detector(name, limit):
+    import cv2
+    table = {"FAST": lambda: cv2.FastFeatureDetector_create(), "ORB": lambda: cv2.ORB_create(nfeatures=limit),
+             "BRISK": lambda: cv2.BRISK_create(), "AKAZE": lambda: cv2.AKAZE_create(), "KAZE": lambda: cv2.KAZE_create(),
+             "SIFT": lambda: cv2.SIFT_create(), "MSER": lambda: cv2.MSER_create(),
+             "SimpleBlob": lambda: cv2.SimpleBlobDetector_create()}
+    return table[name]() if name in table else None
+
+
+def _cv2_extractor(name):
+    import cv2
+    table = {"ORB": lambda: cv2.ORB_create(), "BRISK": lambda: cv2.BRISK_create(), "AKAZE": lambda: cv2.AKAZE_create(),
+             "KAZE": lambda: cv2.KAZE_create(), "SIFT": lambda: cv2.SIFT_create()}
+    return table[name]() if name in table else None
+
+
+def _get_keypoints(img, featuretype, limit, detector):
+    """features.cpp:145-244 without the grid-based response filter of the dynamic branch (retainBest on both branches).
+    Returns (err, keypoints)."""
+    det = detector if detector is not None else _cv2_detector(featuretype, min(limit, 100000) if featuretype == "ORB" else limit)
+    if det is None:
+        return -3, []
+    kps = list(det.detect(img) if hasattr(det, "detect") else det(img))
+    if len(kps) > limit:
+        kps = sorted(kps, key=lambda k: -k.response)[:limit]                  # cv::KeyPointsFilter::retainBest
+    if len(kps) < 10:
+        return -1, kps
+    return 0, kps
+
+
+def getCorrespondences(img1, img2, featuretype="FAST", extractortype="FREAK", matchertype="GMBSOF", dynamicKeypDet=True,
+                       limitNrfeatures=8000, VFCrefine=False, GMSrefine=False, ratioTest=True, SOFrefine=False,
+                       subPixRefine=0, verbose=0, idxPars_NMSLIB="", queryPars_NMSLIB="", detector=None, extractor=None):
+    """matchinglib::getCorrespondences (matchinglib_correspondences.h:61-78, correspondences.cpp:148-519).
+    Returns (err, finalMatches, kp1, kp2); err as in the reference: 0 ok, -1 missing input, -2 keypoint error,
+    -3 descriptor error, -4 incompatible detector/matcher, -6 incompatible detector/descriptor, and a getMatches failure e
+    as -4 + e (:356-359), i.e. -5 wrong input, -6 matcher not served by this build, -7 too few matches, -8 too few keypoints.
+    `detector` / `extractor` (objects with detect(img) / compute(img, kps)) replace the cv2 factories when given.
+    The post-filters (VFC, GMS, SOF, sub-pixel refinement; :378-506) are outside the B200 hot path."""
+    if img1 is None or img2 is None or np.size(img1) == 0 or np.size(img2) == 0:
+        return -1, [], [], []
+    if VFCrefine or GMSrefine or SOFrefine or subPixRefine:
+        raise NotImplementedError("VFC / GMS / SOF / sub-pixel refinement are outside the B200 hot path")
+    if featuretype in ("MSER", "SimpleBlob") and matchertype == "GMBSOF":
+        return -4, [], [], []
+    if (featuretype != "KAZE" and extractortype == "KAZE") or (featuretype != "AKAZE" and extractortype == "AKAZE") or \
+       (featuretype == "SIFT" and extractortype == "ORB") or (featuretype == "MSD" and extractortype == "SIFT"):
+        return -6, [], [], []
+    e1, kp1 = _get_keypoints(img1, featuretype, limitNrfeatures, detector)
+    e2, kp2 = _get_keypoints(img2, featuretype, limitNrfeatures, detector) if e1 == 0 else (e1, [])
+    if e1 or e2:
+        return -2, [], kp1, kp2
+    ext = extractor if extractor is not None else _cv2_extractor(extractortype)
+    if ext is None:
+        return -3, [], kp1, kp2
+    kp1, d1 = ext.compute(img1, kp1)
+    kp2, d2 = ext.compute(img2, kp2)
+    if d1 is None or d2 is None or len(kp1) != len(d1) or len(kp2) != len(d2):
+        return -3, [], list(kp1 or []), list(kp2 or [])
+    err, matches = getMatchesArray(kp1, kp2, d1, d2, None, matchertype, False, ratioTest, extractortype,
+                                   idxPars_NMSLIB, queryPars_NMSLIB)
+    if err != 0:
+        return -4 + err, [], list(kp1), list(kp2)
+    return 0, matches, list(kp1), list(kp2)
+
+
 def knn2_hamming(query, train, k=2, ignore_tail_bytes=0):
     """Raw k-NN (the cvflann / NMSLIB scan): returns (idx[nq,k] int32, dist[nq,k] int32)."""
     lib = _lib.load()
