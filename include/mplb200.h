@@ -40,7 +40,10 @@ extern "C" {
 typedef struct mpl_dmatch { int32_t queryIdx, trainIdx, imgIdx; float distance; } mpl_dmatch;
 
 /* ---- library / device --------------------------------------------------------------------- */
-int         mpl_init(int device);            /* select device, create stream + scratch; idempotent */
+/* Contexts are per HOST THREAD (own CUDA stream, scratch, pinned staging), created on first use on the device the last
+ * mpl_init() named (default 0) and freed at thread exit or mpl_shutdown() (calling thread's only).  Entry points are
+ * synchronous for their caller; calls from different threads overlap on the GPU -- the way to run a batch of image pairs. */
+int         mpl_init(int device);            /* select device, create the caller's stream + scratch; idempotent */
 int         mpl_shutdown(void);
 const char* mpl_last_error(void);            /* thread-local text of the last failure */
 int         mpl_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);

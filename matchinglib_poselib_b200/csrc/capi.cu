@@ -71,8 +71,12 @@ extern "C" int mpl_prof_read(int id, double* total_ms, long long* launches)
     return MPL_OK;
 }
 
-static MplCtx g_ctx;
-static std::mutex g_mu;            // serialises host-pointer entry points (they share scratch + stream)
+// One context per HOST THREAD: its own stream, scratch buffers and pinned staging, created on first use on the device the
+// last mpl_init() named.  Calls from different threads therefore run concurrently on the GPU (independent image pairs of a
+// batch: the per-pair RANSAC is latency-bound and fills a fraction of the SMs); calls of one thread are synchronous.
+static thread_local MplCtx g_ctx;
+static thread_local std::mutex g_mu;            // the entry points keep their lock_guard; never contended across threads
+static std::atomic<int> g_device{0};
 
 MplCtx* mpl_ctx() { return &g_ctx; }
 std::mutex& mpl_ctx_mutex() { return g_mu; }
@@ -90,8 +94,8 @@ void MplBuf::release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
 
 // Pinned host staging for results: device -> host copies land here at full PCIe rate (a copy into pageable memory is
 // staged by the driver in small synchronous pieces), then one memcpy hands them to the caller's buffer.
-static void*  g_stage = nullptr;
-static size_t g_stage_cap = 0;
+static thread_local void*  g_stage = nullptr;
+static thread_local size_t g_stage_cap = 0;
 static int stage_ensure(size_t bytes)
 {
     if (bytes <= g_stage_cap) return MPL_OK;
@@ -103,8 +107,24 @@ static int stage_ensure(size_t bytes)
 }
 static void stage_release() { if (g_stage) cudaFreeHost(g_stage); g_stage = nullptr; g_stage_cap = 0; }
 
+// frees a thread's stream, scratch and staging when the thread ends
+struct CtxGuard {
+    ~CtxGuard() {
+        if (!g_ctx.ready) return;
+        if (cudaSetDevice(g_ctx.device) != cudaSuccess) return;
+        cudaStreamSynchronize(g_ctx.stream);
+        for (auto& b : g_ctx.bufs) b.release();
+        stage_release();
+        cudaStreamDestroy(g_ctx.stream);
+        g_ctx.ready = false;
+        (void)cudaGetLastError();
+    }
+};
+
 static int init_locked(int device)
 {
+    static thread_local CtxGuard guard;
+    (void)guard;
     if (g_ctx.ready && g_ctx.device == device) return MPL_OK;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -131,11 +151,18 @@ static int init_locked(int device)
 
 int mpl_ensure_ctx_locked()
 {
-    if (g_ctx.ready) { MPL_CUDA_CHECK(cudaSetDevice(g_ctx.device)); return MPL_OK; }
-    return init_locked(0);
+    const int device = g_device.load(std::memory_order_relaxed);
+    if (g_ctx.ready && g_ctx.device == device) { MPL_CUDA_CHECK(cudaSetDevice(device)); return MPL_OK; }
+    return init_locked(device);
 }
 
-extern "C" int mpl_init(int device) { std::lock_guard<std::mutex> g(g_mu); return init_locked(device); }
+extern "C" int mpl_init(int device)
+{
+    std::lock_guard<std::mutex> g(g_mu);
+    int rc = init_locked(device);
+    if (rc == MPL_OK) g_device.store(device, std::memory_order_relaxed);
+    return rc;
+}
 
 extern "C" int mpl_shutdown(void)
 {
@@ -145,7 +172,6 @@ extern "C" int mpl_shutdown(void)
     cudaStreamSynchronize(g_ctx.stream);
     for (auto& b : g_ctx.bufs) b.release();
     stage_release();
-   
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.ready = false;
     return MPL_OK;

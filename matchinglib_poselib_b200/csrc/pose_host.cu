@@ -79,7 +79,7 @@ static void jacobi_eig9(double A[9][9], double V[9][9], double w[9])
 }
 
 // ---- minimal-sample drawing: getSubset + checkSubset (modelest.cpp:567-650) ---------------------------
-static uint64_t g_seed = 0x9E3779B97F4A7C15ull;
+static thread_local uint64_t g_seed = 0x9E3779B97F4A7C15ull;   // per calling thread, like the contexts
 extern "C" int mpl_ransac_set_seed(unsigned long long seed) { g_seed = seed ? seed : 0x9E3779B97F4A7C15ull; return MPL_OK; }
 static inline uint32_t next_rand(uint64_t& s) { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16) & 0x7FFFFFFF; }
 

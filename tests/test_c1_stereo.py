@@ -97,3 +97,28 @@ def test_gpu_device_resident_pipeline(oracle_chain):
     assert np.array_equal(r2["samples"], s) and np.array_equal(r2["mask"], r["mask"])       # deterministic for a given seed
     r3 = poselib.matchAndEstimatePose(G["l_desc"][:3], G["r_desc"], G["l_norm"][:3], G["r_norm"], "LINEAR", False, _threshold(), 50)
     assert len(r3["matches"]) == 3 and r3["count"] == 0 and len(r3["samples"]) == 0         # fewer than 5 correspondences
+
+
+@pytest.mark.gpu
+def test_gpu_concurrent_host_threads_equal_sequential():
+    """Contexts are per host thread: 8 threads running the pair pipeline and getMatches at the same time (different seeds
+    and slices of the stereo pair) return exactly what the same calls return one after the other."""
+    from concurrent.futures import ThreadPoolExecutor
+    import __graft_entry__ as g
+    g.build()
+    from matchinglib_poselib_b200 import poselib, matchinglib, _lib
+    _lib.check(_lib.load().mpl_init(0), "mpl_init")
+    ld, rd, ln, rn = (np.ascontiguousarray(G[k]) for k in ("l_desc", "r_desc", "l_norm", "r_norm"))   # NpzFile is not thread-safe
+    nl, th = len(ld), _threshold()
+
+    def job(i):
+        lo = 37 * i
+        r = poselib.matchAndEstimatePose(ld[lo:], rd, ln[lo:], rn, "LINEAR", True, th, 400, 0.999, True, seed=11 + i)
+        err, mt = matchinglib.getMatchesArray(range(nl - lo), range(len(rd)), ld[lo:], rd, None, "BRUTEFORCENMS", False, True)
+        return r["matches"].tobytes(), r["samples"].tobytes(), r["mask"].tobytes(), int(r["count"]), int(r["iters"]), err, mt.tobytes()
+
+    seq = [job(i) for i in range(8)]
+    for _ in range(3):
+        with ThreadPoolExecutor(8) as ex:
+            par = list(ex.map(job, range(8)))
+        assert par == seq
