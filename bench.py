@@ -27,6 +27,10 @@ import sys
 import threading
 import time
 
+# Batches of image pairs run one host thread per pair in flight, each on its own CUDA stream: give the driver enough
+# hardware queues (default 8) that those streams do not alias.  Must be set before CUDA initialises.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -384,7 +388,7 @@ def bench_pair_pipeline(g, reps):
     # a batch of pairs: one host thread per pair in flight (contexts are per thread: own stream and scratch), the GPU
     # overlaps the latency-bound per-pair RANSAC kernels of different pairs
     from concurrent.futures import ThreadPoolExecutor
-    n_threads = min(16, os.cpu_count() or 1)
+    n_threads = min(32, 2 * (os.cpu_count() or 1))            # threads mostly wait for the device
     n_pairs = 8 * n_threads
 
     def one(i):
