@@ -57,6 +57,44 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// Hamming distance of NW 32-bit words.  POPC issues at a quarter of the LOP3 rate (16 vs 64 lanes/clk/SM, measured:
+// profiles/r1_microbench.json), so part of the counting moves to the logic pipe: carry-save adders (Harley-Seal) fold
+// three XOR words into a sum word and a carry word (one LOP3 each).  Three adders per 8 words balance the two pipes:
+//   8 words -> popc(s3) + popc(x7) + 2 (popc(c1) + popc(c2) + popc(c3)) = 5 POPC + 14 LOP3   (plain: 8 POPC + 8 LOP3)
+// (the full tree, 4 POPC + 22 LOP3, is logic-pipe bound and measured slower).
+__device__ __forceinline__ void csa(uint32_t& h, uint32_t& l, uint32_t a, uint32_t b, uint32_t c)
+{
+    const uint32_t u = a ^ b;
+    h = (a & b) | (u & c);
+    l = u ^ c;
+}
+template <int NW>
+__device__ __forceinline__ unsigned hamming_words(const uint32_t (&q)[NW], const uint32_t (&t)[NW])
+{
+    unsigned ones = 0, twos = 0;
+    if constexpr (NW % 8 == 0) {
+#pragma unroll
+        for (int g = 0; g < NW; g += 8) {
+            uint32_t x[8];
+#pragma unroll
+            for (int w = 0; w < 8; ++w) x[w] = q[g + w] ^ t[g + w];
+            uint32_t c1, s1, c2, s2, c3, s3;
+            csa(c1, s1, x[0], x[1], x[2]);
+            csa(c2, s2, x[3], x[4], x[5]);
+            csa(c3, s3, s1, s2, x[6]);
+            ones += __popc(s3) + __popc(x[7]);
+            twos += __popc(c1) + __popc(c2) + __popc(c3);
+        }
+    } else {
+        static_assert(NW == 4, "rows are multiples of 16 bytes");
+        uint32_t c, s;
+        csa(c, s, q[0] ^ t[0], q[1] ^ t[1], q[2] ^ t[2]);
+        ones = __popc(s) + __popc(q[3] ^ t[3]);
+        twos = __popc(c);
+    }
+    return ones + 2 * twos;
+}
+
 template <int W16> struct HammingCfg {
     static constexpr int RQ = (W16 <= 2) ? 4 : (W16 <= 4 ? 2 : 1);   // queries per thread
     static constexpr int kTileRows = kTileBytes / (16 * W16);
@@ -132,9 +170,7 @@ hamming_top2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict
             }
 #pragma unroll
             for (int j = 0; j < RQ; ++j) {
-                unsigned d = 0;
-#pragma unroll
-                for (int w = 0; w < W16 * 4; ++w) d += __popc(qr[j][w] ^ tr[w]);
+                const unsigned d = hamming_words<W16 * 4>(qr[j], tr);
                 const unsigned key = (d << kIdxBits) | lrow;
                 const unsigned hi  = max(k1[j], key);
                 k1[j] = min(k1[j], key);
