@@ -43,7 +43,7 @@ C3 = dict(n=10000, h=100000, seed=1003)
 L2_FLUSH_BYTES = 512 << 20       # > 126 MB L2: written between timed iterations
 # integer-ALU instructions (LOP3 + IADD3 + LEA + VIMNMX) per descriptor pair in the SASS inner loop of hamming_top2_kernel<W16>
 # (cuobjdump -sass, bytes per descriptor -> count): the executed-work side of the Hamming roofline
-HAMMING_ALU_PER_PAIR = {32: 27.0}
+HAMMING_ALU_PER_PAIR = {32: 19.0}        # 15 LOP3 + 3 VIMNMX + 1 IADD3 (5 POPC and 3 IMAD go to other pipes)
 
 
 def peaks():
@@ -358,7 +358,7 @@ def bench_hamming(g, steps, warmup):
                       kernel="hamming_top2_kernel", kernel_ms=kern_ms,
                       note="compute-bound on the integer pipe, not HBM (algorithmic bytes are 0.65 MB): see alu"),
         # SURVEY 8(d) counts ceil(B/4) POPC per pair (the reference's scalar form).  The kernel folds 8 XOR words through 3
-        # carry-save adders and issues 5 POPC + ~27 logic/add/min-max instructions per pair, so that figure can exceed 1: the
+        # carry-save adders and issues 5 POPC + 19 logic/add/min-max instructions per pair, so that figure can exceed 1: the
         # binding pipe is the integer ALU (LOP3/IADD3/VIMNMX, 64 lanes/clk/SM = the measured SHF rate).
         alu=dict(bound="int popc issue (algorithmic count); executed: int alu issue", achieved_gpopc_s=popc / (kern_ms * 1e-3) / 1e9,
                  peak_gpopc_s=pp["popc_gops"], frac=popc / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], popc_per_pair=nb // 4,

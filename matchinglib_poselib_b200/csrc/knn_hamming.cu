@@ -64,9 +64,9 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
 // (the full tree, 4 POPC + 22 LOP3, is logic-pipe bound and measured slower).
 __device__ __forceinline__ void csa(uint32_t& h, uint32_t& l, uint32_t a, uint32_t b, uint32_t c)
 {
-    const uint32_t u = a ^ b;
-    h = (a & b) | (u & c);
-    l = u ^ c;
+    // explicit LOP3s: left to itself the compiler folds the operand XORs into the sum and then needs two LOP3 per carry
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(l) : "r"(a), "r"(b), "r"(c));     // a ^ b ^ c
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(h) : "r"(a), "r"(b), "r"(c));     // majority
 }
 template <int NW>
 __device__ __forceinline__ unsigned hamming_words(const uint32_t (&q)[NW], const uint32_t (&t)[NW])
@@ -296,8 +296,7 @@ int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, i
              mpl_key64* partial, cudaStream_t st)
 {
     using Cfg = HammingCfg<W16>;
-    int rows_per_split = (nt + n_splits - 1) / n_splits;
-    rows_per_split = ((rows_per_split + Cfg::kTileRows - 1) / Cfg::kTileRows) * Cfg::kTileRows;
+    const int rows_per_split = (nt + n_splits - 1) / n_splits;    // the last TMA tile of a split may be partial
     if (rows_per_split > (1 << kIdxBits)) { mpl_set_error("hamming: split of %d rows exceeds 2^20", rows_per_split); return MPL_ERR_LIMIT; }
     const int eff_splits = (nt + rows_per_split - 1) / rows_per_split;
     if (eff_splits != n_splits) { mpl_set_error("hamming: internal split mismatch %d vs %d", eff_splits, n_splits); return MPL_ERR_BAD_ARG; }
@@ -315,22 +314,30 @@ int tile_rows(int w16) { return kTileBytes / (16 * w16); }
 
 }  // namespace
 
-// Number of train splits so that grid = q-blocks x splits is ~4 CTAs per SM (a multiple of the SM
-// count when the split count is free), every split <= 2^20 rows and a whole number of TMA tiles.
+// Number of train splits.  CTAs that share an SM share its integer pipes, so the scan time is the largest number of train
+// rows any SM is handed: ceil(q-blocks x splits / SMs) x (rows per split + a per-CTA prologue worth ~24 rows).  Pick the
+// split count that minimises it with at least two CTAs per SM when the problem allows (latency hiding); C1: 8 q-blocks x
+// 37 splits = 2 x 148 CTAs of 222 rows.  Every split holds <= 2^20 rows (index bits of the in-kernel key).
 int mpl_hamming_pick_splits(int nq, int nt, int w16, int sm_count)
 {
     const int qblocks = (nq + queries_per_cta(w16) - 1) / queries_per_cta(w16);
-    const int tr = tile_rows(w16);
-    int want = (4 * sm_count + qblocks - 1) / qblocks;
-    const int max_splits = (nt + tr - 1) / tr;
     const int min_splits = (nt + (1 << kIdxBits) - 1) / (1 << kIdxBits);
-    if (want > max_splits) want = max_splits;
-    if (want < min_splits) want = min_splits;
-    if (want < 1) want = 1;
-    // normalise so that ceil(nt / rows_per_split) == splits after rounding rows_per_split up to a tile
-    int rps = (nt + want - 1) / want;
-    rps = ((rps + tr - 1) / tr) * tr;
-    return (nt + rps - 1) / rps;
+    int max_splits = nt / 32;                                   // >= 32 rows per split
+    if (max_splits < min_splits) max_splits = min_splits;
+    if (max_splits < 1) max_splits = 1;
+    const int cap = (8 * sm_count + qblocks - 1) / qblocks;       // no point beyond 8 CTAs per SM
+    if (max_splits > cap && cap >= min_splits) max_splits = cap;
+    long long best_cost = -1; int best = min_splits > 0 ? min_splits : 1;
+    for (int sp = best; sp <= max_splits; ++sp) {
+        const int rps = (nt + sp - 1) / sp;
+        if ((nt + rps - 1) / rps != sp) continue;                 // not a reachable split count
+        const long long ctas = (long long)qblocks * sp;
+        const long long per_sm = (ctas + sm_count - 1) / sm_count;
+        long long cost = per_sm * (rps + 24);
+        if (per_sm < 2 && sp < max_splits) cost += cost / 2;      // a lone CTA per SM cannot hide its own latencies
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = sp; }
+    }
+    return best;
 }
 
 int mpl_launch_pack_rows_u8(const uint8_t* src, int n, size_t src_step, int nbytes_used, uint8_t* dst, int w16,
