@@ -136,16 +136,26 @@ __device__ __forceinline__ float sampson_err(const double (&E)[9], const double4
     return __double2float_rn(__ddiv_rn(__dmul_rn(r, r), den));
 }
 
+// Few models (one image pair: ~5 000; a refit: <= 10) leave most SMs idle and every thread with a long latency-bound
+// loop, so the correspondences are then split over the S CTAs of a thread-block cluster (S = 2, 4, 8): CTA rank r scores
+// the models of its block against correspondences [n r / S, n (r+1) / S), and rank 0 adds the partial (count, sum) pairs
+// in rank order through distributed shared memory -- deterministic, no scratch, no atomics.  S = 1 (the C3 regime, one
+// CTA per 128 models) is the plain sequential sum.
 __global__ void __launch_bounds__(kScoreThreads)
 sampson_score_kernel(const double* __restrict__ models, int m, const double4* __restrict__ corr, int n, double th2,
-                     int32_t* __restrict__ counts, double* __restrict__ errsums)
+                     int32_t* __restrict__ counts, double* __restrict__ errsums, int S)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double4* tile = reinterpret_cast<double4*>(smem_raw);                 // [kScoreStages][kChunk]
     __shared__ __align__(8) uint64_t full_bar[kScoreStages];
+    __shared__ double part_sum[kScoreThreads];
+    __shared__ int part_good[kScoreThreads];
     const int tid = threadIdx.x;
-    const int mi = blockIdx.x * kScoreThreads + tid;
-    const int n_chunks = (n + kChunk - 1) / kChunk;
+    const int rank = S > 1 ? (int)(blockIdx.x % S) : 0;
+    const int mi = (int)(blockIdx.x / S) * kScoreThreads + tid;
+    const int i_lo = (int)((long long)n * rank / S), i_hi = (int)((long long)n * (rank + 1) / S);
+    const int n_loc = i_hi - i_lo;
+    const int n_chunks = (n_loc + kChunk - 1) / kChunk;
     if (tid == 0) {
         for (int s = 0; s < kScoreStages; ++s) mbar_init(&full_bar[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -153,9 +163,9 @@ sampson_score_kernel(const double* __restrict__ models, int m, const double4* __
     __syncthreads();
     auto issue = [&](int ci) {
         const int s = ci % kScoreStages;
-        const int cnt = min(kChunk, n - ci * kChunk);
+        const int cnt = min(kChunk, n_loc - ci * kChunk);
         mbar_expect_tx(&full_bar[s], (uint32_t)cnt * 32u);
-        tma_bulk_g2s(tile + s * kChunk, corr + (size_t)ci * kChunk, (uint32_t)cnt * 32u, &full_bar[s]);
+        tma_bulk_g2s(tile + s * kChunk, corr + i_lo + (size_t)ci * kChunk, (uint32_t)cnt * 32u, &full_bar[s]);
     };
     if (tid == 0) for (int i = 0; i < kScoreStages && i < n_chunks; ++i) issue(i);
 
@@ -168,7 +178,7 @@ sampson_score_kernel(const double* __restrict__ models, int m, const double4* __
         const int s = ci % kScoreStages;
         mbar_wait(&full_bar[s], (uint32_t)((ci / kScoreStages) & 1));
         const double4* t = tile + s * kChunk;
-        const int cnt = min(kChunk, n - ci * kChunk);
+        const int cnt = min(kChunk, n_loc - ci * kChunk);
 #pragma unroll 4
         for (int i = 0; i < cnt; ++i) {
             const float e = sampson_err(E, t[i]);                        // two LDS.128, warp-wide broadcast
@@ -177,6 +187,24 @@ sampson_score_kernel(const double* __restrict__ models, int m, const double4* __
         }
         __syncthreads();
         if (tid == 0 && ci + kScoreStages < n_chunks) issue(ci + kScoreStages);
+    }
+    if (S > 1) {
+        part_good[tid] = good; part_sum[tid] = esum;
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (rank == 0) {
+            for (int r = 1; r < S; ++r) {
+                uint32_t ag, as;
+                asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ag) : "r"(smem_u32(&part_good[tid])), "r"(r));
+                asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(as) : "r"(smem_u32(&part_sum[tid])), "r"(r));
+                int g2; double s2;
+                asm volatile("ld.shared::cluster.s32 %0, [%1];" : "=r"(g2) : "r"(ag) : "memory");
+                asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(s2) : "r"(as) : "memory");
+                good += g2; esum = __dadd_rn(esum, s2);
+            }
+        }
+        // the partials of ranks > 0 must stay alive until rank 0 has read them
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (rank != 0) return;
     }
     if (mi < m) { counts[mi] = good; if (errsums) errsums[mi] = esum; }
 }
@@ -279,8 +307,17 @@ int mpl_launch_sampson_score(const double* models, int m, const void* corr, int 
         MPL_CUDA_CHECK(cudaFuncSetAttribute(sampson_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
+    const int blocks = (m + kScoreThreads - 1) / kScoreThreads;
+    int S = 1;                                                    // cluster size: fill ~2 CTAs per SM, >= 64 correspondences per rank
+    while (S < 8 && blocks * S < 2 * 148 && n / (2 * S) >= 64) S *= 2;
     MplProfScope prof(MPL_PROF_SCORE, st);
-    sampson_score_kernel<<<(m + kScoreThreads - 1) / kScoreThreads, kScoreThreads, smem, st>>>(models, m, (const double4*)corr, n, th * th, counts, errsums);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(blocks * S)); cfg.blockDim = dim3(kScoreThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    MPL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampson_score_kernel, models, m, (const double4*)corr, n, th * th, counts, errsums, S));
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
 }
