@@ -234,11 +234,11 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
 
     lib.mpl_prof_enable(0)
     barrier = (lambda: dist.barrier()) if world > 1 else None
-    # Single GPU: the step (memset + 7 kernels of the library, all enqueued on the caller's stream) is captured once
-    # into a CUDA graph and replayed -- same kernels, same arguments, no per-launch host gaps.
+    # The step (memset + 7 kernels of the library, all enqueued on the caller's stream, + the all-gather at N > 1) is
+    # captured once into a CUDA graph and replayed -- same kernels, same arguments, no per-launch host gaps.
     run = step
     graphed = False
-    if world == 1 and os.environ.get("MPL_BENCH_NO_GRAPH") is None:
+    if os.environ.get("MPL_BENCH_NO_GRAPH") is None:                # N > 1: the NCCL all-gather is captured with the kernels
         try:
             step()
             lc = g.launches()
@@ -253,6 +253,11 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
         except Exception as e:                                     # capture not possible: time the plain launches
             sys.stderr.write("bench: CUDA graph capture failed (%s); timing plain launches\n" % e)
             run, graphed = step, False
+    if world > 1:                                                  # every rank replays, or none does
+        flag = torch.tensor([1 if graphed else 0], device=g.dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            run, graphed = step, False
     l0 = g.launches()
     with ClockSampler(g.dev.index) as cs:
         ms = g.time_steps(run, steps, warmup, barrier)
@@ -260,7 +265,7 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
         # the timed region lasts a few ms: keep the same work running until NVML has sampled it.  Every rank must issue
         # the SAME number of steps (they contain a collective), so the padding is a fixed count, not a deadline.
         for _ in range(600 if world > 1 else 0):
-            step()
+            run()
         t_end = time.time() + 1.0
         while world == 1 and len(cs.samples) < 8 and time.time() < t_end:
             run()
@@ -612,7 +617,8 @@ def main():
             "metric": METRIC, "value": pairs / (step_ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16/tf32 tensor-core ranking, exact fp32 re-rank)",
             "data": "synthetic",
-            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else "train rows sharded over %d ranks, NCCL all-gather of top-2 keys + merge" % world),
+            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else "train rows sharded over %d ranks, NCCL all-gather of top-2 keys + merge" % world,
+                           launch="CUDA graph replay of the step" if r.get("graphed") else "stream launches"),
             "clocks": r["clocks"],
             "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=ncu_traffic("l2_tc_rank_kernel"),
                              kernel=kname, kernel_ms=k_ms,
