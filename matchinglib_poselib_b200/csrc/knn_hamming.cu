@@ -250,7 +250,7 @@ __global__ void merge_top2_kernel(const ulonglong2* __restrict__ partial, int n_
 }
 
 // Lowe ratio test + cv::DMatch emission on merged keys (matchers.cpp:601-625; nmslib_matchers.h:399-421), order-preserving:
-// one CTA, every thread owns a contiguous chunk of queries (count, block scan, write).  out = 16-byte header (count) followed
+// one CTA, every warp owns a contiguous chunk of queries (ballot counts, block scan, write).  out = 16-byte header (count) followed
 // by the matches in ascending queryIdx, so one D2H copy brings back both.  ratio_test == 0: every query emits its nearest.
 // An absent second neighbour compares as FLT_MAX / INT_MAX, like the idx/dist arrays of merge_top2_kernel would.
 __global__ void __launch_bounds__(1024)
@@ -258,8 +258,10 @@ ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test,
 {
     __shared__ int warp_sums[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int per = (nq + 1023) / 1024;
-    const int start = min(nq, tid * per), end = min(nq, start + per);
+    // warp w owns the contiguous query range [w * per, (w + 1) * per), per a multiple of 32: lanes read consecutive keys
+    // (coalesced 512 B), ballots give the order inside the warp
+    const int per = ((nq + 1023) / 1024) * 32;
+    const int start = min(nq, wid * per), end = min(nq, start + per);
     auto dist_f = [&](mpl_key64 k) {
         if (k == MPL_KEY_INVALID) return is_float ? 3.402823466e+38f : (float)0x7FFFFFFF;
         const uint32_t d = (uint32_t)(k >> 32);
@@ -267,11 +269,11 @@ ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test,
     };
     auto passes = [&](const ulonglong2 k) { return !ratio_test || dist_f(k.x) < 0.75f * dist_f(k.y); };
     int sum = 0;
-    for (int i = start; i < end; ++i) sum += passes(keys[i]) ? 1 : 0;
-    int x = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-    if (lane == 31) warp_sums[wid] = x;
+    for (int i = start; i < end; i += 32) {
+        const bool p = (i + lane < end) && passes(keys[i + lane]);
+        sum += __popc(__ballot_sync(0xffffffffu, p));
+    }
+    if (lane == 0) warp_sums[wid] = sum;
     __syncthreads();
     if (wid == 0) {
         int w = warp_sums[lane];
@@ -280,13 +282,17 @@ ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test,
         warp_sums[lane] = w;
     }
     __syncthreads();
-    int pos = (wid ? warp_sums[wid - 1] : 0) + x - sum;
-    for (int i = start; i < end; ++i) {
-        const ulonglong2 k = keys[i];
-        if (!passes(k)) continue;
-        const int ti = k.x == MPL_KEY_INVALID ? -1 : (int)(uint32_t)(k.x & 0xFFFFFFFFull);
-        out[1 + pos] = make_int4(i, ti, -1, __float_as_int(dist_f(k.x)));      // queryIdx, trainIdx, imgIdx = -1, distance
-        ++pos;
+    int pos = wid ? warp_sums[wid - 1] : 0;
+    for (int i = start; i < end; i += 32) {
+        ulonglong2 k = make_ulonglong2(MPL_KEY_INVALID, MPL_KEY_INVALID);
+        const bool p = (i + lane < end) && passes(k = keys[i + lane]);
+        const unsigned b = __ballot_sync(0xffffffffu, p);
+        if (p) {
+            const int ti = k.x == MPL_KEY_INVALID ? -1 : (int)(uint32_t)(k.x & 0xFFFFFFFFull);
+            // queryIdx, trainIdx, imgIdx = -1, distance
+            out[1 + pos + __popc(b & ((1u << lane) - 1u))] = make_int4(i + lane, ti, -1, __float_as_int(dist_f(k.x)));
+        }
+        pos += __popc(b);
     }
     if (tid == 1023) out[0] = make_int4(pos, 0, 0, 0);
 }

@@ -30,7 +30,7 @@ namespace {
 
 struct PipeCounters { int n_matches; int first_failed_sample; };
 
-// One CTA, order-preserving compaction: every thread owns a contiguous chunk of queries (count, block scan, write).
+// One CTA, order-preserving compaction: every warp owns a contiguous chunk of queries (ballot counts, block scan, write).
 // Hamming keys are (dist << 32 | trainIdx); a query passes iff (float)d0 < 0.75f * (float)d1 (ratio != 0), or always.
 // Writes the cv::DMatch records AND the 32-byte correspondence records (x1, y1, x2, y2) of the survivors.
 __global__ void __launch_bounds__(1024)
@@ -40,8 +40,8 @@ ratio_compact_gather_kernel(const ulonglong2* __restrict__ keys, int nq, int rat
 {
     __shared__ int warp_sums[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int per = (nq + 1023) / 1024;
-    const int start = min(nq, tid * per), end = min(nq, start + per);
+    const int per = ((nq + 1023) / 1024) * 32;                   // queries per warp, lanes read consecutive keys
+    const int start = min(nq, wid * per), end = min(nq, start + per);
     auto passes = [&](const ulonglong2 k) {
         if (k.x == MPL_KEY_INVALID) return false;
         if (!ratio_test) return true;
@@ -49,11 +49,11 @@ ratio_compact_gather_kernel(const ulonglong2* __restrict__ keys, int nq, int rat
         return (float)(uint32_t)(k.x >> 32) < 0.75f * (float)(uint32_t)(k.y >> 32);
     };
     int sum = 0;
-    for (int i = start; i < end; ++i) sum += passes(keys[i]) ? 1 : 0;
-    int x = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-    if (lane == 31) warp_sums[wid] = x;
+    for (int i = start; i < end; i += 32) {
+        const bool p = (i + lane < end) && passes(keys[i + lane]);
+        sum += __popc(__ballot_sync(0xffffffffu, p));
+    }
+    if (lane == 0) warp_sums[wid] = sum;
     __syncthreads();
     if (wid == 0) {
         int w = warp_sums[lane];
@@ -62,16 +62,20 @@ ratio_compact_gather_kernel(const ulonglong2* __restrict__ keys, int nq, int rat
         warp_sums[lane] = w;
     }
     __syncthreads();
-    int pos = (wid ? warp_sums[wid - 1] : 0) + x - sum;
-    for (int i = start; i < end; ++i) {
-        const ulonglong2 k = keys[i];
-        if (!passes(k)) continue;
-        const int ti = (int)(uint32_t)(k.x & 0xFFFFFFFFull);
-        mpl_dmatch m; m.queryIdx = i; m.trainIdx = ti; m.imgIdx = -1; m.distance = (float)(uint32_t)(k.x >> 32);
-        matches[pos] = m;
-        const double2 a = pts1[i], b = pts2[ti];
-        corr[pos] = make_double4(a.x, a.y, b.x, b.y);
-        ++pos;
+    int pos = wid ? warp_sums[wid - 1] : 0;
+    for (int i = start; i < end; i += 32) {
+        ulonglong2 k = make_ulonglong2(MPL_KEY_INVALID, MPL_KEY_INVALID);
+        const bool p = (i + lane < end) && passes(k = keys[i + lane]);
+        const unsigned b = __ballot_sync(0xffffffffu, p);
+        if (p) {
+            const int o = pos + __popc(b & ((1u << lane) - 1u));
+            const int ti = (int)(uint32_t)(k.x & 0xFFFFFFFFull);
+            mpl_dmatch m; m.queryIdx = i + lane; m.trainIdx = ti; m.imgIdx = -1; m.distance = (float)(uint32_t)(k.x >> 32);
+            matches[o] = m;
+            const double2 a = pts1[i + lane], c = pts2[ti];
+            corr[o] = make_double4(a.x, a.y, c.x, c.y);
+        }
+        pos += __popc(b);
     }
     if (tid == 1023) { ctr->n_matches = pos; ctr->first_failed_sample = 0x7FFFFFFF; }
 }
