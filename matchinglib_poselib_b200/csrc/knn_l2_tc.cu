@@ -194,11 +194,13 @@ __device__ __forceinline__ void write_aug(uint4* dst, bool is_t, float norm, boo
 __global__ void __launch_bounds__(256)
 l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const float* __restrict__ q, int nq, size_t q_ld, int dim,
                     void* __restrict__ tp, void* __restrict__ qp, int kp16, float* __restrict__ tnorm, int nt_pad,
-                    float* __restrict__ qnorm, uint4* __restrict__ taug, uint4* __restrict__ qaug, TcHeader* hdr)
+                    float* __restrict__ qnorm, uint4* __restrict__ taug, uint4* __restrict__ qaug, TcHeader* hdr,
+                    uint32_t* __restrict__ gthr, int n_gthr)
 {
     const int lane = threadIdx.x & 31;
     const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
     const int total = nt_pad + nq;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = 0xFFFFFFFFu;   // "nothing published"
     const bool vec_ok = (((uintptr_t)q | (uintptr_t)t) & 15) == 0 && ((q_ld | t_ld) & 3) == 0;
     unsigned inexact = 0;
     bool nonint = false;
@@ -291,6 +293,7 @@ struct TcParams {
     int max_slots;                   // candidate slots per query block
     int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
     uint4* cand;                     // [qblock][slot][LPS][BM rows][2 x uint4] = 4 scores + 4 train indices
+    uint32_t* gthr;                  // [NQB * BM] per query: smallest list threshold any CTA has published (order-preserving uint)
     const TcHeader* hdr;
 };
 
@@ -360,9 +363,15 @@ __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
 // filter or evicted by the drain scores >= the list's final NC-th best: the certificate's tau stays valid.  Entries are
 // drained in arrival (= ascending train index) order with strict '<', i.e. the list is exactly what one-by-one
 // insertion would have produced (lower train index wins ties).
+// float <-> uint whose unsigned order is the float order (scores can be negative): atomicMin target
+__device__ __forceinline__ uint32_t ord_of(float f) { const uint32_t b = __float_as_uint(f); return b ^ ((b >> 31) ? 0xFFFFFFFFu : 0x80000000u); }
+__device__ __forceinline__ float ord_to_float(uint32_t o) { return __uint_as_float((o & 0x80000000u) ? (o ^ 0x80000000u) : ~o); }   // 0xFFFFFFFF -> NaN (ignored by fminf)
+
 template <class List>
 struct EpiState {
     List L;
+    uint32_t* gq;                    // this query's entry of TcParams::gthr
+    float gpub;                      // what this thread last published there
     float thr;                       // filter threshold: min(own NC-th best, partner list's published NC-th best), possibly stale
     float ext;                       // the partner's published value as read at the start of the tile
     uint32_t pbase, pptr;            // shared-memory byte addresses: first entry of this thread / next free entry
@@ -384,6 +393,9 @@ __device__ __forceinline__ void epi_drain(EpiState<List>& S)
     S.pptr = S.pbase;
     S.thr = fminf(S.L.last(), S.ext);
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pub), "r"(__float_as_uint(S.L.last())), "r"(S.qb) : "memory");
+    // ... and to the CTAs that cover other train ranges of the same query block (and the other UMMA half): every list's
+    // last entry bounds the query's final k-th best from above, so all lists may filter with the smallest one published
+    if (S.L.last() < S.gpub) { S.gpub = S.L.last(); atomicMin(S.gq, ord_of(S.gpub)); }
 }
 
 // one bit per group of 4 columns whose minimum is below thr: sign(min - thr) (FADD on the fma pipe) funnelled into the mask
@@ -451,7 +463,7 @@ __device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t tad
 // the tile's MMAs, so it is split).  The whole warp runs the loop (uniform control flow), one elected lane issues.
 // Accumulators are handed over per M block: t_full / t_empty index = accumulator buffer * 2 + m; a B slab is released
 // when BOTH issuers' MMAs on it have retired (b_empty counts 2 commits), likewise the resident A block (a_empty).
-template <int MODE>   // 0 = bf16 (kind::f16), 1 = tf32
+template <int MODE, int SPS>   // MODE 0 = bf16 (kind::f16), 1 = tf32; SPS = K slabs per B ring stage (one barrier round trip per stage)
 __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_addr, uint32_t aa_addr,
                                                uint32_t b_addr, uint32_t tmem_base, uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full,
                                                uint64_t* b_empty, uint64_t* t_full, uint64_t* t_empty)
@@ -478,26 +490,29 @@ __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1
         const uint32_t d = tmem_base + b * 256 + m * 128;
         MPL_TWAIT(w_te, mbar_wait(&t_empty[b * 2 + m], ((it >> 1) & 1) ^ 1));    // epilogue drained this accumulator block
         tc_fence_after();
-        for (int s = 0; s < n_slabs; ++s) {
+        for (int s = 0; s < n_slabs; s += SPS) {
             MPL_TWAIT(w_bf, mbar_wait(&b_full[stage], sphase));
             tc_fence_after();
 #ifdef MPL_TC_TRACE
             tq = clock64();
 #endif
             if (elect_one()) {
-                const uint32_t sb = b_addr + stage * STAGE_BYTES;
-                const uint64_t bd = hi128 | (uint64_t)(sb >> 4);
-                const uint64_t ad = ad0 + (uint64_t)(s * (A_SLAB >> 4));
+                const uint32_t sb = b_addr + stage * (SPS * B_SLAB + BN * AUG_BYTES);
                 if (s == 0) {                                                    // aug K step first: D = |t|^2 (overwrites)
-                    const uint64_t bda = hi32 | (uint64_t)((sb + B_SLAB) >> 4);
+                    const uint64_t bda = hi32 | (uint64_t)((sb + SPS * B_SLAB) >> 4);
                     if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
                 }
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {                                    // 4 x 32 bytes of K per slab row
-                    if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                for (int j = 0; j < SPS; ++j) {
+                    const uint64_t bd = hi128 | (uint64_t)((sb + j * B_SLAB) >> 4);
+                    const uint64_t ad = ad0 + (uint64_t)((s + j) * (A_SLAB >> 4));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {                                // 4 x 32 bytes of K per slab row
+                        if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                    }
                 }
-                tc_commit(&b_empty[stage]);                                      // slab free once both issuers' MMAs retire
-                if (s == n_slabs - 1) {
+                tc_commit(&b_empty[stage]);                                      // stage free once both issuers' MMAs retire
+                if (s + SPS >= n_slabs) {
                     tc_commit(&t_full[b * 2 + m]);
                     if (u + 1 < u1 && last_of_qb) tc_commit(a_empty);            // only when the producer will wait for it
                 }
@@ -525,23 +540,26 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wg = (warp - 4) >> 2, m = wg & 1, hf = wg >> 1, quad = warp & 3, row = quad * 32 + lane;
     EpiState<List> S;
-    S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
+    S.L.reset(); S.thr = INFINITY; S.ext = INFINITY; S.gpub = INFINITY;
     S.pbase = S.pptr = pend_s + (uint32_t)(threadIdx.x - 128) * 8u;
     S.pub = share_s + 8u * (uint32_t)(hf * BM + m * UM + row);
     const uint32_t partner = share_s + 8u * (uint32_t)((hf ^ 1) * BM + m * UM + row);
     int tile = (int)(u0 - (u0 / p.NT) * p.NT);
     S.qb = (int)(u0 / p.NT);
+    S.gq = p.gthr + (size_t)S.qb * BM + m * UM + row;
     unsigned it = 0;
     auto flush = [&]() {
         epi_drain(S);
         const int slot = (int)blockIdx.x - tc_owner((long long)S.qb * p.NT, p.U, G);
         S.L.store(p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2);
-        S.L.reset(); S.thr = INFINITY; S.ext = INFINITY;
+        S.L.reset(); S.thr = INFINITY; S.ext = INFINITY; S.gpub = INFINITY;
+        S.gq += BM;                                                              // flush() ends a query block
     };
     const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + m * 128 + hf * 64;
     for (long long u = u0; u < u1; ++u, ++it) {
         const uint32_t b = it & 1;
         const uint32_t taddr = tbase + b * 256;
+        const uint32_t gv = __ldcg(S.gq);                                        // issued before the wait: latency hidden
         mbar_wait(&t_full[b * 2 + m], (it >> 1) & 1);
         tc_fence_after();
         uint32_t ra[32], rb[32];
@@ -555,8 +573,9 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         // query-block tag guards against a stale value from the partner's previous segment.
         float ox; int oq;
         asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(partner) : "memory");
-        if (EXACT) ox = __fadd_rn(ox, 1.0f);
-        S.ext = (oq == S.qb) ? ox : INFINITY;
+        float gx = ord_to_float(gv);                                             // NaN while nothing is published
+        if (EXACT) { ox = __fadd_rn(ox, 1.0f); gx = __fadd_rn(gx, 1.0f); }
+        S.ext = fminf((oq == S.qb) ? ox : INFINITY, gx);
         S.thr = fminf(S.thr, S.ext);
         tc_wait_ld_regs(ra); tc_wait_ld_regs(rb);
         unsigned mask = group_mask(ra, S.thr) | (group_mask(rb, S.thr) << 8);
@@ -596,7 +615,12 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     unsigned char* sA = smem;                                    // n_slabs x 32 KB
     unsigned char* sAa = smem + n_slabs * A_SLAB;                // 8 KB
     unsigned char* sB = sAa + A_AUG;                             // ring of n_stages x 20 KB
-    int n_stages = (SMEM_DATA - n_slabs * A_SLAB - A_AUG) / STAGE_BYTES;
+    // B ring stage = `sps` K slabs of one train tile + the tile's aug slab; two slabs per stage (a whole tile at dim <= 128
+    // in bf16 mode) when at least 3 such stages fit: half the barrier round trips and commits on the issuers' critical path
+    const int ring_bytes = SMEM_DATA - n_slabs * A_SLAB - A_AUG;
+    const int sps = ((n_slabs & 1) == 0 && ring_bytes / (2 * B_SLAB + BN * AUG_BYTES) >= 3) ? 2 : 1;
+    const int stage_bytes = sps * B_SLAB + BN * AUG_BYTES;
+    int n_stages = ring_bytes / stage_bytes;
     if (n_stages > MAX_STAGES) n_stages = MAX_STAGES;
     const int G = gridDim.x;
     const long long u0 = (long long)blockIdx.x * p.U / G, u1 = (long long)(blockIdx.x + 1) * p.U / G;
@@ -640,12 +664,13 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
                 __syncwarp();
                 ++a_cnt; cur_qb = qb;
             }
-            for (int s = 0; s < n_slabs; ++s) {
+            for (int s = 0; s < n_slabs; s += sps) {
                 mbar_wait(&b_empty[stage], sphase ^ 1);
                 if (elect_one()) {
-                    mbar_expect_tx(&b_full[stage], (uint32_t)(B_SLAB + (s == 0 ? BN * AUG_BYTES : 0)));
-                    tma_load_2d(sB + stage * STAGE_BYTES, mapB, s * KS, tile * BN, &b_full[stage]);
-                    if (s == 0) tma_load_2d(sB + stage * STAGE_BYTES + B_SLAB, mapBa, 0, tile * BN, &b_full[stage]);
+                    unsigned char* dst = sB + stage * stage_bytes;
+                    mbar_expect_tx(&b_full[stage], (uint32_t)(sps * B_SLAB + (s == 0 ? BN * AUG_BYTES : 0)));
+                    for (int j = 0; j < sps; ++j) tma_load_2d(dst + j * B_SLAB, mapB, (s + j) * KS, tile * BN, &b_full[stage]);
+                    if (s == 0) tma_load_2d(dst + sps * B_SLAB, mapBa, 0, tile * BN, &b_full[stage]);
                 }
                 __syncwarp();
                 if (++stage == n_stages) { stage = 0; sphase ^= 1; }
@@ -654,10 +679,11 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     } else if (warp == 1 || warp == 3) {
         // ===== MMA issuers: warp 1 -> UMMA M block 0, warp 3 -> M block 1 =====
         const int m = warp >> 1;
-        if (tf32) mma_issue_loop<1>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
-                                    a_full, a_empty, b_full, b_empty, t_full, t_empty);
-        else      mma_issue_loop<0>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base,
-                                    a_full, a_empty, b_full, b_empty, t_full, t_empty);
+#define MPL_ISSUE(MODE, SPS) mma_issue_loop<MODE, SPS>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base, \
+                                                       a_full, a_empty, b_full, b_empty, t_full, t_empty)
+        if (tf32) { if (sps == 2) MPL_ISSUE(1, 2); else MPL_ISSUE(1, 1); }
+        else      { if (sps == 2) MPL_ISSUE(0, 2); else MPL_ISSUE(0, 1); }
+#undef MPL_ISSUE
     } else if (warp >= 4) {
         // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile =====
         // Exact-integer mode (bf16-exact integer data, e.g. OpenCV SIFT): the scores are exact, so sorted top-2 lists give
@@ -832,7 +858,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
 struct TcPlan {
     int NQB, NT, G, max_slots, kp16, kp32;
     long long U;
-    size_t off_tnorm, off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_list, off_part, total;
+    size_t off_tnorm, off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_list, off_part, off_gthr, total;
 };
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -861,6 +887,7 @@ TcPlan make_plan(int nq, int nt, int dim, int sm_count)
     P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * BM * 32);
     P.off_list = o;  o = align256(o + (size_t)nq * 4);
     P.off_part = o;  o = align256(o + mpl_l2_list_scratch_entries(nq, sm_count) * 16);
+    P.off_gthr = o;  o = align256(o + (size_t)P.NQB * BM * 4);
     P.total = o;
     return P;
 }
@@ -915,6 +942,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     uint4* cand = (uint4*)(base + P.off_cand);
     int* flist = (int*)(base + P.off_list);
     mpl_key64* part = (mpl_key64*)(base + P.off_part);
+    uint32_t* gthr = (uint32_t*)(base + P.off_gthr);
 
     static bool attr_set = false;
     if (!attr_set) {
@@ -939,7 +967,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MplProfScope prof(MPL_PROF_L2_PREP, st);
         const int rows = P.NT * BN + nq;
         int blocks = (rows + 7) / 8; if (blocks > sm_count * 16) blocks = sm_count * 16;
-        l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr);
+        l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr, gthr, P.NQB * BM);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         l2_prep_tf32_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
@@ -948,7 +976,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MplProfScope prof(MPL_PROF_L2_TC, st);
         TcParams prm;
         prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots;
-        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.hdr = hdr;
+        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
         l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }

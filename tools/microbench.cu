@@ -235,13 +235,15 @@ int main()
             printf(", \"umma_m128_n%d_k16_bf16_chains%d_cycles_per_mma\": %.1f", N, chains, (double)h[0] / n);
         }
     }
-    for (int ce : {1, 2}) {
-        const int n = 2000;
-        long long* cyc = (long long*)buf;
-        k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, 128, 2, ce);
-        if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
-        long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
-        printf(", \"umma_m128_n128_commit_every_%d_mma_cycles_per_mma\": %.1f", 4 * ce, (double)h[0] / n);
+    for (int chains : {1, 2}) {
+        for (int ce : {1, 2, 4, 8, 16}) {
+            const int n = 4096;
+            long long* cyc = (long long*)buf;
+            k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, 128, chains, ce);
+            if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
+            long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
+            printf(", \"umma_m128_n128_chains%d_commit_every_%d_mma_cycles_per_mma\": %.1f", chains, 4 * ce, (double)h[0] / n);
+        }
     }
     printf("}\n");
     return 0;
