@@ -556,11 +556,20 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         S.gq += BM;                                                              // flush() ends a query block
     };
     const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + m * 128 + hf * 64;
+#ifdef MPL_TC_TRACE
+    long long e_wait = 0, e_fast = 0, e_slow = 0, e_start = clock64(), e_q; int e_groups = 0;
+#endif
     for (long long u = u0; u < u1; ++u, ++it) {
         const uint32_t b = it & 1;
         const uint32_t taddr = tbase + b * 256;
         const uint32_t gv = __ldcg(S.gq);                                        // issued before the wait: latency hidden
+#ifdef MPL_TC_TRACE
+        e_q = clock64();
+#endif
         mbar_wait(&t_full[b * 2 + m], (it >> 1) & 1);
+#ifdef MPL_TC_TRACE
+        e_wait += clock64() - e_q; e_q = clock64();
+#endif
         tc_fence_after();
         uint32_t ra[32], rb[32];
         tc_ld32(taddr, ra);
@@ -580,13 +589,24 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         tc_wait_ld_regs(ra); tc_wait_ld_regs(rb);
         unsigned mask = group_mask(ra, S.thr) | (group_mask(rb, S.thr) << 8);
         mask = __reduce_or_sync(0xffffffffu, mask);                               // warp-uniform: tcgen05.ld is .aligned
+#ifdef MPL_TC_TRACE
+        e_fast += clock64() - e_q; e_q = clock64(); e_groups += __popc(mask);
+#endif
         epi_events(mask, col0, taddr, S);
+#ifdef MPL_TC_TRACE
+        e_slow += clock64() - e_q;
+#endif
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&t_empty[b * 2 + m]);
         if (++tile == p.NT) { flush(); tile = 0; ++S.qb; }
     }
     if (tile != 0) flush();
+#ifdef MPL_TC_TRACE
+    if (blockIdx.x == 3 && lane == 0 && (warp == 4 || warp == 19))
+        printf("epilogue warp %d: total %lld cycles for %lld tiles; wait t_full %lld  fast path %lld  slow path %lld  flagged groups %d\n",
+               warp, clock64() - e_start, u1 - u0, e_wait, e_fast, e_slow, e_groups);
+#endif
 }
 
 struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
