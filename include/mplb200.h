@@ -48,6 +48,12 @@ int         mpl_shutdown(void);
 const char* mpl_last_error(void);            /* thread-local text of the last failure */
 int         mpl_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
 long long   mpl_kernel_launch_count(void);   /* kernels launched by this library since mpl_init */
+/* Pinned host memory for descriptor matrices and keypoints (what cv::Mat::data should point at for the fastest calls):
+ * anonymous 2 MiB-aligned pages with MADV_HUGEPAGE, registered with cudaHostRegister.  Huge pages matter: with 4 KiB pages
+ * (cudaHostAlloc in an already fragmented process) the same host-to-device copy was measured at 25-40 GB/s, with 2 MiB
+ * pages at the PCIe link rate (52 GB/s).  Any host pointer is accepted by the entry points; this is the fast one. */
+void*       mpl_host_alloc(size_t bytes);    /* NULL on failure (mpl_last_error) */
+int         mpl_host_free(void* p);
 /* Device timers per kernel class (CUDA events on the launching stream), off by default.  Class ids:
  * 0 Hamming scan, 1 exact L2 scan, 2 tensor-core L2 ranking, 3 L2 re-rank/certify, 4 top-2 merge,
  * 5 five-point solve, 6 Sampson scoring, 7 L2 operand preparation.  mpl_prof_read waits for the recorded

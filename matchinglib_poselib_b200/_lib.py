@@ -31,6 +31,8 @@ SIGNATURES = {
     "mpl_last_error": (c_char_p, []),
     "mpl_device_info": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_kernel_launch_count": (c_ll, []),
+    "mpl_host_alloc": (c_void_p, [c_size_t]),
+    "mpl_host_free": (c_int, [c_void_p]),
     "mpl_prof_enable": (c_int, [c_int]),
     "mpl_prof_read": (c_int, [c_int, c_void_p, c_void_p]),
     "mpl_knn2_hamming": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),

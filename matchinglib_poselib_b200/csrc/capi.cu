@@ -7,6 +7,8 @@
 
 #include <atomic>
 #include <cstdarg>
+#include <map>
+#include <sys/mman.h>
 #include <cstring>
 #include <cstdlib>
 #include <climits>
@@ -174,6 +176,54 @@ extern "C" int mpl_shutdown(void)
     stage_release();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx.ready = false;
+    return MPL_OK;
+}
+
+// ---- huge-page pinned host memory -----------------------------------------------------------------
+static std::mutex g_host_mu;
+static std::map<void*, std::pair<void*, size_t>> g_host_allocs;      // user pointer -> (mmap base, mmap size)
+
+extern "C" void* mpl_host_alloc(size_t bytes)
+{
+    if (bytes == 0) { mpl_set_error("mpl_host_alloc: zero bytes"); return nullptr; }
+    {
+        std::lock_guard<std::mutex> g(g_mu);
+        if (mpl_ensure_ctx_locked()) return nullptr;
+    }
+    const size_t H = (size_t)2 << 20;
+    const size_t size = ((bytes + H - 1) / H) * H + H;
+    void* base = mmap(nullptr, size, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (base == MAP_FAILED) { mpl_set_error("mpl_host_alloc: mmap of %zu bytes failed", size); return nullptr; }
+    char* al = (char*)((((uintptr_t)base + H - 1) / H) * H);
+    const size_t usable = ((bytes + H - 1) / H) * H;
+    (void)madvise(al, usable, MADV_HUGEPAGE);                      // advisory: THP off just means 4 KiB pages
+    for (size_t o = 0; o < usable; o += 4096) al[o] = 0;           // first touch after the advice
+    cudaError_t e = cudaHostRegister(al, usable, cudaHostRegisterDefault);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        munmap(base, size);
+        mpl_set_error("mpl_host_alloc: cudaHostRegister failed (%s)", cudaGetErrorString(e));
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> g(g_host_mu);
+    g_host_allocs[al] = std::make_pair(base, size);
+    return al;
+}
+
+extern "C" int mpl_host_free(void* p)
+{
+    if (!p) return MPL_OK;
+    std::pair<void*, size_t> rec;
+    {
+        std::lock_guard<std::mutex> g(g_host_mu);
+        auto it = g_host_allocs.find(p);
+        if (it == g_host_allocs.end()) { mpl_set_error("mpl_host_free: unknown pointer"); return MPL_ERR_BAD_ARG; }
+        rec = it->second;
+        g_host_allocs.erase(it);
+    }
+    (void)cudaHostUnregister(p);
+    (void)cudaGetLastError();
+    munmap(rec.first, rec.second);
     return MPL_OK;
 }
 

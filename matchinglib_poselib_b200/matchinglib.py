@@ -21,6 +21,22 @@ _NP_TO_CV = {np.dtype(np.uint8): CV_8U, np.dtype(np.float32): CV_32F, np.dtype(n
              np.dtype(np.int8): 1, np.dtype(np.uint16): 2, np.dtype(np.int16): 3, np.dtype(np.int32): 4}
 
 
+def pinned_array(shape, dtype):
+    """numpy array in the library's huge-page pinned host memory (mpl_host_alloc): descriptor matrices and keypoints
+    placed here reach the GPU at the PCIe link rate.  Freed when the array (and every view of it) is gone."""
+    import weakref
+    lib = _lib.load()
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    ptr = lib.mpl_host_alloc(max(n, 1))
+    if not ptr:
+        raise MemoryError(_lib.last_error())
+    buf = (ctypes.c_char * max(n, 1)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    weakref.finalize(buf, lib.mpl_host_free, ctypes.c_void_p(ptr))
+    return arr
+
+
 def _mat_fields(m):
     """(data pointer keep-alive array, rows, cols, step, cv type) of a 2-D row-major array.
     Like the reference (matchers.cpp:567, 634) the data is read in place with cols as row length;

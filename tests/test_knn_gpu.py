@@ -222,3 +222,20 @@ def test_l2_tc_equals_exact_scan_at_c2_size(m):
         lib.mpl_set_l2_path(0)
     assert np.array_equal(idx, ei) and np.array_equal(dist.view(np.int32), ed.view(np.int32))
     assert mode == 0 and fb < 200
+
+
+def test_pinned_array_round_trip(m):
+    """mpl_host_alloc memory (huge pages + cudaHostRegister) is ordinary writable host memory that the entry points accept;
+    results equal those from pageable arrays, and the allocation is released with the array."""
+    import gc
+    q, t = datagen.sift_like(700, 900, 128, seed=12)
+    pq, pt = m.pinned_array(q.shape, q.dtype), m.pinned_array(t.shape, t.dtype)
+    pq[...] = q; pt[...] = t
+    assert pq.ctypes.data % (2 << 20) == 0
+    i1, d1 = m.knn2_l2(pq, pt, 2, False)
+    i2, d2 = m.knn2_l2(q, t, 2, False)
+    assert np.array_equal(i1, i2) and np.array_equal(d1.view(np.int32), d2.view(np.int32))
+    lib = m._lib.load()
+    assert lib.mpl_host_free(pq.ctypes.data + 64) != 0            # not an allocation base
+    del pq, pt
+    gc.collect()
