@@ -773,6 +773,38 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
                   const float* __restrict__ qnorm, const uint4* __restrict__ cand, int NT, long long U, int G, int max_slots,
                   long long train_offset, TcHeader* hdr, mpl_key64* __restrict__ keys_out, int* __restrict__ fallback_list)
 {
+    if (hdr->not_bf16_exact == 0 && hdr->not_integer == 0) {
+        // Exact-integer mode (the ranking kernel kept top-2 lists): every value is an integer that bf16 holds exactly.  If
+        // (|q| + |t|max)^2 < 2^24 as well, every product, partial sum and distance on both sides is an integer below 2^24,
+        // i.e. exact in fp32 in any order: score + |q|^2 IS the reference distance, the union of the lists' top-2 (ties
+        // kept by lowest train index) contains the two nearest, no margin is needed and no descriptor row is read again.
+        // One THREAD per query (the first ceil(nq / 256) blocks; the others have nothing to do), coalesced 32-byte
+        // records.  A query outside the bound cannot be certified from top-2 lists and takes the exact scan.
+        const int q1 = blockIdx.x * blockDim.x + threadIdx.x;
+        if (q1 >= nq) return;
+        const int qb1 = q1 / BM, row1 = q1 - qb1 * BM;
+        const int f1 = tc_owner((long long)qb1 * NT, U, G), l1 = tc_owner((long long)qb1 * NT + NT - 1, U, G);
+        const float qq1 = qnorm[q1];
+        const float sq1 = sqrtf(qq1), st1 = sqrtf(__uint_as_float(hdr->max_tnorm_bits));
+        if (!((sq1 + st1) * (sq1 + st1) < 16777216.f * 0.999f)) { fallback_list[atomicAdd(&hdr->fallback_count, 1u)] = q1; return; }
+        mpl_key64 k0 = MPL_KEY_INVALID, k1 = MPL_KEY_INVALID;
+        for (int sl = 0; sl < (l1 - f1 + 1) * LPS; ++sl) {
+            const uint4* rec = cand + (((size_t)qb1 * max_slots * LPS + sl) * BM + row1) * 2;
+            const uint4 sc = rec[0], id = rec[1];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int ti = (int)(e == 0 ? id.x : id.y);
+                if (ti < 0 || ti >= nt) continue;
+                float d = __fadd_rn(__uint_as_float(e == 0 ? sc.x : sc.y), qq1);
+                if (MODE == 1) d = sqrtf(d);
+                const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
+                const mpl_key64 hi = max(k0, key);
+                k0 = min(k0, key); k1 = min(k1, hi);
+            }
+        }
+        reinterpret_cast<ulonglong2*>(keys_out)[q1] = make_ulonglong2(k0, k1);
+        return;
+    }
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
@@ -786,36 +818,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     const float sq = sqrtf(qq), st = sqrtf(tmax);
     float eps = 1.2207031e-4f * (sq + st) * (sq + st);                            // 2^-13 (|q| + |t|max)^2
     if (hdr->not_bf16_exact) eps += 3.90625e-3f * sq * st;                        // 2^-8 |q| |t|max
-    // Exact-integer mode (the ranking kernel kept top-2 lists): every value is an integer that bf16 holds exactly.  If
-    // (|q| + |t|max)^2 < 2^24 as well, every product, partial sum and distance on both sides is an integer below 2^24,
-    // i.e. exact in fp32 in any order: score + |q|^2 IS the reference distance, the union of the lists' top-2 (ties kept
-    // by lowest train index) contains the two nearest, and no margin is needed.  Beyond that bound the top-2 lists
-    // cannot be certified and the query takes the exact scan.
-    const bool lists2 = hdr->not_bf16_exact == 0 && hdr->not_integer == 0;
-    const bool exact_ok = lists2 && (sq + st) * (sq + st) < 16777216.f * 0.999f;
-    if (exact_ok) eps = 0.f;
-    const int nc = lists2 ? 2 : NC;
-    if (exact_ok) {
-        // score + |q|^2 is the reference distance bit for bit: no row is read again.  Lane-local top-2 of the keys
-        // (dist, trainIdx), then a butterfly merge over the warp.
-        mpl_key64 k0 = MPL_KEY_INVALID, k1 = MPL_KEY_INVALID;
-        for (int c = lane; c < n_cand; c += 32) {
-            const int slot = c / NC, e = c - slot * NC;
-            if (e >= 2) continue;
-            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
-            const uint4 sc = rec[0], id = rec[1];
-            const int ti = (int)(e == 0 ? id.x : id.y);
-            if (ti < 0 || ti >= nt) continue;
-            float d = __fadd_rn(__uint_as_float(e == 0 ? sc.x : sc.y), qq);
-            if (MODE == 1) d = sqrtf(d);
-            const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
-            const mpl_key64 hi = max(k0, key);
-            k0 = min(k0, key); k1 = min(k1, hi);
-        }
-        warp_top2(k0, k1);
-        if (lane == 0) { keys_out[2 * (size_t)qi] = k0; keys_out[2 * (size_t)qi + 1] = k1; }
-        return;                                    // k1 invalid only if fewer than two train rows exist: nothing to certify
-    }
+    constexpr int nc = NC;                                        // general mode: top-4 lists, certificate below
     // pass A: the two smallest scores over all candidates, and tau = min over slots of the slot's 4th best
     float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
     for (int c = lane; c < n_cand; c += 32) {
@@ -864,7 +867,6 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         // certificate: every non-candidate has score >= tau, hence reference distance >= tau + |q|^2 - eps
         bool ok;
         if (b1 == MPL_KEY_INVALID) ok = (tau == INFINITY);                         // fewer than 2 train rows scanned in total
-        else if (lists2) ok = exact_ok;
         else {
             float d2 = __uint_as_float((uint32_t)(b1 >> 32));
             if (MODE == 1) d2 = __fmul_rn(d2, d2) * 1.000002f;                     // back to the squared domain, rounding margin
