@@ -195,10 +195,11 @@ __device__ __forceinline__ int list_splits(int n, int nt, int grid)
 template <int MODE>
 __global__ void __launch_bounds__(256)
 l2_exact_list_kernel(const float* __restrict__ q, const int* __restrict__ qlist, const unsigned* __restrict__ count, size_t q_ld,
-                     const float* __restrict__ t, int nt, size_t t_ld, int dim, long long train_offset, mpl_key64* __restrict__ partial)
+                     const float* __restrict__ t, int nt, size_t t_ld, int dim, long long train_offset, mpl_key64* __restrict__ partial,
+                     unsigned* __restrict__ ticket, ulonglong2* __restrict__ keys_out)
 {
     const int n = (int)*count;
-    if (n == 0) return;
+    if (n == 0) return;                                            // the usual case: one empty launch, nothing else
     const int rps = list_splits(n, nt, gridDim.x);
     const int splits = (nt + rps - 1) / rps;
     const int items = ((n + TQ - 1) / TQ) * splits;
@@ -206,19 +207,19 @@ l2_exact_list_kernel(const float* __restrict__ q, const int* __restrict__ qlist,
         l2_exact_tile<MODE>(q, n, qlist, q_ld, t, nt, t_ld, dim, rps, train_offset, w / splits, w % splits, partial);
         __syncthreads();
     }
-}
-
-__global__ void l2_list_merge_kernel(const int* __restrict__ qlist, const unsigned* __restrict__ count, int nt, int grid_of_scan,
-                                     const ulonglong2* __restrict__ partial, ulonglong2* __restrict__ keys_out)
-{
-    const int n = (int)*count;
-    if (n == 0) return;
-    const int rps = list_splits(n, nt, grid_of_scan);
-    const int splits = (nt + rps - 1) / rps;
-    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    // the last CTA to finish merges the per-split partial lists (no second launch)
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    const ulonglong2* part2 = reinterpret_cast<const ulonglong2*>(partial);
+    for (int p = threadIdx.x; p < n; p += blockDim.x) {
         mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
         for (int s = 0; s < splits; ++s) {
-            const ulonglong2 v = partial[(size_t)s * n + p];
+            const ulonglong2 v = __ldcg(part2 + (size_t)s * n + p);
             const mpl_key64 hi = max(b0, v.x);
             b0 = min(b0, v.x);
             b1 = min(min(b1, hi), v.y);
@@ -342,17 +343,12 @@ size_t mpl_l2_list_scratch_entries(int nq, int sm_count) { return (size_t)2 * sm
 
 int mpl_launch_l2_exact_list(const float* q, const int* qlist, const unsigned* count, size_t q_ld, const float* t, int nt, size_t t_ld,
                              int dim, int order_mode, long long train_offset, mpl_key64* partial, mpl_key64* keys_out, int sm_count,
-                             cudaStream_t st)
+                             unsigned* ticket, cudaStream_t st)
 {
     const int grid = 2 * sm_count;
-    {
-        MplProfScope prof(MPL_PROF_L2_EXACT, st);
-        if (order_mode == 0) l2_exact_list_kernel<0><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial);
-        else                 l2_exact_list_kernel<1><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial);
-        MPL_CUDA_CHECK(cudaGetLastError());
-        mpl_count_launch();
-    }
-    l2_list_merge_kernel<<<8, 256, 0, st>>>(qlist, count, nt, grid, (const ulonglong2*)partial, (ulonglong2*)keys_out);
+    MplProfScope prof(MPL_PROF_L2_EXACT, st);
+    if (order_mode == 0) l2_exact_list_kernel<0><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial, ticket, (ulonglong2*)keys_out);
+    else                 l2_exact_list_kernel<1><<<grid, 256, 0, st>>>(q, qlist, count, q_ld, t, nt, t_ld, dim, train_offset, partial, ticket, (ulonglong2*)keys_out);
     MPL_CUDA_CHECK(cudaGetLastError());
     mpl_count_launch();
     return MPL_OK;

@@ -72,7 +72,8 @@ struct TcHeader {                    // first 256 bytes of the scratch buffer (z
     unsigned max_tnorm_bits;         // max |t|^2 (float bits; non-negative floats order like uints)
     unsigned fallback_count;         // queries that failed certification
     unsigned not_integer;            // some value is not an integer: the exact-integer mode (top-2 lists, no certificate) is off
-    unsigned pad[60];
+    unsigned scan_ticket;            // CTAs of the fallback scan that have finished (the last one merges)
+    unsigned pad[59];
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------
@@ -1010,7 +1011,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
     return mpl_launch_l2_exact_list(d_q, flist, &hdr->fallback_count, q_ld, d_t, nt, t_ld, dim, sqrt_out ? 1 : 0, train_offset, part,
-                                    d_keys_out, sm_count, st);
+                                    d_keys_out, sm_count, &hdr->scan_ticket, st);
 }
 
 // Number of queries of the last call on this scratch buffer that took the exact-scan fallback (diagnostics / tests).

@@ -65,7 +65,7 @@ int mpl_l2_pick_splits(int nq, int nt, int sm_count);
 size_t mpl_l2_list_scratch_entries(int nq, int sm_count);
 int mpl_launch_l2_exact_list(const float* q, const int* qlist, const unsigned* count, size_t q_ld, const float* t, int nt, size_t t_ld,
                              int dim, int order_mode, long long train_offset, mpl_key64* partial, mpl_key64* keys_out, int sm_count,
-                             cudaStream_t st);
+                             unsigned* ticket /* zeroed by the caller */, cudaStream_t st);
 int mpl_launch_l2_rerank(const float* q, int nq, size_t q_ld, const float* t, size_t t_ld, int dim,
                          const int32_t* cand, int n_cand, int order_mode, long long train_offset,
                          mpl_key64* out, cudaStream_t st);
