@@ -188,7 +188,7 @@ __device__ __forceinline__ void write_aug(uint4* dst, bool is_t, float norm, boo
     dst[0] = w0; dst[1] = make_uint4(0, 0, 0, 0);
 }
 
-// One pass, one warp per row (rows [0, nt_pad) train, then [nt_pad, nt_pad + nq) queries): |x|^2, max |t|^2, whether
+// One pass, 8 lanes per row (rows [0, nt_pad) train, then [nt_pad, nt_pad + nq) queries): |x|^2, max |t|^2, whether
 // every value is exactly representable in bf16 (true for OpenCV SIFT: integers 0..255), and -- speculatively -- the
 // bf16 operand rows (kp16 = dim rounded up to 64, zero padded) and bf16 aug rows.  No host round trip: the flag lives
 // in device memory; if it ends up set, l2_prep_tf32_kernel overwrites the operands with fp32 rows read as tf32.
@@ -206,46 +206,55 @@ l2_prep_bf16_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
     unsigned inexact = 0;
     bool nonint = false;
     float tmax = 0.f;
-    for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < total; row += warps_per_grid) {
+    // 8 lanes per row, 4 rows per warp and iteration: 128-byte coalesced reads per row segment, a 3-step reduction, and
+    // four group leaders instead of one lane doing the per-row bookkeeping
+    const int sub = lane >> 3, sl = lane & 7;
+    for (int base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4; base < total; base += warps_per_grid * 4) {
+        const int row = base + sub;
+        const bool live = row < total;
         const bool is_t = row < nt_pad;
         const int r = is_t ? row : row - nt_pad;
-        if (is_t && r >= nt) {                                   // train pad row of the last tile
-            if (lane == 0) { tnorm[r] = INFINITY; write_aug(taug + 2 * (size_t)r, true, INFINITY, true); }
-            continue;
-        }
-        const float* x = is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld;
-        const float sc = is_t ? 1.f : -2.f;
-        char* dst = (char*)(is_t ? tp : qp) + (size_t)r * kp16 * 2;
+        const bool pad = live && is_t && r >= nt;                // train pad row of the last tile
         float s = 0.f;
-        for (int i = 4 * lane; i < kp16; i += 128) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (i + 3 < dim && vec_ok) v = *reinterpret_cast<const float4*>(x + i);
-            else {
-                if (i < dim) v.x = x[i];
-                if (i + 1 < dim) v.y = x[i + 1];
-                if (i + 2 < dim) v.z = x[i + 2];
-                if (i + 3 < dim) v.w = x[i + 3];
+        if (live && !pad) {
+            const float* x = is_t ? t + (size_t)r * t_ld : q + (size_t)r * q_ld;
+            const float sc = is_t ? 1.f : -2.f;
+            char* dst = (char*)(is_t ? tp : qp) + (size_t)r * kp16 * 2;
+            for (int i = 4 * sl; i < kp16; i += 32) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i + 3 < dim && vec_ok) v = *reinterpret_cast<const float4*>(x + i);
+                else {
+                    if (i < dim) v.x = x[i];
+                    if (i + 1 < dim) v.y = x[i + 1];
+                    if (i + 2 < dim) v.z = x[i + 2];
+                    if (i + 3 < dim) v.w = x[i + 3];
+                }
+                inexact |= (__float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w)) & 0xFFFFu;
+                nonint |= (v.x != truncf(v.x)) | (v.y != truncf(v.y)) | (v.z != truncf(v.z)) | (v.w != truncf(v.w));   // NaN/inf: true
+                s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+                __nv_bfloat162 lo = __floats2bfloat162_rn(sc * v.x, sc * v.y), hi = __floats2bfloat162_rn(sc * v.z, sc * v.w);
+                uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(dst + 2 * i) = o;
             }
-            inexact |= (__float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w)) & 0xFFFFu;
-            nonint |= (v.x != truncf(v.x)) | (v.y != truncf(v.y)) | (v.z != truncf(v.z)) | (v.w != truncf(v.w));   // NaN/inf: true
-            s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
-            __nv_bfloat162 lo = __floats2bfloat162_rn(sc * v.x, sc * v.y), hi = __floats2bfloat162_rn(sc * v.z, sc * v.w);
-            uint2 o; o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
-            *reinterpret_cast<uint2*>(dst + 2 * i) = o;
         }
 #pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) {
-            (is_t ? tnorm : qnorm)[r] = s;
-            write_aug((is_t ? taug : qaug) + 2 * (size_t)r, is_t, s, true);
+        for (int o = 4; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (live && sl == 0) {
+            if (pad) { tnorm[r] = INFINITY; write_aug(taug + 2 * (size_t)r, true, INFINITY, true); }
+            else {
+                (is_t ? tnorm : qnorm)[r] = s;
+                write_aug((is_t ? taug : qaug) + 2 * (size_t)r, is_t, s, true);
+            }
         }
-        if (is_t) tmax = fmaxf(tmax, s);
+        if (live && is_t && !pad) tmax = fmaxf(tmax, s);
     }
     // one atomic per CTA (a same-address atomic per warp serialises in L2 and dominated this kernel)
     __shared__ unsigned s_inexact, s_tmax;
     if (threadIdx.x == 0) { s_inexact = 0; s_tmax = 0; }
     __syncthreads();
     inexact = (__any_sync(0xffffffffu, inexact != 0) ? 1u : 0u) | (__any_sync(0xffffffffu, nonint) ? 2u : 0u);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
     if (lane == 0) {
         if (inexact) atomicOr(&s_inexact, inexact);
         if (tmax > 0.f) atomicMax(&s_tmax, __float_as_uint(tmax));
@@ -989,7 +998,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     {
         MplProfScope prof(MPL_PROF_L2_PREP, st);
         const int rows = P.NT * BN + nq;
-        int blocks = (rows + 7) / 8; if (blocks > sm_count * 16) blocks = sm_count * 16;
+        int blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;      // 4 rows per warp and iteration
         l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr, gthr, P.NQB * BM);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         l2_prep_tf32_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
