@@ -218,6 +218,33 @@ def make_c2(rank=0):
     return q, (t0 if rank == 0 else shard(rank))
 
 
+def setup_peers(g, dist, rank, world, nq):
+    """One gather buffer + one sync block per rank in CUDA IPC memory, mapped into every rank: (peer_gather[], peer_sync[])."""
+    lib, m = g.lib, g.m
+    ptrs, handles = [], []
+    for nbytes in (int(lib.mpl_peer_gather_bytes(nq, world)), 256):
+        p = ctypes.c_void_p(0)
+        h = (ctypes.c_ubyte * 64)()
+        m._lib.check(lib.mpl_peer_alloc(nbytes, ctypes.byref(p), h), "mpl_peer_alloc")
+        ptrs.append(p.value); handles.append(bytes(h))
+    everyone = [None] * world
+    dist.all_gather_object(everyone, handles)
+    out = []
+    for which in range(2):
+        arr = (ctypes.c_void_p * world)()
+        for r in range(world):
+            if r == rank:
+                arr[r] = ptrs[which]
+            else:
+                p = ctypes.c_void_p(0)
+                h = (ctypes.c_ubyte * 64).from_buffer_copy(everyone[r][which])
+                m._lib.check(lib.mpl_peer_open(h, ctypes.byref(p)), "mpl_peer_open")
+                arr[r] = p.value
+        out.append(arr)
+    dist.barrier()
+    return out
+
+
 def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     torch, lib, m = g.torch, g.lib, g.m
     q, t = make_c2(rank)
@@ -230,10 +257,20 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     d_idx = torch.empty((nq, 2), dtype=torch.int32, device=g.dev)
     d_dist = torch.empty((nq, 2), dtype=torch.float32, device=g.dev)
 
+    # N > 1: the per-rank top-2 keys are exchanged through NVLink peer memory inside the merge kernel itself
+    # (mpl_allgather_merge_top2_dev); MPL_BENCH_NCCL=1 selects the NCCL all-gather + merge pair instead.
+    peers = None
+    if world > 1 and os.environ.get("MPL_BENCH_NCCL") is None:
+        peers = setup_peers(g, dist, rank, world, nq)
+
     def step():
         st = g.stream()
         m._lib.check(lib.mpl_knn2_l2f32_dev(d_q.data_ptr(), nq, dim, d_t.data_ptr(), nt, dim, dim, 0, rank * nt,
                                             d_scr.data_ptr(), scr_bytes, d_keys.data_ptr(), st), "knn2_l2f32_dev")
+        if peers is not None:
+            m._lib.check(lib.mpl_allgather_merge_top2_dev(d_keys.data_ptr(), nq, rank, world, peers[0], peers[1], 2, 1,
+                                                          d_idx.data_ptr(), d_dist.data_ptr(), None, st), "allgather_merge")
+            return
         if world > 1:
             dist.all_gather_into_tensor(d_all.view(-1, 2), d_keys)   # NCCL over NVLink: 16 B x nq per rank
         m._lib.check(lib.mpl_merge_top2_dev(d_all.data_ptr(), world, nq, 2, 1, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
@@ -276,6 +313,15 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
         while world == 1 and len(cs.samples) < 8 and time.time() < t_end:
             run()
         torch.cuda.synchronize()
+    if peers is not None:                                       # the peer-memory exchange must give what NCCL + merge gives
+        step()
+        torch.cuda.synchronize()
+        got_i, got_d = d_idx.clone(), d_dist.clone()
+        dist.all_gather_into_tensor(d_all.view(-1, 2), d_keys)
+        m._lib.check(lib.mpl_merge_top2_dev(d_all.data_ptr(), world, nq, 2, 1, d_idx.data_ptr(), d_dist.data_ptr(), None, g.stream()), "merge")
+        torch.cuda.synchronize()
+        if not (torch.equal(got_i, d_idx) and torch.equal(got_d.view(torch.int32), d_dist.view(torch.int32))):
+            raise RuntimeError("rank %d: peer-memory all-gather + merge differs from NCCL all-gather + merge" % rank)
     launches = launches * steps // (steps + warmup)             # kernels launched inside the K timed steps
     if graphed:
         launches = per_step * steps
@@ -623,7 +669,7 @@ def main():
             "metric": METRIC, "value": pairs / (step_ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16/tf32 tensor-core ranking, exact fp32 re-rank)",
             "data": "synthetic",
-            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else "train rows sharded over %d ranks, NCCL all-gather of top-2 keys + merge" % world,
+            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else ("train rows sharded over %d ranks, " % world) + ("NCCL all-gather of top-2 keys + merge" if os.environ.get("MPL_BENCH_NCCL") else "top-2 keys all-gathered over NVLink peer memory inside the merge kernel"),
                            launch="CUDA graph replay of the step" if r.get("graphed") else "stream launches"),
             "clocks": r["clocks"],
             "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=ncu_traffic("l2_tc_rank_kernel"),

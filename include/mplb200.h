@@ -103,6 +103,23 @@ int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
                         const char* matcher_name, int ratio_test, int nr_threads /*ignored*/,
                         mpl_dmatch* out, int* n_out);
 
+/* ---- sharded database regime: all-gather over NVLink peer memory fused with the merge -----------------
+ * Every rank (one process per GPU) allocates one gather buffer of mpl_peer_gather_bytes(nq, world) and one 256-byte sync
+ * block with mpl_peer_alloc (zeroed, returns a 64-byte CUDA IPC handle), exchanges the handles (e.g. torch.distributed
+ * all_gather_object) and maps the other ranks' allocations with mpl_peer_open.  mpl_allgather_merge_top2_dev then
+ * replaces "NCCL all-gather of every rank's keys_out + mpl_merge_top2_dev": one kernel stores the local keys into every
+ * rank's buffer, signals, waits for the world's arrivals and merges (same (dist, idx) key order: the result equals the
+ * one-GPU scan).  peer_gather[r] / peer_sync[r]: rank r's allocations as seen from this process (own ones at [rank]).
+ * Every rank must call it the same number of times; world <= 8.  Capturable into a CUDA graph. */
+size_t mpl_peer_gather_bytes(int nq, int world);
+int mpl_peer_alloc(size_t bytes, void** d_ptr, unsigned char* ipc_handle64);
+int mpl_peer_open(const unsigned char* ipc_handle64, void** d_ptr);
+int mpl_peer_close(void* d_ptr);
+int mpl_peer_free(void* d_ptr);
+int mpl_allgather_merge_top2_dev(const void* d_keys_local, int nq, int rank, int world, void* const* peer_gather,
+                                 void* const* peer_sync, int k, int is_float, void* d_idx, void* d_dist, void* d_keys_merged,
+                                 void* stream);
+
 /* ---- brute-force k-NN, device pointers (bench `value`, multi-GPU plumbing) ------------------
  * Descriptor rows must be in the library's device layout: row stride = w16*16 bytes, zero padded
  * (mpl_pack_rows_u8_dev produces it; 32-byte ORB rows already are, with w16 = 2).

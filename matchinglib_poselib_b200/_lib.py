@@ -32,6 +32,12 @@ SIGNATURES = {
     "mpl_device_info": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_kernel_launch_count": (c_ll, []),
     "mpl_host_alloc": (c_void_p, [c_size_t]),
+    "mpl_peer_gather_bytes": (c_size_t, [c_int, c_int]),
+    "mpl_peer_alloc": (c_int, [c_size_t, c_void_p, c_void_p]),
+    "mpl_peer_open": (c_int, [c_void_p, c_void_p]),
+    "mpl_peer_close": (c_int, [c_void_p]),
+    "mpl_peer_free": (c_int, [c_void_p]),
+    "mpl_allgather_merge_top2_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_host_free": (c_int, [c_void_p]),
     "mpl_prof_enable": (c_int, [c_int]),
     "mpl_prof_read": (c_int, [c_int, c_void_p, c_void_p]),

@@ -304,6 +304,51 @@ extern "C" int mpl_merge_top2_dev(const void* d_keys_parts, int n_parts, int nq,
                                  is_float ? 0 : -1, (mpl_key64*)d_keys_merged, (cudaStream_t)stream);
 }
 
+// ---- peer memory for the sharded database regime ---------------------------------------------------
+extern "C" size_t mpl_peer_gather_bytes(int nq, int world) { return (size_t)2 * (world > 0 ? world : 1) * (nq > 0 ? nq : 0) * 2 * sizeof(mpl_key64) + 256; }
+
+extern "C" int mpl_peer_alloc(size_t bytes, void** d_ptr, unsigned char* ipc_handle64)
+{
+    if (!d_ptr || !ipc_handle64 || bytes == 0) { mpl_set_error("mpl_peer_alloc: bad argument"); return MPL_ERR_BAD_ARG; }
+    {
+        std::lock_guard<std::mutex> g(g_mu);
+        int rc = mpl_ensure_ctx_locked();
+        if (rc) return rc;
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    MPL_CUDA_CHECK(cudaMalloc(d_ptr, bytes));
+    MPL_CUDA_CHECK(cudaMemset(*d_ptr, 0, bytes));
+    cudaIpcMemHandle_t h;
+    MPL_CUDA_CHECK(cudaIpcGetMemHandle(&h, *d_ptr));
+    memcpy(ipc_handle64, &h, 64);
+    return MPL_OK;
+}
+extern "C" int mpl_peer_open(const unsigned char* ipc_handle64, void** d_ptr)
+{
+    if (!d_ptr || !ipc_handle64) { mpl_set_error("mpl_peer_open: bad argument"); return MPL_ERR_BAD_ARG; }
+    {
+        std::lock_guard<std::mutex> g(g_mu);
+        int rc = mpl_ensure_ctx_locked();
+        if (rc) return rc;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle64, 64);
+    MPL_CUDA_CHECK(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return MPL_OK;
+}
+extern "C" int mpl_peer_close(void* d_ptr) { if (d_ptr) MPL_CUDA_CHECK(cudaIpcCloseMemHandle(d_ptr)); return MPL_OK; }
+extern "C" int mpl_peer_free(void* d_ptr) { if (d_ptr) MPL_CUDA_CHECK(cudaFree(d_ptr)); return MPL_OK; }
+
+extern "C" int mpl_allgather_merge_top2_dev(const void* d_keys_local, int nq, int rank, int world, void* const* peer_gather,
+                                            void* const* peer_sync, int k, int is_float, void* d_idx, void* d_dist, void* d_keys_merged,
+                                            void* stream)
+{
+    if (k != 1 && k != 2) { mpl_set_error("allgather_merge: k must be 1 or 2"); return MPL_ERR_BAD_ARG; }
+    if (!d_keys_local || !peer_gather || !peer_sync) { mpl_set_error("allgather_merge: null argument"); return MPL_ERR_BAD_ARG; }
+    return mpl_launch_allgather_merge((const mpl_key64*)d_keys_local, nq, rank, world, peer_gather, peer_sync, k, (int32_t*)d_idx, d_dist,
+                                      is_float ? 0 : -1, (mpl_key64*)d_keys_merged, (cudaStream_t)stream);
+}
+
 // upload a strided host matrix (rows x row_bytes, stride step) into a dense device buffer
 static int upload_rows(MplBuf& buf, const void* h, int rows, size_t row_bytes, size_t step, size_t dst_pitch, cudaStream_t st)
 {

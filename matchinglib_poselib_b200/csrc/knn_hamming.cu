@@ -297,6 +297,71 @@ ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test,
     if (tid == 1023) out[0] = make_int4(pos, 0, 0, 0);
 }
 
+// All-gather of every rank's per-query top-2 keys over NVLink peer memory, fused with the merge (the database regime,
+// DESIGN.md section 6): each rank stores its local keys into slot [parity][rank] of EVERY rank's gather buffer (plain
+// 16-byte stores through the peer mappings), publishes with a system-scope fence + one atomic per CTA on every rank's
+// arrival counter, waits until all world x gridDim.x arrivals of this step have reached its own counter, then merges the
+// world parts out of its own buffer.  One kernel instead of an NCCL all-gather (latency-bound at 16 B x Q per rank) plus a
+// merge launch.  Steps alternate between two buffers: a rank can run at most one step ahead of a peer (it cannot pass the
+// wait of step e+1 before that peer has finished merging step e and arrived in e+1), so its early stores never land in a
+// buffer a peer is still reading.  sync words per rank: [0] step counter, [1] arrivals (monotone), [2] CTA ticket.
+struct MplPeerSet { ulonglong2* gather[8]; unsigned* sync[8]; };
+
+__global__ void __launch_bounds__(256)
+allgather_merge_kernel(const ulonglong2* __restrict__ local_keys, int nq, int rank, int world, MplPeerSet P, int k,
+                       int32_t* __restrict__ idx, uint32_t* __restrict__ dist, int float_sqrt, ulonglong2* __restrict__ merged)
+{
+    unsigned* my = P.sync[rank];
+    __shared__ unsigned s_epoch;
+    if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile unsigned*>(&my[0]);
+    __syncthreads();
+    const unsigned e = s_epoch, par = e & 1u;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    for (int q = gtid; q < nq; q += gsize) {
+        const ulonglong2 v = local_keys[q];
+        for (int p = 0; p < world; ++p) P.gather[p][((size_t)par * world + rank) * nq + q] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int p = 0; p < world; ++p) atomicAdd_system(&P.sync[p][1], 1u);
+        const unsigned target = (e + 1u) * (unsigned)world * gridDim.x;
+        while ((int)(*reinterpret_cast<volatile unsigned*>(&my[1]) - target) < 0) { }
+        __threadfence_system();
+    }
+    __syncthreads();
+    const ulonglong2* mine = P.gather[rank] + (size_t)par * world * nq;
+    for (int q = gtid; q < nq; q += gsize) {
+        mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
+        for (int p = 0; p < world; ++p) {
+            const ulonglong2 v = __ldcg(mine + (size_t)p * nq + q);                 // written by peer p: not through L1
+            const mpl_key64 hi = max(b0, v.x);
+            b0 = min(b0, v.x);
+            b1 = min(min(b1, hi), v.y);
+        }
+        if (merged) merged[q] = make_ulonglong2(b0, b1);
+        if (idx) {
+            const mpl_key64 kk[2] = {b0, b1};
+            for (int c = 0; c < k; ++c) {
+                int32_t id; uint32_t dv;
+                if (kk[c] == MPL_KEY_INVALID) { id = -1; dv = float_sqrt >= 0 ? 0x7F7FFFFFu : 0x7FFFFFFFu; }
+                else {
+                    id = (int32_t)(uint32_t)(kk[c] & 0xFFFFFFFFull);
+                    dv = (uint32_t)(kk[c] >> 32);
+                    if (float_sqrt == 1) dv = __float_as_uint(sqrtf(__uint_as_float(dv)));
+                }
+                idx[(size_t)q * k + c] = id;
+                dist[(size_t)q * k + c] = dv;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                                                         // the last CTA closes the step
+        __threadfence();
+        if (atomicAdd(&my[2], 1u) == gridDim.x - 1) { my[2] = 0; __threadfence(); my[0] = e + 1u; }
+    }
+}
+
 template <int W16>
 int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, int n_pairs, long long train_offset,
              mpl_key64* partial, cudaStream_t st)
@@ -390,6 +455,21 @@ int mpl_launch_ratio_dmatch(const mpl_key64* keys, int nq, int ratio_test, int i
 {
     MplProfScope prof(MPL_PROF_MERGE, st);
     ratio_dmatch_kernel<<<1, 1024, 0, st>>>((const ulonglong2*)keys, nq, ratio_test, is_float, (int4*)out);
+    MPL_CUDA_CHECK(cudaGetLastError());
+    mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_allgather_merge(const mpl_key64* local_keys, int nq, int rank, int world, void* const* peer_gather, void* const* peer_sync,
+                               int k, int32_t* idx, void* dist, int float_sqrt, mpl_key64* merged, cudaStream_t st)
+{
+    if (nq <= 0) return MPL_OK;
+    if (world < 1 || world > 8 || rank < 0 || rank >= world) { mpl_set_error("allgather_merge: world %d / rank %d out of range (1..8)", world, rank); return MPL_ERR_BAD_ARG; }
+    MplPeerSet P;
+    for (int p = 0; p < 8; ++p) { P.gather[p] = p < world ? (ulonglong2*)peer_gather[p] : nullptr; P.sync[p] = p < world ? (unsigned*)peer_sync[p] : nullptr; }
+    int grid = (nq + 255) / 256; if (grid > 64) grid = 64;                          // co-resident: the CTAs wait on each other's peers
+    MplProfScope prof(MPL_PROF_MERGE, st);
+    allgather_merge_kernel<<<grid, 256, 0, st>>>((const ulonglong2*)local_keys, nq, rank, world, P, k, idx, (uint32_t*)dist, float_sqrt, (ulonglong2*)merged);
     MPL_CUDA_CHECK(cudaGetLastError());
     mpl_count_launch();
     return MPL_OK;

@@ -54,6 +54,9 @@ int mpl_hamming_pick_splits(int nq, int nt, int w16, int sm_count);
 // merge n_parts partial lists per query (layout [part][nq][2]) into idx/dist (k = 1|2 columns).
 int mpl_launch_merge_top2(const mpl_key64* partial, int n_parts, int nq, int k, int32_t* idx, void* dist,
                           int float_sqrt, mpl_key64* merged_keys, cudaStream_t st);
+// all-gather over peer memory fused with the merge (knn_hamming.cu: allgather_merge_kernel)
+int mpl_launch_allgather_merge(const mpl_key64* local_keys, int nq, int rank, int world, void* const* peer_gather, void* const* peer_sync,
+                               int k, int32_t* idx, void* dist, int float_sqrt, mpl_key64* merged, cudaStream_t st);
 // ratio test + cv::DMatch compaction of merged keys [nq][2]: out = 16-byte header {count} + up to nq 16-byte matches.
 int mpl_launch_ratio_dmatch(const mpl_key64* keys, int nq, int ratio_test, int is_float, void* out, cudaStream_t st);
 

@@ -239,3 +239,46 @@ def test_pinned_array_round_trip(m):
     assert lib.mpl_host_free(pq.ctypes.data + 64) != 0            # not an allocation base
     del pq, pt
     gc.collect()
+
+
+def test_allgather_merge_over_peer_memory_two_ranks_one_device(m):
+    """allgather_merge_kernel with two 'ranks' as two streams of one device (peer pointers are then plain device pointers):
+    every rank ends with the merge of both shards' keys, step after step (the buffers alternate), equal to
+    mpl_merge_top2_dev over the gathered parts and to the one-piece scan."""
+    import ctypes
+    import torch
+    lib = m._lib.load()
+    dev = torch.device("cuda:0")
+    nq, nt, nb = 3000, 4096, 32
+    q, t = datagen.binary_descriptors(nq, nt, nb, seed=21)
+    world = 2
+    gbytes = int(lib.mpl_peer_gather_bytes(nq, world))
+    gather = [torch.zeros(gbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
+    sync = [torch.zeros(64, dtype=torch.int32, device=dev) for _ in range(world)]
+    pg = (ctypes.c_void_p * world)(*[g.data_ptr() for g in gather])
+    ps = (ctypes.c_void_p * world)(*[s.data_ptr() for s in sync])
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    d_q = torch.from_numpy(q).to(dev)
+    half = nt // 2
+    shards = [torch.from_numpy(np.ascontiguousarray(t[r * half:(r + 1) * half])).to(dev) for r in range(world)]
+    scr_bytes = int(lib.mpl_knn_hamming_scratch_bytes(nq, half, nb // 16))
+    for step in range(3):                                           # three steps: both buffer parities, counters keep growing
+        if step == 1:                                               # change the data so that a stale buffer would show
+            d_q = torch.from_numpy(np.ascontiguousarray(q[::-1])).to(dev)
+        keys = [torch.empty((nq, 2), dtype=torch.int64, device=dev) for _ in range(world)]
+        scr = [torch.empty(scr_bytes, dtype=torch.uint8, device=dev) for _ in range(world)]
+        idx = [torch.empty((nq, 2), dtype=torch.int32, device=dev) for _ in range(world)]
+        dist = [torch.empty((nq, 2), dtype=torch.int32, device=dev) for _ in range(world)]
+        torch.cuda.synchronize()
+        for r in range(world):
+            st = ctypes.c_void_p(streams[r].cuda_stream)
+            m._lib.check(lib.mpl_knn2_hamming_dev(d_q.data_ptr(), nq, shards[r].data_ptr(), half, nb // 16, r * half, scr[r].data_ptr(), scr_bytes,
+                                                  keys[r].data_ptr(), st), "hamming_dev")
+            m._lib.check(lib.mpl_allgather_merge_top2_dev(keys[r].data_ptr(), nq, r, world, pg, ps, 2, 0, idx[r].data_ptr(), dist[r].data_ptr(), None, st),
+                         "allgather_merge")
+        torch.cuda.synchronize()
+        qq = q if step == 0 else np.ascontiguousarray(q[::-1])
+        ei, ed = m.knn2_hamming(qq, t, 2)
+        for r in range(world):
+            assert np.array_equal(idx[r].cpu().numpy(), ei) and np.array_equal(dist[r].cpu().numpy(), ed), (step, r)
+    assert int(sync[0][0].item()) == 3 and int(sync[1][0].item()) == 3
