@@ -219,16 +219,22 @@ def make_c2(rank=0):
 
 
 def setup_peers(g, dist, rank, world, nq):
-    """One gather buffer + one sync block per rank in CUDA IPC memory, mapped into every rank: (peer_gather[], peer_sync[])."""
+    """One gather buffer + one sync block per rank in CUDA IPC memory, mapped into every rank: (peer_gather[], peer_sync[]).
+    Every rank reaches the collective whatever happens locally; raises afterwards if any step failed."""
     lib, m = g.lib, g.m
-    ptrs, handles = [], []
-    for nbytes in (int(lib.mpl_peer_gather_bytes(nq, world)), 256):
-        p = ctypes.c_void_p(0)
-        h = (ctypes.c_ubyte * 64)()
-        m._lib.check(lib.mpl_peer_alloc(nbytes, ctypes.byref(p), h), "mpl_peer_alloc")
-        ptrs.append(p.value); handles.append(bytes(h))
+    ptrs, handles, err = [], [], None
+    try:
+        for nbytes in (int(lib.mpl_peer_gather_bytes(nq, world)), 256):
+            p = ctypes.c_void_p(0)
+            h = (ctypes.c_ubyte * 64)()
+            m._lib.check(lib.mpl_peer_alloc(nbytes, ctypes.byref(p), h), "mpl_peer_alloc")
+            ptrs.append(p.value); handles.append(bytes(h))
+    except Exception as e:
+        err, handles = e, None
     everyone = [None] * world
     dist.all_gather_object(everyone, handles)
+    if err is not None or any(h is None for h in everyone):
+        raise RuntimeError("peer allocation failed on some rank (%s)" % err)
     out = []
     for which in range(2):
         arr = (ctypes.c_void_p * world)()
@@ -241,7 +247,6 @@ def setup_peers(g, dist, rank, world, nq):
                 m._lib.check(lib.mpl_peer_open(h, ctypes.byref(p)), "mpl_peer_open")
                 arr[r] = p.value
         out.append(arr)
-    dist.barrier()
     return out
 
 
@@ -261,7 +266,15 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
     # (mpl_allgather_merge_top2_dev); MPL_BENCH_NCCL=1 selects the NCCL all-gather + merge pair instead.
     peers = None
     if world > 1 and os.environ.get("MPL_BENCH_NCCL") is None:
-        peers = setup_peers(g, dist, rank, world, nq)
+        try:
+            peers = setup_peers(g, dist, rank, world, nq)
+        except Exception as e:                                     # no peer access between some pair of GPUs: NCCL path
+            sys.stderr.write("bench: rank %d: peer memory setup failed (%s); using the NCCL all-gather\n" % (rank, e))
+            peers = None
+        ok = torch.tensor([1 if peers is not None else 0], device=g.dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)                  # every rank uses the same exchange
+        if int(ok.item()) == 0:
+            peers = None
 
     def step():
         st = g.stream()
@@ -337,6 +350,7 @@ def bench_l2(g, steps, warmup, world=1, rank=0, dist=None):
                idx=d_idx.cpu().numpy(), dist=d_dist.cpu().numpy(), q=q, t=t)
     res["launches_timed"] = launches
     res["graphed"] = graphed
+    res["peer_exchange"] = peers is not None
     return res
 
 
@@ -669,7 +683,7 @@ def main():
             "metric": METRIC, "value": pairs / (step_ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16/tf32 tensor-core ranking, exact fp32 re-rank)",
             "data": "synthetic",
-            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else ("train rows sharded over %d ranks, " % world) + ("NCCL all-gather of top-2 keys + merge" if os.environ.get("MPL_BENCH_NCCL") else "top-2 keys all-gathered over NVLink peer memory inside the merge kernel"),
+            "config": dict(workload=WORKLOAD, l2_between_steps="flushed (512 MiB write)", train_sharding="none" if world == 1 else ("train rows sharded over %d ranks, " % world) + ("top-2 keys all-gathered over NVLink peer memory inside the merge kernel" if r.get("peer_exchange") else "NCCL all-gather of top-2 keys + merge"),
                            launch="CUDA graph replay of the step" if r.get("graphed") else "stream launches"),
             "clocks": r["clocks"],
             "roofline": dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, traffic=ncu_traffic("l2_tc_rank_kernel"),
