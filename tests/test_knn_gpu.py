@@ -282,3 +282,22 @@ def test_allgather_merge_over_peer_memory_two_ranks_one_device(m):
         for r in range(world):
             assert np.array_equal(idx[r].cpu().numpy(), ei) and np.array_equal(dist[r].cpu().numpy(), ed), (step, r)
     assert int(sync[0][0].item()) == 3 and int(sync[1][0].item()) == 3
+
+
+def test_hamming_database_shard_beyond_2_pow_20_rows(m):
+    """Database regime on one GPU: 2.3 M train rows (more than one 2^20-row split, global indices above 2^21).  Planted
+    exact copies and their later duplicates must come back as (0, first index), (0, duplicate index); a few queries are
+    checked against the oracle over the whole shard."""
+    rng = np.random.default_rng(77)
+    nt, nq, nb = 2_300_000, 64, 32
+    t = rng.integers(0, 256, (nt, nb), dtype=np.uint8)
+    pos = np.sort(rng.choice(nt - 1000, nq, replace=False)); pos[-1] = nt - 1000; pos[0] = 0
+    dup = np.minimum(pos + 1 + rng.integers(0, 900, nq), nt - 1)
+    t[dup] = t[pos]
+    q = t[pos].copy()
+    idx, dist = m.knn2_hamming(q, t, 2)
+    assert np.array_equal(idx[:, 0], pos) and np.array_equal(idx[:, 1], dup) and not dist.any()
+    q2 = rng.integers(0, 256, (6, nb), dtype=np.uint8)
+    i2, d2 = m.knn2_hamming(q2, t, 2)
+    oi, od = orc.knn_hamming(q2, t, 2, 0, threads=8)
+    assert np.array_equal(i2, oi) and np.array_equal(d2, od)
