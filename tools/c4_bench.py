@@ -41,6 +41,8 @@ def main():
     ap.add_argument("--threads", type=int, default=32)
     ap.add_argument("--pool", type=int, default=4)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--samples", type=int, default=1000, help="RANSAC samples per pair (0: matching only; diagnostic)")
+    ap.add_argument("--refine", type=int, default=1)
     args = ap.parse_args()
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
     import torch
@@ -57,7 +59,7 @@ def main():
 
     def one(p):
         (q, t, p1, p2), th = pool[(p // world) % args.pool]
-        r = poselib.matchAndEstimatePose(q, t, p1, p2, "LINEAR", True, th, 1000, 0.999, True, seed=5 + p)
+        r = poselib.matchAndEstimatePose(q, t, p1, p2, "LINEAR", True, th, args.samples, 0.999, bool(args.refine), seed=5 + p)
         return r["count"]
 
     sync = (lambda: dist.barrier()) if world > 1 else (lambda: None)
@@ -79,7 +81,7 @@ def main():
     if rank == 0:
         res = dict(metric="image pairs/s (AKAZE 61 B 5000x5000 Hamming k=2 + ratio, per-pair RANSAC 5pt with refit)", value=args.pairs / float(tm.item()),
                    unit="image pairs/s", n_gpus=world, pairs=args.pairs, seconds=float(tm.item()), host_threads_per_rank=args.threads,
-                   host_cores=os.cpu_count(), scaling="strong", min_inliers=int(mn.item()), data="synthetic (pool of %d pairs per rank)" % args.pool,
+                   host_cores=os.cpu_count(), ransac_samples=args.samples, refit=bool(args.refine), scaling="strong", min_inliers=int(mn.item()), data="synthetic (pool of %d pairs per rank)" % args.pool,
                    api="poselib.matchAndEstimatePose -> mpl_match_pose_pair, pinned host buffers", descriptor_pairs_per_s=args.pairs * 25e6 / float(tm.item()))
         line = json.dumps(res)
         print(line)
