@@ -107,6 +107,7 @@ static int stage_ensure(size_t bytes)
     g_stage_cap = want;
     return MPL_OK;
 }
+int mpl_stage_ensure(size_t bytes, void** ptr) { int rc = stage_ensure(bytes); if (rc) return rc; *ptr = g_stage; return MPL_OK; }
 static void stage_release() { if (g_stage) cudaFreeHost(g_stage); g_stage = nullptr; g_stage_cap = 0; }
 
 // frees a thread's stream, scratch and staging when the thread ends

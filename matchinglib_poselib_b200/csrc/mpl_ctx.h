@@ -26,6 +26,10 @@ struct MplCtx {
 MplCtx*     mpl_ctx();
 std::mutex& mpl_ctx_mutex();
 int         mpl_ensure_ctx_locked();   // caller holds mpl_ctx_mutex()
+// The calling thread's pinned host staging area, grown to at least `bytes` (contents are NOT preserved when it grows).
+// Device -> host reads that land here are true asynchronous copies; a copy into pageable memory (a std::vector, the stack)
+// is staged by the driver and blocks inside the call.
+int         mpl_stage_ensure(size_t bytes, void** ptr);
 
 // ---- knn_l2_tc.cu: tcgen05 ranking kernel + exact re-rank --------------------------------------
 bool   mpl_l2tc_supported(int nq, int nt, int dim);

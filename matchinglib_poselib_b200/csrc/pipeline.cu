@@ -171,9 +171,11 @@ extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, c
     ratio_compact_gather_kernel<<<1, 1024, 0, st>>>((const ulonglong2*)d_keys, n1, ratio_test ? 1 : 0, d_pts1, d_pts2, d_matches,
                                                     (double4*)d_corr, d_ctr);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    PipeCounters c;
-    MPL_CUDA_CHECK(cudaMemcpyAsync(&c, d_ctr, sizeof(c), cudaMemcpyDeviceToHost, st));
+    PipeCounters* h_c = nullptr;                                                             // pinned: the read is a true async copy
+    if ((rc = mpl_stage_ensure(sizeof(PipeCounters), (void**)&h_c))) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(h_c, d_ctr, sizeof(PipeCounters), cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));                                               // the one mid-pipeline read: 8 bytes
+    PipeCounters c = *h_c;
     const int n = c.n_matches;
     *n_matches = n;
     if (n > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(matches, d_matches, (size_t)n * sizeof(mpl_dmatch), cudaMemcpyDeviceToHost, st));
@@ -181,8 +183,9 @@ extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, c
     if (n >= 5 && h > 0) {
         draw_samples_kernel<<<(h + 127) / 128, 128, 0, st>>>((const double4*)d_corr, n, h, seed, d_samples, d_ctr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        MPL_CUDA_CHECK(cudaMemcpyAsync(&c, d_ctr, sizeof(c), cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(h_c, d_ctr, sizeof(PipeCounters), cudaMemcpyDeviceToHost, st));
         MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        c = *h_c;
         h_use = c.first_failed_sample < h ? c.first_failed_sample : h;
         if (samples_out && h_use > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(samples_out, d_samples, (size_t)h_use * 20, cudaMemcpyDeviceToHost, st));
     }

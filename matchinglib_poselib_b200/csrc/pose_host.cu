@@ -231,29 +231,37 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
     double* d_misc = R.d_misc; uint8_t* d_mask = R.d_mask;
     *n_inl = 0;
     if (iters_run) *iters_run = 0;
+    // every device -> host read of this function lands in the thread's pinned staging area:
+    // | off (h+1) i32 | counts (<= 10 h) i32 | errsums (<= 10 h) f64 | gram partials | small (bestE, refit counts / sums) |
+    const size_t m_max = (size_t)10 * h_use;
+    const int gb = mpl_gram_blocks(n);
+    const size_t o_cnt = (((size_t)h_use + 1) * 4 + 15) & ~(size_t)15, o_err = o_cnt + ((m_max * 4 + 15) & ~(size_t)15),
+                 o_part = o_err + m_max * 8, o_small = o_part + (size_t)gb * 45 * 8;
+    char* h_stage = nullptr;
+    if ((rc = mpl_stage_ensure(o_small + 512, (void**)&h_stage))) return rc;
+    int32_t* off = (int32_t*)h_stage; int32_t* counts = (int32_t*)(h_stage + o_cnt); double* errsums = (double*)(h_stage + o_err);
+    double* part = (double*)(h_stage + o_part);
+    double* bestE = (double*)(h_stage + o_small); double* rc_err = bestE + 16; int32_t* rc_counts = (int32_t*)(bestE + 32); int32_t* h_rnm = rc_counts + 16;
     if ((rc = mpl_launch_fivept_solve(d_corr, n, d_samples, h_use, d_models, d_nm, st))) return rc;
     if ((rc = mpl_launch_compact_models(d_models, d_nm, h_use, d_off, d_dense, st))) return rc;
-    std::vector<int32_t> off((size_t)h_use + 1);
-    MPL_CUDA_CHECK(cudaMemcpyAsync(off.data(), d_off, ((size_t)h_use + 1) * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(off, d_off, ((size_t)h_use + 1) * 4, cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
     const int m = off[h_use];
-    std::vector<int32_t> counts((size_t)std::max(m, 1));
-    std::vector<double> errsums((size_t)std::max(m, 1));
+    if (m < 0 || (size_t)m > m_max) { mpl_set_error("ransac: model count %d out of range", m); return MPL_ERR_CUDA; }
     if (m > 0) {
         if ((rc = mpl_launch_sampson_score(d_dense, m, d_corr, n, th, d_counts, d_errsums, st))) return rc;
-        MPL_CUDA_CHECK(cudaMemcpyAsync(counts.data(), d_counts, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
-        MPL_CUDA_CHECK(cudaMemcpyAsync(errsums.data(), d_errsums, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(counts, d_counts, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(errsums, d_errsums, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
     }
     if (models_out) MPL_CUDA_CHECK(cudaMemcpyAsync(models_out, d_dense, (size_t)m * 72, cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
     if (n_models_out) for (int s = 0; s < h_use; ++s) n_models_out[s] = off[s + 1] - off[s];
-    if (counts_out) memcpy(counts_out, counts.data(), (size_t)m * 4);
-    if (errsums_out) memcpy(errsums_out, errsums.data(), (size_t)m * 8);
+    if (counts_out) memcpy(counts_out, counts, (size_t)m * 4);
+    if (errsums_out) memcpy(errsums_out, errsums, (size_t)m * 8);
 
-    Replay r = replay_selection(counts.data(), errsums.data(), off.data(), h_use, n, conf, max_iters);
+    Replay r = replay_selection(counts, errsums, off, h_use, n, conf, max_iters);
     if (iters_run) *iters_run = r.iters_run;
     if (r.best_model < 0) return MPL_OK;                      // runRANSAC returns false (maxGoodCount == 0)
-    double bestE[9];
     MPL_CUDA_CHECK(cudaMemcpyAsync(bestE, d_dense + (size_t)r.best_model * 9, 72, cudaMemcpyDeviceToHost, st));
     if ((rc = mpl_launch_sampson_mask(d_dense + (size_t)r.best_model * 9, d_corr, n, th, d_mask, nullptr, st))) return rc;
     int best_count = r.best_count;
@@ -262,10 +270,8 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
     if (refine) {                                              // modelest.cpp:420-464
         double* d_basis = d_misc; double* d_rmodels = d_misc + 36; int32_t* d_rnm = (int32_t*)(d_misc + 36 + 90);
         double* d_gram = d_misc + 36 + 90 + 8;
-        const int gb = mpl_gram_blocks(n);
         if ((rc = mpl_launch_gram(d_corr, d_mask, n, d_gram, st))) return rc;
-        std::vector<double> part((size_t)gb * 45);
-        MPL_CUDA_CHECK(cudaMemcpyAsync(part.data(), d_gram, part.size() * 8, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(part, d_gram, (size_t)gb * 45 * 8, cudaMemcpyDeviceToHost, st));
         MPL_CUDA_CHECK(cudaStreamSynchronize(st));
         double G[9][9], V[9][9], w[9];
         int k = 0;
@@ -277,11 +283,10 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
         for (int b = 0; b < 4; ++b) for (int c = 0; c < 9; ++c) basis[9 * b + c] = V[c][ord[5 + b]];    // Vt rows 5..8 (five-point.cpp:388)
         MPL_CUDA_CHECK(cudaMemcpyAsync(d_basis, basis, sizeof(basis), cudaMemcpyHostToDevice, st));
         if ((rc = mpl_launch_fivept_from_basis(d_basis, d_rmodels, d_rnm, st))) return rc;
-        int rnm = 0;
-        MPL_CUDA_CHECK(cudaMemcpyAsync(&rnm, d_rnm, 4, cudaMemcpyDeviceToHost, st));
+        MPL_CUDA_CHECK(cudaMemcpyAsync(h_rnm, d_rnm, 4, cudaMemcpyDeviceToHost, st));
         MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+        const int rnm = *h_rnm > 10 ? 10 : *h_rnm;
         if (rnm > 0) {
-            int32_t rc_counts[10]; double rc_err[10];
             if ((rc = mpl_launch_sampson_score(d_rmodels, rnm, d_corr, n, th, d_counts, d_errsums, st))) return rc;
             MPL_CUDA_CHECK(cudaMemcpyAsync(rc_counts, d_counts, (size_t)rnm * 4, cudaMemcpyDeviceToHost, st));
             MPL_CUDA_CHECK(cudaMemcpyAsync(rc_err, d_errsums, (size_t)rnm * 8, cudaMemcpyDeviceToHost, st));
