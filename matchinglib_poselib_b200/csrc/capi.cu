@@ -107,8 +107,28 @@ static int stage_ensure(size_t bytes)
     g_stage_cap = want;
     return MPL_OK;
 }
+// second, independent area (the pair pipeline's own results, alive across mpl_ransac_run_locked's use of the first)
+static thread_local void*  g_stage2 = nullptr;
+static thread_local size_t g_stage2_cap = 0;
+int mpl_stage2_ensure(size_t bytes, void** ptr)
+{
+    if (bytes > g_stage2_cap) {
+        if (g_stage2) { cudaFreeHost(g_stage2); g_stage2 = nullptr; g_stage2_cap = 0; }
+        const size_t want = bytes + bytes / 4 + 4096;
+        MPL_CUDA_CHECK(cudaHostAlloc(&g_stage2, want, cudaHostAllocDefault));
+        g_stage2_cap = want;
+    }
+    *ptr = g_stage2;
+    return MPL_OK;
+}
 int mpl_stage_ensure(size_t bytes, void** ptr) { int rc = stage_ensure(bytes); if (rc) return rc; *ptr = g_stage; return MPL_OK; }
-static void stage_release() { if (g_stage) cudaFreeHost(g_stage); g_stage = nullptr; g_stage_cap = 0; }
+static void stage_release()
+{
+    if (g_stage) cudaFreeHost(g_stage);
+    g_stage = nullptr; g_stage_cap = 0;
+    if (g_stage2) cudaFreeHost(g_stage2);
+    g_stage2 = nullptr; g_stage2_cap = 0;
+}
 
 // frees a thread's stream, scratch and staging when the thread ends
 struct CtxGuard {

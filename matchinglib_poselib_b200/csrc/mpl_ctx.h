@@ -30,6 +30,7 @@ int         mpl_ensure_ctx_locked();   // caller holds mpl_ctx_mutex()
 // Device -> host reads that land here are true asynchronous copies; a copy into pageable memory (a std::vector, the stack)
 // is staged by the driver and blocks inside the call.
 int         mpl_stage_ensure(size_t bytes, void** ptr);
+int         mpl_stage2_ensure(size_t bytes, void** ptr);   // a second area with the same rules
 
 // ---- knn_l2_tc.cu: tcgen05 ranking kernel + exact re-rank --------------------------------------
 bool   mpl_l2tc_supported(int nq, int nt, int dim);

@@ -171,14 +171,18 @@ extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, c
     ratio_compact_gather_kernel<<<1, 1024, 0, st>>>((const ulonglong2*)d_keys, n1, ratio_test ? 1 : 0, d_pts1, d_pts2, d_matches,
                                                     (double4*)d_corr, d_ctr);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    PipeCounters* h_c = nullptr;                                                             // pinned: the read is a true async copy
-    if ((rc = mpl_stage_ensure(sizeof(PipeCounters), (void**)&h_c))) return rc;
+    // pinned staging of this call's results: | counters 256 B | matches n1 x 16 | samples h x 20 | mask n1 |  (true async copies;
+    // handed to the caller's buffers by memcpy after the last wait)
+    char* h_st = nullptr;
+    const size_t o_m = 256, o_s = o_m + (size_t)n1 * sizeof(mpl_dmatch), o_k = o_s + (((size_t)h_alloc * 20 + 15) & ~(size_t)15);
+    if ((rc = mpl_stage2_ensure(o_k + (size_t)n1 + 16, (void**)&h_st))) return rc;
+    PipeCounters* h_c = (PipeCounters*)h_st;
     MPL_CUDA_CHECK(cudaMemcpyAsync(h_c, d_ctr, sizeof(PipeCounters), cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));                                               // the one mid-pipeline read: 8 bytes
     PipeCounters c = *h_c;
     const int n = c.n_matches;
     *n_matches = n;
-    if (n > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(matches, d_matches, (size_t)n * sizeof(mpl_dmatch), cudaMemcpyDeviceToHost, st));
+    if (n > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(h_st + o_m, d_matches, (size_t)n * sizeof(mpl_dmatch), cudaMemcpyDeviceToHost, st));
     int h_use = 0;
     if (n >= 5 && h > 0) {
         draw_samples_kernel<<<(h + 127) / 128, 128, 0, st>>>((const double4*)d_corr, n, h, seed, d_samples, d_ctr);
@@ -187,14 +191,18 @@ extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, c
         MPL_CUDA_CHECK(cudaStreamSynchronize(st));
         c = *h_c;
         h_use = c.first_failed_sample < h ? c.first_failed_sample : h;
-        if (samples_out && h_use > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(samples_out, d_samples, (size_t)h_use * 20, cudaMemcpyDeviceToHost, st));
+        if (samples_out && h_use > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(h_st + o_s, d_samples, (size_t)h_use * 20, cudaMemcpyDeviceToHost, st));
     }
     if (n_samples) *n_samples = h_use;
     if (h_use > 0) {
         // max_iters = h: the pre-drawn samples ARE the iteration budget (reference: 1000, five-point.cpp:117)
-        rc = mpl_ransac_run_locked(ctx, n, h_use, th, h_use, conf, refine, E, mask, n_inl, iters_run, nullptr, nullptr, nullptr, nullptr);
+        rc = mpl_ransac_run_locked(ctx, n, h_use, th, h_use, conf, refine, E, mask ? (uint8_t*)(h_st + o_k) : nullptr, n_inl, iters_run,
+                                   nullptr, nullptr, nullptr, nullptr);
         if (rc) return rc;
     }
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (n > 0) memcpy(matches, h_st + o_m, (size_t)n * sizeof(mpl_dmatch));
+    if (samples_out && h_use > 0) memcpy(samples_out, h_st + o_s, (size_t)h_use * 20);
+    if (mask && h_use > 0 && *n_inl > 0) memcpy(mask, h_st + o_k, (size_t)n);
     return MPL_OK;
 }
