@@ -110,12 +110,16 @@ int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
  * replaces "NCCL all-gather of every rank's keys_out + mpl_merge_top2_dev": one kernel stores the local keys into every
  * rank's buffer, signals, waits for the world's arrivals and merges (same (dist, idx) key order: the result equals the
  * one-GPU scan).  peer_gather[r] / peer_sync[r]: rank r's allocations as seen from this process (own ones at [rank]).
- * Every rank must call it the same number of times; world <= 8.  Capturable into a CUDA graph. */
+ * Every rank must call it the same number of times with the same nq; world <= 8.  Capturable into a CUDA graph.  The wait
+ * for the peers is bounded (mpl_peer_status). */
 size_t mpl_peer_gather_bytes(int nq, int world);
 int mpl_peer_alloc(size_t bytes, void** d_ptr, unsigned char* ipc_handle64);
 int mpl_peer_open(const unsigned char* ipc_handle64, void** d_ptr);
 int mpl_peer_close(void* d_ptr);
 int mpl_peer_free(void* d_ptr);
+/* *timed_out = 1 when some step of mpl_allgather_merge_top2_dev gave up waiting for its peers (4 s; a rank that never
+ * launched, or launched with another nq); the merged result of that step is undefined.  Synchronises `stream` first. */
+int mpl_peer_status(const void* d_sync_own, int* timed_out, void* stream);
 int mpl_allgather_merge_top2_dev(const void* d_keys_local, int nq, int rank, int world, void* const* peer_gather,
                                  void* const* peer_sync, int k, int is_float, void* d_idx, void* d_dist, void* d_keys_merged,
                                  void* stream);
@@ -154,13 +158,15 @@ int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t,
  * mpl_ransac5pt replaces CvModelEstimator3::runRANSAC with CvEMEstimator kernels
  *   (MP/poselib/source/five-point-nister/modelest.cpp:343-474; five-point.cpp:366-503):
  *   p1, p2: n x 2 doubles (camera-normalised coordinates, row-major, contiguous);
- *   samples: h x 5 int32 PRE-DRAWN minimal samples (NULL: max_iters samples are drawn inside with the
- *   getSubset/checkSubset rules of modelest.cpp:567-650 from an internal generator, mpl_ransac_set_seed);
+ *   samples: h x 5 int32 PRE-DRAWN minimal samples (NULL: max_iters samples are drawn inside like getSubset does,
+ *   modelest.cpp:567-610 -- five distinct indices; checkSubset never rejects in the reference, :622-649 -- from an
+ *   internal generator, mpl_ransac_set_seed);
  *   th: Sampson threshold (inlier iff (float)err <= th*th); max_iters (reference: 1000) and conf
  *   (reference: 0.999) drive the same sequential selection + adaptive stop as modelest.cpp:377-416, replayed
  *   over per-model (count, sum err) computed on the device; refine != 0 adds the least-squares refit on all
- *   inliers (modelest.cpp:420-464).  Outputs: E[9] row-major (unit Frobenius norm), mask[n] 0/1, *n_inl
- *   (0 = no model: runRANSAC returned false), *iters_run.  Optional debug outputs (NULL to skip; when any is
+ *   inliers (modelest.cpp:420-464; device Givens QR of the n x 9 constraint rows + one-sided Jacobi SVD of the triangle).
+ *   Outputs: E[9] row-major (unit Frobenius norm), mask[n] 0/1, *n_inl (0 = runRANSAC returned false -- no model, or a
+ *   refit without a model, modelest.cpp:443-445; E and mask are then untouched), *iters_run.  Optional debug outputs (NULL to skip; when any is
  *   given all h samples are solved and scored): models [<=10h][9] dense in sample-major order,
  *   n_models[h], counts[<=10h], errsums[<=10h].
  * mpl_estimate_essential_api mirrors poselib::estimateEssentialMat(E, p1, p2, "RANSAC", threshold, refine, mask)
@@ -183,14 +189,47 @@ int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const 
  *   The per-point triangulation / cheirality / distance tests of all four (R, +-t) combinations run on the device. */
 int mpl_get_pose_triang_pts_api(const double* E, const double* p1, const double* p2, int n, uint8_t* mask, int mask_given,
                                 double dist, int translatE, double* R, double* t, double* Q);
-/* mpl_match_pose_pair: both halves of the hot path for ONE image pair with the matches staying on the device in
- *   between (the reference driver's sequence tests/poselib-test/main.cpp:1522-1599 with host vectors
- *   between the steps): binary descriptors (nbytes per row) -> brute-force k=2 (matcher_name "LINEAR" or
- *   "BRUTEFORCENMS") -> ratio test + cv::DMatch list in ascending queryIdx (matchers.cpp:601-625) -> correspondences
- *   (pts1[queryIdx], pts2[trainIdx]; pts are n x 2 camera-normalised doubles) -> h minimal samples drawn on the device
- *   with getSubset/checkSubset's rules (modelest.cpp:567-650; counter-based generator from `seed`) -> 5-point RANSAC as
- *   in mpl_ransac5pt with max_iters = h.  Outputs: matches[<= n1] / *n_matches, samples_out[h x 5] (optional) /
- *   *n_samples (samples usable before getSubset failed), E[9], mask[*n_matches] over the match list, *n_inl, *iters_run. */
+/* ---- both halves of the hot path for a batch of image pairs, device resident in between --------------------------
+ * (SURVEY.md 8(e) "batch of image pairs", 8(f) N3; the reference driver's per-pair sequence tests/poselib-test/main.cpp:
+ *  1461-1599, 1717 with host vectors between the steps.)  For every pair: descriptors (uint8 rows of `cols` bytes, or float32
+ *  rows of `cols` values) -> brute-force k = 2 (matcher_name "LINEAR" or "BRUTEFORCENMS") -> ratio test + cv::DMatch list in
+ *  ascending queryIdx (matchers.cpp:601-625) -> correspondences (pts1[queryIdx], pts2[trainIdx]) -> h minimal samples drawn
+ *  on the device (getSubset, modelest.cpp:567-610: five distinct indices; counter-based generator from the pair's seed) ->
+ *  5-point RANSAC as in mpl_ransac5pt with max_iters = h, selection replayed on the device (modelest.cpp:394-415), refit
+ *  (:420-464).  pts_mode 0: pts are n x 2 doubles, camera-normalised by the caller.  pts_mode 1: pts are n x 2 floats in
+ *  pixels (cv::KeyPoint::pt); the library applies ImgToCamCoordTrans (pose_helper.cpp:1100-1109) with K0 / K1 (row-major
+ *  3 x 3) and Remove_LensDist (pose_helper.cpp:1169-1279) with dist0 / dist1 (8 OpenCV coefficients; all ~0 = no
+ *  undistortion, as the reference decides) on the device, float -> double as the driver does (main.cpp:1588-1596); a pair
+ *  with fewer than 16 surviving correspondences gets status 1 (the driver skips it).  th is in camera units
+ *  (main.cpp:1597-1599).  Pairs are processed in sub-batches on two internal streams (uploads overlap kernels); one call
+ *  from one host thread keeps the GPU busy.  Host buffers in mpl_host_alloc memory upload at the PCIe link rate. */
+typedef struct mpl_pair_io {
+    const void* desc1; const void* desc2;      /* cv::Mat::data of the two descriptor matrices, n1 / n2 rows */
+    size_t step1, step2;                       /* cv::Mat::step (bytes per row) */
+    const void* pts1; const void* pts2;        /* keypoint coordinates, n1 x 2 / n2 x 2 (see pts_mode) */
+    int n1, n2;
+    unsigned long long seed;                   /* minimal-sample generator seed of this pair */
+    mpl_dmatch* matches;                       /* out: >= n1 entries */
+    uint8_t* mask;                             /* out (may be NULL): >= n1 bytes, RANSAC inlier mask over the match list */
+    int32_t* samples;                          /* out (may be NULL): h x 5, the samples that were drawn */
+} mpl_pair_io;
+typedef struct mpl_pair_params {
+    int cv_type;                               /* 0 = CV_8U (Hamming), 5 = CV_32F (L2) */
+    int cols;                                  /* descriptor length (bytes or floats) */
+    const char* matcher_name;                  /* "LINEAR" | "BRUTEFORCENMS" */
+    int ratio_test;
+    int pts_mode;                              /* 0: double camera-normalised, 1: float pixels + K0 / K1 / dist0 / dist1 */
+    double K0[9], K1[9], dist0[8], dist1[8];
+    double th; int h; double conf; int refine; /* as mpl_ransac5pt (h = sample budget = max_iters) */
+} mpl_pair_params;
+typedef struct mpl_pair_result {
+    int n_matches, n_corr, n_samples, n_inl, iters_run, status;   /* n_inl = 0: runRANSAC returned false; status 1: undistortion failed */
+    double E[9];
+} mpl_pair_result;
+int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const mpl_pair_params* prm, mpl_pair_result* results);
+/* mpl_match_pose_pair: the same for ONE pair of binary descriptors with camera-normalised double keypoints (a batch of
+ *   one: same kernels, same results).  Outputs: matches[<= n1] / *n_matches, samples_out[h x 5] (optional) / *n_samples,
+ *   E[9], mask[*n_matches] over the match list, *n_inl, *iters_run. */
 int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, const uint8_t* desc2, int n2, size_t step2, int nbytes,
                         const double* pts1, const double* pts2, const char* matcher_name, int ratio_test,
                         double th, int h, double conf, int refine, unsigned long long seed,

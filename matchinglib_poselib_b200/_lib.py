@@ -23,6 +23,25 @@ class DMatch(ctypes.Structure):
                 ("distance", ctypes.c_float)]
 
 
+class PairIO(ctypes.Structure):
+    """mpl_pair_io"""
+    _fields_ = [("desc1", c_void_p), ("desc2", c_void_p), ("step1", c_size_t), ("step2", c_size_t), ("pts1", c_void_p), ("pts2", c_void_p),
+                ("n1", c_int), ("n2", c_int), ("seed", ctypes.c_ulonglong), ("matches", c_void_p), ("mask", c_void_p), ("samples", c_void_p)]
+
+
+class PairParams(ctypes.Structure):
+    """mpl_pair_params"""
+    _fields_ = [("cv_type", c_int), ("cols", c_int), ("matcher_name", c_char_p), ("ratio_test", c_int), ("pts_mode", c_int),
+                ("K0", c_double * 9), ("K1", c_double * 9), ("dist0", c_double * 8), ("dist1", c_double * 8),
+                ("th", c_double), ("h", c_int), ("conf", c_double), ("refine", c_int)]
+
+
+class PairResult(ctypes.Structure):
+    """mpl_pair_result"""
+    _fields_ = [("n_matches", c_int), ("n_corr", c_int), ("n_samples", c_int), ("n_inl", c_int), ("iters_run", c_int), ("status", c_int),
+                ("E", c_double * 9)]
+
+
 # name -> (restype, argtypes).  Every symbol include/mplb200.h declares is listed here; the CPU test
 # suite checks that the built library exports each of them.
 SIGNATURES = {
@@ -37,6 +56,7 @@ SIGNATURES = {
     "mpl_peer_open": (c_int, [c_void_p, c_void_p]),
     "mpl_peer_close": (c_int, [c_void_p]),
     "mpl_peer_free": (c_int, [c_void_p]),
+    "mpl_peer_status": (c_int, [c_void_p, c_void_p, c_void_p]),
     "mpl_allgather_merge_top2_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_host_free": (c_int, [c_void_p]),
     "mpl_prof_enable": (c_int, [c_int]),
@@ -65,6 +85,7 @@ SIGNATURES = {
     "mpl_match_pose_pair": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_void_p, c_void_p, c_char_p, c_int,
                                     c_double, c_int, c_double, c_int, ctypes.c_ulonglong, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_match_pose_batch": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "mpl_get_pose_triang_pts_api": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p]),
     "mpl_ransac_pack_corr_dev": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "mpl_ransac_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -94,6 +94,23 @@ int MplBuf::ensure(size_t bytes)
 }
 void MplBuf::release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
 
+int MplLane::ensure_host(size_t bytes)
+{
+    if (bytes <= host_cap) return MPL_OK;
+    if (host) { cudaFreeHost(host); host = nullptr; host_cap = 0; }
+    const size_t want = bytes + bytes / 4 + 4096;
+    MPL_CUDA_CHECK(cudaHostAlloc(&host, want, cudaHostAllocDefault));
+    host_cap = want;
+    return MPL_OK;
+}
+void MplLane::release()
+{
+    if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); stream = nullptr; }
+    arena.release();
+    if (host) cudaFreeHost(host);
+    host = nullptr; host_cap = 0; busy = 0;
+}
+
 // Pinned host staging for results: device -> host copies land here at full PCIe rate (a copy into pageable memory is
 // staged by the driver in small synchronous pieces), then one memcpy hands them to the caller's buffer.
 static thread_local void*  g_stage = nullptr;
@@ -130,17 +147,24 @@ static void stage_release()
     g_stage2 = nullptr; g_stage2_cap = 0;
 }
 
-// frees a thread's stream, scratch and staging when the thread ends
+// frees the calling thread's streams, scratch and staging (caller has made the context's device current)
+static void ctx_release()
+{
+    if (!g_ctx.ready) return;
+    cudaStreamSynchronize(g_ctx.stream);
+    for (auto& b : g_ctx.bufs) b.release();
+    for (auto& l : g_ctx.lanes) l.release();
+    stage_release();
+    cudaStreamDestroy(g_ctx.stream);
+    g_ctx.ready = false;
+    (void)cudaGetLastError();
+}
+// ... when the thread ends
 struct CtxGuard {
     ~CtxGuard() {
         if (!g_ctx.ready) return;
         if (cudaSetDevice(g_ctx.device) != cudaSuccess) return;
-        cudaStreamSynchronize(g_ctx.stream);
-        for (auto& b : g_ctx.bufs) b.release();
-        stage_release();
-        cudaStreamDestroy(g_ctx.stream);
-        g_ctx.ready = false;
-        (void)cudaGetLastError();
+        ctx_release();
     }
 };
 
@@ -157,7 +181,7 @@ static int init_locked(int device)
         return MPL_ERR_NO_DEVICE;
     }
     if (device < 0 || device >= n) { mpl_set_error("device %d out of range (0..%d)", device, n - 1); return MPL_ERR_BAD_ARG; }
-    if (g_ctx.ready) { for (auto& b : g_ctx.bufs) b.release(); stage_release(); cudaStreamDestroy(g_ctx.stream); g_ctx.ready = false; }
+    if (g_ctx.ready) { cudaSetDevice(g_ctx.device); ctx_release(); }
     MPL_CUDA_CHECK(cudaSetDevice(device));
     cudaDeviceProp p;
     MPL_CUDA_CHECK(cudaGetDeviceProperties(&p, device));
@@ -192,11 +216,7 @@ extern "C" int mpl_shutdown(void)
     std::lock_guard<std::mutex> g(g_mu);
     if (!g_ctx.ready) return MPL_OK;
     cudaSetDevice(g_ctx.device);
-    cudaStreamSynchronize(g_ctx.stream);
-    for (auto& b : g_ctx.bufs) b.release();
-    stage_release();
-    cudaStreamDestroy(g_ctx.stream);
-    g_ctx.ready = false;
+    ctx_release();
     return MPL_OK;
 }
 
@@ -360,6 +380,17 @@ extern "C" int mpl_peer_open(const unsigned char* ipc_handle64, void** d_ptr)
 extern "C" int mpl_peer_close(void* d_ptr) { if (d_ptr) MPL_CUDA_CHECK(cudaIpcCloseMemHandle(d_ptr)); return MPL_OK; }
 extern "C" int mpl_peer_free(void* d_ptr) { if (d_ptr) MPL_CUDA_CHECK(cudaFree(d_ptr)); return MPL_OK; }
 
+extern "C" int mpl_peer_status(const void* d_sync_own, int* timed_out, void* stream)
+{
+    if (!d_sync_own || !timed_out) { mpl_set_error("mpl_peer_status: null argument"); return MPL_ERR_BAD_ARG; }
+    unsigned w[4] = {0, 0, 0, 0};
+    MPL_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    MPL_CUDA_CHECK(cudaMemcpy(w, d_sync_own, sizeof(w), cudaMemcpyDeviceToHost));
+    *timed_out = w[3] ? 1 : 0;
+    if (w[3]) mpl_set_error("allgather_merge: timed out waiting for the peer ranks (step %u)", w[0]);
+    return MPL_OK;
+}
+
 extern "C" int mpl_allgather_merge_top2_dev(const void* d_keys_local, int nq, int rank, int world, void* const* peer_gather,
                                             void* const* peer_sync, int k, int is_float, void* d_idx, void* d_dist, void* d_keys_merged,
                                             void* stream)
@@ -463,8 +494,8 @@ extern "C" int mpl_knn2_hamming(const uint8_t* q, int nq, size_t q_step, const u
 // ------------------------------------------------------------------------------------------------
 // float L2
 // ------------------------------------------------------------------------------------------------
-static int g_l2_path = 0;
-extern "C" int mpl_set_l2_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_l2_path = path; return MPL_OK; }
+static std::atomic<int> g_l2_path{0};
+extern "C" int mpl_set_l2_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_l2_path.store(path, std::memory_order_relaxed); return MPL_OK; }
 
 extern "C" size_t mpl_knn_l2_scratch_bytes(int nq, int nt, int dim)
 {
@@ -485,7 +516,8 @@ extern "C" int mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const vo
     if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
     int sm = g_ctx.ready ? g_ctx.sm_count : 148;
     // auto: the tensor-core path pays off once the scan is big enough to hide its 5 launches (prep, pack, rank, certify, list)
-    const bool want_tc = (g_l2_path == 2) || (g_l2_path == 0 && mpl_l2tc_supported(nq, nt, dim) && (long long)nq * nt >= (1ll << 22));
+    const int l2_path = g_l2_path.load(std::memory_order_relaxed);
+    const bool want_tc = (l2_path == 2) || (l2_path == 0 && mpl_l2tc_supported(nq, nt, dim) && (long long)nq * nt >= (1ll << 22));
     if (want_tc) {
         if (!mpl_l2tc_supported(nq, nt, dim)) { mpl_set_error("l2: tensor-core path forced but shape unsupported (dim=%d)", dim); return MPL_ERR_BAD_ARG; }
         return mpl_l2tc_top2((const float*)d_q, nq, q_ld, (const float*)d_t, nt, t_ld, dim, sqrt_out, train_offset,

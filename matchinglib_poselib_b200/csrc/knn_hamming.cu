@@ -104,7 +104,7 @@ template <int W16> struct HammingCfg {
 template <int W16>
 __global__ void __launch_bounds__(kThreads)
 hamming_top2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t, int nt,
-                    int rows_per_split, long long train_offset, mpl_key64* __restrict__ partial)
+                    int rows_per_split, long long train_offset, mpl_key64* __restrict__ partial, const int2* __restrict__ dims)
 {
     using Cfg = HammingCfg<W16>;
     constexpr int RQ = Cfg::RQ;
@@ -112,14 +112,21 @@ hamming_top2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict
     __shared__ __align__(128) uint4 tile[kStages][kTileBytes / 16];
     __shared__ __align__(8) uint64_t full_bar[kStages];
 
-    // blockIdx.z = image pair of a batch (independent problems of identical shape)
+    // blockIdx.z = image pair of a batch: independent problems stored at the common strides nq / nt rows; their own
+    // sizes come from dims[pair] = (rows of queries, rows of train) when given, else every pair is nq x nt
     q += (size_t)blockIdx.z * nq * W16;
     t += (size_t)blockIdx.z * nt * W16;
     partial += (size_t)blockIdx.z * gridDim.y * nq * 2;
+    const int nq_stride = nq;
+    if (dims) {
+        const int2 d = dims[blockIdx.z];
+        nq = d.x; nt = d.y;
+        if ((int)blockIdx.x * Cfg::kQueriesPerCta >= nq) return;
+    }
     const int tid   = threadIdx.x;
     const int split = blockIdx.y;
     const int row0  = split * rows_per_split;                        // first train row of this split
-    const int rows  = min(rows_per_split, nt - row0);                // > 0 by construction
+    const int rows  = max(0, min(rows_per_split, nt - row0));        // > 0 by construction except for an empty pair
     const int n_tiles = (rows + TR - 1) / TR;
 
     if (tid == 0) {
@@ -199,7 +206,7 @@ hamming_top2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict
             }
         }
         out.x = o[0]; out.y = o[1];
-        reinterpret_cast<ulonglong2*>(partial)[(size_t)split * nq + qi] = out;
+        reinterpret_cast<ulonglong2*>(partial)[(size_t)split * nq_stride + qi] = out;
     }
 }
 
@@ -304,8 +311,11 @@ ratio_dmatch_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test,
 // world parts out of its own buffer.  One kernel instead of an NCCL all-gather (latency-bound at 16 B x Q per rank) plus a
 // merge launch.  Steps alternate between two buffers: a rank can run at most one step ahead of a peer (it cannot pass the
 // wait of step e+1 before that peer has finished merging step e and arrived in e+1), so its early stores never land in a
-// buffer a peer is still reading.  sync words per rank: [0] step counter, [1] arrivals (monotone), [2] CTA ticket.
+// buffer a peer is still reading.  sync words per rank: [0] step counter, [1] arrivals (monotone), [2] CTA ticket, [3] time-out flag.
+// Contract: every rank launches the same nq (hence the same grid: min(ceil(nq / 256), 64) CTAs, all co-resident -- 64 CTAs
+// of 256 threads always fit on the 148 SMs).
 struct MplPeerSet { ulonglong2* gather[8]; unsigned* sync[8]; };
+constexpr unsigned long long kPeerTimeoutNs = 4000000000ull;     // 4 s: far above any rank start skew inside one step
 
 __global__ void __launch_bounds__(256)
 allgather_merge_kernel(const ulonglong2* __restrict__ local_keys, int nq, int rank, int world, MplPeerSet P, int k,
@@ -326,7 +336,16 @@ allgather_merge_kernel(const ulonglong2* __restrict__ local_keys, int nq, int ra
     if (threadIdx.x == 0) {
         for (int p = 0; p < world; ++p) atomicAdd_system(&P.sync[p][1], 1u);
         const unsigned target = (e + 1u) * (unsigned)world * gridDim.x;
-        while ((int)(*reinterpret_cast<volatile unsigned*>(&my[1]) - target) < 0) { }
+        // bounded wait: a peer that never launches (failed rank, different nq / grid) must not hang this GPU.  After
+        // kPeerTimeoutNs the CTA records the failure in sync word [3] (read by mpl_peer_status) and goes on; the merged
+        // result of that step is then undefined and the host path falls back to NCCL (sharded.py) or fails.
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int)(*reinterpret_cast<volatile unsigned*>(&my[1]) - target) < 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&my[3], 1u); break; }
+            __nanosleep(64);
+        }
         __threadfence_system();
     }
     __syncthreads();
@@ -364,7 +383,7 @@ allgather_merge_kernel(const ulonglong2* __restrict__ local_keys, int nq, int ra
 
 template <int W16>
 int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, int n_pairs, long long train_offset,
-             mpl_key64* partial, cudaStream_t st)
+             mpl_key64* partial, const int2* dims, cudaStream_t st)
 {
     using Cfg = HammingCfg<W16>;
     const int rows_per_split = (nt + n_splits - 1) / n_splits;    // the last TMA tile of a split may be partial
@@ -374,7 +393,7 @@ int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, i
     dim3 grid((nq + Cfg::kQueriesPerCta - 1) / Cfg::kQueriesPerCta, n_splits, n_pairs);
     MplProfScope prof(MPL_PROF_HAMMING, st);
     hamming_top2_kernel<W16><<<grid, kThreads, 0, st>>>((const uint4*)q, nq, (const uint4*)t, nt, rows_per_split,
-                                                         train_offset, partial);
+                                                         train_offset, partial, dims);
     MPL_CUDA_CHECK(cudaGetLastError());
     mpl_count_launch();
     return MPL_OK;
@@ -425,16 +444,17 @@ int mpl_launch_pack_rows_u8(const uint8_t* src, int n, size_t src_step, int nbyt
 }
 
 int mpl_launch_hamming_top2(const uint8_t* q, int nq, const uint8_t* t, int nt, int w16, int n_splits, int n_pairs,
-                            long long train_offset, mpl_key64* partial, cudaStream_t st)
+                            long long train_offset, mpl_key64* partial, cudaStream_t st, const void* pair_dims)
 {
+    const int2* dims = (const int2*)pair_dims;
     if (nq <= 0 || nt <= 0 || n_pairs <= 0) return MPL_OK;
     if (n_pairs > 65535) { mpl_set_error("hamming: at most 65535 pairs per batch launch"); return MPL_ERR_LIMIT; }
     switch (w16) {
-        case 1:  return launch_w<1>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
-        case 2:  return launch_w<2>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
-        case 4:  return launch_w<4>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
-        case 8:  return launch_w<8>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
-        case 16: return launch_w<16>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, st);
+        case 1:  return launch_w<1>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, dims, st);
+        case 2:  return launch_w<2>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, dims, st);
+        case 4:  return launch_w<4>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, dims, st);
+        case 8:  return launch_w<8>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, dims, st);
+        case 16: return launch_w<16>(q, nq, t, nt, n_splits, n_pairs, train_offset, partial, dims, st);
         default: mpl_set_error("hamming: unsupported row width w16=%d (use 1,2,4,8,16)", w16); return MPL_ERR_BAD_ARG;
     }
 }

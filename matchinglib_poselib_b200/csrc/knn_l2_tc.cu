@@ -976,11 +976,9 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     mpl_key64* part = (mpl_key64*)(base + P.off_part);
     uint32_t* gthr = (uint32_t*)(base + P.off_gthr);
 
-    static bool attr_set = false;
-    if (!attr_set) {
-        MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
+    // per launch, not once per process: the attribute belongs to the CURRENT device's copy of the function (mpl_init may
+    // re-target, per-thread contexts call concurrently); the call costs about a microsecond
+    MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     uint4* taug = (uint4*)(base + P.off_taug); uint4* qaug = (uint4*)(base + P.off_qaug);
     alignas(64) TcMaps maps;
     int rc;

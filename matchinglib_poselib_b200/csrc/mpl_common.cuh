@@ -48,8 +48,9 @@ typedef unsigned long long mpl_key64;
 int mpl_launch_pack_rows_u8(const uint8_t* src, int n, size_t src_step, int nbytes_used, uint8_t* dst, int w16,
                             cudaStream_t st);
 // partial[(split*nq + q)*2 + {0,1}] = best two keys of query q inside train split `split`.
+// pair_dims (device, optional): int2 (nq, nt) per pair of a batch stored at the common strides nq / nt rows (n_splits = 1)
 int mpl_launch_hamming_top2(const uint8_t* q, int nq, const uint8_t* t, int nt, int w16, int n_splits, int n_pairs,
-                            long long train_offset, mpl_key64* partial, cudaStream_t st);
+                            long long train_offset, mpl_key64* partial, cudaStream_t st, const void* pair_dims = nullptr);
 int mpl_hamming_pick_splits(int nq, int nt, int w16, int sm_count);
 // merge n_parts partial lists per query (layout [part][nq][2]) into idx/dist (k = 1|2 columns).
 int mpl_launch_merge_top2(const mpl_key64* partial, int n_parts, int nq, int k, int32_t* idx, void* dist,

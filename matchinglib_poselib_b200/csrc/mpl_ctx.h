@@ -15,12 +15,25 @@ struct MplBuf {
 enum { MPL_BUF_Q = 0, MPL_BUF_T, MPL_BUF_RAW, MPL_BUF_PART, MPL_BUF_KEYS, MPL_BUF_IDX, MPL_BUF_DIST,
        MPL_BUF_R0, MPL_BUF_R1, MPL_BUF_R2, MPL_BUF_R3, MPL_BUF_R4, MPL_BUF_R5, MPL_BUF_COUNT };
 
+// One of the two pipeline lanes of the pair-batch path (pipeline.cu): its own stream, one device arena and one pinned
+// host area, so that the uploads of sub-batch k+1 overlap the kernels of sub-batch k.
+struct MplLane {
+    cudaStream_t stream = nullptr;
+    MplBuf arena;
+    void*  host = nullptr;       // cudaHostAlloc: pair table (H2D source) + results (D2H destination)
+    size_t host_cap = 0;
+    int    busy = 0;             // a sub-batch is in flight
+    int  ensure_host(size_t bytes);
+    void release();
+};
+
 struct MplCtx {
     bool ready = false;
     int device = -1, sm_count = 148, cc_major = 0, cc_minor = 0;
     size_t total_mem = 0;
     cudaStream_t stream = nullptr;
     MplBuf bufs[MPL_BUF_COUNT];
+    MplLane lanes[2];
 };
 
 MplCtx*     mpl_ctx();

@@ -1,17 +1,19 @@
-// pipeline.cu -- device-resident hand-off between the two halves of the hot path:
-//   binary-descriptor k-NN  ->  Lowe ratio test + cv::DMatch compaction  ->  keypoint gather into RANSAC's
-//   correspondence records  ->  minimal-sample drawing  ->  5-point solve + Sampson scoring  ->  selection.
-// In the reference these are separate host steps with std::vector traffic in between (tests/poselib-test/main.cpp:
-// 1522-1599: getCorrespondences -> ratio-filtered matches -> ImgToCamCoordTrans -> estimateEssentialMat).  Here the matches
-// never leave the device between the scan and the scoring; the host sees the match list, the inlier mask and E at the end
-// (one 8-byte read of the match count in the middle, needed to size the launches).
+// pipeline.cu -- both halves of the hot path for a BATCH of image pairs, device resident from the descriptor upload to the
+// final (matches, E, inlier mask): SURVEY.md section 8(e) "batch of image pairs" and section 8(f) N3.
 //
-// Reference semantics kept:
-//   ratio test + DMatch emission, ascending queryIdx   matchers.cpp:601-625 (LINEAR), nmslib_matchers.h:399-421
-//   minimal samples: 5 distinct indices, every prefix passing checkSubset in both images, <= 300 attempts
-//                                                      modelest.cpp:567-650 (the generator is NOT std::rand: the reference
-//                                                      seeds with time(), modelest.cpp:58, so no sequence is promised)
-//   everything from the solve on                       pose_host.cu (mpl_ransac_run_locked)
+// The reference driver does, per image pair and on the host (tests/poselib-test/main.cpp:1461-1599, 1717):
+//   getCorrespondences -> getMatches (k-NN + ratio test)           matchers.cpp:525-714 / nmslib_matchers.h:159-424
+//   points from kp1[queryIdx].pt / kp2[trainIdx].pt                main.cpp:1522-1527
+//   ImgToCamCoordTrans (float)((x - cx) / fx)                      pose_helper.cpp:1100-1109
+//   Remove_LensDist -> LensDist_Oulu (10 iterations, proof test)   pose_helper.cpp:1169-1279
+//   p1, p2 <- n x 2 CV_64F                                         main.cpp:1588-1596
+//   estimateEssentialMat(E, p1, p2, "RANSAC", th, refine, mask)    pose_estim.cpp:857-890 -> modelest.cpp:343-474
+// Here a call takes any number of pairs; they are processed in sub-batches on two pipeline lanes (own stream, device arena
+// and pinned host area each), so the uploads of one sub-batch overlap the kernels of the other and ONE host thread keeps
+// the GPU busy.  Per sub-batch: H2D of descriptors / keypoints -> batched row packing -> Hamming scan with blockIdx.z = pair
+// (float descriptors: the tensor-core L2 path per pair) -> ratio test + cv::DMatch compaction + keypoint gather + camera
+// normalisation + lens undistortion (one CTA per pair) -> minimal samples -> chunked solve / score / device selection
+// replay -> refit -> one D2H of the results.  No host synchronisation in between.
 #include "mpl_common.cuh"
 #include "mpl_ctx.h"
 #include "mpl_ransac.h"
@@ -19,121 +21,454 @@
 
 #include <float.h>
 #include <string.h>
-
-int mpl_hamming_keys_locked(const uint8_t* q, int nq, size_t q_step, const uint8_t* t, int nt, size_t t_step, int nbytes,
-                            int ignore_tail_bytes, mpl_key64** d_keys);
-int mpl_ransac_device_inputs_locked(MplCtx* ctx, int n, int h_use, void** d_corr, int32_t** d_samples);
-int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iters, double conf, int refine, double* E, uint8_t* mask,
-                          int* n_inl, int* iters_run, double* models_out, int32_t* n_models_out, int32_t* counts_out, double* errsums_out);
+#include <algorithm>
+#include <vector>
 
 namespace {
 
-struct PipeCounters { int n_matches; int first_failed_sample; };
+struct CamParams {          // by value to the gather kernel
+    double fx[2], fy[2], cx[2], cy[2];
+    double k[2][8];         // OpenCV order k1 k2 p1 p2 k3 k4 k5 k6
+    int pts_mode;           // 0: double camera-normalised coordinates; 1: float pixel coordinates (cv::KeyPoint::pt)
+    int undistort;          // Remove_LensDist's own switch: !(nearZero(sum(dist1)) && nearZero(sum(dist2)))
+};
 
-// One CTA, order-preserving compaction: every warp owns a contiguous chunk of queries (ballot counts, block scan, write).
-// Hamming keys are (dist << 32 | trainIdx); a query passes iff (float)d0 < 0.75f * (float)d1 (ratio != 0), or always.
-// Writes the cv::DMatch records AND the 32-byte correspondence records (x1, y1, x2, y2) of the survivors.
-__global__ void __launch_bounds__(1024)
-ratio_compact_gather_kernel(const ulonglong2* __restrict__ keys, int nq, int ratio_test, const double2* __restrict__ pts1,
-                            const double2* __restrict__ pts2, mpl_dmatch* __restrict__ matches, double4* __restrict__ corr,
-                            PipeCounters* __restrict__ ctr)
+// LensDist_Oulu (pose_helper.cpp:1232-1279), iters = 10 (declaration default, pose_helper.cpp:67): operation order and the
+// float <-> double conversions are the reference's (the library is compiled without FMA contraction).
+__device__ bool lens_dist_oulu(const float dx, const float dy, float& cx, float& cy, const double* d)
 {
-    __shared__ int warp_sums[32];
+    const double k1 = d[0], k2 = d[1], p1 = d[2], p2 = d[3], k3 = d[4], k4 = d[5], k5 = d[6], k6 = d[7];
+    double r2, _2xy, rad_corr, delta0, delta1;
+    for (int i = 0; i < 10; ++i) {
+        r2 = (double)cx * (double)cx + (double)cy * (double)cy;
+        _2xy = 2.0 * (double)cx * (double)cy;
+        rad_corr = (1.0 + ((k3 * r2 + k2) * r2 + k1) * r2) / (1.0 + ((k6 * r2 + k5) * r2 + k4) * r2);
+        delta0 = p1 * _2xy + p2 * (r2 + 2.0 * (double)cx * (double)cx);
+        delta1 = p1 * (r2 + 2.0 * (double)cy * (double)cy) + p2 * _2xy;
+        cx = (float)(((double)dx - delta0) / rad_corr);
+        cy = (float)(((double)dy - delta1) / rad_corr);
+    }
+    r2 = (double)cx * (double)cx + (double)cy * (double)cy;
+    _2xy = 2.0 * (double)cx * (double)cy;
+    rad_corr = (1.0 + ((k3 * r2 + k2) * r2 + k1) * r2) / (1.0 + ((k6 * r2 + k5) * r2 + k4) * r2);
+    delta0 = p1 * _2xy + p2 * (r2 + 2.0 * (double)cx * (double)cx);
+    delta1 = p1 * (r2 + 2.0 * (double)cy * (double)cy) + p2 * _2xy;
+    const float px = (float)((double)cx * rad_corr + delta0 - (double)dx);
+    const float py = (float)((double)cy * rad_corr + delta1 - (double)dy);
+    return !(sqrtf(px * px + py * py) > 0.25f);
+}
+
+// correspondence of (query qi, train ti): camera coordinates as the driver forms them; false = dropped by Remove_LensDist
+__device__ __forceinline__ bool make_corr(const CamParams& C, const void* pts1, const void* pts2, int qi, int ti, double4& out)
+{
+    if (C.pts_mode == 0) {
+        const double2 a = ((const double2*)pts1)[qi], b = ((const double2*)pts2)[ti];
+        out = make_double4(a.x, a.y, b.x, b.y);
+        return true;
+    }
+    const float2 a = ((const float2*)pts1)[qi], b = ((const float2*)pts2)[ti];
+    // ImgToCamCoordTrans (pose_helper.cpp:1100-1109)
+    float x1 = (float)(((double)a.x - C.cx[0]) / C.fx[0]), y1 = (float)(((double)a.y - C.cy[0]) / C.fy[0]);
+    float x2 = (float)(((double)b.x - C.cx[1]) / C.fx[1]), y2 = (float)(((double)b.y - C.cy[1]) / C.fy[1]);
+    bool ok = true;
+    if (C.undistort) {                                             // Remove_LensDist (pose_helper.cpp:1189-1199)
+        const float d1x = x1, d1y = y1, d2x = x2, d2y = y2;
+        ok = lens_dist_oulu(d1x, d1y, x1, y1, C.k[0]);
+        if (ok) ok = lens_dist_oulu(d2x, d2y, x2, y2, C.k[1]);
+    }
+    out = make_double4((double)x1, (double)y1, (double)x2, (double)y2);   // main.cpp:1588-1596
+    return ok;
+}
+
+// One CTA per pair, order-preserving double compaction: (a) queries that pass the ratio test -> cv::DMatch list
+// (matchers.cpp:601-625 / nmslib_matchers.h:399-421), (b) of those, the ones whose points survive undistortion -> RANSAC's
+// 32-byte correspondence records + their index in the match list.  Also initialises the pair's RANSAC state.
+__global__ void __launch_bounds__(1024)
+pair_gather_kernel(const ulonglong2* __restrict__ keys, const int2* __restrict__ dims, const unsigned long long* __restrict__ seeds,
+                   int nq_stride, int nt_stride, int ratio_test, int is_float, CamParams C, const char* __restrict__ pts1,
+                   const char* __restrict__ pts2, mpl_dmatch* __restrict__ matches, double4* __restrict__ corr, int32_t* __restrict__ corr_src,
+                   MplPairState* __restrict__ st, int h)
+{
+    __shared__ int wsum_m[32], wsum_c[32];
+    const int p = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nq = dims[p].x, nt = dims[p].y;
+    keys += (size_t)p * nq_stride; matches += (size_t)p * nq_stride; corr += (size_t)p * nq_stride; corr_src += (size_t)p * nq_stride;
+    const size_t pe = C.pts_mode == 0 ? 16 : 8;
+    const void* P1 = pts1 + (size_t)p * nq_stride * pe;
+    const void* P2 = pts2 + (size_t)p * nt_stride * pe;
     const int per = ((nq + 1023) / 1024) * 32;                   // queries per warp, lanes read consecutive keys
     const int start = min(nq, wid * per), end = min(nq, start + per);
+    auto dist_f = [&](mpl_key64 k) {
+        if (k == MPL_KEY_INVALID) return is_float ? 3.402823466e+38f : (float)0x7FFFFFFF;
+        const uint32_t d = (uint32_t)(k >> 32);
+        return is_float ? __uint_as_float(d) : (float)(int32_t)d;
+    };
     auto passes = [&](const ulonglong2 k) {
         if (k.x == MPL_KEY_INVALID) return false;
-        if (!ratio_test) return true;
-        if (k.y == MPL_KEY_INVALID) return false;
-        return (float)(uint32_t)(k.x >> 32) < 0.75f * (float)(uint32_t)(k.y >> 32);
+        return !ratio_test || dist_f(k.x) < 0.75f * dist_f(k.y);
     };
-    int sum = 0;
-    for (int i = start; i < end; i += 32) {
-        const bool p = (i + lane < end) && passes(keys[i + lane]);
-        sum += __popc(__ballot_sync(0xffffffffu, p));
-    }
-    if (lane == 0) warp_sums[wid] = sum;
-    __syncthreads();
-    if (wid == 0) {
-        int w = warp_sums[lane];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
-        warp_sums[lane] = w;
-    }
-    __syncthreads();
-    int pos = wid ? warp_sums[wid - 1] : 0;
+    int sum_m = 0, sum_c = 0;
     for (int i = start; i < end; i += 32) {
         ulonglong2 k = make_ulonglong2(MPL_KEY_INVALID, MPL_KEY_INVALID);
-        const bool p = (i + lane < end) && passes(k = keys[i + lane]);
-        const unsigned b = __ballot_sync(0xffffffffu, p);
-        if (p) {
-            const int o = pos + __popc(b & ((1u << lane) - 1u));
-            const int ti = (int)(uint32_t)(k.x & 0xFFFFFFFFull);
-            mpl_dmatch m; m.queryIdx = i + lane; m.trainIdx = ti; m.imgIdx = -1; m.distance = (float)(uint32_t)(k.x >> 32);
-            matches[o] = m;
-            const double2 a = pts1[i + lane], c = pts2[ti];
-            corr[o] = make_double4(a.x, a.y, c.x, c.y);
-        }
-        pos += __popc(b);
+        const bool pm = (i + lane < end) && passes(k = keys[i + lane]);
+        double4 c;
+        const bool pc = pm && make_corr(C, P1, P2, i + lane, (int)(uint32_t)(k.x & 0xFFFFFFFFull), c);
+        sum_m += __popc(__ballot_sync(0xffffffffu, pm));
+        sum_c += __popc(__ballot_sync(0xffffffffu, pc));
     }
-    if (tid == 1023) { ctr->n_matches = pos; ctr->first_failed_sample = 0x7FFFFFFF; }
+    if (lane == 0) { wsum_m[wid] = sum_m; wsum_c[wid] = sum_c; }
+    __syncthreads();
+    if (wid == 0) {
+        int a = wsum_m[lane], b = wsum_c[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int ya = __shfl_up_sync(0xffffffffu, a, o), yb = __shfl_up_sync(0xffffffffu, b, o);
+            if (lane >= o) { a += ya; b += yb; }
+        }
+        wsum_m[lane] = a; wsum_c[lane] = b;
+    }
+    __syncthreads();
+    const int total_m = wsum_m[31], total_c = wsum_c[31];
+    // Remove_LensDist returns false when fewer than 16 correspondences survive (pose_helper.cpp:1203-1204): the driver skips the pair
+    const bool undist_failed = C.pts_mode == 1 && C.undistort && total_c < 16;
+    int pos_m = wid ? wsum_m[wid - 1] : 0, pos_c = wid ? wsum_c[wid - 1] : 0;
+    for (int i = start; i < end; i += 32) {
+        ulonglong2 k = make_ulonglong2(MPL_KEY_INVALID, MPL_KEY_INVALID);
+        const bool pm = (i + lane < end) && passes(k = keys[i + lane]);
+        double4 c = make_double4(0, 0, 0, 0);
+        const int ti = (int)(uint32_t)(k.x & 0xFFFFFFFFull);
+        const bool pc = pm && make_corr(C, P1, P2, i + lane, ti, c);
+        const unsigned bm = __ballot_sync(0xffffffffu, pm), bc = __ballot_sync(0xffffffffu, pc);
+        const unsigned below = (1u << lane) - 1u;
+        const int om = pos_m + __popc(bm & below);
+        if (pm) {
+            mpl_dmatch m; m.queryIdx = i + lane; m.trainIdx = ti; m.imgIdx = -1; m.distance = dist_f(k.x);
+            matches[om] = m;
+        }
+        if (pc && !undist_failed) {
+            const int oc = pos_c + __popc(bc & below);
+            corr[oc] = c; corr_src[oc] = om;
+        }
+        pos_m += __popc(bm); pos_c += __popc(bc);
+    }
+    if (tid == 0) {
+        MplPairState S;
+        S.n1 = nq; S.n2 = nt; S.n_matches = total_m; S.n = undist_failed ? 0 : total_c; S.niters = h; S.iters_run = 0; S.best_count = 0;
+        S.best_slot = -1; S.refit_nm = 0; S.n_inl = 0; S.status = undist_failed ? 1 : 0; S.pad = 0; S.errminsum = DBL_MAX;
+        for (int k = 0; k < 9; ++k) S.E[k] = 0.0;
+        S.seed = seeds[p];
+        st[p] = S;
+    }
 }
 
-__device__ __forceinline__ uint64_t splitmix64(uint64_t& s)
+// descriptor rows of every (pair, side) from the raw upload area into the scan layout (w16 x 16-byte rows, zero padded,
+// `used` payload bytes: BRUTEFORCENMS drops the last packed word)
+__global__ void pack_pairs_kernel(const uint8_t* __restrict__ raw, const unsigned long long* __restrict__ offs, const int2* __restrict__ dims,
+                                  int nbytes, int used, int row_bytes, int nq_stride, int nt_stride, uint8_t* __restrict__ dq, uint8_t* __restrict__ dt)
 {
-    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    return z ^ (z >> 31);
+    const int p = blockIdx.y >> 1, side = blockIdx.y & 1;
+    const int n = side ? dims[p].y : dims[p].x;
+    const uint8_t* src = raw + offs[2 * p + side];
+    uint8_t* dst = side ? dt + (size_t)p * nt_stride * row_bytes : dq + (size_t)p * nq_stride * row_bytes;
+    const size_t total = (size_t)n * row_bytes;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / row_bytes;
+        const int c = (int)(i - r * row_bytes);
+        dst[i] = c < used ? src[r * nbytes + c] : (uint8_t)0;
+    }
 }
 
-// checkSubset for the LAST point of the prefix (modelest.cpp:613-650), on one image's coordinates
-__device__ __forceinline__ bool subset_ok_dev(const double* x, const double* y, int count)
+// inlier mask over the MATCH list (what the caller indexes with its cv::DMatch vector): matches dropped by the undistortion
+// never reach RANSAC and read 0
+__global__ void __launch_bounds__(256)
+mask_to_matches_kernel(const MplPairState* __restrict__ st, const uint8_t* __restrict__ mask_corr, const int32_t* __restrict__ corr_src,
+                       int nq_stride, uint8_t* __restrict__ mask_match)
 {
-    const int i = count - 1;
-    for (int j = 0; j < i; ++j) {
-        const double dx1 = x[j] - x[i], dy1 = y[j] - y[i];
-        for (int k = 0; k < j; ++k) {
-            const double dx2 = x[k] - x[i], dy2 = y[k] - y[i];
-            if (fabs(dx2 * dy1 - dy2 * dx1) <= (double)FLT_EPSILON * (fabs(dx1) + fabs(dy1) + fabs(dx2) + fabs(dy2))) return false;
-        }
-    }
-    return true;
+    const int p = blockIdx.x;
+    const int nm = st[p].n_matches, n = st[p].n;
+    const bool have = st[p].n_inl > 0;
+    uint8_t* mm = mask_match + (size_t)p * nq_stride;
+    for (int i = threadIdx.x; i < nm; i += blockDim.x) mm[i] = 0;
+    __syncthreads();
+    if (!have) return;
+    const uint8_t* mc = mask_corr + (size_t)p * nq_stride;
+    const int32_t* src = corr_src + (size_t)p * nq_stride;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mm[src[i]] = mc[i];
 }
 
-// thread = one minimal sample, its own counter-based random stream (seed, sample id): getSubset's rules
-// (modelest.cpp:567-610).  A sample that cannot be completed within 300 attempts records its index; the host then
-// truncates the run there, like the reference's loop ends when getSubset fails.
-__global__ void draw_samples_kernel(const double4* __restrict__ corr, int n, int h, unsigned long long seed, int32_t* __restrict__ samples,
-                                    PipeCounters* __restrict__ ctr)
+inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Arena {              // offsets inside a lane's device arena for a sub-batch of `bs` pairs
+    size_t dims, offs, seeds, raw, dq, dt, keys, pts1, pts2, matches, corr, src, state, samples, models, nm, counts, errs,
+           maskc, maskm, basis, rmodels, rnm, l2scr, total;
+};
+
+struct BatchPlan {
+    int cv_type, cols, used, w16, row_bytes;       // binary: row_bytes = w16 * 16; float: row_bytes = ld * 4
+    int is_float, sqrt_out, ignore_tail;
+    int nq_stride, nt_stride, h, bs;
+    size_t pe;                                      // bytes per keypoint
+    size_t l2_scratch;
+    CamParams cam;
+};
+
+Arena make_arena(const BatchPlan& P, size_t raw_bytes)
 {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= h) return;
-    uint64_t st = seed ^ (0xD1B54A32D192ED03ull * (uint64_t)(s + 1));
-    int idx[5]; double x1[5], y1[5], x2[5], y2[5];
-    int i = 0, iters = 0;
-    const int max_attempts = 300;
-    for (; iters < max_attempts; ++iters) {
-        for (i = 0; i < 5 && iters < max_attempts;) {
-            const int c = (int)(splitmix64(st) % (uint64_t)n);
-            int j = 0;
-            for (; j < i; ++j) if (c == idx[j]) break;
-            if (j < i) continue;
-            const double4 p = corr[c];
-            idx[i] = c; x1[i] = p.x; y1[i] = p.y; x2[i] = p.z; y2[i] = p.w;
-            if (!subset_ok_dev(x1, y1, i + 1) || !subset_ok_dev(x2, y2, i + 1)) { ++iters; continue; }
-            ++i;
+    Arena A; size_t o = 0;
+    const size_t bs = (size_t)P.bs, nq = (size_t)P.nq_stride, nt = (size_t)P.nt_stride, h = (size_t)(P.h > 0 ? P.h : 1);
+    auto take = [&](size_t bytes) { const size_t at = o; o = al256(o + bytes); return at; };
+    A.dims = take(bs * 8); A.offs = take(bs * 16); A.seeds = take(bs * 8);
+    A.raw = take(raw_bytes);
+    A.dq = take(bs * nq * P.row_bytes); A.dt = take(bs * nt * P.row_bytes);
+    A.keys = take(bs * nq * 16);
+    A.pts1 = take(bs * nq * P.pe); A.pts2 = take(bs * nt * P.pe);
+    A.matches = take(bs * nq * sizeof(mpl_dmatch)); A.corr = take(bs * nq * 32); A.src = take(bs * nq * 4);
+    A.state = take(bs * sizeof(MplPairState));
+    A.samples = take(bs * h * 20); A.models = take(bs * h * 720); A.nm = take(bs * h * 4);
+    A.counts = take(bs * h * 40); A.errs = take(bs * h * 80);
+    A.maskc = take(bs * nq); A.maskm = take(bs * nq);
+    A.basis = take(bs * 36 * 8); A.rmodels = take(bs * 90 * 8); A.rnm = take(bs * 4);
+    A.l2scr = take(P.l2_scratch);
+    A.total = o;
+    return A;
+}
+
+struct HostArea { size_t dims, offs, seeds, state, matches, maskm, samples, total; };
+HostArea make_host_area(const BatchPlan& P, bool want_samples)
+{
+    HostArea H; size_t o = 0;
+    const size_t bs = (size_t)P.bs, nq = (size_t)P.nq_stride, h = (size_t)(P.h > 0 ? P.h : 1);
+    auto take = [&](size_t bytes) { const size_t at = o; o = al256(o + bytes); return at; };
+    H.dims = take(bs * 8); H.offs = take(bs * 16); H.seeds = take(bs * 8);
+    H.state = take(bs * sizeof(MplPairState)); H.matches = take(bs * nq * sizeof(mpl_dmatch)); H.maskm = take(bs * nq);
+    H.samples = take(want_samples ? bs * h * 20 : 16);
+    H.total = o;
+    return H;
+}
+
+// Enqueue one sub-batch (pairs [p0, p0 + nb)) on a lane: uploads, every kernel, downloads.  Nothing synchronises.
+int enqueue_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, int p0, int nb, const mpl_pair_params* prm, bool want_samples)
+{
+    int rc;
+    cudaStream_t st = L.stream;
+    size_t raw_bytes = 0;
+    const size_t elem = P.is_float ? 4 : 1;
+    for (int i = 0; i < nb; ++i) raw_bytes += al256((size_t)pairs[p0 + i].n1 * P.cols * elem) + al256((size_t)pairs[p0 + i].n2 * P.cols * elem);
+    const Arena A = make_arena(P, P.is_float ? 16 : raw_bytes);
+    const HostArea H = make_host_area(P, want_samples);
+    if ((rc = L.arena.ensure(A.total))) return rc;
+    if ((rc = L.ensure_host(H.total))) return rc;
+    char* D = (char*)L.arena.ptr; char* HS = (char*)L.host;
+    int2* h_dims = (int2*)(HS + H.dims); unsigned long long* h_offs = (unsigned long long*)(HS + H.offs);
+    unsigned long long* h_seeds = (unsigned long long*)(HS + H.seeds);
+    // ---- uploads
+    size_t off = 0;
+    for (int i = 0; i < nb; ++i) {
+        const mpl_pair_io& pr = pairs[p0 + i];
+        h_dims[i] = make_int2(pr.n1, pr.n2);
+        h_seeds[i] = pr.seed;
+        const void* src[2] = {pr.desc1, pr.desc2}; const int n[2] = {pr.n1, pr.n2}; const size_t stp[2] = {pr.step1, pr.step2};
+        for (int s = 0; s < 2; ++s) {
+            const size_t rowb = (size_t)P.cols * elem;
+            char* dst; size_t dpitch;
+            if (P.is_float) {                                      // straight into the scan layout (row pitch ld floats)
+                dst = D + (s ? A.dt + (size_t)i * P.nt_stride * P.row_bytes : A.dq + (size_t)i * P.nq_stride * P.row_bytes);
+                dpitch = (size_t)P.row_bytes;
+                h_offs[2 * i + s] = 0;
+            } else {
+                h_offs[2 * i + s] = off; dst = D + A.raw + off; dpitch = rowb; off += al256((size_t)n[s] * rowb);
+            }
+            if (n[s] == 0) continue;
+            if (stp[s] == rowb && dpitch == rowb) MPL_CUDA_CHECK(cudaMemcpyAsync(dst, src[s], (size_t)n[s] * rowb, cudaMemcpyHostToDevice, st));
+            else MPL_CUDA_CHECK(cudaMemcpy2DAsync(dst, dpitch, src[s], stp[s], rowb, n[s], cudaMemcpyHostToDevice, st));
         }
-        break;
+        if (pr.n1) MPL_CUDA_CHECK(cudaMemcpyAsync(D + A.pts1 + (size_t)i * P.nq_stride * P.pe, pr.pts1, (size_t)pr.n1 * P.pe, cudaMemcpyHostToDevice, st));
+        if (pr.n2) MPL_CUDA_CHECK(cudaMemcpyAsync(D + A.pts2 + (size_t)i * P.nt_stride * P.pe, pr.pts2, (size_t)pr.n2 * P.pe, cudaMemcpyHostToDevice, st));
     }
-    if (!(i == 5 && iters < max_attempts)) { atomicMin(&ctr->first_failed_sample, s); for (int j = 0; j < 5; ++j) idx[j] = j; }
-    for (int j = 0; j < 5; ++j) samples[5 * s + j] = idx[j];
+    MPL_CUDA_CHECK(cudaMemcpyAsync(D + A.dims, HS + H.dims, (size_t)nb * 8, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(D + A.offs, HS + H.offs, (size_t)nb * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(D + A.seeds, HS + H.seeds, (size_t)nb * 8, cudaMemcpyHostToDevice, st));
+    const int2* d_dims = (const int2*)(D + A.dims);
+    mpl_key64* d_keys = (mpl_key64*)(D + A.keys);
+    // ---- k-NN
+    if (!P.is_float) {
+        int blocks = (int)(((size_t)std::max(P.nq_stride, P.nt_stride) * P.row_bytes + 255) / 256);
+        blocks = std::max(1, std::min(blocks, 64));
+        pack_pairs_kernel<<<dim3(blocks, 2 * nb), 256, 0, st>>>((const uint8_t*)(D + A.raw), (const unsigned long long*)(D + A.offs), d_dims,
+                                                                 P.cols, P.used, P.row_bytes, P.nq_stride, P.nt_stride, (uint8_t*)(D + A.dq), (uint8_t*)(D + A.dt));
+        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        if ((rc = mpl_launch_hamming_top2((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, 1, nb, 0,
+                                          d_keys, st, d_dims))) return rc;
+    } else {
+        const size_t ld = (size_t)P.row_bytes / 4;
+        MPL_CUDA_CHECK(cudaMemsetAsync(d_keys, 0xFF, (size_t)nb * P.nq_stride * 16, st));
+        for (int i = 0; i < nb; ++i) {
+            const mpl_pair_io& pr = pairs[p0 + i];
+            mpl_key64* ko = d_keys + (size_t)i * P.nq_stride * 2;
+            if (pr.n1 == 0) continue;
+            if ((rc = mpl_knn2_l2f32_dev(D + A.dq + (size_t)i * P.nq_stride * P.row_bytes, pr.n1, ld, D + A.dt + (size_t)i * P.nt_stride * P.row_bytes,
+                                         pr.n2, ld, P.cols, P.sqrt_out, 0, D + A.l2scr, P.l2_scratch, ko, (void*)st))) return rc;
+        }
+    }
+    // ---- ratio test, DMatch list, correspondences, RANSAC state
+    MplPairState* d_state = (MplPairState*)(D + A.state);
+    pair_gather_kernel<<<nb, 1024, 0, st>>>((const ulonglong2*)d_keys, d_dims, (const unsigned long long*)(D + A.seeds), P.nq_stride, P.nt_stride,
+                                            prm->ratio_test ? 1 : 0, P.is_float, P.cam, D + A.pts1, D + A.pts2, (mpl_dmatch*)(D + A.matches),
+                                            (double4*)(D + A.corr), (int32_t*)(D + A.src), d_state, P.h);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    // ---- RANSAC
+    const int h = P.h;
+    if (h > 0) {
+        int32_t* d_samples = (int32_t*)(D + A.samples); double* d_models = (double*)(D + A.models); int32_t* d_nm = (int32_t*)(D + A.nm);
+        int32_t* d_counts = (int32_t*)(D + A.counts); double* d_errs = (double*)(D + A.errs);
+        const void* d_corr = D + A.corr;
+        if ((rc = mpl_launch_draw_samples_batch(d_state, nb, h, d_samples, st))) return rc;
+        // solve in two chunks: the first fills about one wave of the solver (its latency does not depend on the thread count up
+        // to there), the second takes whatever the adaptive stop leaves; score / replay in growing sub-chunks so that pairs that
+        // stop early (modelest.cpp:403-404) never pay for the samples behind their stop
+        int c0 = ((32768 / nb + 63) / 64) * 64;
+        c0 = std::max(64, std::min(c0, h));
+        for (int s0 = 0; s0 < h;) {
+            const int c = s0 == 0 ? std::min(c0, h) : h - s0;
+            if ((rc = mpl_launch_solve_chunk(d_corr, (size_t)P.nq_stride, d_state, nb, d_samples, h, s0, c, d_models, d_nm, st))) return rc;
+            int sc = 64;
+            for (int u = s0; u < s0 + c;) {
+                const int cc = std::min(sc, s0 + c - u);
+                if ((rc = mpl_launch_score_slots(d_corr, (size_t)P.nq_stride, d_state, nb, d_models, d_nm, h, u, cc, prm->th, P.nq_stride / 2,
+                                                 d_counts, d_errs, st))) return rc;
+                if ((rc = mpl_launch_replay_chunk(d_state, nb, d_models, d_nm, d_counts, d_errs, h, u, cc, prm->conf, st))) return rc;
+                u += cc;
+                if (u >= 128) sc = std::min(sc * 2, 512);
+            }
+            s0 += c;
+        }
+        if ((rc = mpl_launch_refit(d_corr, (size_t)P.nq_stride, d_state, nb, prm->th, prm->refine ? 1 : 0, (uint8_t*)(D + A.maskc), (size_t)P.nq_stride,
+                                   (double*)(D + A.basis), (double*)(D + A.rmodels), (int32_t*)(D + A.rnm), st))) return rc;
+    }
+    mask_to_matches_kernel<<<nb, 256, 0, st>>>(d_state, (const uint8_t*)(D + A.maskc), (const int32_t*)(D + A.src), P.nq_stride, (uint8_t*)(D + A.maskm));
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    // ---- downloads
+    MPL_CUDA_CHECK(cudaMemcpyAsync(HS + H.state, D + A.state, (size_t)nb * sizeof(MplPairState), cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(HS + H.matches, D + A.matches, (size_t)nb * P.nq_stride * sizeof(mpl_dmatch), cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(HS + H.maskm, D + A.maskm, (size_t)nb * P.nq_stride, cudaMemcpyDeviceToHost, st));
+    if (want_samples && h > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(HS + H.samples, D + A.samples, (size_t)nb * h * 20, cudaMemcpyDeviceToHost, st));
+    return MPL_OK;
+}
+
+// Wait for a lane's sub-batch and hand its results to the caller's buffers.
+int finish_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, int p0, int nb, bool want_samples, mpl_pair_result* results)
+{
+    MPL_CUDA_CHECK(cudaStreamSynchronize(L.stream));
+    const HostArea H = make_host_area(P, want_samples);
+    const char* HS = (const char*)L.host;
+    const MplPairState* S = (const MplPairState*)(HS + H.state);
+    for (int i = 0; i < nb; ++i) {
+        const mpl_pair_io& pr = pairs[p0 + i];
+        mpl_pair_result& R = results[p0 + i];
+        R.n_matches = S[i].n_matches; R.n_corr = S[i].n; R.n_samples = (S[i].n >= 5) ? P.h : 0; R.n_inl = S[i].n_inl;
+        R.iters_run = S[i].iters_run; R.status = S[i].status;
+        memcpy(R.E, S[i].E, sizeof(R.E));
+        if (R.n_inl <= 0) memset(R.E, 0, sizeof(R.E));
+        if (pr.matches && R.n_matches > 0) memcpy(pr.matches, HS + H.matches + (size_t)i * P.nq_stride * sizeof(mpl_dmatch), (size_t)R.n_matches * sizeof(mpl_dmatch));
+        if (pr.mask && R.n_matches > 0) memcpy(pr.mask, HS + H.maskm + (size_t)i * P.nq_stride, (size_t)R.n_matches);
+        if (pr.samples && R.n_samples > 0) memcpy(pr.samples, HS + H.samples + (size_t)i * P.h * 20, (size_t)P.h * 20);
+    }
+    return MPL_OK;
 }
 
 }  // namespace
 
 // See include/mplb200.h.
+extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const mpl_pair_params* prm, mpl_pair_result* results)
+{
+    if (n_pairs < 0 || (n_pairs > 0 && (!pairs || !results)) || !prm || !prm->matcher_name) { mpl_set_error("mpl_match_pose_batch: null argument"); return MPL_ERR_BAD_ARG; }
+    const bool linear = strcmp(prm->matcher_name, "LINEAR") == 0, nms = strcmp(prm->matcher_name, "BRUTEFORCENMS") == 0;
+    if (!linear && !nms) { mpl_set_error("mpl_match_pose_batch: matcher %s is not served (no CPU fallback)", prm->matcher_name); return MPL_ERR_BAD_ARG; }
+    if ((prm->cv_type != 0 && prm->cv_type != 5) || prm->cols <= 0 || prm->h < 0 || (prm->pts_mode != 0 && prm->pts_mode != 1)) {
+        mpl_set_error("mpl_match_pose_batch: bad parameters (cv_type %d, cols %d, h %d, pts_mode %d)", prm->cv_type, prm->cols, prm->h, prm->pts_mode);
+        return MPL_ERR_BAD_ARG;
+    }
+    BatchPlan P;
+    memset(&P, 0, sizeof(P));
+    P.cv_type = prm->cv_type; P.cols = prm->cols; P.is_float = prm->cv_type == 5; P.h = prm->h;
+    P.sqrt_out = (P.is_float && nms) ? 1 : 0;
+    P.ignore_tail = (!P.is_float && nms) ? ((P.cols & 1) ? 1 : 2) : 0;
+    P.pe = prm->pts_mode == 0 ? 16 : 8;
+    if (P.is_float) {
+        P.row_bytes = ((P.cols + 3) / 4) * 16; P.used = P.cols; P.w16 = 0;
+    } else {
+        P.used = P.cols - P.ignore_tail;
+        if (P.used <= 0 || P.used > 256) { mpl_set_error("mpl_match_pose_batch: unsupported descriptor length %d", P.cols); return MPL_ERR_LIMIT; }
+        int w = (P.used + 15) / 16; P.w16 = 1; while (P.w16 < w) P.w16 *= 2;
+        P.row_bytes = P.w16 * 16;
+    }
+    bool want_samples = false;
+    int nq_max = 1, nt_max = 1;
+    const size_t min_step = (size_t)P.cols * (P.is_float ? 4 : 1);
+    for (int i = 0; i < n_pairs; ++i) {
+        const mpl_pair_io& pr = pairs[i];
+        if (pr.n1 < 0 || pr.n2 < 0 || (pr.n1 > 0 && (!pr.desc1 || !pr.pts1 || pr.step1 < min_step)) || (pr.n2 > 0 && (!pr.desc2 || !pr.pts2 || pr.step2 < min_step))) {
+            mpl_set_error("mpl_match_pose_batch: pair %d: bad descriptor / keypoint arguments", i); return MPL_ERR_BAD_ARG;
+        }
+        if (pr.n2 > (1 << 20)) { mpl_set_error("mpl_match_pose_batch: pair %d: more than 2^20 train rows", i); return MPL_ERR_LIMIT; }
+        nq_max = std::max(nq_max, pr.n1); nt_max = std::max(nt_max, pr.n2);
+        want_samples |= pr.samples != nullptr;
+        memset(&results[i], 0, sizeof(results[i]));
+    }
+    if (n_pairs == 0) return MPL_OK;
+    P.nq_stride = (nq_max + 7) & ~7; P.nt_stride = (nt_max + 7) & ~7;
+    // camera model (pts_mode 1)
+    P.cam.pts_mode = prm->pts_mode;
+    const double* K[2] = {prm->K0, prm->K1}; const double* dd[2] = {prm->dist0, prm->dist1};
+    double dsum[2] = {0, 0};
+    for (int c = 0; c < 2; ++c) {
+        P.cam.fx[c] = K[c][0]; P.cam.cx[c] = K[c][2]; P.cam.fy[c] = K[c][4]; P.cam.cy[c] = K[c][5];
+        for (int k = 0; k < 8; ++k) { P.cam.k[c][k] = dd[c][k]; dsum[c] += dd[c][k]; }
+    }
+    auto near_zero = [](double d) { return d < 1e-3 && d > -1e-3; };          // pose_helper.h:82-87
+    P.cam.undistort = (near_zero(dsum[0]) && near_zero(dsum[1])) ? 0 : 1;     // pose_helper.cpp:1176
+    if (prm->pts_mode == 1 && (P.cam.fx[0] == 0 || P.cam.fy[0] == 0 || P.cam.fx[1] == 0 || P.cam.fy[1] == 0)) {
+        mpl_set_error("mpl_match_pose_batch: pts_mode 1 needs the camera matrices K0, K1"); return MPL_ERR_BAD_ARG;
+    }
+
+    std::lock_guard<std::mutex> g(mpl_ctx_mutex());
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    MplCtx* ctx = mpl_ctx();
+    P.l2_scratch = P.is_float ? mpl_knn_l2_scratch_bytes(P.nq_stride, P.nt_stride, P.cols) + 256 : 16;
+    // sub-batch size: the model slots (720 B per sample) are the big array -- keep a lane's arena under ~1 GiB
+    const size_t per_pair = (size_t)std::max(P.h, 1) * (720 + 20 + 4 + 120) + (size_t)P.nq_stride * (P.row_bytes + 16 + P.pe + 16 + 32 + 4 + 2 + P.cols)
+                            + (size_t)P.nt_stride * (P.row_bytes + P.pe + P.cols);
+    int bs = (int)std::min<size_t>(256, std::max<size_t>(1, ((size_t)1 << 30) / per_pair));
+    if (P.is_float) bs = std::min(bs, 32);                                       // one tensor-core pipeline per pair on the lane's stream
+    bs = std::min(bs, n_pairs);
+    // two lanes need at least two sub-batches; split small batches in halves so that uploads and kernels overlap
+    if (n_pairs >= 16 && n_pairs <= bs) bs = (n_pairs + 1) / 2;
+    P.bs = bs;
+    const int n_sub = (n_pairs + bs - 1) / bs;
+    for (auto& L : ctx->lanes) if (!L.stream) MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    int inflight_p0[2] = {0, 0}, inflight_nb[2] = {0, 0};
+    rc = MPL_OK;
+    for (int k = 0; k < n_sub && rc == MPL_OK; ++k) {
+        MplLane& L = ctx->lanes[k & 1];
+        if (L.busy) { rc = finish_sub_batch(L, P, pairs, inflight_p0[k & 1], inflight_nb[k & 1], want_samples, results); L.busy = 0; if (rc) break; }
+        const int p0 = k * bs, nb = std::min(bs, n_pairs - p0);
+        rc = enqueue_sub_batch(L, P, pairs, p0, nb, prm, want_samples);
+        if (rc == MPL_OK) { L.busy = 1; inflight_p0[k & 1] = p0; inflight_nb[k & 1] = nb; }
+    }
+    for (int j = 0; j < 2; ++j) {                                   // drain in submission order
+        const int lane = (n_sub + j) & 1;
+        MplLane& L = ctx->lanes[lane];
+        if (!L.busy) continue;
+        if (rc == MPL_OK) rc = finish_sub_batch(L, P, pairs, inflight_p0[lane], inflight_nb[lane], want_samples, results);
+        else cudaStreamSynchronize(L.stream);
+        L.busy = 0;
+    }
+    return rc;
+}
+
+// One pair = a batch of one (same kernels, same results); see include/mplb200.h.
 extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, const uint8_t* desc2, int n2, size_t step2, int nbytes,
                                    const double* pts1, const double* pts2, const char* matcher_name, int ratio_test,
                                    double th, int h, double conf, int refine, unsigned long long seed,
@@ -142,67 +477,22 @@ extern "C" int mpl_match_pose_pair(const uint8_t* desc1, int n1, size_t step1, c
 {
     if (!desc1 || !desc2 || !pts1 || !pts2 || !matcher_name || !matches || !n_matches || !E || !n_inl || n1 < 0 || n2 < 0 || nbytes <= 0 ||
         h < 0 || step1 < (size_t)nbytes || step2 < (size_t)nbytes) { mpl_set_error("mpl_match_pose_pair: bad argument"); return MPL_ERR_BAD_ARG; }
-    const bool linear = strcmp(matcher_name, "LINEAR") == 0, nms = strcmp(matcher_name, "BRUTEFORCENMS") == 0;
-    if (!linear && !nms) { mpl_set_error("mpl_match_pose_pair: matcher %s is not served (no CPU fallback)", matcher_name); return MPL_ERR_BAD_ARG; }
-    // BRUTEFORCENMS drops the last packed word: 2 bytes for even, 1 byte for odd descriptor lengths
-    const int ignore_tail = nms ? ((nbytes & 1) ? 1 : 2) : 0;
-    if (ignore_tail >= nbytes || nbytes - ignore_tail > 256) { mpl_set_error("mpl_match_pose_pair: unsupported descriptor length"); return MPL_ERR_LIMIT; }
     *n_matches = 0; *n_inl = 0;
     if (n_samples) *n_samples = 0;
     if (iters_run) *iters_run = 0;
     if (n1 == 0 || n2 == 0) return MPL_OK;
-    std::lock_guard<std::mutex> g(mpl_ctx_mutex());
-    int rc = mpl_ensure_ctx_locked();
+    mpl_pair_io io; memset(&io, 0, sizeof(io));
+    io.desc1 = desc1; io.desc2 = desc2; io.step1 = step1; io.step2 = step2; io.pts1 = pts1; io.pts2 = pts2; io.n1 = n1; io.n2 = n2;
+    io.seed = seed; io.matches = matches; io.mask = mask; io.samples = samples_out;
+    mpl_pair_params prm; memset(&prm, 0, sizeof(prm));
+    prm.cv_type = 0; prm.cols = nbytes; prm.matcher_name = matcher_name; prm.ratio_test = ratio_test; prm.pts_mode = 0;
+    prm.th = th; prm.h = h; prm.conf = conf; prm.refine = refine;
+    mpl_pair_result res;
+    const int rc = mpl_match_pose_batch(&io, 1, &prm, &res);
     if (rc) return rc;
-    MplCtx* ctx = mpl_ctx(); cudaStream_t st = ctx->stream; MplBuf* B = ctx->bufs;
-    // RANSAC scratch first, at its largest possible size (n1 correspondences), so that nothing is reallocated later
-    void* d_corr = nullptr; int32_t* d_samples = nullptr;
-    const int h_alloc = h > 0 ? h : 1;
-    if ((rc = mpl_ransac_device_inputs_locked(ctx, n1 > 5 ? n1 : 5, h_alloc, &d_corr, &d_samples))) return rc;
-    if ((rc = B[MPL_BUF_IDX].ensure(((size_t)n1 + n2) * 16))) return rc;                     // keypoints of both images
-    if ((rc = B[MPL_BUF_DIST].ensure(256 + (size_t)n1 * sizeof(mpl_dmatch)))) return rc;     // counters | matches
-    double2* d_pts1 = (double2*)B[MPL_BUF_IDX].ptr; double2* d_pts2 = d_pts1 + n1;
-    PipeCounters* d_ctr = (PipeCounters*)B[MPL_BUF_DIST].ptr;
-    mpl_dmatch* d_matches = (mpl_dmatch*)((char*)B[MPL_BUF_DIST].ptr + 256);
-    MPL_CUDA_CHECK(cudaMemcpyAsync(d_pts1, pts1, (size_t)n1 * 16, cudaMemcpyHostToDevice, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(d_pts2, pts2, (size_t)n2 * 16, cudaMemcpyHostToDevice, st));
-    mpl_key64* d_keys = nullptr;
-    if ((rc = mpl_hamming_keys_locked(desc1, n1, step1, desc2, n2, step2, nbytes, ignore_tail, &d_keys))) return rc;
-    ratio_compact_gather_kernel<<<1, 1024, 0, st>>>((const ulonglong2*)d_keys, n1, ratio_test ? 1 : 0, d_pts1, d_pts2, d_matches,
-                                                    (double4*)d_corr, d_ctr);
-    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    // pinned staging of this call's results: | counters 256 B | matches n1 x 16 | samples h x 20 | mask n1 |  (true async copies;
-    // handed to the caller's buffers by memcpy after the last wait)
-    char* h_st = nullptr;
-    const size_t o_m = 256, o_s = o_m + (size_t)n1 * sizeof(mpl_dmatch), o_k = o_s + (((size_t)h_alloc * 20 + 15) & ~(size_t)15);
-    if ((rc = mpl_stage2_ensure(o_k + (size_t)n1 + 16, (void**)&h_st))) return rc;
-    PipeCounters* h_c = (PipeCounters*)h_st;
-    MPL_CUDA_CHECK(cudaMemcpyAsync(h_c, d_ctr, sizeof(PipeCounters), cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaStreamSynchronize(st));                                               // the one mid-pipeline read: 8 bytes
-    PipeCounters c = *h_c;
-    const int n = c.n_matches;
-    *n_matches = n;
-    if (n > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(h_st + o_m, d_matches, (size_t)n * sizeof(mpl_dmatch), cudaMemcpyDeviceToHost, st));
-    int h_use = 0;
-    if (n >= 5 && h > 0) {
-        draw_samples_kernel<<<(h + 127) / 128, 128, 0, st>>>((const double4*)d_corr, n, h, seed, d_samples, d_ctr);
-        MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        MPL_CUDA_CHECK(cudaMemcpyAsync(h_c, d_ctr, sizeof(PipeCounters), cudaMemcpyDeviceToHost, st));
-        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-        c = *h_c;
-        h_use = c.first_failed_sample < h ? c.first_failed_sample : h;
-        if (samples_out && h_use > 0) MPL_CUDA_CHECK(cudaMemcpyAsync(h_st + o_s, d_samples, (size_t)h_use * 20, cudaMemcpyDeviceToHost, st));
-    }
-    if (n_samples) *n_samples = h_use;
-    if (h_use > 0) {
-        // max_iters = h: the pre-drawn samples ARE the iteration budget (reference: 1000, five-point.cpp:117)
-        rc = mpl_ransac_run_locked(ctx, n, h_use, th, h_use, conf, refine, E, mask ? (uint8_t*)(h_st + o_k) : nullptr, n_inl, iters_run,
-                                   nullptr, nullptr, nullptr, nullptr);
-        if (rc) return rc;
-    }
-    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-    if (n > 0) memcpy(matches, h_st + o_m, (size_t)n * sizeof(mpl_dmatch));
-    if (samples_out && h_use > 0) memcpy(samples_out, h_st + o_s, (size_t)h_use * 20);
-    if (mask && h_use > 0 && *n_inl > 0) memcpy(mask, h_st + o_k, (size_t)n);
+    *n_matches = res.n_matches; *n_inl = res.n_inl;
+    if (n_samples) *n_samples = res.n_samples;
+    if (iters_run) *iters_run = res.iters_run;
+    if (res.n_inl > 0) memcpy(E, res.E, 72);
     return MPL_OK;
 }

@@ -3,9 +3,10 @@
 //   mpl_estimate_essential_api poselib::estimateEssentialMat(..., "RANSAC", ...) over raw arrays
 //   mpl_ransac_*_dev           device-pointer stages for the benchmark / device-resident pipelines
 // Host logic here is what the reference also does sequentially and cheaply: the model selection replay
-// (modelest.cpp:394-415), cvRANSACUpdateNumIters1 (:86-109), getSubset/checkSubset (:567-650) and the small
-// dense linear algebra of the refit (9x9 symmetric eigenproblem).  Every O(models x correspondences) and
-// O(samples) computation runs in ransac5pt.cu on the device.
+// (modelest.cpp:394-415), cvRANSACUpdateNumIters1 (:86-109), getSubset (:567-610).  Every O(models x correspondences) and
+// O(samples) computation, and the least-squares refit, runs in ransac5pt.cu / ransac_batch.cu on the device.  (The pair
+// batch path replays the selection on the device too: ransac_batch.cu replay_chunk_kernel; this host replay is the
+// independent statement of the same rule that the tests cross-check it against.)
 #include "mpl_common.cuh"
 #include "mpl_ctx.h"
 #include "mpl_ransac.h"
@@ -56,74 +57,34 @@ static Replay replay_selection(const int32_t* counts, const double* errsums, con
     return r;
 }
 
-// cyclic Jacobi eigen-decomposition of a symmetric 9x9 matrix; V columns = eigenvectors
-static void jacobi_eig9(double A[9][9], double V[9][9], double w[9])
-{
-    for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) V[i][j] = (i == j);
-    for (int sweep = 0; sweep < 100; ++sweep) {
-        double off = 0, diag = 0;
-        for (int i = 0; i < 9; ++i) { diag += A[i][i] * A[i][i]; for (int j = i + 1; j < 9; ++j) off += A[i][j] * A[i][j]; }
-        if (off <= 1e-60 * diag || off == 0) break;
-        for (int p = 0; p < 8; ++p)
-            for (int q = p + 1; q < 9; ++q) {
-                if (A[p][q] == 0) continue;
-                const double theta = (A[q][q] - A[p][p]) / (2 * A[p][q]);
-                const double t = (theta >= 0 ? 1 : -1) / (std::fabs(theta) + std::sqrt(theta * theta + 1));
-                const double c = 1 / std::sqrt(t * t + 1), s = t * c;
-                for (int k = 0; k < 9; ++k) { const double x = A[k][p], y = A[k][q]; A[k][p] = c * x - s * y; A[k][q] = s * x + c * y; }
-                for (int k = 0; k < 9; ++k) { const double x = A[p][k], y = A[q][k]; A[p][k] = c * x - s * y; A[q][k] = s * x + c * y; }
-                for (int k = 0; k < 9; ++k) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - s * y; V[k][q] = s * x + c * y; }
-            }
-    }
-    for (int i = 0; i < 9; ++i) w[i] = A[i][i];
-}
-
 // ---- minimal-sample drawing: getSubset + checkSubset (modelest.cpp:567-650) ---------------------------
 static thread_local uint64_t g_seed = 0x9E3779B97F4A7C15ull;   // per calling thread, like the contexts
 extern "C" int mpl_ransac_set_seed(unsigned long long seed) { g_seed = seed ? seed : 0x9E3779B97F4A7C15ull; return MPL_OK; }
 static inline uint32_t next_rand(uint64_t& s) { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16) & 0x7FFFFFFF; }
 
-static bool subset_ok(const double* p, const int* idx, int count)
-{   // checkSubset with checkPartialSubsets: only the last point of the prefix is tested
-    const int i = count - 1;
-    const double xi = p[2 * idx[i]], yi = p[2 * idx[i] + 1];
-    for (int j = 0; j < i; ++j) {
-        const double dx1 = p[2 * idx[j]] - xi, dy1 = p[2 * idx[j] + 1] - yi;
-        for (int k = 0; k < j; ++k) {
-            const double dx2 = p[2 * idx[k]] - xi, dy2 = p[2 * idx[k] + 1] - yi;
-            if (std::fabs(dx2 * dy1 - dy2 * dx1) <= (double)FLT_EPSILON * (std::fabs(dx1) + std::fabs(dy1) + std::fabs(dx2) + std::fabs(dy2)))
-                return false;
-        }
-    }
-    return true;
-}
-
-// Draws up to h samples; stops early (returns the number drawn) when getSubset fails after 300 attempts.
+// checkSubset (modelest.cpp:613-650) is called with checkPartialSubsets = true (set in the constructor, :57), i.e. with
+// i0 = i1 = count - 1, and ends in `return i >= i1`: whether or not its collinearity loop breaks, i == i1 at that point, so
+// the reference ACCEPTS EVERY SUBSET and getSubset reduces to "5 distinct indices" (its 300-attempt failure path is dead
+// code for count >= 5).  Reproduced as is: no collinearity rejection here either (round 1 rejected, which truncated runs on
+// real match lists with many-to-one matches where the reference proceeds).
+// Draws h samples (always succeeds for n >= 5; *n_drawn = h).
 extern "C" int mpl_ransac_draw_samples(const double* p1, const double* p2, int n, int h, int32_t* samples, int* n_drawn)
 {
     if (!p1 || !p2 || !samples || !n_drawn || n < 5 || h < 0) { mpl_set_error("draw_samples: bad argument"); return MPL_ERR_BAD_ARG; }
     uint64_t s = g_seed;
-    int drawn = 0;
-    for (; drawn < h; ++drawn) {
-        int idx[5]; int i = 0, iters = 0;
-        const int max_attempts = 300;
-        for (; iters < max_attempts; ++iters) {
-            for (i = 0; i < 5 && iters < max_attempts;) {
-                const int c = (int)(next_rand(s) % (uint32_t)n);
-                idx[i] = c;
-                int j = 0;
-                for (; j < i; ++j) if (c == idx[j]) break;
-                if (j < i) continue;
-                if (!subset_ok(p1, idx, i + 1) || !subset_ok(p2, idx, i + 1)) { ++iters; continue; }
-                ++i;
-            }
-            break;
+    for (int d = 0; d < h; ++d) {
+        int idx[5];
+        for (int i = 0; i < 5;) {
+            const int c = (int)(next_rand(s) % (uint32_t)n);      // modelest.cpp:585 idx_i = rand() % count
+            int j = 0;
+            for (; j < i; ++j) if (c == idx[j]) break;
+            if (j < i) continue;                                   // :586-590 duplicate: draw again
+            idx[i++] = c;
         }
-        if (!(i == 5 && iters < max_attempts)) break;
-        for (int j = 0; j < 5; ++j) samples[5 * drawn + j] = idx[j];
+        for (int j = 0; j < 5; ++j) samples[5 * d + j] = idx[j];
     }
     g_seed = s;
-    *n_drawn = drawn;
+    *n_drawn = h;
     return MPL_OK;
 }
 
@@ -159,7 +120,7 @@ static int ransac_bufs_locked(MplCtx* ctx, int n, int h_use, RansacBufs& R)
     if ((rc = B[MPL_BUF_R2].ensure((size_t)h_use * 20 + (size_t)(h_use + 1) * 8))) return rc;   // samples | n_models | offsets
     if ((rc = B[MPL_BUF_R3].ensure((size_t)h_use * 90 * 8))) return rc;              // models [h][10][9]
     if ((rc = B[MPL_BUF_R4].ensure((size_t)h_use * 90 * 8))) return rc;              // dense models
-    if ((rc = B[MPL_BUF_R5].ensure((size_t)h_use * 10 * 12 + (size_t)n * 8 + 4096 + 148 * 45 * 8))) return rc;   // counts | errsums | mask | misc
+    if ((rc = B[MPL_BUF_R5].ensure((size_t)h_use * 10 * 12 + (size_t)n * 8 + 8192))) return rc;   // counts | errsums | misc (state, basis, refit models) | mask
     R.d_p1 = (double*)B[MPL_BUF_R0].ptr; R.d_p2 = R.d_p1 + 2 * (size_t)n;
     R.d_corr = B[MPL_BUF_R1].ptr;
     R.d_samples = (int32_t*)B[MPL_BUF_R2].ptr;
@@ -169,8 +130,8 @@ static int ransac_bufs_locked(MplCtx* ctx, int n, int h_use, RansacBufs& R)
     R.d_dense = (double*)B[MPL_BUF_R4].ptr;
     R.d_errsums = (double*)B[MPL_BUF_R5].ptr;
     R.d_counts = (int32_t*)(R.d_errsums + (size_t)h_use * 10);
-    R.d_misc = (double*)(((uintptr_t)(R.d_counts + (size_t)h_use * 10) + 63) & ~(uintptr_t)63);  // 64-byte aligned: basis[36] models[90] nm gram[...]
-    R.d_mask = (uint8_t*)(R.d_misc + 36 + 90 + 8 + 148 * 45);
+    R.d_misc = (double*)(((uintptr_t)(R.d_counts + (size_t)h_use * 10) + 63) & ~(uintptr_t)63);  // 64-byte aligned: state (256 B) | basis[36] | models[90] | nm
+    R.d_mask = (uint8_t*)(R.d_misc + 32 + 36 + 90 + 8);
     return MPL_OK;
 }
 
@@ -234,14 +195,11 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
     // every device -> host read of this function lands in the thread's pinned staging area:
     // | off (h+1) i32 | counts (<= 10 h) i32 | errsums (<= 10 h) f64 | gram partials | small (bestE, refit counts / sums) |
     const size_t m_max = (size_t)10 * h_use;
-    const int gb = mpl_gram_blocks(n);
     const size_t o_cnt = (((size_t)h_use + 1) * 4 + 15) & ~(size_t)15, o_err = o_cnt + ((m_max * 4 + 15) & ~(size_t)15),
-                 o_part = o_err + m_max * 8, o_small = o_part + (size_t)gb * 45 * 8;
+                 o_small = (o_err + m_max * 8 + 15) & ~(size_t)15;
     char* h_stage = nullptr;
-    if ((rc = mpl_stage_ensure(o_small + 512, (void**)&h_stage))) return rc;
+    if ((rc = mpl_stage_ensure(o_small + 2 * sizeof(MplPairState) + 64, (void**)&h_stage))) return rc;
     int32_t* off = (int32_t*)h_stage; int32_t* counts = (int32_t*)(h_stage + o_cnt); double* errsums = (double*)(h_stage + o_err);
-    double* part = (double*)(h_stage + o_part);
-    double* bestE = (double*)(h_stage + o_small); double* rc_err = bestE + 16; int32_t* rc_counts = (int32_t*)(bestE + 32); int32_t* h_rnm = rc_counts + 16;
     if ((rc = mpl_launch_fivept_solve(d_corr, n, d_samples, h_use, d_models, d_nm, st))) return rc;
     if ((rc = mpl_launch_compact_models(d_models, d_nm, h_use, d_off, d_dense, st))) return rc;
     MPL_CUDA_CHECK(cudaMemcpyAsync(off, d_off, ((size_t)h_use + 1) * 4, cudaMemcpyDeviceToHost, st));
@@ -262,50 +220,25 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
     Replay r = replay_selection(counts, errsums, off, h_use, n, conf, max_iters);
     if (iters_run) *iters_run = r.iters_run;
     if (r.best_model < 0) return MPL_OK;                      // runRANSAC returns false (maxGoodCount == 0)
-    MPL_CUDA_CHECK(cudaMemcpyAsync(bestE, d_dense + (size_t)r.best_model * 9, 72, cudaMemcpyDeviceToHost, st));
-    if ((rc = mpl_launch_sampson_mask(d_dense + (size_t)r.best_model * 9, d_corr, n, th, d_mask, nullptr, st))) return rc;
-    int best_count = r.best_count;
-    double errminsum = r.errminsum;
-
-    if (refine) {                                              // modelest.cpp:420-464
-        double* d_basis = d_misc; double* d_rmodels = d_misc + 36; int32_t* d_rnm = (int32_t*)(d_misc + 36 + 90);
-        double* d_gram = d_misc + 36 + 90 + 8;
-        if ((rc = mpl_launch_gram(d_corr, d_mask, n, d_gram, st))) return rc;
-        MPL_CUDA_CHECK(cudaMemcpyAsync(part, d_gram, (size_t)gb * 45 * 8, cudaMemcpyDeviceToHost, st));
-        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-        double G[9][9], V[9][9], w[9];
-        int k = 0;
-        for (int a = 0; a < 9; ++a) for (int b = a; b < 9; ++b, ++k) { double v = 0; for (int blk = 0; blk < gb; ++blk) v += part[(size_t)blk * 45 + k]; G[a][b] = G[b][a] = v; }
-        jacobi_eig9(G, V, w);
-        int ord[9]; for (int i = 0; i < 9; ++i) ord[i] = i;
-        for (int i = 0; i < 9; ++i) for (int j = i + 1; j < 9; ++j) if (w[ord[j]] > w[ord[i]]) std::swap(ord[i], ord[j]);   // descending, like singular values
-        double basis[36];
-        for (int b = 0; b < 4; ++b) for (int c = 0; c < 9; ++c) basis[9 * b + c] = V[c][ord[5 + b]];    // Vt rows 5..8 (five-point.cpp:388)
-        MPL_CUDA_CHECK(cudaMemcpyAsync(d_basis, basis, sizeof(basis), cudaMemcpyHostToDevice, st));
-        if ((rc = mpl_launch_fivept_from_basis(d_basis, d_rmodels, d_rnm, st))) return rc;
-        MPL_CUDA_CHECK(cudaMemcpyAsync(h_rnm, d_rnm, 4, cudaMemcpyDeviceToHost, st));
-        MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-        const int rnm = *h_rnm > 10 ? 10 : *h_rnm;
-        if (rnm > 0) {
-            if ((rc = mpl_launch_sampson_score(d_rmodels, rnm, d_corr, n, th, d_counts, d_errsums, st))) return rc;
-            MPL_CUDA_CHECK(cudaMemcpyAsync(rc_counts, d_counts, (size_t)rnm * 4, cudaMemcpyDeviceToHost, st));
-            MPL_CUDA_CHECK(cudaMemcpyAsync(rc_err, d_errsums, (size_t)rnm * 8, cudaMemcpyDeviceToHost, st));
-            MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-            int pick = -1;
-            for (int i = 0; i < rnm; ++i) {
-                if (rc_counts[i] > std::max(best_count, 4)) { pick = i; best_count = rc_counts[i]; errminsum = rc_err[i]; }
-                else if (rc_counts[i] == best_count && errminsum < DBL_MAX && errminsum > rc_err[i]) { pick = i; errminsum = rc_err[i]; }
-            }
-            if (pick >= 0) {
-                MPL_CUDA_CHECK(cudaMemcpyAsync(bestE, d_rmodels + 9 * pick, 72, cudaMemcpyDeviceToHost, st));
-                if ((rc = mpl_launch_sampson_mask(d_rmodels + 9 * pick, d_corr, n, th, d_mask, nullptr, st))) return rc;
-            }
-        }
-    }
+    // inlier mask of the selected model and the least-squares refit (modelest.cpp:420-464) on the device: the same kernels
+    // the pair-batch path uses (ransac_batch.cu), here for a batch of one.  The state record carries the selection.
+    MplPairState* h_state = (MplPairState*)(h_stage + o_small);
+    MplPairState* d_state = (MplPairState*)d_misc;
+    double* d_basis = d_misc + 32; double* d_rmodels = d_basis + 36; int32_t* d_rnm = (int32_t*)(d_rmodels + 90);
+    memset(h_state, 0, sizeof(*h_state));
+    h_state->n = n; h_state->niters = max_iters; h_state->iters_run = r.iters_run; h_state->best_count = r.best_count; h_state->best_slot = 0;
+    h_state->errminsum = r.errminsum;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(d_state, h_state, sizeof(MplPairState), cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(&d_state->E[0], d_dense + (size_t)r.best_model * 9, 72, cudaMemcpyDeviceToDevice, st));
+    if ((rc = mpl_launch_refit(d_corr, (size_t)n, d_state, 1, th, refine ? 1 : 0, d_mask, (size_t)n, d_basis, d_rmodels, d_rnm, st))) return rc;
+    MplPairState* h_out = h_state + 1;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(h_out, d_state, sizeof(MplPairState), cudaMemcpyDeviceToHost, st));
     if (mask) MPL_CUDA_CHECK(cudaMemcpyAsync(mask, d_mask, (size_t)n, cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
-    memcpy(E, bestE, 72);
-    *n_inl = best_count;
+    // modelest.cpp:443-445: a refit that yields no model makes runRANSAC return false (n_inl = 0; E and mask are then not
+    // results -- findEssentialMat returns before writing them, five-point.cpp:117-118)
+    *n_inl = h_out->n_inl;
+    if (h_out->n_inl > 0) memcpy(E, h_out->E, 72);
     return MPL_OK;
 }
 

@@ -72,14 +72,6 @@ fivept_solve_kernel(const double4* __restrict__ corr, int n, const int32_t* __re
     n_models[s] = cnt;
 }
 
-// models from a caller-supplied null-space basis (least-squares refit, modelest.cpp:420-464)
-__global__ void fivept_from_basis_kernel(const double* __restrict__ basis /* [4][9] */, double* __restrict__ models, int32_t* __restrict__ n_models)
-{
-    double ee[4][9];
-    for (int b = 0; b < 4; ++b) for (int k = 0; k < 9; ++k) ee[b][k] = basis[9 * b + k];
-    n_models[0] = fivept::solve_from_basis(ee, models);
-}
-
 // single-block exclusive scan of n_models -> offsets[h+1]: each thread owns a contiguous chunk (local sum, one block
 // scan of the 1024 partial sums, then the chunk's running prefix) -- two barriers in total instead of four per 1024
 // elements
@@ -209,55 +201,6 @@ sampson_score_kernel(const double* __restrict__ models, int m, const double4* __
     if (mi < m) { counts[mi] = good; if (errsums) errsums[mi] = esum; }
 }
 
-// inlier mask of ONE model (the selected hypothesis): mask[i] = err_i <= th^2
-__global__ void sampson_mask_kernel(const double* __restrict__ model, const double4* __restrict__ corr, int n, double th2,
-                                    uint8_t* __restrict__ mask, float* __restrict__ err)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double E[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) E[k] = model[k];
-    const float e = sampson_err(E, corr[i]);
-    mask[i] = ((double)e <= th2) ? 1 : 0;
-    if (err) err[i] = e;
-}
-
-// Gram matrix Q^T Q (9x9, upper triangle) of the epipolar constraint rows of the masked correspondences
-// (least-squares refit, modelest.cpp:420-446).  Deterministic: per-block partial sums in a fixed order;
-// the host adds the blocks in order.
-__global__ void __launch_bounds__(256) gram_kernel(const double4* __restrict__ corr, const uint8_t* __restrict__ mask, int n,
-                                                   double* __restrict__ partial /* [gridDim.x][45] */)
-{
-    __shared__ double sm[8][45];
-    double acc[45];
-#pragma unroll
-    for (int k = 0; k < 45; ++k) acc[k] = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        if (!mask[i]) continue;
-        const double4 c = corr[i];
-        const double r[9] = {c.x * c.z, c.y * c.z, c.z, c.x * c.w, c.y * c.w, c.w, c.x, c.y, 1.0};
-        int k = 0;
-#pragma unroll
-        for (int a = 0; a < 9; ++a)
-#pragma unroll
-            for (int b = a; b < 9; ++b) acc[k++] += r[a] * r[b];
-    }
-#pragma unroll
-    for (int k = 0; k < 45; ++k) {
-        double v = acc[k];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5][k] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 45) {
-        double v = 0;
-        for (int w = 0; w < 8; ++w) v += sm[w][threadIdx.x];
-        partial[blockIdx.x * 45 + threadIdx.x] = v;
-    }
-}
-
 }  // namespace
 
 // ---- launch wrappers (declared in mpl_ransac.h) ------------------------------------------------------
@@ -280,13 +223,6 @@ int mpl_launch_fivept_solve(const void* corr, int n, const int32_t* samples, int
     return MPL_OK;
 }
 
-int mpl_launch_fivept_from_basis(const double* basis, double* models, int32_t* n_models, cudaStream_t st)
-{
-    fivept_from_basis_kernel<<<1, 1, 0, st>>>(basis, models, n_models);
-    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    return MPL_OK;
-}
-
 int mpl_launch_compact_models(const double* models, const int32_t* n_models, int h, int32_t* offsets, double* dense, cudaStream_t st)
 {
     if (h <= 0) return MPL_OK;
@@ -301,12 +237,9 @@ int mpl_launch_compact_models(const double* models, const int32_t* n_models, int
 int mpl_launch_sampson_score(const double* models, int m, const void* corr, int n, double th, int32_t* counts, double* errsums, cudaStream_t st)
 {
     if (m <= 0) return MPL_OK;
-    static bool attr_set = false;
     const size_t smem = (size_t)kScoreStages * kChunk * 32;
-    if (!attr_set) {
-        MPL_CUDA_CHECK(cudaFuncSetAttribute(sampson_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    // per launch: the attribute is per device (mpl_init may re-target; per-thread contexts call concurrently)
+    MPL_CUDA_CHECK(cudaFuncSetAttribute(sampson_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int blocks = (m + kScoreThreads - 1) / kScoreThreads;
     int S = 1;                                                    // cluster size: fill ~2 CTAs per SM, >= 64 correspondences per rank
     while (S < 8 && blocks * S < 2 * 148 && n / (2 * S) >= 64) S *= 2;
@@ -318,23 +251,6 @@ int mpl_launch_sampson_score(const double* models, int m, const void* corr, int 
     at[0].val.clusterDim.x = (unsigned)S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     MPL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampson_score_kernel, models, m, (const double4*)corr, n, th * th, counts, errsums, S));
-    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    return MPL_OK;
-}
-
-int mpl_launch_sampson_mask(const double* model, const void* corr, int n, double th, uint8_t* mask, float* err, cudaStream_t st)
-{
-    if (n <= 0) return MPL_OK;
-    sampson_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(model, (const double4*)corr, n, th * th, mask, err);
-    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-    return MPL_OK;
-}
-
-int mpl_gram_blocks(int n) { int b = (n + 255) / 256; return b > 148 ? 148 : (b < 1 ? 1 : b); }
-
-int mpl_launch_gram(const void* corr, const uint8_t* mask, int n, double* partial, cudaStream_t st)
-{
-    gram_kernel<<<mpl_gram_blocks(n), 256, 0, st>>>((const double4*)corr, mask, n, partial);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
 }

@@ -93,3 +93,52 @@ def recover_pose(E, p1, p2, mask=None, dist=50.0, translatE=False, triang=triang
         return g4, np.eye(3), np.zeros((3, 1)), np.zeros((n, 3)), (np.zeros(n, np.uint8) if mask is not None else None)
     R, tt = combos[k]
     return good[k], R, tt, Qs[k][:3].T.copy(), (masks[k] if mask is not None else None)
+
+
+# ---- the driver's pixel -> camera conversion in front of estimateEssentialMat (tests/poselib-test/main.cpp:1522-1596) ----
+def img_to_cam(points, K):
+    """poselib::ImgToCamCoordTrans (pose_helper.cpp:1100-1109): float32 in, float32 out, arithmetic in double."""
+    pts = np.asarray(points, np.float32)
+    K = np.asarray(K, np.float64)
+    x = ((pts[:, 0].astype(np.float64) - K[0, 2]) / K[0, 0]).astype(np.float32)
+    y = ((pts[:, 1].astype(np.float64) - K[1, 2]) / K[1, 1]).astype(np.float32)
+    return np.stack([x, y], 1)
+
+
+def lens_dist_oulu(distorted, dist, iters=10):
+    """poselib::LensDist_Oulu (pose_helper.cpp:1232-1279), vectorised over points.  Returns (corrected float32 [n,2], ok [n])."""
+    d = np.asarray(dist, np.float64).reshape(-1)
+    k1, k2, p1, p2, k3, k4, k5, k6 = d[:8]
+    dx = distorted[:, 0].astype(np.float64); dy = distorted[:, 1].astype(np.float64)
+    cx = distorted[:, 0].astype(np.float32).copy(); cy = distorted[:, 1].astype(np.float32).copy()
+
+    def terms(cx, cy):
+        x = cx.astype(np.float64); y = cy.astype(np.float64)
+        r2 = x * x + y * y
+        _2xy = 2.0 * x * y
+        rad = (1.0 + ((k3 * r2 + k2) * r2 + k1) * r2) / (1.0 + ((k6 * r2 + k5) * r2 + k4) * r2)
+        d0 = p1 * _2xy + p2 * (r2 + 2.0 * x * x)
+        d1 = p1 * (r2 + 2.0 * y * y) + p2 * _2xy
+        return x, y, rad, d0, d1
+    for _ in range(iters):
+        x, y, rad, d0, d1 = terms(cx, cy)
+        cx = ((dx - d0) / rad).astype(np.float32)
+        cy = ((dy - d1) / rad).astype(np.float32)
+    x, y, rad, d0, d1 = terms(cx, cy)
+    px = (x * rad + d0 - dx).astype(np.float32); py = (y * rad + d1 - dy).astype(np.float32)
+    ok = ~(np.sqrt(px * px + py * py, dtype=np.float32) > np.float32(0.25))
+    return np.stack([cx, cy], 1), ok
+
+
+def remove_lens_dist(points1, points2, dist1, dist2):
+    """poselib::Remove_LensDist (pose_helper.cpp:1169-1228).  Returns (ok, points1, points2, keep mask over the input)."""
+    near_zero = lambda v: -1e-3 < v < 1e-3                                     # pose_helper.h:82-87
+    n = len(points1)
+    if near_zero(float(np.sum(dist1))) and near_zero(float(np.sum(dist2))):
+        return True, points1, points2, np.ones(n, bool)
+    c1, ok1 = lens_dist_oulu(points1, dist1)
+    c2, ok2 = lens_dist_oulu(points2, dist2)
+    keep = ok1 & ok2
+    if int(keep.sum()) < 16:
+        return False, points1, points2, keep
+    return True, c1[keep], c2[keep], keep

@@ -394,6 +394,11 @@ int orc_ransac5pt(const double *p1, const double *p2, int n, const int32_t *samp
         int k = 0;
         for (int i = 0; i < n; ++i) if (bestmask[i]) { a1[2*k] = p1[2*i]; a1[2*k+1] = p1[2*i+1]; a2[2*k] = p2[2*i]; a2[2*k+1] = p2[2*i+1]; ++k; }
         int nm = orc_run5point(a1, a2, k, models);
+        if (nm <= 0) {                                      /* modelest.cpp:443-445: "return result" with result still false */
+            free(a1); free(a2); free(mask); free(bestmask);
+            if (n_inl) *n_inl = 0;
+            return 0;
+        }
         for (int m = 0; m < nm; ++m) {
             int good = orc_sampson(models + 9 * m, p1, p2, n, th, NULL, mask, &esum);
             if (good > (best > 4 ? best : 4)) { memcpy(bestmask, mask, n); memcpy(E_out, models + 9 * m, 72); best = good; errminsum = esum; }

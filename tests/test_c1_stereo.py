@@ -43,6 +43,26 @@ def test_oracle_chain_recovers_the_calibration(oracle_chain):
     assert good == c["r"]["count"] and ang < 1.0 and dot > 0.998
 
 
+def test_oracle_refit_conditioning_floor(oracle_chain):
+    """CPU: how well-defined is the refit E on this pair?  Perturb the correspondences by 1e-16 .. 1e-14 relative and re-run
+    the ORACLE: the inlier count must not move, the refit E moves by up to ~1e-5 (the non-refit E by < 1e-7).  This is
+    the floor the GPU-vs-oracle tolerance of the refit (1e-4, a few times the floor) is set against."""
+    c = oracle_chain
+    rng = np.random.default_rng(3)
+    worst_refit, worst_plain = 0.0, 0.0
+    base_plain = oransac.ransac5pt(c["p1"], c["p2"], c["s"], _threshold(), refine=False)
+    for eps in (1e-16, 1e-15, 1e-14):
+        for _ in range(3):
+            p1 = c["p1"] * (1 + eps * rng.standard_normal(c["p1"].shape)); p2 = c["p2"] * (1 + eps * rng.standard_normal(c["p2"].shape))
+            r = oransac.ransac5pt(p1, p2, c["s"], _threshold(), refine=True)
+            assert r["count"] == c["r"]["count"]
+            worst_refit = max(worst_refit, min(np.linalg.norm(r["E"] - c["r"]["E"]), np.linalg.norm(r["E"] + c["r"]["E"])))
+            r0 = oransac.ransac5pt(p1, p2, c["s"], _threshold(), refine=False)
+            worst_plain = max(worst_plain, min(np.linalg.norm(r0["E"] - base_plain["E"]), np.linalg.norm(r0["E"] + base_plain["E"])))
+    print("oracle perturbation floor on the C1 pair: refit E moves %.3g, minimal-sample E moves %.3g" % (worst_refit, worst_plain))
+    assert worst_refit < 1e-4 and worst_plain < 1e-6
+
+
 @pytest.mark.gpu
 def test_gpu_chain_equals_oracle_chain(oracle_chain):
     import __graft_entry__ as g
@@ -58,15 +78,19 @@ def test_gpu_chain_equals_oracle_chain(oracle_chain):
     exp = c["r"]
     assert got["count"] == exp["count"] and got["iters"] == exp["iters"] and np.array_equal(got["mask"], exp["mask"])
     # The final E is the least-squares refit on all 2291 inliers (modelest.cpp:420-464).  On this real pair its degree-10
-    # polynomial is ill-conditioned: perturbing the inputs of the ORACLE by 1e-15 relative moves its own E by 2e-5
-    # (measured), so 1e-6 is below what any two evaluation orders can agree on here; the inlier set, count and
-    # iteration count -- which BASELINE asks to be exact -- are.  (Minimal-sample models agree to 1e-6: test_ransac_gpu.)
-    assert min(np.linalg.norm(got["E"] - exp["E"]), np.linalg.norm(got["E"] + exp["E"])) < 1e-3
+    # polynomial is ill-conditioned: test_oracle_refit_conditioning_floor (CPU, below) measures how far the ORACLE's own E
+    # moves under 1e-16..1e-14 relative input noise (up to ~1.4e-5), so north_star's 1e-6 is below what two evaluation
+    # orders can agree on HERE; the inlier set, count and iteration count -- which must be exact -- are.  Minimal-sample
+    # models agree to 1e-6 (test_ransac_gpu, test_pair_batch_gpu).  The bar is a few times that floor.
+    dE = min(np.linalg.norm(got["E"] - exp["E"]), np.linalg.norm(got["E"] + exp["E"]))
+    print("C1 refit: |E_gpu - E_oracle|_F = %.3g (oracle's own perturbation floor ~1e-5)" % dE)
+    assert dE < 1e-4
     good, R, t, Q, mk = poselib.getPoseTriangPts(got["E"], c["p1"], c["p2"], mask=got["mask"], dist=130.0)
     eg, eR, et, eQ, em = opose.recover_pose(exp["E"], c["p1"], c["p2"], mask=exp["mask"], dist=130.0)
     assert good == eg and np.array_equal(mk.reshape(-1) != 0, em != 0)
     ang = np.degrees(np.arccos(np.clip((np.trace(R @ eR.T) - 1) / 2, -1, 1)))
-    assert ang < 1e-2 and np.allclose(t, et, atol=1e-3)                           # same conditioning as E above
+    print("C1 pose: rotation difference to the oracle %.3g deg, |dt| %.3g" % (ang, np.abs(t - et).max()))
+    assert ang < 1e-3 and np.allclose(t, et, atol=1e-4)                           # north_star: 1e-3 degrees
     ang, dot = _pose_error(R, t)
     assert ang < 1.0 and dot > 0.998
 
@@ -74,7 +98,7 @@ def test_gpu_chain_equals_oracle_chain(oracle_chain):
 @pytest.mark.gpu
 def test_gpu_device_resident_pipeline(oracle_chain):
     """mpl_match_pose_pair (matches stay on the device between the scan and the scoring): the match list equals the
-    oracle's, the device-drawn samples obey getSubset's rules, and RANSAC on exactly those samples equals the oracle's."""
+    oracle's, the device-drawn samples are getSubset's (five distinct indices; checkSubset never rejects in the reference), and RANSAC on exactly those samples equals the oracle's."""
     import __graft_entry__ as g
     g.build()
     from matchinglib_poselib_b200 import poselib, _lib
@@ -86,13 +110,10 @@ def test_gpu_device_resident_pipeline(oracle_chain):
     n = len(c["mt"])
     assert s.shape == (1000, 5) and s.min() >= 0 and s.max() < n
     assert all(len(set(row)) == 5 for row in s.tolist())
-    for row in s[:200]:                                           # checkSubset on every prefix, both images
-        for k in range(3, 6):
-            assert datagen_pose._subset_ok(c["p1"][row[:k]]) and datagen_pose._subset_ok(c["p2"][row[:k]])
     assert len(np.unique(s, axis=0)) > 990                        # independent streams per sample
     exp = oransac.ransac5pt(c["p1"], c["p2"], s, _threshold(), refine=True)
     assert r["count"] == exp["count"] and r["iters"] == exp["iters"] and np.array_equal(r["mask"], exp["mask"])
-    assert min(np.linalg.norm(r["E"] - exp["E"]), np.linalg.norm(r["E"] + exp["E"])) < 1e-3
+    assert min(np.linalg.norm(r["E"] - exp["E"]), np.linalg.norm(r["E"] + exp["E"])) < 1e-4
     r2 = poselib.matchAndEstimatePose(G["l_desc"], G["r_desc"], G["l_norm"], G["r_norm"], "LINEAR", True, _threshold(), 1000, 0.999, True, seed=7)
     assert np.array_equal(r2["samples"], s) and np.array_equal(r2["mask"], r["mask"])       # deterministic for a given seed
     r3 = poselib.matchAndEstimatePose(G["l_desc"][:3], G["r_desc"], G["l_norm"][:3], G["r_norm"], "LINEAR", False, _threshold(), 50)

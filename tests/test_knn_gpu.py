@@ -301,3 +301,62 @@ def test_hamming_database_shard_beyond_2_pow_20_rows(m):
     i2, d2 = m.knn2_hamming(q2, t, 2)
     oi, od = orc.knn_hamming(q2, t, 2, 0, threads=8)
     assert np.array_equal(i2, oi) and np.array_equal(d2, od)
+
+
+@pytest.mark.parametrize("kind,mode", [("sift", 0), ("sift", 1), ("signed", 0), ("signed", 1)])
+def test_l2_default_path_vs_oracle_at_c2_size(m, kind, mode):
+    """BASELINE config C2 at its own size (20 000 x 20 000 x 128) through the DEFAULT path (auto -> tensor-core ranking +
+    exact re-rank) against the ORACLE: sift = bf16-exact integers (kind::f16 ranking), signed = unit-norm floats (kind::tf32
+    ranking + top-4 + certificate + exact re-rank); mode 0 = LINEAR (cvflann order, squared), 1 = BRUTEFORCENMS (NMSLIB
+    4-lane order, sqrt).  Distances bit-exact fp32, indices equal."""
+    import ctypes
+    lib = m._lib.load()
+    q, t = datagen.sift_like(20000, 20000, 128, seed=1002) if kind == "sift" else datagen.signed_float(20000, 20000, 128, seed=1002)
+    lib.mpl_set_l2_path(0)
+    idx, dist = m.knn2_l2(q, t, 2, bool(mode))
+    fb, tf = ctypes.c_uint(0), ctypes.c_uint(0)
+    m._lib.check(lib.mpl_knn_l2_last_stats_host(ctypes.byref(fb), ctypes.byref(tf)), "stats")
+    oi, od = orc.knn_l2(q, t, 2, mode, threads=os.cpu_count() or 8)
+    assert np.array_equal(dist.view(np.int32), od.view(np.int32)), (kind, mode)
+    assert np.array_equal(idx, oi), (kind, mode)
+    assert tf.value == (0 if kind == "sift" else 1)
+    print("C2 %s mode %d: tf32 ranking %d, uncertified queries rescanned exactly: %d of 20000" % (kind, mode, tf.value, fb.value))
+    assert fb.value < 400
+
+
+def test_c2_gpu_vs_reference_nmslib_near_ties_only(m):
+    """north_star's float bar against the reference's OWN code: the compiled vendored NMSLIB (oracle/_ref, built -Ofast, so
+    its fp32 sums are not reproducible bit for bit).  Every query whose first neighbour differs must be a near-tie within
+    1e-5 relative distance."""
+    if orc.ref_lib() is None:
+        pytest.skip("oracle/_ref/libnmslib_ref.so was not built (no /root/reference at build time)")
+    q, t = datagen.sift_like(4000, 20000, 128, seed=1002)
+    idx, dist = m.knn2_l2(q, t, 2, True)
+    ri, rd = orc.ref_nmslib_l2(q, t, threads=os.cpu_count() or 8)
+    diff = np.nonzero(idx[:, 0] != ri[:, 0])[0]
+    gaps = [abs(float(dist[i, 0]) - float(rd[i, 0])) / max(float(rd[i, 0]), 1e-30) for i in diff]
+    print("first-neighbour disagreements with the reference's NMSLIB: %d of %d, max relative distance gap %.3g" % (len(diff), len(q), max(gaps) if gaps else 0.0))
+    assert all(g < 1e-5 for g in gaps)
+    np.testing.assert_allclose(dist[:, 0], rd[:, 0], rtol=1e-5)
+
+
+def test_reinit_on_second_device(m):
+    """mpl_init(1) after work on device 0: the opt-in shared-memory attributes are per device."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU visible")
+    import datagen_pose
+    lib = m._lib.load()
+    q, t = datagen.sift_like(2100, 2100, 128, seed=2)
+    sc = datagen_pose.make_scene(500, 0.3, seed=5)
+    s = datagen_pose.draw_samples_fast(500, 64, seed=6)
+    try:
+        for dev in (0, 1, 0):
+            m._lib.check(lib.mpl_init(dev), "mpl_init")
+            idx, dist = m.knn2_l2(q, t, 2, False)
+            oi, od = orc.knn_l2(q, t, 2, 0, threads=8)
+            assert np.array_equal(idx, oi) and np.array_equal(dist.view(np.int32), od.view(np.int32))
+            r = m.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], refine=True)
+            assert r["ok"]
+    finally:
+        m._lib.check(lib.mpl_init(0), "mpl_init")

@@ -123,3 +123,64 @@ def test_estimate_essential_api(m):
         m.estimateEssentialMat(sc["p1"], sc["p2"], "USAC", sc["th"])
     with pytest.raises(AssertionError):
         m.estimateEssentialMat(sc["p1"][:4], sc["p2"][:4], "RANSAC", sc["th"])
+
+
+def test_c3_full_size_vs_oracle_subset(m):
+    """BASELINE config C3 at its own size: 10 000 correspondences x 100 000 pre-drawn samples, all solved and scored on the
+    GPU; the oracle runs a stratified 2 000-sample subset (every 50th sample) with full trace, and the whole run with its
+    adaptive stop.  Reports the real-root-set mismatch rate of the 5-point solver (five-point.cpp:435-455: a root is kept iff
+    |imag| <= 1e-10 of cv::solvePoly's iterate; the GPU polynomial comes from a different null-space basis -- Householder
+    instead of SVD -- so near-double roots can fall on the other side)."""
+    n, h = 10000, 100000
+    sc = datagen_pose.make_scene(n, 0.3, seed=1003)
+    s = datagen_pose.draw_samples_fast(n, h, seed=1004)
+    got = m.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], max_iters=h, trace=True)
+    off = np.concatenate([[0], np.cumsum(got["n_models"])])
+    assert off[-1] == len(got["models"]) and 3.5 * h < off[-1] < 6 * h
+    sub = np.arange(0, h, 50)
+    ref = orc.ransac5pt(sc["p1"], sc["p2"], s[sub], sc["th"], max_iters=len(sub), trace=True)
+    roff = np.concatenate([[0], np.cumsum(ref["n_models"])])
+    mismatched, checked_models, loose = 0, 0, 0
+    for k, si in enumerate(sub):
+        a = got["models"][off[si]:off[si + 1]]; b = ref["models"][roff[k]:roff[k + 1]]
+        if len(a) != len(b):
+            mismatched += 1
+            continue
+        if len(a) == 0:
+            continue
+        d = np.minimum(np.linalg.norm(a[:, None] - b[None], axis=2), np.linalg.norm(a[:, None] + b[None], axis=2))
+        j = d.argmin(1)
+        if sorted(j.tolist()) != list(range(len(a))):
+            mismatched += 1
+            continue
+        tight = d.min(1) < 1e-10
+        loose += int((~tight).sum())
+        checked_models += int(tight.sum())
+        assert np.array_equal(got["counts"][off[si]:off[si + 1]][tight], ref["counts"][roff[k]:roff[k + 1]][j][tight]), si
+    rate = mismatched / len(sub)
+    print("C3: %d models from %d samples; oracle subset %d samples: real-root-set mismatch rate %.4f (%d samples), "
+          "%d models compared with exact inlier counts, %d models looser than 1e-10" % (off[-1], h, len(sub), rate, mismatched, checked_models, loose))
+    assert rate < 0.01 and checked_models > 0.9 * roff[-1]
+    # the whole run, as estimateEssentialMat would drive it: identical (count, iterations, mask), E to 1e-6
+    for refine in (False, True):
+        g = m.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], max_iters=h, refine=refine)
+        e = orc.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], max_iters=h, refine=refine)
+        assert g["count"] == e["count"] and g["iters"] == e["iters"] and np.array_equal(g["mask"], e["mask"])
+        assert _edist(g["E"], e["E"]) < 1e-6
+
+
+def test_refit_distribution_vs_oracle(m):
+    """Least-squares refit (modelest.cpp:420-464; device Givens QR + Jacobi SVD of the triangle) over 100 scenes: the inlier
+    set must be the oracle's and |E_gpu - E_oracle| is reported (median far below 1e-6 on synthetic scenes)."""
+    ds = []
+    for k in range(100):
+        n = 200 + 37 * k
+        sc = datagen_pose.make_scene(n, 0.1 + 0.004 * k, seed=900 + k)
+        s = datagen_pose.draw_samples_fast(n, 200, seed=k)
+        g = m.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], max_iters=200, refine=True)
+        e = orc.ransac5pt(sc["p1"], sc["p2"], s, sc["th"], max_iters=200, refine=True)
+        assert g["count"] == e["count"] and g["iters"] == e["iters"] and np.array_equal(g["mask"], e["mask"]), k
+        ds.append(_edist(g["E"], e["E"]))
+    ds = np.array(ds)
+    print("refit |E_gpu - E_oracle| over 100 scenes: median %.3g, 90%% %.3g, max %.3g" % (np.median(ds), np.quantile(ds, 0.9), ds.max()))
+    assert np.median(ds) < 1e-9 and ds.max() < 1e-6
