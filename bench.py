@@ -11,8 +11,15 @@ region.  `parts` carries the other two legs of the metric on their own configs: 
 8192 x 8192 x 32 B) and RANSAC 5-point scoring (C3, 10 000 correspondences x 100 000 pre-drawn samples).
 
 N > 1 (torchrun, one rank per GPU): the database regime -- every rank holds its own 20 000-row train
-shard, the queries are replicated, per-rank top-2 keys are all-gathered over NCCL and merged
-(weak scaling: pairs grow with N).
+shard, the queries are replicated, per-rank top-2 keys are exchanged over NVLink peer memory inside the merge
+kernel (weak scaling: pairs grow with N).
+
+At EVERY N the line also carries the two workloads BASELINE.json names for multi-GPU:
+  parts.database_c5    10 000 ORB queries x 12.5 M train rows PER RANK (100 M on 8 GPUs), Hamming top-2 per shard +
+                       peer-memory all-gather fused with the merge; planted copies + an oracle spot check (weak scaling)
+  parts.pair_batch_c4  4096 image pairs (AKAZE-like 61 B, 5000 x 5000, + per-pair RANSAC 1000 samples, refit), pair p on
+                       rank p mod N, each rank ONE host thread calling mpl_match_pose_batch from pinned host buffers
+                       (strong scaling)
 
 --impl reference: the reference's CPU path on the host cores (oracle/_ref = the reference's vendored
 NMSLIB compiled from its own sources; falls back to the oracle port), bounded sample per step.
@@ -58,11 +65,12 @@ def peaks():
 def pipe_peaks():
     """Per-pipe issue rates measured on a B200 of this pool with tools/microbench.cu (profiles/r1_microbench.json):
     roofline denominators where MEASURED_PEAKS.json has none (integer POPC, fp64)."""
-    p = os.path.join(ROOT, "profiles", "r1_microbench.json")
-    if os.path.exists(p):
-        d = json.load(open(p))
-        d["_src"] = "measured: tools/microbench.cu -> profiles/r1_microbench.json"
-        return d
+    for name in ("r2_microbench.json", "r1_microbench.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            d = json.load(open(p))
+            d["_src"] = "measured: tools/microbench.cu -> profiles/%s" % name
+            return d
     # CUDA programming guide throughput table x 148 SMs x 1.965 GHz
     return dict(popc_gops=4650.0, dfma_ginst=18600.0, ddiv_rn_gops=1300.0, _src="fallback: programming-guide rates")
 
@@ -70,9 +78,12 @@ def pipe_peaks():
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
     bench command (profiles/r1_ncu_traffic.json); None when there is no capture for the kernel."""
-    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
-    if os.path.exists(p):
-        return json.load(open(p)).get(kernel, {}).get("dram_bytes_per_launch")
+    for name in ("r2_ncu_traffic.json", "r1_ncu_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            v = json.load(open(p)).get(kernel, {}).get("dram_bytes_per_launch")
+            if v is not None:
+                return v
     return None
 
 
@@ -465,69 +476,243 @@ def bench_hamming(g, steps, warmup):
     return dict(
         workload="C1: ORB 8192x8192x32B Hamming k=2 + ratio (LINEAR)", value=pairs / (step_ms * 1e-3), unit="pairs/s", ms_per_step=step_ms,
         dtype="u32 popc",
-        roofline=dict(bound="hbm", achieved=bytes_alg / (kern_ms * 1e-3) / 1e9, peak=pk["hbm_gbs"], unit="GB/s",
-                      frac=bytes_alg / (kern_ms * 1e-3) / 1e9 / pk["hbm_gbs"], traffic=ncu_traffic("hamming_top2_kernel"), peak_src=pk["_src"],
-                      kernel="hamming_top2_kernel", kernel_ms=kern_ms,
-                      note="compute-bound on the integer pipe, not HBM (algorithmic bytes are 0.65 MB): see alu"),
-        # SURVEY 8(d) counts ceil(B/4) POPC per pair (the reference's scalar form).  The kernel folds 8 XOR words through 3
-        # carry-save adders and issues 5 POPC + 19 logic/add/min-max instructions per pair, so that figure can exceed 1: the
-        # binding pipe is the integer ALU (LOP3/IADD3/VIMNMX, 64 lanes/clk/SM = the measured SHF rate).
-        alu=dict(bound="int popc issue (algorithmic count); executed: int alu issue", achieved_gpopc_s=popc / (kern_ms * 1e-3) / 1e9,
-                 peak_gpopc_s=pp["popc_gops"], frac=popc / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], popc_per_pair=nb // 4,
-                 popc_executed_per_pair=5 * (nb // 32) if nb % 32 == 0 else None,
-                 alu_instr_per_pair=HAMMING_ALU_PER_PAIR.get(nb),
-                 alu_frac=(pairs * HAMMING_ALU_PER_PAIR[nb] / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"]) if nb in HAMMING_ALU_PER_PAIR and "shf_funnel_ginst" in pp else None,
-                 peak_src=pp["_src"]),
+        # Bound = the integer pipes, not HBM (algorithmic bytes are 0.65 MB).  SURVEY 8(d) counts ceil(B/4) POPC per pair (the
+        # reference's scalar form); the kernel folds 8 XOR words through 3 carry-save adders and EXECUTES 5 POPC + 19 alu-pipe
+        # instructions (15 LOP3 + 3 VIMNMX + 1 IADD3) per pair: the binding pipe is the alu (64 lanes/clk/SM, measured as the SHF rate).
+        roofline=dict(bound="int alu issue (executed instructions)", achieved=pairs * HAMMING_ALU_PER_PAIR[nb] / (kern_ms * 1e-3) / 1e9,
+                      peak=pp.get("shf_funnel_ginst"), unit="G alu instr/s",
+                      frac=(pairs * HAMMING_ALU_PER_PAIR[nb] / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"]) if "shf_funnel_ginst" in pp else None,
+                      alu_instr_per_pair=HAMMING_ALU_PER_PAIR[nb], popc_executed_per_pair=5,
+                      popc_frac_executed=pairs * 5 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
+                      popc_frac_algorithmic_8_per_pair=popc / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
+                      hbm_gbs_algorithmic=bytes_alg / (kern_ms * 1e-3) / 1e9, hbm_peak_gbs=pk["hbm_gbs"], traffic=ncu_traffic("hamming_top2_kernel"),
+                      kernel="hamming_top2_kernel<2>", kernel_ms=kern_ms, peak_src=pp["_src"]),
+        cpu_baseline=cpu_hamming_c1(q, t),
         e2e=dict(value=pairs / float(np.median(ts)), unit="pairs/s", h2d_bytes_per_step=int(hq.nbytes + ht.nbytes), d2h_bytes_per_step=int(nq * 16),
                  matches=int(len(mt))))
 
 
 # ------------------------------------------------------------------------------------------------
-# C4 unit: ONE image pair, AKAZE-like 61-byte descriptors 5000 x 5000 + per-pair RANSAC (1000 samples), end to end through
-# mpl_match_pose_pair (host buffers in, matches / E / mask out; matches stay on the device between the two halves)
+# C4: batch of image pairs (AKAZE-like 61-byte descriptors 5000 x 5000 + per-pair RANSAC, 1000 samples, refit) through
+# mpl_match_pose_batch: ONE host thread per rank, pinned host buffers in, (matches, E, mask) out, everything in between on
+# the device.  Pair p runs on rank p mod N (independent units, no data-path collective): strong scaling.
 # ------------------------------------------------------------------------------------------------
-def bench_pair_pipeline(g, reps):
-    import datagen, datagen_pose
-    from matchinglib_poselib_b200 import poselib
-    n, nb = 5000, 61
-    sc = datagen_pose.make_scene(n, 0.0, seed=1004)
-    rng = np.random.default_rng(1004)
+C4 = dict(pairs=4096, n=5000, nbytes=61, samples=1000, seed=1004, pool=4)
+
+
+def make_c4_pair(seed, n=None, nb=None, pin=True):
+    import datagen_pose
+    from matchinglib_poselib_b200 import matchinglib
+    n = n or C4["n"]; nb = nb or C4["nbytes"]
+    sc = datagen_pose.make_scene(n, 0.0, seed=seed)
+    rng = np.random.default_rng(seed)
     t = rng.integers(0, 256, (n, nb), dtype=np.uint8)
     q = rng.integers(0, 256, (n, nb), dtype=np.uint8)
     good = rng.random(n) < 0.5                                   # half of the queries are noisy copies of "their" train row
     flips = np.packbits(rng.random((n, nb * 8)) < 0.08, axis=1)
     q[good] = t[good] ^ flips[good]
-    th = sc["th"]
-    r = None
-    ts = []
-    for i in range(reps + 2):
-        g.torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        r = poselib.matchAndEstimatePose(q, t, sc["p1"], sc["p2"], "LINEAR", True, th, 1000, 0.999, True, seed=5)
-        if i >= 2:
-            ts.append(time.perf_counter() - t0)
-    dt = float(np.median(ts))
-    # a batch of pairs: one host thread per pair in flight (contexts are per thread: own stream and scratch), the GPU
-    # overlaps the latency-bound per-pair RANSAC kernels of different pairs
-    from concurrent.futures import ThreadPoolExecutor
-    n_threads = min(32, 2 * (os.cpu_count() or 1))            # threads mostly wait for the device
-    n_pairs = 8 * n_threads
+    arrs = [q, t, np.ascontiguousarray(sc["p1"]), np.ascontiguousarray(sc["p2"])]
+    if pin:                                                      # pinned host buffers, as a capture pipeline would hold them
+        out = []
+        for a in arrs:
+            v = matchinglib.pinned_array(a.shape, a.dtype)
+            v[...] = a
+            out.append(v)
+        arrs = out
+    return arrs, sc["th"]
 
-    def one(i):
-        return poselib.matchAndEstimatePose(q, t, sc["p1"], sc["p2"], "LINEAR", True, th, 1000, 0.999, True, seed=5 + i)["count"]
 
-    with ThreadPoolExecutor(n_threads) as ex:
-        list(ex.map(one, range(2 * n_threads)))                  # warm-up: every thread creates its context
-        g.torch.cuda.synchronize()
+def bench_pair_batch_c4(g, world=1, rank=0, dist=None, n_pairs=None):
+    from matchinglib_poselib_b200 import poselib
+    torch = g.torch
+    n_pairs = n_pairs or C4["pairs"]
+    pool = [make_c4_pair(C4["seed"] + i) for i in range(C4["pool"])]
+    th = pool[0][1]
+    mine = list(range(rank, n_pairs, world))                    # pair p -> rank p mod N
+    pairs = [tuple(pool[(p // world) % C4["pool"]][0]) for p in mine]
+    seeds = [5 + p for p in mine]
+    h = C4["samples"]
+    sync = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+    # unit latency: one pair through the same call (a batch of one)
+    lat = []
+    for i in range(7):
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
-        counts = list(ex.map(one, range(n_pairs)))
-        bt = time.perf_counter() - t0
-    return dict(workload="C4 unit: one pair, AKAZE-like 61 B x 5000 x 5000 Hamming k=2 + ratio, then RANSAC 5pt (1000 device-drawn samples, refit), "
-                         "mpl_match_pose_pair end to end from host buffers",
-                value=n_pairs / bt, unit="image pairs/s", ms_per_pair=dt * 1e3, single_thread_pairs_per_s=1.0 / dt,
-                batch=dict(pairs=n_pairs, host_threads=n_threads, seconds=bt, min_inliers=int(min(counts))),
-                matches=int(len(r["matches"])), inliers=int(r["count"]),
-                ransac_iterations=int(r["iters"]), h2d_bytes_per_pair=int(q.nbytes + t.nbytes + 2 * n * 16), d2h_bytes_per_pair=int(len(r["matches"]) * 17 + 72))
+        one = poselib.matchAndEstimatePoseBatch(pairs[:1], "LINEAR", True, th, h, 0.999, True, seeds=seeds[:1], want_samples=(i == 0))
+        lat.append(time.perf_counter() - t0)
+    unit = one[0]
+    first = poselib.matchAndEstimatePoseBatch(pairs[:1], "LINEAR", True, th, h, 0.999, True, seeds=seeds[:1], want_samples=True)[0]
+    # the batch is marshalled once (ctypes pair table); the timed region is exactly one mpl_match_pose_batch call per rank
+    full = poselib.PairBatch(pairs, "LINEAR", True, th, h, 0.999, True, seeds=seeds)
+    b_match = poselib.PairBatch(pairs, "LINEAR", True, th, 0, 0.999, False, seeds=seeds)
+    b_norefit = poselib.PairBatch(pairs, "LINEAR", True, th, h, 0.999, False, seeds=seeds)
+    poselib.PairBatch(pairs[:min(len(pairs), 512)], "LINEAR", True, th, h, 0.999, True, seeds=seeds[:512]).run()   # warm-up: arenas, first DMA of the pinned pages
+    l0 = g.launches()
+    torch.cuda.synchronize()
+    sync()
+    t0 = time.perf_counter()
+    full.run()
+    dt = time.perf_counter() - t0
+    launches = g.launches() - l0
+    res = full.results()
+    # matching only (h = 0) and matching + RANSAC without the refit, same batch: where the time goes
+    sync(); t0 = time.perf_counter(); b_match.run(); dt_match = time.perf_counter() - t0
+    sync(); t0 = time.perf_counter(); b_norefit.run(); dt_norefit = time.perf_counter() - t0
+    tm = torch.tensor([dt, dt_match, dt_norefit], device=g.dev, dtype=torch.float64)
+    mn = torch.tensor([min(r["count"] for r in res)], device=g.dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)                # slowest rank
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+    dt, dt_match, dt_norefit = (float(x) for x in tm.tolist())
+    out = None
+    if rank == 0:
+        # oracle check of one pair of the batch (same device-drawn samples): matches bit-exact, count / iterations / mask exact
+        from oracle import knn as oknn, ransac as oransac
+        q, t, p1, p2 = (np.asarray(a) for a in pairs[0])
+        idx, dd = oknn.knn_hamming(q, t, 2, 0, threads=os.cpu_count() or 1)
+        t_cpu0 = time.perf_counter()
+        idx, dd = oknn.knn_hamming(q, t, 2, 0, threads=1)
+        omt = oknn.ratio_matches(idx, dd, True)
+        c1 = np.ascontiguousarray(p1[omt["queryIdx"]]); c2 = np.ascontiguousarray(p2[omt["trainIdx"]])
+        exp = oransac.ransac5pt(c1, c2, first["samples"], th, max_iters=h, refine=True)
+        cpu_pair_s = time.perf_counter() - t_cpu0
+        ok = bool(np.array_equal(first["matches"], omt) and first["count"] == exp["count"] and first["iters"] == exp["iters"]
+                  and np.array_equal(first["mask"], exp["mask"]))
+        if not ok:
+            raise RuntimeError("C4: pair 0 differs from the oracle chain")
+        npair_bytes = int(sum(np.asarray(a).nbytes for a in pairs[0]))
+        out = dict(workload="C4: %d image pairs, AKAZE-like 61 B x 5000 x 5000 Hamming k=2 + ratio (LINEAR), per-pair RANSAC 5pt (%d device-drawn samples, "
+                            "adaptive stop, refit); pair p -> rank p mod N; one host thread per rank, mpl_match_pose_batch from pinned host buffers" % (n_pairs, h),
+                   value=n_pairs / dt, unit="image pairs/s", n_gpus=world, scaling="strong", seconds=dt, pairs=n_pairs,
+                   e2e=dict(value=n_pairs / dt, unit="image pairs/s", h2d_bytes_per_step=npair_bytes * n_pairs,
+                            d2h_bytes_per_step=int(n_pairs * (C4["n"] * 17 + 136)), note="the batch call IS the end-to-end path: host buffers in, host results out"),
+                   descriptor_pairs_per_s=n_pairs * float(C4["n"]) ** 2 / dt,
+                   stages=dict(matching_only_pairs_per_s=n_pairs / dt_match, match_ransac_norefit_pairs_per_s=n_pairs / dt_norefit),
+                   unit_latency_ms=float(np.median(lat[2:]) * 1e3), unit_matches=int(len(unit["matches"])), unit_inliers=int(unit["count"]),
+                   unit_ransac_iterations=int(unit["iters"]), min_inliers=int(mn.item()), gpu_launches=int(launches),
+                   host_threads_per_rank=1, host_cores=os.cpu_count(), oracle_check="pair 0: matches bit-exact, count/iterations/mask exact",
+                   cpu_baseline=dict(value=1.0 / cpu_pair_s, unit="image pairs/s", cores=1, kind="port",
+                                     sample="one pair: oracle cvflann-order Hamming scan 5000x5000x61 B + ratio + RANSAC 5pt (adaptive stop, refit), single thread as the reference runs it"),
+                   data="synthetic (pool of %d distinct pairs per rank, every pair its own sample seed)" % C4["pool"])
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# C5: database / loop-closure regime -- 10 000 ORB queries against 12.5 M train rows PER RANK (100 M on 8 GPUs; weak scaling),
+# Hamming top-2 per shard with global indices, then the all-gather over NVLink peer memory fused with the merge.
+# ------------------------------------------------------------------------------------------------
+C5 = dict(nq=10000, rows=12_500_000, nbytes=32, seed=1005)
+
+
+def bench_database_c5(g, steps, world=1, rank=0, dist=None, peers_factory=None):
+    torch, lib, m = g.torch, g.lib, g.m
+    dev = g.dev
+    NQ, ROWS, NB = C5["nq"], C5["rows"], C5["nbytes"]
+    gen = torch.Generator(device=dev); gen.manual_seed(C5["seed"] + rank)
+    t = torch.randint(0, 256, (ROWS, NB), dtype=torch.uint8, device=dev, generator=gen)
+    gq = torch.Generator(device=dev); gq.manual_seed(424242)
+    q = torch.randint(0, 256, (NQ, NB), dtype=torch.uint8, device=dev, generator=gq)          # same on every rank
+    mine = torch.arange(rank, NQ, world, device=dev)                                          # plant query i as row (i * 1237) % ROWS of rank i % world
+    t[(mine * 1237) % ROWS] = q[mine]
+    w16 = NB // 16
+    scr_bytes = int(lib.mpl_knn_hamming_scratch_bytes(NQ, ROWS, w16))
+    scr = torch.empty(scr_bytes, dtype=torch.uint8, device=dev)
+    keys = torch.empty((NQ, 2), dtype=torch.int64, device=dev)
+    idx = torch.empty((NQ, 2), dtype=torch.int32, device=dev)
+    dst = torch.empty((NQ, 2), dtype=torch.int32, device=dev)
+    peers = setup_peers(g, dist, rank, world, NQ) if world > 1 else None
+
+    def step():
+        st = g.stream()
+        m._lib.check(lib.mpl_knn2_hamming_dev(q.data_ptr(), NQ, t.data_ptr(), ROWS, w16, rank * ROWS, scr.data_ptr(), scr_bytes, keys.data_ptr(), st), "hamming")
+        if peers is not None:
+            m._lib.check(lib.mpl_allgather_merge_top2_dev(keys.data_ptr(), NQ, rank, world, peers[0], peers[1], 2, 0, idx.data_ptr(), dst.data_ptr(), None, st), "allgather_merge")
+        else:
+            m._lib.check(lib.mpl_merge_top2_dev(keys.data_ptr(), 1, NQ, 2, 0, idx.data_ptr(), dst.data_ptr(), None, st), "merge")
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    steps = max(3, min(steps, 5))
+    l0 = g.launches()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:                                              # train shard (400 MB) > L2: nothing to flush between steps
+        a.record(); step(); b.record()
+    torch.cuda.synchronize()
+    launches = g.launches() - l0
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    lib.mpl_prof_enable(1); step(); torch.cuda.synchronize(); lib.mpl_prof_enable(0)
+    k_ms, k_n = g.prof_read(PROF["hamming"]); mg_ms, mg_n = g.prof_read(PROF["merge"])
+    if peers is not None:
+        to = ctypes.c_int(0)
+        m._lib.check(lib.mpl_peer_status(peers[1][rank], ctypes.byref(to), g.stream()), "peer_status")
+        if to.value:
+            raise RuntimeError("rank %d: allgather_merge timed out waiting for its peers" % rank)
+    if dist is not None:
+        tm = torch.tensor([ms], device=dev); dist.all_reduce(tm, op=dist.ReduceOp.MAX); ms = float(tm.item())
+    # (1) every query's planted copy: global index = owner * ROWS + (i * 1237) % ROWS, distance 0, runner-up further away
+    i_all = torch.arange(NQ, device=dev)
+    want = (i_all % world) * ROWS + (i_all * 1237) % ROWS
+    planted = bool((idx[:, 0].long() == want).all().item()) and bool((dst[:, 0] == 0).all().item()) and bool((dst[:, 1] > 0).all().item())
+    # (2) oracle spot check of the MERGED result: every rank runs the oracle over its own shard for 48 unplanted probe queries,
+    #     the per-rank oracle top-2 are gathered and merged on the host in (dist, index) order and compared with what the
+    #     GPUs returned for those probes (a second, short pass with the probes appended to nothing else)
+    from oracle import knn as oknn
+    n_probe = 48
+    probe = torch.randint(0, 256, (n_probe, NB), dtype=torch.uint8, device=dev, generator=torch.Generator(device=dev).manual_seed(99))
+    pk = torch.empty((n_probe, 2), dtype=torch.int64, device=dev); pi = torch.empty((n_probe, 2), dtype=torch.int32, device=dev); pd = torch.empty((n_probe, 2), dtype=torch.int32, device=dev)
+    pscr_b = int(lib.mpl_knn_hamming_scratch_bytes(n_probe, ROWS, w16)); pscr = torch.empty(max(pscr_b, 16), dtype=torch.uint8, device=dev)
+    m._lib.check(lib.mpl_knn2_hamming_dev(probe.data_ptr(), n_probe, t.data_ptr(), ROWS, w16, rank * ROWS, pscr.data_ptr(), pscr_b, pk.data_ptr(), g.stream()), "hamming probe")
+    if world > 1:
+        allk = torch.empty((world, n_probe, 2), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allk.view(-1, 2), pk)
+    else:
+        allk = pk.view(1, n_probe, 2)
+    m._lib.check(lib.mpl_merge_top2_dev(allk.data_ptr(), world, n_probe, 2, 0, pi.data_ptr(), pd.data_ptr(), None, g.stream()), "merge probe")
+    torch.cuda.synchronize()
+    t_cpu0 = time.perf_counter()
+    oi, od = oknn.knn_hamming(probe.cpu().numpy(), t.cpu().numpy(), 2, 0, threads=max(1, (os.cpu_count() or 1) // world))
+    cpu_s = time.perf_counter() - t_cpu0
+    okeys = (od.astype(np.int64) << 32) | (oi.astype(np.int64) + rank * ROWS)
+    ok_t = torch.from_numpy(okeys).to(dev)
+    if world > 1:
+        allo = torch.empty((world, n_probe, 2), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allo.view(-1, 2), ok_t)
+    else:
+        allo = ok_t.view(1, n_probe, 2)
+    merged = np.sort(allo.permute(1, 0, 2).reshape(n_probe, -1).cpu().numpy(), axis=1)[:, :2]
+    gi, gd = pi.cpu().numpy(), pd.cpu().numpy()
+    oracle_ok = bool(np.array_equal(merged & 0xFFFFFFFF, gi.astype(np.int64)) and np.array_equal(merged >> 32, gd.astype(np.int64)))
+    ok_all = torch.tensor([1 if (planted and oracle_ok) else 0], device=dev)
+    if dist is not None:
+        dist.all_reduce(ok_all, op=dist.ReduceOp.MIN)
+    if int(ok_all.item()) == 0:
+        raise RuntimeError("rank %d: C5 check failed (planted %s, oracle %s)" % (rank, planted, oracle_ok))
+    out = None
+    if rank == 0:
+        pairs = float(NQ) * ROWS * world
+        pp = pipe_peaks()
+        kern_ms = k_ms / max(k_n, 1)
+        per_gpu = float(NQ) * ROWS
+        alu = HAMMING_ALU_PER_PAIR[NB]
+        out = dict(workload="C5: %d ORB queries x %d train rows per rank (%d rows on %d GPU%s), Hamming k=2, train sharded, top-2 merged over NVLink" %
+                            (NQ, ROWS, ROWS * world, world, "s" if world > 1 else ""),
+                   value=pairs / (ms * 1e-3), unit="pairs/s", n_gpus=world, scaling="weak", ms_per_step=ms, dtype="u32 popc", gpu_launches=int(launches),
+                   exchange="NVLink peer memory inside the merge kernel (mpl_allgather_merge_top2_dev)" if world > 1 else "none (one shard)",
+                   kernels=dict(hamming_top2_ms=kern_ms, merge_or_exchange_ms=mg_ms / max(mg_n, 1)),
+                   roofline=dict(bound="int alu issue (executed LOP3 + VIMNMX + IADD3 per pair)", achieved=per_gpu * alu / (kern_ms * 1e-3) / 1e9,
+                                 peak=pp.get("shf_funnel_ginst"), unit="G alu instr/s per GPU", frac=per_gpu * alu / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"] if "shf_funnel_ginst" in pp else None,
+                                 popc_frac_executed=per_gpu * 5 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], popc_frac_algorithmic_8_per_pair=per_gpu * 8 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
+                                 hbm_gbs=(ROWS * NB) / (kern_ms * 1e-3) / 1e9, kernel="hamming_top2_kernel<2>", kernel_ms=kern_ms, peak_src=pp["_src"]),
+                   checks=dict(planted_neighbours_found=planted, oracle_probe_queries=n_probe, oracle_merged_equal=oracle_ok),
+                   cpu_baseline=dict(value=float(n_probe) * ROWS / cpu_s, unit="pairs/s", cores=max(1, (os.cpu_count() or 1) // world), kind="port",
+                                     sample="%d probe queries x %d rows (this rank's shard), oracle cvflann-order Hamming scan; the full config is %d x that work (extrapolate linearly)" %
+                                            (n_probe, ROWS, (NQ * world) // n_probe)))
+    del t
+    torch.cuda.empty_cache()
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -602,11 +787,116 @@ def bench_ransac(g, steps, warmup):
         workload="C3: RANSAC 5pt, 10000 correspondences x 100000 pre-drawn samples (%d real models)" % n_models,
         value=evals / (step_ms * 1e-3), unit="model*correspondence Sampson evaluations/s", ms_per_step=step_ms, dtype="f64",
         hypotheses_per_ms=h / step_ms, models_per_ms=n_models / step_ms,
+        north_star_target="1e6 hypotheses/ms over 10k correspondences = 1e13 exact-fp64 Sampson evaluations/s = %.1fx the measured fp64 issue ceiling (%.3g evaluations/s); "
+                          "measured here: %.3g hypotheses/ms, %.3g models/ms" % (1e13 / evals_peak, evals_peak, h / step_ms, n_models / step_ms),
+        cpu_baseline=cpu_ransac_c3(sc, samples, n_models, h),
         kernels=dict(sampson_score_ms=score_ms, fivept_solve_ms=so_ms / max(so_n, 1),
                      score_evals_per_s=evals / (score_ms * 1e-3), score_fp64_tflops=evals * 33 / (score_ms * 1e-3) / 1e12),
         best_inliers=int(d_counts[:n_models].max().item()),
         e2e=dict(value=evals / float(np.median(ts)), unit="evaluations/s", h2d_bytes_per_step=int(p1.nbytes + p2.nbytes + samples.nbytes),
                  d2h_bytes_per_step=int(n_models * 12 + n), inliers=int(cnt.value)))
+
+
+# ------------------------------------------------------------------------------------------------
+# C2 second float set: SURF/KAZE-like unit-norm signed floats -> kind::tf32 ranking, top-4 lists, certificate, exact re-rank
+# ------------------------------------------------------------------------------------------------
+def bench_l2_tf32(g, steps, warmup):
+    import datagen
+    torch, lib, m = g.torch, g.lib, g.m
+    q, t = datagen.signed_float(C2["nq"], C2["nt"], C2["dim"], seed=C2["seed"])
+    nq, nt, dim = q.shape[0], t.shape[0], q.shape[1]
+    d_q, d_t = torch.from_numpy(q).to(g.dev), torch.from_numpy(t).to(g.dev)
+    scr_bytes = int(lib.mpl_knn_l2_scratch_bytes(nq, nt, dim))
+    d_scr = torch.empty(scr_bytes, dtype=torch.uint8, device=g.dev)
+    d_keys = torch.empty((nq, 2), dtype=torch.int64, device=g.dev)
+    d_idx = torch.empty((nq, 2), dtype=torch.int32, device=g.dev); d_dist = torch.empty((nq, 2), dtype=torch.float32, device=g.dev)
+
+    def step():
+        st = g.stream()
+        m._lib.check(lib.mpl_knn2_l2f32_dev(d_q.data_ptr(), nq, dim, d_t.data_ptr(), nt, dim, dim, 0, 0, d_scr.data_ptr(), scr_bytes, d_keys.data_ptr(), st), "knn2_l2f32_dev")
+        m._lib.check(lib.mpl_merge_top2_dev(d_keys.data_ptr(), 1, nq, 2, 1, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
+
+    ms = g.time_steps(step, steps, warmup)
+    fb, tf = ctypes.c_uint(0), ctypes.c_uint(0)
+    m._lib.check(lib.mpl_knn_l2_last_stats(d_scr.data_ptr(), ctypes.byref(fb), ctypes.byref(tf), g.stream()), "stats")
+    lib.mpl_prof_enable(1)
+    for _ in range(5):
+        g.flush_l2(); step()
+    torch.cuda.synchronize()
+    lib.mpl_prof_enable(0)
+    kern = {k: g.prof_read(v) for k, v in PROF.items()}
+    tc_ms = kern["l2_tc"][0] / max(kern["l2_tc"][1], 1)
+    ts = []
+    (_, hq), (_, ht) = pinned(q, torch), pinned(t, torch)
+    for i in range(12):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        err, mt = m.getMatchesArray(range(nq), range(nt), hq, ht, None, "LINEAR", False, True)
+        if i >= 4:
+            ts.append(time.perf_counter() - t0)
+    pk, pp = peaks(), pipe_peaks()
+    flops = 2.0 * dim * nq * nt
+    step_ms = float(np.mean(ms))
+    ach = flops / (tc_ms * 1e-3) / 1e12
+    # tf32 tensor peak: measured UMMA issue rate when the microbench has it (kind::tf32, M128 x N256 x K8), else half the measured bf16 rate
+    peak = pp.get("tf32_tflops_issue_bound") or pk["bf16_tflops"] / 2
+    peak_src = (pp["_src"] + ": kind::tf32 UMMA issue rate") if pp.get("tf32_tflops_issue_bound") else "half of MEASURED_PEAKS bf16_tflops (burst)"
+    # a small oracle spot check of this very run (the full-size comparison is tests/test_knn_gpu.py::test_l2_default_path_vs_oracle_at_c2_size)
+    from oracle import knn as oknn
+    oi, od = oknn.knn_l2(q[:256], t, 2, 0, threads=os.cpu_count() or 1)
+    gi, gd = d_idx[:256].cpu().numpy(), d_dist[:256].cpu().numpy()
+    if not (np.array_equal(gi, oi) and np.array_equal(gd.view(np.int32), od.view(np.int32))):
+        raise RuntimeError("tf32-mode float k-NN differs from the oracle")
+    return dict(workload="C2 shape, SURF/KAZE-like unit-norm signed f32 (non-integer): 20000 x 20000 x 128, L2 k=2 (LINEAR); kind::tf32 ranking + top-4 lists + certificate + exact re-rank",
+                value=float(nq) * nt / (step_ms * 1e-3), unit="pairs/s", ms_per_step=step_ms, dtype="f32 (tf32 tensor-core ranking, exact fp32 re-rank)",
+                tf32_mode=int(tf.value), uncertified_queries_rescanned=int(fb.value),
+                roofline=dict(bound="tensor", achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, kernel="l2_tc_rank_kernel (tcgen05 kind::tf32)", kernel_ms=tc_ms,
+                              peak_src=peak_src, step_share={k: (v[0] / max(v[1], 1)) for k, v in kern.items() if v[1]}),
+                e2e=dict(value=float(nq) * nt / float(np.median(ts)), unit="pairs/s", h2d_bytes_per_step=int(hq.nbytes + ht.nbytes), d2h_bytes_per_step=int(nq * 16), matches=int(len(mt))),
+                oracle_check="first 256 queries: idx equal, distances bit-exact")
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baselines of the parts (BASELINE.md section 3 / SURVEY 8(d)): reported next to the GPU numbers, never the target
+# ------------------------------------------------------------------------------------------------
+def cpu_hamming_c1(q, t):
+    """C1 on the host: (i) cvflann LINEAR through cv2.flann_Index -- the very code the reference calls, single thread as in the
+    reference (matchers.cpp:567-588); (ii) the reference's vendored NMSLIB seq_search/bit_hamming (oracle/_ref) with the
+    wrapper's default 8 threads (NMSLIB_SEARCH_THREADS, matchers.cpp:60); (iii) the oracle port as a fallback."""
+    from oracle import knn as oknn
+    out = dict(unit="pairs/s")
+    pairs = float(len(q)) * len(t)
+    try:
+        import cv2
+        cv2.setNumThreads(1)
+        n1 = min(len(q), 2048)
+        t0 = time.perf_counter()
+        ix = cv2.flann_Index(t, dict(algorithm=0), 9)                          # FLANN_DIST_HAMMING
+        ix.knnSearch(q[:n1], 2, params=dict(checks=64))
+        dt = time.perf_counter() - t0
+        out.update(value=float(n1) * len(t) / dt, cores=1, kind="reference",
+                   sample="cv2.flann_Index linear (cvflann HammingLUT, OpenCV %s), first %d of %d queries x %d train rows, single thread, %.2f s" % (cv2.__version__, n1, len(q), len(t), dt))
+    except Exception as e:                                                    # no cv2 on the box: the C port of the same scan
+        t0 = time.perf_counter(); oknn.knn_hamming(q, t, 2, 0, threads=1); dt = time.perf_counter() - t0
+        out.update(value=pairs / dt, cores=1, kind="port", sample="oracle port of cvflann's linear Hamming scan, full C1, single thread (%s)" % type(e).__name__)
+    if oknn.ref_lib() is not None:
+        t0 = time.perf_counter(); oknn.ref_nmslib_hamming(q, t, threads=8); dt = time.perf_counter() - t0
+        out["nmslib_8_threads"] = dict(value=pairs / dt, unit="pairs/s", cores=8, kind="reference", sample="reference NMSLIB seq_search/bit_hamming, full C1, 8 threads (NMSLIB_SEARCH_THREADS), %.2f s" % dt)
+    return out
+
+
+def cpu_ransac_c3(sc, samples, n_models_gpu, h, n_sub=1000):
+    """C3 on the host: the C restatement of run5Point + computeReprojError3 (oracle/ransac5pt_oracle.c), single thread like the
+    reference, full trace over every n-th sample; evaluations/s is per-sample work, so the whole config extrapolates linearly."""
+    from oracle import ransac as oransac
+    sub = np.ascontiguousarray(samples[:: max(1, h // n_sub)][:n_sub])
+    t0 = time.perf_counter()
+    r = oransac.ransac5pt(sc["p1"], sc["p2"], sub, sc["th"], max_iters=len(sub), trace=True)
+    dt = time.perf_counter() - t0
+    evals = float(r["n_models"].sum()) * len(sc["p1"])
+    return dict(value=evals / dt, unit="model*correspondence Sampson evaluations/s (5-point solves included in the time)", cores=1, kind="port",
+                sample="%d of %d samples (stratified), %d models x %d correspondences, %.1f s single thread; whole C3 extrapolated: %.0f s" %
+                       (len(sub), h, int(r["n_models"].sum()), len(sc["p1"]), dt, dt * h / len(sub)),
+                hypotheses_per_ms=len(sub) / (dt * 1e3))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -632,7 +922,7 @@ def cpu_l2_sample(q, t, budget_s=12.0):
     t0 = time.perf_counter(); idx, dist = fn(q[:n1], t, cores); dt = time.perf_counter() - t0
     return dict(value=float(n1) * len(t) / dt, unit="pairs/s", cores=cores, kind=kind,
                 sample="first %d of %d queries x %d train rows, %.1f s, %d threads (%s)" %
-                       (n1, len(q), len(t), dt, cores, "reference NMSLIB seq_search/l2, q%%T striping" if kind == "reference" else "oracle port of cvflann linear L2")), idx
+                       (n1, len(q), len(t), dt, cores, "reference NMSLIB seq_search/l2, q%%T striping" if kind == "reference" else "oracle port of cvflann linear L2")), idx, dist
 
 
 def run_reference(args):
@@ -674,7 +964,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-parts", action="store_true", help="skip the Hamming (C1) and RANSAC (C3) legs")
+    ap.add_argument("--no-parts", action="store_true", help="skip parts: C5 database, C4 pair batch (every N); Hamming C1, RANSAC C3, tf32 float set (N = 1)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -741,14 +1031,48 @@ def main():
             "gpu_launches": int(r["launches_timed"]),
         }
         if not args.no_cpu and world == 1:
-            cb, cidx = cpu_l2_sample(r["q"], r["t"])
+            cb, cidx, cdist = cpu_l2_sample(r["q"], r["t"])
             n1 = len(cidx)
-            agree = float((cidx[:, 0] == r["idx"][:n1, 0]).mean())
-            cb["nn_agreement_with_gpu"] = agree
+            gi = r["idx"][:n1, 0]
+            differ = np.nonzero(cidx[:, 0] != gi)[0]
+            # north_star: float NN indices must agree except for near-ties within 1e-5 relative distance.  For every query
+            # whose first neighbour differs from the reference's NMSLIB (built -Ofast: its fp32 sums are not reproducible),
+            # the two candidates' exact distances (fp64 on the host) must be within 1e-5 of each other.
+            gaps = []
+            for qi in differ:
+                a = np.sqrt(((r["q"][qi].astype(np.float64) - r["t"][gi[qi]].astype(np.float64)) ** 2).sum())
+                b = np.sqrt(((r["q"][qi].astype(np.float64) - r["t"][cidx[qi, 0]].astype(np.float64)) ** 2).sum())
+                gaps.append(abs(a - b) / max(a, b, 1e-300))
+            cb["nn_agreement_with_gpu"] = float((cidx[:, 0] == gi).mean())
+            cb["nn_disagreements"] = int(len(differ))
+            cb["nn_disagreement_max_rel_gap"] = float(max(gaps)) if gaps else 0.0
+            if gaps and max(gaps) >= 1e-5:
+                raise RuntimeError("GPU and reference first neighbours differ beyond a near-tie: relative gap %g" % max(gaps))
             out["cpu_baseline"] = cb
-        if not args.no_parts and world == 1:
-            out["parts"] = dict(hamming_c1=bench_hamming(g, args.steps, args.warmup), ransac_c3=bench_ransac(g, max(3, args.steps // 4), 3),
-                                pair_pipeline_c4=bench_pair_pipeline(g, 10))
+        if world > 1:
+            # oracle check of the MERGED sharded result: 512 queries against the concatenation of every rank's shard
+            from oracle import knn as oknn
+            sel = np.linspace(0, r["nq"] - 1, 512).astype(int)
+            full_t = np.concatenate([make_c2(rk)[1] for rk in range(world)], 0)
+            oi, od = oknn.knn_l2(r["q"][sel], full_t, 2, 0, threads=os.cpu_count() or 1)
+            if not (np.array_equal(r["idx"][sel], oi) and np.array_equal(r["dist"][sel].view(np.int32), od.view(np.int32))):
+                raise RuntimeError("sharded merged top-2 differs from the oracle over the concatenated shards")
+            out["config"]["oracle_check"] = "512 queries vs oracle over the %d concatenated rows: idx equal, distances bit-exact" % len(full_t)
+    parts = {}
+    if not args.no_parts:
+        # the two multi-GPU workloads of BASELINE.json, at every N (collective: every rank takes part, rank 0 reports)
+        c5 = bench_database_c5(g, args.steps, world, rank, dist)
+        c4 = bench_pair_batch_c4(g, world, rank, dist)
+        if rank == 0:
+            parts["database_c5"] = c5
+            parts["pair_batch_c4"] = c4
+        if world == 1:
+            parts["hamming_c1"] = bench_hamming(g, args.steps, args.warmup)
+            parts["ransac_c3"] = bench_ransac(g, max(3, args.steps // 4), 3)
+            parts["l2_tf32_c2"] = bench_l2_tf32(g, max(5, args.steps // 2), 3)
+    if rank == 0 and parts:
+        out["parts"] = parts
+        out["gpu_launches_parts"] = int(sum(v.get("gpu_launches", 0) for v in parts.values() if isinstance(v, dict)))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

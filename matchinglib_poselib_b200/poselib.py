@@ -127,6 +127,75 @@ def pixToCamFact(K0, K1):
     return 4.0 / (np.sqrt(2.0) * (K0[0, 0] + K0[1, 1] + K1[0, 0] + K1[1, 1]))
 
 
+class PairBatch:
+    """A batch of image pairs marshalled once for mpl_match_pose_batch (arguments as matchAndEstimatePoseBatch): run() is
+    exactly one C call, so a caller that streams batches (or a benchmark) pays the Python marshalling outside it."""
+
+    def __init__(self, pairs, matcher_name="LINEAR", ratioTest=True, threshold=1.6, n_samples=1000, confidence=0.999,
+                 refine=True, seeds=None, K0=None, K1=None, dist0=None, dist1=None, want_samples=False):
+        self.lib = _lib.load()
+        n_pairs = self.n_pairs = len(pairs)
+        pix = K0 is not None
+        self.io = (_lib.PairIO * max(n_pairs, 1))()
+        self.res = (_lib.PairResult * max(n_pairs, 1))()
+        self.keep, self.outs = [], []
+        cols, is_float = None, None
+        for i, (d1, d2, p1, p2) in enumerate(pairs):
+            d1, d2 = np.asarray(d1), np.asarray(d2)
+            fl = d1.dtype == np.float32
+            if is_float is None:
+                is_float, cols = fl, d1.shape[1]
+            if fl != is_float or d2.dtype != d1.dtype or d1.shape[1] != cols or d2.shape[1] != cols or (not fl and d1.dtype != np.uint8):
+                raise AssertionError("all pairs of a batch need descriptors of one type and length")
+            if d1.strides[1] != d1.itemsize:
+                d1 = np.ascontiguousarray(d1)
+            if d2.strides[1] != d2.itemsize:
+                d2 = np.ascontiguousarray(d2)
+            if pix:
+                p1 = np.ascontiguousarray(p1, np.float32); p2 = np.ascontiguousarray(p2, np.float32)
+            else:
+                p1, p2 = _pts(p1), _pts(p2)
+            if p1.shape != (d1.shape[0], 2) or p2.shape != (d2.shape[0], 2):
+                raise AssertionError("descriptor / keypoint shapes do not agree")
+            n1 = d1.shape[0]
+            m = np.zeros(max(n1, 1), DMATCH); k = np.zeros(max(n1, 1), np.uint8)
+            sm = np.zeros((max(n_samples, 1), 5), np.int32) if want_samples else None
+            self.keep.append((d1, d2, p1, p2))
+            self.outs.append((m, k, sm))
+            e = self.io[i]
+            e.desc1, e.desc2 = d1.ctypes.data, d2.ctypes.data
+            e.step1 = d1.strides[0] if n1 > 1 else cols * d1.itemsize
+            e.step2 = d2.strides[0] if d2.shape[0] > 1 else cols * d2.itemsize
+            e.pts1, e.pts2, e.n1, e.n2 = p1.ctypes.data, p2.ctypes.data, n1, d2.shape[0]
+            e.seed = int(seeds[i]) if seeds is not None else 1 + i
+            e.matches, e.mask = m.ctypes.data, k.ctypes.data
+            e.samples = sm.ctypes.data if sm is not None else None
+        prm = self.prm = _lib.PairParams()
+        prm.cv_type, prm.cols = (5 if is_float else 0), int(cols or 1)
+        prm.matcher_name, prm.ratio_test, prm.pts_mode = matcher_name.encode(), int(bool(ratioTest)), int(pix)
+        if pix:
+            for dst, src, nn in ((prm.K0, K0, 9), (prm.K1, K1 if K1 is not None else K0, 9), (prm.dist0, dist0, 8), (prm.dist1, dist1, 8)):
+                v = np.zeros(nn) if src is None else np.asarray(src, np.float64).reshape(-1)[:nn]
+                for j in range(len(v)):
+                    dst[j] = float(v[j])
+        prm.th, prm.h, prm.conf, prm.refine = float(threshold), int(n_samples), float(confidence), int(bool(refine))
+
+    def run(self):
+        _lib.check(self.lib.mpl_match_pose_batch(self.io, self.n_pairs, ctypes.byref(self.prm), self.res), "mpl_match_pose_batch")
+        return self
+
+    def results(self):
+        out = []
+        for i in range(self.n_pairs):
+            r, (m, k, sm) = self.res[i], self.outs[i]
+            d = dict(matches=m[: r.n_matches], ok=r.n_inl > 0, E=np.array(list(r.E)).reshape(3, 3), mask=k[: r.n_matches], count=r.n_inl,
+                     iters=r.iters_run, n_corr=r.n_corr, status=r.status)
+            if sm is not None:
+                d["samples"] = sm[: r.n_samples]
+            out.append(d)
+        return out
+
+
 def matchAndEstimatePoseBatch(pairs, matcher_name="LINEAR", ratioTest=True, threshold=1.6, n_samples=1000, confidence=0.999,
                               refine=True, seeds=None, K0=None, K1=None, dist0=None, dist1=None, want_samples=False):
     """mpl_match_pose_batch: both halves of the hot path for a list of image pairs in ONE call (device resident between
@@ -135,59 +204,5 @@ def matchAndEstimatePoseBatch(pairs, matcher_name="LINEAR", ratioTest=True, thre
     given -- float32 pixel coordinates (cv::KeyPoint::pt) that the library normalises (ImgToCamCoordTrans) and undistorts
     (Remove_LensDist, dist0 / dist1: 8 OpenCV coefficients) on the device.  `threshold` is in camera units
     (pixToCamFact).  Returns one dict per pair: matches, ok, E, mask (over matches), count, iters, n_corr, status[, samples]."""
-    lib = _lib.load()
-    n_pairs = len(pairs)
-    pix = K0 is not None
-    io = (_lib.PairIO * max(n_pairs, 1))()
-    res = (_lib.PairResult * max(n_pairs, 1))()
-    keep, outs = [], []
-    cols, is_float = None, None
-    for i, (d1, d2, p1, p2) in enumerate(pairs):
-        d1, d2 = np.asarray(d1), np.asarray(d2)
-        fl = d1.dtype == np.float32
-        if is_float is None:
-            is_float, cols = fl, d1.shape[1]
-        if fl != is_float or d2.dtype != d1.dtype or d1.shape[1] != cols or d2.shape[1] != cols or (not fl and d1.dtype != np.uint8):
-            raise AssertionError("all pairs of a batch need descriptors of one type and length")
-        if d1.strides[1] != d1.itemsize:
-            d1 = np.ascontiguousarray(d1)
-        if d2.strides[1] != d2.itemsize:
-            d2 = np.ascontiguousarray(d2)
-        if pix:
-            p1 = np.ascontiguousarray(p1, np.float32); p2 = np.ascontiguousarray(p2, np.float32)
-        else:
-            p1, p2 = _pts(p1), _pts(p2)
-        if p1.shape != (d1.shape[0], 2) or p2.shape != (d2.shape[0], 2):
-            raise AssertionError("descriptor / keypoint shapes do not agree")
-        n1 = d1.shape[0]
-        m = np.zeros(max(n1, 1), DMATCH); k = np.zeros(max(n1, 1), np.uint8)
-        sm = np.zeros((max(n_samples, 1), 5), np.int32) if want_samples else None
-        keep.append((d1, d2, p1, p2))
-        outs.append((m, k, sm))
-        e = io[i]
-        e.desc1, e.desc2 = d1.ctypes.data, d2.ctypes.data
-        e.step1 = d1.strides[0] if n1 > 1 else cols * d1.itemsize
-        e.step2 = d2.strides[0] if d2.shape[0] > 1 else cols * d2.itemsize
-        e.pts1, e.pts2, e.n1, e.n2 = p1.ctypes.data, p2.ctypes.data, n1, d2.shape[0]
-        e.seed = int(seeds[i]) if seeds is not None else 1 + i
-        e.matches, e.mask = m.ctypes.data, k.ctypes.data
-        e.samples = sm.ctypes.data if sm is not None else None
-    prm = _lib.PairParams()
-    prm.cv_type, prm.cols = (5 if is_float else 0), int(cols or 1)
-    prm.matcher_name, prm.ratio_test, prm.pts_mode = matcher_name.encode(), int(bool(ratioTest)), int(pix)
-    if pix:
-        for dst, src, nn in ((prm.K0, K0, 9), (prm.K1, K1 if K1 is not None else K0, 9), (prm.dist0, dist0, 8), (prm.dist1, dist1, 8)):
-            v = np.zeros(nn) if src is None else np.asarray(src, np.float64).reshape(-1)[:nn]
-            for j in range(len(v)):
-                dst[j] = float(v[j])
-    prm.th, prm.h, prm.conf, prm.refine = float(threshold), int(n_samples), float(confidence), int(bool(refine))
-    _lib.check(lib.mpl_match_pose_batch(io, n_pairs, ctypes.byref(prm), res), "mpl_match_pose_batch")
-    out = []
-    for i in range(n_pairs):
-        r, (m, k, sm) = res[i], outs[i]
-        d = dict(matches=m[: r.n_matches], ok=r.n_inl > 0, E=np.array(list(r.E)).reshape(3, 3), mask=k[: r.n_matches], count=r.n_inl,
-                 iters=r.iters_run, n_corr=r.n_corr, status=r.status)
-        if sm is not None:
-            d["samples"] = sm[: r.n_samples]
-        out.append(d)
-    return out
+    return PairBatch(pairs, matcher_name, ratioTest, threshold, n_samples, confidence, refine, seeds, K0, K1, dist0, dist1,
+                     want_samples).run().results()

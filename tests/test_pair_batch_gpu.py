@@ -141,7 +141,8 @@ def test_pixel_keypoints_and_undistortion(P):
             xd = x * rad + d[2] * 2 * x * y + d[3] * (r2 + 2 * x * x); yd = y * rad + d[2] * (r2 + 2 * y * y) + d[3] * 2 * x * y
             return np.stack([xd * K[0, 0] + K[0, 2], yd * K[1, 1] + K[1, 2]], 1).astype(np.float32)
         px1, px2 = to_pix(p1, K0, dist0), to_pix(p2, K1, dist1)
-        px1[5] = (1e5, 1e5)                                                 # a wild keypoint: its undistortion fails the proof test
+        omt = oracle_matches(q, t, "LINEAR")
+        px1[omt["queryIdx"][3]] = (1e5, 1e5)                                # a wild keypoint of a matched query: its undistortion fails the proof test
         thc = 1.6 * P.pixToCamFact(K0, K1)
         r = P.matchAndEstimatePoseBatch([(q, t, px1, px2)], "LINEAR", True, thc, 300, 0.999, True, seeds=[3], K0=K0, K1=K1, dist0=dist0, dist1=dist1,
                                         want_samples=True)[0]

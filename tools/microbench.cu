@@ -117,7 +117,7 @@ __global__ void k_ldtm(uint32_t* out, int iters)
 
 // tcgen05.mma issue rate: one thread issues `n` back-to-back MMAs (kind::f16, bf16 operands, M = 128, K = 16) on zeroed
 // shared-memory operands (K-major, 128-byte swizzle), `chains` accumulators used round-robin, then one commit.
-__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0)
+__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0, int tf32 = 0)
 {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -143,7 +143,8 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
         const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem), b = a + 16384;
         const uint64_t hi = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
         const uint64_t ad = hi | (uint64_t)((a >> 4) & 0x3FFF), bd = hi | (uint64_t)((b >> 4) & 0x3FFF);
-        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t fmt = tf32 ? 2u : 1u;           // a / b format: 1 = bf16 (kind::f16), 2 = tf32 (kind::tf32, K = 8 per MMA)
+        const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t d1 = tmem + (chains > 1 ? (uint32_t)N : 0u);
         const long long t0 = clock64();
         for (int i = 0; i < n; i += 4) {
@@ -151,10 +152,16 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
             asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
             if (pred) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                                 ::"r"((k & 1) ? d1 : tmem), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(1u) : "memory");
+                for (int k = 0; k < 4; ++k) {
+                    if (tf32)
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                     "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                                     ::"r"((k & 1) ? d1 : tmem), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(1u) : "memory");
+                    else
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                     "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                                     ::"r"((k & 1) ? d1 : tmem), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(1u) : "memory");
+                }
                 if (commit_every && ((i >> 2) % commit_every) == 0)
                     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(&bar2)) : "memory");
             }
@@ -234,6 +241,16 @@ int main()
             long long h[148]; cudaMemcpy(h, cyc, sizeof(long long) * (sms < 148 ? sms : 148), cudaMemcpyDeviceToHost);
             printf(", \"umma_m128_n%d_k16_bf16_chains%d_cycles_per_mma\": %.1f", N, chains, (double)h[0] / n);
         }
+    }
+    for (int N : {128, 256}) {                          // kind::tf32: M128 x N x K8 per MMA -> tf32 tensor peak = 2*128*N*8 / cycles
+        const int n = 2000;
+        long long* cyc = (long long*)buf;
+        k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, N, 1, 0, 1);
+        if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma tf32 failed\n"); break; }
+        long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
+        const double cpm = (double)h[0] / n;
+        printf(", \"umma_m128_n%d_k8_tf32_cycles_per_mma\": %.1f", N, cpm);
+        if (N == 256) printf(", \"tf32_tflops_issue_bound\": %.1f", 2.0 * 128 * N * 8 / cpm * sms * clk_khz * 1e3 / 1e12);
     }
     for (int chains : {1, 2}) {
         for (int ce : {1, 2, 4, 8, 16}) {
