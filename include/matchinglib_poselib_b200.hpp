@@ -64,6 +64,38 @@ inline int getMatches(const std::vector<cv::KeyPoint>& keypoints1, const std::ve
 
 }  // namespace matchinglib
 
+// matchinglib/include/matchinglib/gms.h (global namespace in the reference), source/gms.cpp:54-82 -> MatchGMS
+// (thirdparty/gms-1.0): the grid statistics run on the GPU (mpl_gms_filter); getCorrespondences (correspondences.cpp:386)
+// calls the first overload with useScale = useRotation = false.
+inline int filterMatchesGMS(const std::vector<cv::KeyPoint>& keypoints1, const cv::Size imageSize1,
+                            const std::vector<cv::KeyPoint>& keypoints2, const cv::Size imageSize2,
+                            const std::vector<cv::DMatch>& matches, std::vector<bool>& inlierMask,
+                            const bool useScale = false, const bool useRotation = false)
+{
+    static_assert(sizeof(cv::DMatch) == sizeof(mpl_dmatch), "cv::DMatch layout");
+    std::vector<uchar> m(matches.size() + 1);
+    int n = 0;
+    const int rc = mpl_gms_filter(keypoints1.data(), (int)keypoints1.size(), sizeof(cv::KeyPoint), imageSize1.width, imageSize1.height,
+                                  keypoints2.data(), (int)keypoints2.size(), sizeof(cv::KeyPoint), imageSize2.width, imageSize2.height,
+                                  reinterpret_cast<const mpl_dmatch*>(matches.data()), (int)matches.size(), useScale ? 1 : 0, useRotation ? 1 : 0,
+                                  m.data(), &n);
+    if (rc != 0) { std::cout << mpl_last_error() << std::endl; return 0; }
+    if (n > 0) inlierMask.assign(m.begin(), m.begin() + (std::ptrdiff_t)matches.size());     // MatchGMS.cpp:92-96: assigned only by a run with inliers
+    return n;
+}
+inline int filterMatchesGMS(const std::vector<cv::KeyPoint>& keypoints1, const cv::Size imageSize1,
+                            const std::vector<cv::KeyPoint>& keypoints2, const cv::Size imageSize2,
+                            const std::vector<cv::DMatch>& matches, std::vector<cv::DMatch>& matches_filtered,
+                            const bool useScale = false, const bool useRotation = false)
+{
+    std::vector<bool> inlierMask;
+    const int n = filterMatchesGMS(keypoints1, imageSize1, keypoints2, imageSize2, matches, inlierMask, useScale, useRotation);
+    matches_filtered.clear();                                                    // gms.cpp:71-80
+    matches_filtered.resize((size_t)n);
+    if (n) for (size_t i = 0, j = 0; i < inlierMask.size(); i++) if (inlierMask[i]) matches_filtered[j++] = matches[i];
+    return n;
+}
+
 namespace poselib {
 
 // pose_estim.cpp:857-890 -> findEssentialMat (five-point-nister/five-point.cpp:69-148), method "RANSAC".
@@ -93,9 +125,10 @@ inline bool estimateEssentialMat(cv::OutputArray E, cv::InputArray p1, cv::Input
                                               refine ? 1 : 0, e_buf, &n_E, m.data());
     if (rc == MPL_ERR_ASSERT) CV_Error(cv::Error::StsAssert, mpl_last_error());
     if (rc < 0) { std::cout << mpl_last_error() << std::endl; return false; }
-    cv::Mat(3 * (npoints == 5 ? n_E : 1), 3, CV_64F, e_buf).copyTo(E);
+    if (rc != 1) return false;                                                   // :117-118: on failure neither E nor mask is written
     if (mask.needed()) cv::Mat(1, npoints, CV_8U, m.data()).copyTo(mask);        // :130-135
-    return rc == 1;
+    cv::Mat(3 * (npoints == 5 ? n_E : 1), 3, CV_64F, e_buf).copyTo(E);           // :137-141
+    return true;
 }
 
 // poselib::getPoseTriangPts (pose_estim.h:192-200; pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338)

@@ -103,6 +103,17 @@ int mpl_get_matches_api(int n_keypoints1, int n_keypoints2,
                         const char* matcher_name, int ratio_test, int nr_threads /*ignored*/,
                         mpl_dmatch* out, int* n_out);
 
+/* ---- GMS post-filter ---------------------------------------------------------------
+ * mpl_gms_filter replaces filterMatchesGMS(keypoints1, imageSize1, keypoints2, imageSize2, matches, inlierMask, useScale,
+ *   useRotation) (MP/matchinglib/source/gms.cpp:54-60 -> MatchGMS, MP/matchinglib/thirdparty/gms-1.0/src/MatchGMS.cpp;
+ *   called by getCorrespondences with GMSrefine, correspondences.cpp:386, useScale = useRotation = false).
+ *   kp1 / kp2: arrays of records whose first 8 bytes are the pixel position (float x, float y) -- pass &keypoints[0] with
+ *   kp_stride = sizeof(cv::KeyPoint) = 28, or packed float pairs with kp_stride = 8.  inlier_mask[n_matches] 0/1,
+ *   *n_inliers = the reference's return value.  Bit-exact against the reference's grid arithmetic. */
+int mpl_gms_filter(const void* kp1, int n1, size_t kp_stride1, int width1, int height1, const void* kp2, int n2, size_t kp_stride2,
+                   int width2, int height2, const mpl_dmatch* matches, int n_matches, int use_scale, int use_rotation,
+                   uint8_t* inlier_mask, int* n_inliers);
+
 /* ---- sharded database regime: all-gather over NVLink peer memory fused with the merge -----------------
  * Every rank (one process per GPU) allocates one gather buffer of mpl_peer_gather_bytes(nq, world) and one 256-byte sync
  * block with mpl_peer_alloc (zeroed, returns a 64-byte CUDA IPC handle), exchanges the handles (e.g. torch.distributed

@@ -7,7 +7,7 @@ josefmaierfl/matchinglib_poselib behind the reference's own API names.
 Everything computes in lib/libmplb200.so (hand-written CUDA, C ABI in include/mplb200.h).
 """
 from . import _lib, matchinglib, poselib  # noqa: F401
-from .matchinglib import getCorrespondences, getMatches, getMatchesArray, knn2_hamming, knn2_l2, pinned_array  # noqa: F401
+from .matchinglib import filterMatchesGMS, getCorrespondences, getMatches, getMatchesArray, knn2_hamming, knn2_l2, pinned_array  # noqa: F401
 from .poselib import estimateEssentialMat, ransac5pt  # noqa: F401
 
-__all__ = ["getCorrespondences", "pinned_array", "getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib", "poselib", "estimateEssentialMat", "ransac5pt"]
+__all__ = ["filterMatchesGMS", "getCorrespondences", "pinned_array", "getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib", "poselib", "estimateEssentialMat", "ransac5pt"]

@@ -68,6 +68,7 @@ SIGNATURES = {
     "mpl_ratio_matches_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_get_matches_api": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_size_t, c_int,
                                     c_void_p, c_int, c_int, c_size_t, c_int, c_char_p, c_int, c_int, c_void_p, c_void_p]),
+    "mpl_gms_filter": (c_int, [c_void_p, c_int, c_size_t, c_int, c_int, c_void_p, c_int, c_size_t, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_knn_hamming_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mpl_pack_rows_u8_dev": (c_int, [c_void_p, c_int, c_size_t, c_int, c_void_p, c_int, c_void_p]),
     "mpl_knn2_hamming_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),

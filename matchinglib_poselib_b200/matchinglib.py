@@ -130,11 +130,12 @@ def getCorrespondences(img1, img2, featuretype="FAST", extractortype="FREAK", ma
     -3 descriptor error, -4 incompatible detector/matcher, -6 incompatible detector/descriptor, and a getMatches failure e
     as -4 + e (:356-359), i.e. -5 wrong input, -6 matcher not served by this build, -7 too few matches, -8 too few keypoints.
     `detector` / `extractor` (objects with detect(img) / compute(img, kps)) replace the cv2 factories when given.
-    The post-filters (VFC, GMS, SOF, sub-pixel refinement; :378-506) are outside the B200 hot path."""
+    GMSrefine runs the GMS grid filter on the GPU (mpl_gms_filter; :378-396); the other post-filters (VFC, SOF, sub-pixel
+    refinement; :415-506) are outside the B200 hot path."""
     if img1 is None or img2 is None or np.size(img1) == 0 or np.size(img2) == 0:
         return -1, [], [], []
-    if VFCrefine or GMSrefine or SOFrefine or subPixRefine:
-        raise NotImplementedError("VFC / GMS / SOF / sub-pixel refinement are outside the B200 hot path")
+    if VFCrefine or SOFrefine or subPixRefine:
+        raise NotImplementedError("VFC / SOF / sub-pixel refinement are outside the B200 hot path")
     if featuretype in ("MSER", "SimpleBlob") and matchertype == "GMBSOF":
         return -4, [], [], []
     if (featuretype != "KAZE" and extractortype == "KAZE") or (featuretype != "AKAZE" and extractortype == "AKAZE") or \
@@ -155,7 +156,33 @@ def getCorrespondences(img1, img2, featuretype="FAST", extractortype="FREAK", ma
                                    idxPars_NMSLIB, queryPars_NMSLIB)
     if err != 0:
         return -4 + err, [], list(kp1), list(kp2)
+    if GMSrefine:                                                              # correspondences.cpp:378-396
+        imgSi = (np.shape(img1)[1], np.shape(img1)[0])                         # cv::Size imgSi = img1.size()
+        n_gms, inl = filterMatchesGMS(kp1, imgSi, kp2, imgSi, matches, False, False)
+        if n_gms >= 2:                                                         # MIN_FINAL_MATCHES
+            matches = matches[inl]
     return 0, matches, list(kp1), list(kp2)
+
+
+def _kp_xy(keypoints):
+    """[n, 2] float32 pixel positions from cv2.KeyPoint objects, (x, y) tuples or an array."""
+    if len(keypoints) and hasattr(keypoints[0], "pt"):
+        return np.array([k.pt for k in keypoints], np.float32).reshape(-1, 2)
+    return np.ascontiguousarray(np.asarray(keypoints, np.float32).reshape(-1, 2))
+
+
+def filterMatchesGMS(keypoints1, imageSize1, keypoints2, imageSize2, matches, useScale=False, useRotation=False):
+    """filterMatchesGMS (matchinglib/source/gms.cpp:54-60 -> thirdparty/gms-1.0 MatchGMS) on the GPU (mpl_gms_filter).
+    imageSize = (width, height); matches: DMATCH_DTYPE array.  Returns (n_inliers, inlierMask bool [len(matches)])."""
+    lib = _lib.load()
+    k1, k2 = _kp_xy(keypoints1), _kp_xy(keypoints2)
+    m = np.ascontiguousarray(matches, DMATCH_DTYPE)
+    mask = np.zeros(max(len(m), 1), np.uint8)
+    n = ctypes.c_int(0)
+    _lib.check(lib.mpl_gms_filter(_lib.ptr(k1), len(k1), 8, int(imageSize1[0]), int(imageSize1[1]), _lib.ptr(k2), len(k2), 8,
+                                  int(imageSize2[0]), int(imageSize2[1]), _lib.ptr(m), len(m), int(bool(useScale)), int(bool(useRotation)),
+                                  _lib.ptr(mask), ctypes.byref(n)), "mpl_gms_filter")
+    return n.value, mask[: len(m)].astype(bool)
 
 
 def knn2_hamming(query, train, k=2, ignore_tail_bytes=0):

@@ -34,7 +34,7 @@ def test_error_codes_before_any_device_work(m):
     flat = np.full((480, 720), 128, np.uint8)
     assert m.getCorrespondences(flat, flat, "ORB", "ORB", "LINEAR")[0] == -2          # < 10 keypoints
     with pytest.raises(NotImplementedError):
-        m.getCorrespondences(img, img2, "ORB", "ORB", "LINEAR", GMSrefine=True)
+        m.getCorrespondences(img, img2, "ORB", "ORB", "LINEAR", SOFrefine=True)
 
 
 @pytest.mark.gpu

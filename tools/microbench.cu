@@ -117,7 +117,8 @@ __global__ void k_ldtm(uint32_t* out, int iters)
 
 // tcgen05.mma issue rate: one thread issues `n` back-to-back MMAs (kind::f16, bf16 operands, M = 128, K = 16) on zeroed
 // shared-memory operands (K-major, 128-byte swizzle), `chains` accumulators used round-robin, then one commit.
-__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0, int tf32 = 0)
+template <int TF32>
+__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0)
 {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -143,7 +144,7 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
         const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem), b = a + 16384;
         const uint64_t hi = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
         const uint64_t ad = hi | (uint64_t)((a >> 4) & 0x3FFF), bd = hi | (uint64_t)((b >> 4) & 0x3FFF);
-        const uint32_t fmt = tf32 ? 2u : 1u;           // a / b format: 1 = bf16 (kind::f16), 2 = tf32 (kind::tf32, K = 8 per MMA)
+        const uint32_t fmt = TF32 ? 2u : 1u;           // a / b format: 1 = bf16 (kind::f16), 2 = tf32 (kind::tf32, K = 8 per MMA)
         const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t d1 = tmem + (chains > 1 ? (uint32_t)N : 0u);
         const long long t0 = clock64();
@@ -153,7 +154,7 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
             if (pred) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    if (tf32)
+                    if (TF32)
                         asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
                                      ::"r"((k & 1) ? d1 : tmem), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(1u) : "memory");
@@ -230,13 +231,14 @@ int main()
         const double bytes = (double)warps * iters * 4 * 4096;
         printf(", \"ldtm_x32_%dwarps_B_per_clk_per_sm\": %.1f", warps, bytes / (ms * 1e-3 * clk_khz * 1e3));
     }
-    cudaFuncSetAttribute(k_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(k_umma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(k_umma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     for (int N : {64, 128, 256}) {
         for (int chains : {1, 2}) {
             if (N * chains > 512) continue;
             const int n = 2000;
             long long* cyc = (long long*)buf;
-            k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, N, chains);
+            k_umma<0><<<sms, 64, 64 * 1024>>>(cyc, n, N, chains);
             if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
             long long h[148]; cudaMemcpy(h, cyc, sizeof(long long) * (sms < 148 ? sms : 148), cudaMemcpyDeviceToHost);
             printf(", \"umma_m128_n%d_k16_bf16_chains%d_cycles_per_mma\": %.1f", N, chains, (double)h[0] / n);
@@ -245,7 +247,7 @@ int main()
     for (int N : {128, 256}) {                          // kind::tf32: M128 x N x K8 per MMA -> tf32 tensor peak = 2*128*N*8 / cycles
         const int n = 2000;
         long long* cyc = (long long*)buf;
-        k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, N, 1, 0, 1);
+        k_umma<1><<<sms, 64, 64 * 1024>>>(cyc, n, N, 1, 0);
         if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma tf32 failed\n"); break; }
         long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
         const double cpm = (double)h[0] / n;
@@ -256,7 +258,7 @@ int main()
         for (int ce : {1, 2, 4, 8, 16}) {
             const int n = 4096;
             long long* cyc = (long long*)buf;
-            k_umma<<<sms, 64, 64 * 1024>>>(cyc, n, 128, chains, ce);
+            k_umma<0><<<sms, 64, 64 * 1024>>>(cyc, n, 128, chains, ce);
             if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma failed\n"); break; }
             long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
             printf(", \"umma_m128_n128_chains%d_commit_every_%d_mma_cycles_per_mma\": %.1f", chains, 4 * ce, (double)h[0] / n);
