@@ -182,8 +182,9 @@ int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t,
  *   n_models[h], counts[<=10h], errsums[<=10h].
  * mpl_estimate_essential_api mirrors poselib::estimateEssentialMat(E, p1, p2, "RANSAC", threshold, refine, mask)
  *   (MP/poselib/source/pose_estim.cpp:857-890 -> findEssentialMat five-point.cpp:69-148): returns 1/0 like the
- *   reference's bool (negative MPL_ERR_* on failure; MPL_ERR_ASSERT where CV_Assert would throw; any method
- *   other than "RANSAC" is refused -- no CPU fallback).  n == 5: solver only, *n_E models stacked in E_out. */
+ *   reference's bool (negative MPL_ERR_* on failure; MPL_ERR_ASSERT where CV_Assert would throw).  method "RANSAC" or
+ *   "ARRSAC" (the reference's default, mpl_arrsac5pt); "LMEDS" / "USAC" / anything else is refused -- no CPU fallback.
+ *   n == 5: solver only, *n_E models stacked in E_out. */
 int mpl_ransac_set_seed(unsigned long long seed);
 int mpl_ransac_draw_samples(const double* p1, const double* p2, int n, int h, int32_t* samples, int* n_drawn);
 int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double th,
@@ -191,6 +192,20 @@ int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samp
                   double* models, int32_t* n_models, int32_t* counts, double* errsums);
 int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const char* method, double threshold,
                                int refine, double* E_out, int* n_E, uint8_t* mask);
+/* mpl_arrsac5pt replaces CvModelEstimator3::runARRSAC (MP/poselib/source/five-point-nister/modelest.cpp:197-341) -- what
+ *   poselib::estimateEssentialMat runs for its DEFAULT method "ARRSAC" (pose_estim.cpp:866-869): theia::Arrsac
+ *   (MP/poselib/include/arrsac/arrsac.h:206-545: PROSAC-ordered initial hypotheses verified by SPRT on the first block of
+ *   100 correspondences, inner RANSAC on the best support, preemptive breadth-first scoring in blocks of 100 / sub-blocks
+ *   of 20) with parameters (5, th^2, 500, 100, 14, 8), then findInliers, the acceptance rule (< 15 inliers, or < 50 of
+ *   more than 200 -> false) and, with refine, robustEssentialRefine (pose_estim.cpp:337-837: pseudo-Huber IRLS, threshold
+ *   th / 50).  Hypothesis generation (5-point / 8-point solves, ValidModel) and verification (inlier bit matrix) run on
+ *   the device in speculative batches; the schedule is the reference's, walked on the host.  Parity is statistical (own
+ *   solver roundings; see csrc/arrsac.cu).  *n_inl = 0: the reference returned false.  n_hypotheses / n_batches: optional
+ *   diagnostics.  mpl_arrsac_set_seed sets the two sampler states (0 = cv::RNG's default 0xffffffff); like the reference's
+ *   function-local static generators they keep running across calls of a thread. */
+int mpl_arrsac_set_seed(unsigned long long prosac_state, unsigned long long random_state);
+int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refine, double* E, uint8_t* mask, int* n_inl,
+                  int* n_hypotheses, int* n_batches);
 /* mpl_get_pose_triang_pts_api mirrors poselib::getPoseTriangPts(E, p1, p2, R, t, Q, mask, dist, translatE)
  *   (MP/poselib/source/pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338, decomposeEssentialMat :340-352):
  *   E 3x3 row-major, p1/p2 n x 2 doubles (camera-normalised).  mask (may be NULL): n bytes; mask_given != 0 -> its

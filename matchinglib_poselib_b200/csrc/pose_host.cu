@@ -250,9 +250,9 @@ extern "C" int mpl_estimate_essential_api(const double* p1, const double* p2, in
 {
     if (!method) { mpl_set_error("estimateEssentialMat: null method"); return MPL_ERR_BAD_ARG; }
     const std::string m(method);
-    if (m != "RANSAC") {
-        // pose_estim.cpp:878-887: USAC / unknown methods print and exit(1); ARRSAC / LMEDS are other algorithms.
-        mpl_set_error("estimateEssentialMat: method %s is not served by the B200 hot path (only RANSAC; no CPU fallback)", method);
+    if (m != "RANSAC" && m != "ARRSAC") {
+        // pose_estim.cpp:878-887: USAC / unknown methods print and exit(1); LMEDS is another algorithm (not served).
+        mpl_set_error("estimateEssentialMat: method %s is not served by the B200 hot path (RANSAC, ARRSAC; no CPU fallback)", method);
         return MPL_ERR_BAD_ARG;
     }
     if (n < 5 || !p1 || !p2) { mpl_set_error("CV_Assert(npoints >= 5 && points2.checkVector(2) == npoints)"); return MPL_ERR_ASSERT; }
@@ -283,6 +283,11 @@ extern "C" int mpl_estimate_essential_api(const double* p1, const double* p2, in
         return 1;
     }
     int n_inl = 0, iters = 0;
+    if (m == "ARRSAC") {                                       // pose_estim.cpp:866-869
+        int rc = mpl_arrsac5pt(p1, p2, n, threshold, refine, E_out, mask, &n_inl, nullptr, nullptr);
+        if (rc) return rc;
+        return n_inl > 0 ? 1 : 0;
+    }
     int rc = mpl_ransac5pt(p1, p2, n, nullptr, 0, threshold, 1000, 0.999, refine, E_out, mask, &n_inl, &iters,
                            nullptr, nullptr, nullptr, nullptr);
     if (rc) return rc;

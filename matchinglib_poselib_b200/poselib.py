@@ -49,8 +49,8 @@ def ransac5pt(p1, p2, samples, threshold, max_iters=1000, confidence=0.999, refi
 
 
 def estimateEssentialMat(p1, p2, method="ARRSAC", threshold=1.6, refine=True, want_mask=True):
-    """poselib::estimateEssentialMat.  Returns (ok, E, mask).  Only method "RANSAC" is served (the reference's
-    default "ARRSAC" and "LMEDS"/"USAC" are other algorithms; there is no CPU fallback)."""
+    """poselib::estimateEssentialMat.  Returns (ok, E, mask).  Methods "ARRSAC" (the reference's default; mpl_arrsac5pt)
+    and "RANSAC" are served; "LMEDS" / "USAC" raise (no CPU fallback)."""
     lib = _lib.load()
     p1, p2 = _pts(p1), _pts(p2)
     n = p1.shape[0]
@@ -67,6 +67,24 @@ def estimateEssentialMat(p1, p2, method="ARRSAC", threshold=1.6, refine=True, wa
     if n == 5:
         return bool(rc), E[: n_E.value].reshape(-1, 3), mask.reshape(1, -1)
     return bool(rc), E[0].reshape(3, 3), (mask.reshape(1, -1) if want_mask else None)
+
+
+def arrsac5pt(p1, p2, threshold, refine=True, seed=None):
+    """runARRSAC (modelest.cpp:197-341) through mpl_arrsac5pt.  seed = (prosac_state, random_state) restarts the two sampler
+    streams (None: they keep running, like the reference's static generators).  Returns dict(ok, E, mask, count,
+    n_hypotheses, n_batches)."""
+    lib = _lib.load()
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if n < 5 or p2.shape[0] != n:
+        raise AssertionError("CV_Assert(npoints >= 5 && points2.checkVector(2) == npoints)")
+    if seed is not None:
+        lib.mpl_arrsac_set_seed(int(seed[0]), int(seed[1]))
+    E = np.zeros(9); mask = np.zeros(n, np.uint8)
+    cnt, nh, nb = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+    _lib.check(lib.mpl_arrsac5pt(_lib.ptr(p1), _lib.ptr(p2), n, float(threshold), int(bool(refine)), _lib.ptr(E), _lib.ptr(mask),
+                                 ctypes.byref(cnt), ctypes.byref(nh), ctypes.byref(nb)), "mpl_arrsac5pt")
+    return dict(ok=cnt.value > 0, E=E.reshape(3, 3), mask=mask, count=cnt.value, n_hypotheses=nh.value, n_batches=nb.value)
 
 
 def getPoseTriangPts(E, p1, p2, mask=None, dist=50.0, translatE=False):

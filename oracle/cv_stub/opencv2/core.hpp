@@ -1,9 +1,16 @@
-// Minimal stand-in for <opencv2/core.hpp>: ONLY what the reference's thirdparty/gms-1.0/src/MatchGMS.cpp touches, so that
-// that file can be compiled unmodified where it lies under /root/reference (oracle/Makefile, target ref_gms).  The image has
-// no OpenCV C++ SDK.  TEST INFRASTRUCTURE ONLY.  Semantics follow OpenCV's documented behaviour for these members:
-// Mat::zeros / ptr / at / row (a view sharing the data) / setTo, cv::sum (sum of all elements; count of true for vector<bool>).
+// Minimal stand-in for <opencv2/core.hpp>: ONLY what the reference sources compiled into oracle/_ref touch -- thirdparty/
+// gms-1.0/src/MatchGMS.cpp (Mat, Size, KeyPoint, DMatch, sum) and poselib/include/arrsac/*.h (RNG) -- so that those files
+// can be compiled unmodified where they lie under /root/reference (oracle/Makefile, targets ref_gms, ref_arrsac).  The image
+// has no OpenCV C++ SDK.  TEST INFRASTRUCTURE ONLY.  Semantics follow OpenCV's documented behaviour for these members:
+// Mat::zeros / ptr / at / row (a view sharing the data) / setTo, cv::sum (sum of all elements; count of true for vector<bool>),
+// RNG (multiply-with-carry, default state 0xffffffff, uniform(a, b) = a + next() % (b - a)).
 #pragma once
+#include <algorithm>
+#include <cassert>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
 #include <cstring>
 #include <memory>
 #include <vector>
@@ -32,6 +39,18 @@ public:
 private:
     std::shared_ptr<std::vector<int>> buf;
     int* base = nullptr;
+};
+
+// cv::Ptr: a shared_ptr (sample_consensus_estimator.h holds its sampler / quality measurement in one)
+template <class T> using Ptr = std::shared_ptr<T>;
+
+class RNG {
+public:
+    unsigned long long state;
+    RNG() : state(0xffffffffULL) {}
+    explicit RNG(unsigned long long s) : state(s ? s : 0xffffffffULL) {}
+    unsigned next() { state = (unsigned long long)(unsigned)state * 4164903690U + (unsigned)(state >> 32); return (unsigned)state; }
+    int uniform(int a, int b) { return a == b ? a : (int)(next() % (unsigned)(b - a) + a); }
 };
 
 inline Scalar sum(const Mat& m) { Scalar s; const int* p = m.data_i(); for (size_t i = 0; i < (size_t)m.rows * m.cols; ++i) s.val[0] += p[i]; return s; }
