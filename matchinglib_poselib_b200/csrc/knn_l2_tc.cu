@@ -468,6 +468,64 @@ __device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t tad
     }
 }
 
+// Slow path without the TMEM round trip (round 2): the flagged group index is warp-uniform, so a uniform switch picks the
+// group's four accumulators straight out of the registers the fast path has just scanned (no dynamic register indexing, no
+// tcgen05.ld + wait: ~40 instead of ~400 clocks per event).  That needs the 32 loaded registers alive during the events,
+// which the register budget (96 at 640 threads) only allows for ONE 32-column chunk at a time: the epilogue therefore
+// handles the two chunks of its 64 columns one after the other (load, scan, events; load, scan, events).
+// Why it matters: an accumulator buffer goes back to the MMA issuer only when the SLOWEST of its 8 epilogue warps is done
+// with it; with ~1.3 events per warp and tile the slowest warp had 3 - 4 events, i.e. the old slow path (not the scan)
+// set the tile time.
+#ifndef MPL_TC_REG_EVENTS
+#define MPL_TC_REG_EVENTS 1
+#endif
+template <class List>
+__device__ __forceinline__ void epi_events_reg(unsigned mask, int col0, const uint32_t (&r)[32], EpiState<List>& S)
+{
+#pragma unroll 1
+    while (mask) {                                                               // warp-uniform
+        const int g = __ffs(mask) - 1;
+        mask &= mask - 1;
+        uint32_t v0, v1, v2, v3;
+        switch (g) {
+            case 0: v0 = r[0]; v1 = r[1]; v2 = r[2]; v3 = r[3]; break;
+            case 1: v0 = r[4]; v1 = r[5]; v2 = r[6]; v3 = r[7]; break;
+            case 2: v0 = r[8]; v1 = r[9]; v2 = r[10]; v3 = r[11]; break;
+            case 3: v0 = r[12]; v1 = r[13]; v2 = r[14]; v3 = r[15]; break;
+            case 4: v0 = r[16]; v1 = r[17]; v2 = r[18]; v3 = r[19]; break;
+            case 5: v0 = r[20]; v1 = r[21]; v2 = r[22]; v3 = r[23]; break;
+            case 6: v0 = r[24]; v1 = r[25]; v2 = r[26]; v3 = r[27]; break;
+            default: v0 = r[28]; v1 = r[29]; v2 = r[30]; v3 = r[31]; break;
+        }
+        const int col = col0 + 4 * g;
+        const uint32_t v[4] = {v0, v1, v2, v3};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (__uint_as_float(v[e]) < S.thr) {
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(S.pptr), "r"(v[e]), "r"(col + e) : "memory");
+                S.pptr += PEND_STRIDE;
+            }
+        }
+        if (__any_sync(0xffffffffu, S.pptr > S.pbase + (PEND_CAP - 4) * PEND_STRIDE)) epi_drain(S);
+    }
+}
+
+// group flags of ONE 32-column chunk: bit g = columns 4g .. 4g+3 hold something below thr
+__device__ __forceinline__ unsigned group_mask32(const uint32_t (&r)[32], float thr)
+{
+    unsigned lo = 0, hi = 0;                                                      // two independent chains of 4
+#pragma unroll
+    for (int g = 3; g >= 0; --g) {
+        const float m0 = fminf(fminf(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1])),
+                               fminf(__uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3])));
+        const float m1 = fminf(fminf(__uint_as_float(r[16 + 4 * g]), __uint_as_float(r[16 + 4 * g + 1])),
+                               fminf(__uint_as_float(r[16 + 4 * g + 2]), __uint_as_float(r[16 + 4 * g + 3])));
+        lo = __funnelshift_l(__float_as_uint(__fsub_rn(m0, thr)), lo, 1);
+        hi = __funnelshift_l(__float_as_uint(__fsub_rn(m1, thr)), hi, 1);
+    }
+    return (lo & 0xFu) | ((hi & 0xFu) << 4);
+}
+
 // MMA issuer of ONE UMMA M block (two issuer warps per CTA, m = 0 and m = 1: the scalar work between two tcgen05.mma --
 // barrier waits, descriptor arithmetic, commits -- costs a single warp more time per tile than the tensor pipe needs for
 // the tile's MMAs, so it is split).  The whole warp runs the loop (uniform control flow), one elected lane issues.
@@ -581,6 +639,36 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         e_wait += clock64() - e_q; e_q = clock64();
 #endif
         tc_fence_after();
+#if defined(MPL_TC_DEBUG) && MPL_TC_DEBUG == 1
+        const int col0 = tile * BN + hf * 64; (void)col0; (void)gv; (void)partner; (void)taddr;
+#elif MPL_TC_REG_EVENTS
+        uint32_t ra[32];
+        tc_ld32(taddr, ra);
+        const int col0 = tile * BN + hf * 64;
+        float ox; int oq;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(ox), "=r"(oq) : "r"(partner) : "memory");
+        float gx = ord_to_float(gv);                                             // NaN while nothing is published
+        if (EXACT) { ox = __fadd_rn(ox, 1.0f); gx = __fadd_rn(gx, 1.0f); }
+        S.ext = fminf((oq == S.qb) ? ox : INFINITY, gx);
+        S.thr = fminf(S.thr, S.ext);
+        tc_wait_ld_regs(ra);
+        {
+            const unsigned mask = __reduce_or_sync(0xffffffffu, group_mask32(ra, S.thr));
+#ifdef MPL_TC_TRACE
+            e_groups += __popc(mask);
+#endif
+            epi_events_reg(mask, col0, ra, S);
+        }
+        tc_ld32(taddr + 32, ra);
+        tc_wait_ld_regs(ra);
+        {
+            const unsigned mask = __reduce_or_sync(0xffffffffu, group_mask32(ra, S.thr));
+#ifdef MPL_TC_TRACE
+            e_groups += __popc(mask);
+#endif
+            epi_events_reg(mask, col0 + 32, ra, S);
+        }
+#else
         uint32_t ra[32], rb[32];
         tc_ld32(taddr, ra);
         tc_ld32(taddr + 32, rb);
@@ -605,6 +693,7 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
         epi_events(mask, col0, taddr, S);
 #ifdef MPL_TC_TRACE
         e_slow += clock64() - e_q;
+#endif
 #endif
         tc_fence_before();
         __syncwarp();

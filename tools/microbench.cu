@@ -118,7 +118,7 @@ __global__ void k_ldtm(uint32_t* out, int iters)
 // tcgen05.mma issue rate: one thread issues `n` back-to-back MMAs (kind::f16, bf16 operands, M = 128, K = 16) on zeroed
 // shared-memory operands (K-major, 128-byte swizzle), `chains` accumulators used round-robin, then one commit.
 template <int TF32>
-__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0)
+__global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_every = 0, const unsigned char* gsrc = nullptr, int tma_kb_per_mma_x16 = 0)
 {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -140,6 +140,25 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = slot;
+    __shared__ uint64_t tbar;
+    __shared__ volatile int s_done;
+    if (threadIdx.x == 32) { asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tbar)) : "memory"); s_done = 0; }
+    __syncthreads();
+    if (warp == 1 && gsrc && threadIdx.x == 32) {
+        // concurrent TMA traffic into another shared-memory region: 16 KB bulk copies back to back until the MMA warp is done
+        // (tma_kb_per_mma_x16 = pacing: after each copy wait so that the average is x/16 KB per MMA issued at 64 clk)
+        unsigned char* dst = smem + 16384 + 32768;
+        uint32_t ph = 0;
+        while (!s_done) {
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tbar)), "r"(16384) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(gsrc + (size_t)blockIdx.x * 16384), "r"(16384), "r"((uint32_t)__cvta_generic_to_shared(&tbar)) : "memory");
+            asm volatile("{\n\t.reg .pred p;\n\tWT: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DT;\n\tbra WT;\n\tDT:\n\t}"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(&tbar)), "r"(ph) : "memory");
+            ph ^= 1;
+            if (tma_kb_per_mma_x16 > 0) { const long long t1 = clock64() + (long long)(16 * 16 * 64) / tma_kb_per_mma_x16 ; while (clock64() < t1 && !s_done) {} }
+        }
+    }
     if (warp == 0) {                                   // whole warp runs the loop (uniform), one elected lane issues
         const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem), b = a + 16384;
         const uint64_t hi = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
@@ -173,6 +192,7 @@ __global__ void k_umma(long long* cycles, int n, int N, int chains, int commit_e
             asm volatile("{\n\t.reg .pred p;\n\tW: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t@p bra D;\n\tbra W;\n\tD:\n\t}"
                          ::"r"((uint32_t)__cvta_generic_to_shared(&bar)) : "memory");
             cycles[blockIdx.x] = clock64() - t0;
+            s_done = 1;
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -253,6 +273,20 @@ int main()
         const double cpm = (double)h[0] / n;
         printf(", \"umma_m128_n%d_k8_tf32_cycles_per_mma\": %.1f", N, cpm);
         if (N == 256) printf(", \"tf32_tflops_issue_bound\": %.1f", 2.0 * 128 * N * 8 / cpm * sms * clk_khz * 1e3 / 1e12);
+    }
+    {   // MMA rate while TMA bulk copies stream into the same SM's shared memory (the ranking kernel's situation: 36 KB of B per 18 MMAs = 2 KB per MMA)
+        unsigned char* gsrc; cudaMalloc(&gsrc, (size_t)sms * 16384); cudaMemset(gsrc, 0, (size_t)sms * 16384);
+        cudaFuncSetAttribute(k_umma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        for (int N : {128, 256}) {
+            for (int pace : {0, 32, 64}) {              // 0 = copies back to back (as fast as TMA goes); 32 / 64 = 2 / 4 KB per 64 clocks
+                const int n = 4000;
+                long long* cyc = (long long*)buf;
+                k_umma<0><<<sms, 64, 96 * 1024>>>(cyc, n, N, 1, 0, gsrc, pace);
+                if (cudaDeviceSynchronize() != cudaSuccess) { fprintf(stderr, "k_umma+tma failed\n"); break; }
+                long long h[1]; cudaMemcpy(h, cyc, sizeof(long long), cudaMemcpyDeviceToHost);
+                printf(", \"umma_m128_n%d_with_tma_pace%d_cycles_per_mma\": %.1f", N, pace, (double)h[0] / n);
+            }
+        }
     }
     for (int chains : {1, 2}) {
         for (int ce : {1, 2, 4, 8, 16}) {
