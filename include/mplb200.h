@@ -186,6 +186,10 @@ int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t,
  *   "ARRSAC" (the reference's default, mpl_arrsac5pt); "LMEDS" / "USAC" / anything else is refused -- no CPU fallback.
  *   n == 5: solver only, *n_E models stacked in E_out. */
 int mpl_ransac_set_seed(unsigned long long seed);
+/* Experiment switch, default 0 = the reference's 300 Durand-Kerner sweeps (cv::solvePoly, five-point.cpp:430).  1: the
+ * minimal solver stops once a sweep moved every root by less than 2^-40 relative (DESIGN.md 4.4 reports the measured
+ * root-set / inlier-count differences and the speed-up); process-wide. */
+int mpl_set_solver_early_exit(int on);
 int mpl_ransac_draw_samples(const double* p1, const double* p2, int n, int h, int32_t* samples, int* n_drawn);
 int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double th,
                   int max_iters, double conf, int refine, double* E, uint8_t* mask, int* n_inl, int* iters_run,

@@ -78,6 +78,7 @@ SIGNATURES = {
     "mpl_knn_l2_last_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_knn_l2_last_stats_host": (c_int, [c_void_p, c_void_p]),
     "mpl_knn2_l2f32_dev": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "mpl_set_solver_early_exit": (c_int, [c_int]),
     "mpl_ransac_set_seed": (c_int, [ctypes.c_ulonglong]),
     "mpl_ransac_draw_samples": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "mpl_ransac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_double, c_int,

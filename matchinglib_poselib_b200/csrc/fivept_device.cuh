@@ -266,6 +266,10 @@ __device__ inline int durand_kerner10(const double* c, double* re, double* im)
 // Same iteration for the full degree (the common case), every index a compile-time constant: the ten iterates and the
 // coefficients stay in registers instead of dynamically indexed local memory.  300 sweeps are the reference's: the
 // iteration practically never becomes bit-stationary (measured on the oracle: 99.5 % of the samples use all sweeps).
+// EARLY (off by default, mpl_set_solver_early_exit): leave the loop once a whole sweep moved every root by less than
+// 2^-40 of its magnitude.  The iteration converges quadratically, so every later sweep of the reference only re-rounds the
+// last bits; the roots then differ from the 300-sweep roots by a few ulp (DESIGN.md section 4.4 has the measured effect).
+template <bool EARLY>
 __device__ __forceinline__ void durand_kerner_deg10(const double (&c)[11], double (&re)[10], double (&im)[10])
 {
     {
@@ -276,6 +280,7 @@ __device__ __forceinline__ void durand_kerner_deg10(const double (&c)[11], doubl
 #pragma unroll 1
     for (int iter = 0; iter < 300; ++iter) {
         bool changed = false;
+        bool settled = true;
         double max_diff = 0;
 #pragma unroll
         for (int i = 0; i < 10; ++i) {
@@ -316,8 +321,10 @@ __device__ __forceinline__ void durand_kerner_deg10(const double (&c)[11], doubl
             changed |= (nre != pr) || (nim != pi);
             re[i] = nre; im[i] = nim;
             max_diff = fmax(max_diff, fabs(qr) + fabs(qi));
+            if (EARLY) settled &= (fabs(qr) + fabs(qi)) <= 9.094947017729282e-13 * (fabs(nre) + fabs(nim));   // 2^-40
         }
         if (!changed || !(max_diff > 0)) break;
+        if (EARLY && settled) break;
     }
 #pragma unroll
     for (int i = 0; i < 10; ++i) if (fabs(im[i]) < 1e-100) im[i] = 0;
@@ -325,6 +332,7 @@ __device__ __forceinline__ void durand_kerner_deg10(const double (&c)[11], doubl
 
 // ---- steps 3-6 from a given null-space basis -------------------------------------------------------
 // models: up to 10 x 9 doubles; returns the count.
+template <bool EARLY = false>
 __device__ inline int solve_from_basis(const double ee[4][9], double* models)
 {
     double A[10][20];
@@ -360,7 +368,7 @@ __device__ inline int solve_from_basis(const double ee[4][9], double* models)
             for (int j = 0; j < 5; ++j) c[i + j] = fma((double)perm[s][3] * t2[i], bw[perm[s][2]][j], c[i + j]);
     }
     double re[10], im[10];
-    if (fabs(c[10]) > 2.220446049250313e-16) durand_kerner_deg10(c, re, im);
+    if (fabs(c[10]) > 2.220446049250313e-16) durand_kerner_deg10<EARLY>(c, re, im);
     else durand_kerner10(c, re, im);
     int count = 0;
     for (int i = 0; i < 10; ++i) {

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+bool mpl_solver_early_exit();   // pose_host.cu: mpl_set_solver_early_exit (experiment switch, default off)
 int mpl_launch_pack_corr(const double* p1, const double* p2, int n, void* corr /* n x 32 B */, cudaStream_t st);
 int mpl_launch_fivept_solve(const void* corr, int n, const int32_t* samples, int h, double* models /* h x 90 */,
                             int32_t* n_models /* h */, cudaStream_t st);

@@ -201,13 +201,14 @@ inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Arena {              // offsets inside a lane's device arena for a sub-batch of `bs` pairs
     size_t dims, offs, seeds, raw, dq, dt, keys, pts1, pts2, matches, corr, src, state, samples, models, nm, counts, errs,
-           maskc, maskm, basis, rmodels, rnm, l2scr, total;
+           maskc, maskm, basis, rmodels, rnm, l2scr, part, total;
 };
 
 struct BatchPlan {
     int cv_type, cols, used, w16, row_bytes;       // binary: row_bytes = w16 * 16; float: row_bytes = ld * 4
     int is_float, sqrt_out, ignore_tail;
     int nq_stride, nt_stride, h, bs;
+    int splits;                                     // train splits of the Hamming scan (> 1 only for batches too small to fill the GPU)
     size_t pe;                                      // bytes per keypoint
     size_t l2_scratch;
     CamParams cam;
@@ -230,6 +231,7 @@ Arena make_arena(const BatchPlan& P, size_t raw_bytes)
     A.maskc = take(bs * nq); A.maskm = take(bs * nq);
     A.basis = take(bs * 36 * 8); A.rmodels = take(bs * 90 * 8); A.rnm = take(bs * 4);
     A.l2scr = take(P.l2_scratch);
+    A.part = take(P.splits > 1 ? bs * (size_t)P.splits * nq * 16 : 16);
     A.total = o;
     return A;
 }
@@ -298,8 +300,17 @@ int enqueue_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, 
         pack_pairs_kernel<<<dim3(blocks, 2 * nb), 256, 0, st>>>((const uint8_t*)(D + A.raw), (const unsigned long long*)(D + A.offs), d_dims,
                                                                  P.cols, P.used, P.row_bytes, P.nq_stride, P.nt_stride, (uint8_t*)(D + A.dq), (uint8_t*)(D + A.dt));
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        if ((rc = mpl_launch_hamming_top2((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, 1, nb, 0,
-                                          d_keys, st, d_dims))) return rc;
+        if (P.splits > 1) {
+            // a batch of a few pairs cannot fill the GPU with one CTA row per pair: split the train rows as the single-pair
+            // matcher does and merge the per-split keys (one merge launch per pair; only taken for nb <= 8)
+            mpl_key64* d_part = (mpl_key64*)(D + A.part);
+            if ((rc = mpl_launch_hamming_top2((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, P.splits, nb, 0,
+                                              d_part, st, d_dims))) return rc;
+            for (int i = 0; i < nb; ++i)
+                if ((rc = mpl_launch_merge_top2(d_part + (size_t)i * P.splits * P.nq_stride * 2, P.splits, P.nq_stride, 2, nullptr, nullptr, -1,
+                                                d_keys + (size_t)i * P.nq_stride * 2, st))) return rc;
+        } else if ((rc = mpl_launch_hamming_top2((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, 1, nb, 0,
+                                                 d_keys, st, d_dims))) return rc;
     } else {
         const size_t ld = (size_t)P.row_bytes / 4;
         MPL_CUDA_CHECK(cudaMemsetAsync(d_keys, 0xFF, (size_t)nb * P.nq_stride * 16, st));
@@ -446,6 +457,11 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
     // two lanes need at least two sub-batches; split small batches in halves so that uploads and kernels overlap
     if (n_pairs >= 16 && n_pairs <= bs) bs = (n_pairs + 1) / 2;
     P.bs = bs;
+    P.splits = 1;
+    if (!P.is_float && bs <= 8) {
+        const int sp = mpl_hamming_pick_splits(P.nq_stride, P.nt_stride, P.w16, std::max(1, ctx->sm_count / bs));
+        if (sp > 1 && (P.nt_stride + sp - 1) / sp >= 32) P.splits = sp;
+    }
     const int n_sub = (n_pairs + bs - 1) / bs;
     for (auto& L : ctx->lanes) if (!L.stream) MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
     int inflight_p0[2] = {0, 0}, inflight_nb[2] = {0, 0};

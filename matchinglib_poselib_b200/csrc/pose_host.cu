@@ -12,12 +12,19 @@
 #include "mpl_ransac.h"
 #include "../../include/mplb200.h"
 
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 #include <cstring>
 #include <mutex>
 #include <string>
 #include <vector>
+
+// Experiment switch (default OFF): the minimal solver leaves cv::solvePoly's Durand-Kerner loop once a sweep moved every root
+// by < 2^-40 relative instead of running all 300 sweeps.  Not the shipping default: see DESIGN.md section 4.4.
+static std::atomic<int> g_solver_early{0};
+bool mpl_solver_early_exit() { return g_solver_early.load(std::memory_order_relaxed) != 0; }
+extern "C" int mpl_set_solver_early_exit(int on) { g_solver_early.store(on ? 1 : 0, std::memory_order_relaxed); return MPL_OK; }
 
 // cvRANSACUpdateNumIters1 (modelest.cpp:86-109)
 static int update_num_iters(double p, double ep, int model_points, int max_iters)

@@ -48,6 +48,7 @@ __global__ void pack_corr_kernel(const double* __restrict__ p1, const double* __
     if (i < n) corr[i] = make_double4(p1[2 * i], p1[2 * i + 1], p2[2 * i], p2[2 * i + 1]);
 }
 
+template <bool EARLY>
 __global__ void __launch_bounds__(64)
 fivept_solve_kernel(const double4* __restrict__ corr, int n, const int32_t* __restrict__ samples, int h,
                     double* __restrict__ models /* [h][10][9] */, int32_t* __restrict__ n_models)
@@ -67,7 +68,7 @@ fivept_solve_kernel(const double4* __restrict__ corr, int n, const int32_t* __re
     if (ok) {
         double ee[4][9];
         fivept::null_space_5x9(x1, y1, x2, y2, ee);
-        cnt = fivept::solve_from_basis(ee, models + (size_t)s * 90);
+        cnt = fivept::solve_from_basis<EARLY>(ee, models + (size_t)s * 90);
     }
     n_models[s] = cnt;
 }
@@ -218,7 +219,8 @@ int mpl_launch_fivept_solve(const void* corr, int n, const int32_t* samples, int
 {
     if (h <= 0) return MPL_OK;
     MplProfScope prof(MPL_PROF_SOLVE, st);
-    fivept_solve_kernel<<<(h + 63) / 64, 64, 0, st>>>((const double4*)corr, n, samples, h, models, n_models);
+    if (mpl_solver_early_exit()) fivept_solve_kernel<true><<<(h + 63) / 64, 64, 0, st>>>((const double4*)corr, n, samples, h, models, n_models);
+    else                         fivept_solve_kernel<false><<<(h + 63) / 64, 64, 0, st>>>((const double4*)corr, n, samples, h, models, n_models);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
 }

@@ -111,6 +111,7 @@ __global__ void draw_samples_batch_kernel(const MplPairState* __restrict__ st, i
 }
 
 // ---- solve ----------------------------------------------------------------------------------------------------
+template <bool EARLY>
 __global__ void __launch_bounds__(64)
 solve_chunk_kernel(const double4* __restrict__ corr, size_t corr_stride, const MplPairState* __restrict__ st, int n_pairs,
                    const int32_t* __restrict__ samples, int h, int s0, int c, double* __restrict__ models, int32_t* __restrict__ n_models)
@@ -135,7 +136,7 @@ solve_chunk_kernel(const double4* __restrict__ corr, size_t corr_stride, const M
     if (ok) {
         double ee[4][9];
         fivept::null_space_5x9(x1, y1, x2, y2, ee);
-        cnt = fivept::solve_from_basis(ee, models + ((size_t)p * h + s) * 90);
+        cnt = fivept::solve_from_basis<EARLY>(ee, models + ((size_t)p * h + s) * 90);
     }
     n_models[(size_t)p * h + s] = cnt;
 }
@@ -495,7 +496,8 @@ int mpl_launch_solve_chunk(const void* corr, size_t corr_stride, const MplPairSt
     if (n_pairs <= 0 || c <= 0) return MPL_OK;
     MplProfScope prof(MPL_PROF_SOLVE, s);
     const long long total = (long long)n_pairs * c;
-    solve_chunk_kernel<<<(unsigned)((total + 63) / 64), 64, 0, s>>>((const double4*)corr, corr_stride, st, n_pairs, samples, h, s0, c, models, n_models);
+    if (mpl_solver_early_exit()) solve_chunk_kernel<true><<<(unsigned)((total + 63) / 64), 64, 0, s>>>((const double4*)corr, corr_stride, st, n_pairs, samples, h, s0, c, models, n_models);
+    else                         solve_chunk_kernel<false><<<(unsigned)((total + 63) / 64), 64, 0, s>>>((const double4*)corr, corr_stride, st, n_pairs, samples, h, s0, c, models, n_models);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
 }
