@@ -544,6 +544,9 @@ __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1
     int stage = 0; uint32_t sphase = 0, a_phase = 0; unsigned it = 0;
     int tile = (int)(u0 - (u0 / NT) * NT);                                       // tile index inside the current query block
     bool new_qb = true;
+#ifdef MPL_TC_LAG
+    if (m == 1) { const long long t_go = clock64() + MPL_TC_LAG; while (clock64() < t_go) { } }   // experiment: de-phase the two issuers
+#endif
 #ifdef MPL_TC_TRACE
     long long w_te = 0, w_bf = 0, w_af = 0, w_is = 0, t_start = clock64(), tq;
 #define MPL_TWAIT(acc, stmt) do { tq = clock64(); stmt; acc += clock64() - tq; } while (0)
