@@ -96,20 +96,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-// non-blocking: has the phase with this parity completed?
-__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 // one lane of a converged warp (keeps the surrounding code warp-uniform, so descriptors and addresses stay in
 // uniform registers instead of going through per-lane waterfall loops)
@@ -144,14 +133,13 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
                    "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
                  : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major operand slab, 128-byte swizzle: 8-row groups of 1024 bytes (SBO), descriptor version 1 (sm_100)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+[[maybe_unused]] __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // K-major 32-byte rows, 32-byte swizzle: 8-row groups of 256 bytes (the aug slab)
-__device__ __forceinline__ uint64_t umma_desc_sw32(uint32_t smem_addr) {
+[[maybe_unused]] __device__ __forceinline__ uint64_t umma_desc_sw32(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);
 }
 // instruction descriptor: D = f32, A/B format (1 = bf16, 2 = tf32), both K-major, N = 128, M = 128
@@ -344,12 +332,6 @@ struct TopList2 {
     }
 };
 
-__device__ __forceinline__ float4 lds128(uint32_t saddr) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
-    return v;
-}
-
 __device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
     // the loaded registers become valid here: tie them to the wait so no use can be scheduled above it
     asm volatile("tcgen05.wait::ld.sync.aligned;"
@@ -408,6 +390,10 @@ __device__ __forceinline__ void epi_drain(EpiState<List>& S)
     if (S.L.last() < S.gpub) { S.gpub = S.L.last(); atomicMin(S.gq, ord_of(S.gpub)); }
 }
 
+#ifndef MPL_TC_REG_EVENTS
+#define MPL_TC_REG_EVENTS 1          // 0 = round 1's slow path (TMEM re-read of the flagged groups), kept for A/B builds
+#endif
+#if !MPL_TC_REG_EVENTS
 // one bit per group of 4 columns whose minimum is below thr: sign(min - thr) (FADD on the fma pipe) funnelled into the mask
 __device__ __forceinline__ unsigned group_mask(const uint32_t (&r)[32], float thr)
 {
@@ -468,6 +454,8 @@ __device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t tad
     }
 }
 
+#endif  // !MPL_TC_REG_EVENTS
+
 // Slow path without the TMEM round trip (round 2): the flagged group index is warp-uniform, so a uniform switch picks the
 // group's four accumulators straight out of the registers the fast path has just scanned (no dynamic register indexing, no
 // tcgen05.ld + wait: ~40 instead of ~400 clocks per event).  That needs the 32 loaded registers alive during the events,
@@ -476,9 +464,6 @@ __device__ __forceinline__ void epi_events(unsigned mask, int col0, uint32_t tad
 // Why it matters: an accumulator buffer goes back to the MMA issuer only when the SLOWEST of its 8 epilogue warps is done
 // with it; with ~1.3 events per warp and tile the slowest warp had 3 - 4 events, i.e. the old slow path (not the scan)
 // set the tile time.
-#ifndef MPL_TC_REG_EVENTS
-#define MPL_TC_REG_EVENTS 1
-#endif
 template <class List>
 __device__ __forceinline__ void epi_events_reg(unsigned mask, int col0, const uint32_t (&r)[32], EpiState<List>& S)
 {
@@ -856,17 +841,6 @@ __device__ __forceinline__ float warp_exact_dist(const float* __restrict__ a /* 
     if (MODE == 1) r = __fadd_rn(__fadd_rn(__fadd_rn(l0, l1), l2), l3);
     for (int i = dim4; i < dim; ++i) { const float d = __fsub_rn(a[i], b[i]); r = __fadd_rn(r, __fmul_rn(d, d)); }
     return MODE == 1 ? sqrtf(r) : r;
-}
-
-__device__ __forceinline__ void warp_top2(mpl_key64& b0, mpl_key64& b1)
-{
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const mpl_key64 o0 = __shfl_xor_sync(0xffffffffu, b0, off), o1 = __shfl_xor_sync(0xffffffffu, b1, off);
-        const mpl_key64 hi = max(b0, o0);
-        b0 = min(b0, o0);
-        b1 = min(min(b1, o1), hi);
-    }
 }
 
 template <int MODE>
