@@ -591,7 +591,6 @@ int arrsac_estimate(ArrsacEngine& G, ArrsacState& P, int n)
                     if (est.empty()) { k2++; continue; }
                     P.verified_accum += (int)est.size();
                     const double A = sprt_threshold(P.sigma, P.epsilon, P.tm_ratio, P.verified_accum / (k + j + 1 - k2));
-                    bool stop = false;
                     for (size_t m = 0; m < est.size(); ++m) {
                         double ratio; int inl;
                         const bool ok = G.sprt(est[m], i + 1, P.sigma, P.epsilon, A, &ratio, &inl);
@@ -605,10 +604,9 @@ int arrsac_estimate(ArrsacEngine& G, ArrsacState& P, int n)
                             P.epsilon = ratio == 1.0 ? 0.9999 : ratio;
                             tmax = (int)std::ceil(std::log(1 - P.conf) / std::log(1 - std::pow(P.epsilon, i + 1)));
                             tmax = std::min(P.max_cand, tmax);
-                            if (tmax <= (k + j + 1)) { stop = true; break; }               // arrsac.h:484-485: leaves the model loop only
+                            if (tmax <= (k + j + 1)) break;                                // arrsac.h:484-485: leaves the model loop only
                         } else H.push_back(Hyp{est[m], (double)inl});
                     }
-                    (void)stop;
                     k++;
                 }
                 nh = (int)H.size();

@@ -400,7 +400,6 @@ int launch_w(const uint8_t* q, int nq, const uint8_t* t, int nt, int n_splits, i
 }
 
 int queries_per_cta(int w16) { return w16 <= 2 ? kThreads * 4 : (w16 <= 4 ? kThreads * 2 : kThreads); }
-int tile_rows(int w16) { return kTileBytes / (16 * w16); }
 
 }  // namespace
 
