@@ -210,6 +210,43 @@ int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const 
 int mpl_arrsac_set_seed(unsigned long long prosac_state, unsigned long long random_state);
 int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refine, double* E, uint8_t* mask, int* n_inl,
                   int* n_hypotheses, int* n_batches);
+/* mpl_usac5pt replaces estimateEssentialMatUsac (MP/poselib/source/usac/usac_estimations.cpp:283-735) -- the robust
+ *   estimator behind poselib::estimateEssentialOrPoseUSAC (pose_estim.cpp:1737), the default RobMethod of poselib-test:
+ *   USAC<EssentialMatEstimator>::solve (MP/poselib/include/usac/estimators/USAC.h:345-612; uniform or PROSAC sampling,
+ *   SPRT verification over a random evaluation pool, LOSAC local optimisation, standard / PROSAC / SPRT stopping) with the
+ *   estimator of EssentialMatEstimator.h (5-point minimal solver, collinearity pre-test of the sample, oriented-epipolar
+ *   pre-test of the model, plain-double Sampson error, 8-point refits with Torr weights).  Minimal solves, model tests, the
+ *   inlier bit matrix and the whole local optimisation run on the device; the schedule is the reference's, walked on the host
+ *   over those bits with glibc's rand() restated (csrc/usac.cu).  Parity is statistical.
+ *   p1, p2: n x 2 camera-normalised points.  sorted_idx: n correspondence indices by increasing match distance (PROSAC,
+ *   what getSortedMatchIdx hands over) or NULL (uniform sampling).  mpl_usac_params_default fills the values
+ *   estimateEssentialMatUsac uses (conf 0.99, 50000 hypotheses, LOSAC 5 x 14 / 2.0 / 4, PROSAC 1000 / 20 / 0.99, beta 0.09,
+ *   SPRT delta 0.05 epsilon 0.15, tM 2314 mS 8.5 for the Nister estimator).  estimator: 0 NISTER, 2 STEWENIUS (same device
+ *   solver, tM / mS are the caller's); refine must be 0 (REFINE_WEIGHTS) and degeneracy 0 -- other values return
+ *   MPL_ERR_BAD_ARG, there is no CPU fallback.  Outputs: E[9] (zeros when no model was found, like final_model_params_),
+ *   mask[n], res (may be NULL).  res->ok = 0: solve() returned false (fewer than 5 points, or fewer than minStopLen with
+ *   PROSAC) -- the reference then returns EXIT_FAILURE. */
+typedef struct mpl_usac_params {
+    double th, conf;
+    int max_hypotheses, prevalidate_sample;
+    double prosac_beta, prosac_non_rand_conf; int prosac_max_samples, prosac_min_stop_len;
+    double sprt_delta, sprt_epsilon, sprt_tM, sprt_mS;
+    int lo_inner_sample_size, lo_inner_reps, lo_num_steps; double lo_threshold_multiplier;
+    int estimator, refine, degeneracy;
+    unsigned seed;                              /* srand(seed); the reference uses time(NULL) */
+} mpl_usac_params;
+typedef struct mpl_usac_result {
+    int ok;
+    unsigned hyp_count, model_count, rejected_sample_count, rejected_model_count, total_points_verified,
+             num_local_optimizations, best_inlier_count;
+    double sprt_delta, sprt_epsilon;            /* usac_results_.sprt_delta_/epsilon_: the last stored test (0 if none) */
+    int n_batches, n_launches;
+} mpl_usac_result;
+void mpl_usac_params_default(mpl_usac_params* p, double th);
+int mpl_usac5pt(const double* p1, const double* p2, int n, const unsigned* sorted_idx, const mpl_usac_params* params,
+                double* E, uint8_t* mask, mpl_usac_result* res);
+/* Host logic exposed for the CPU tests: the first `count` values of rand() after srand(seed) as csrc/usac.cu restates them. */
+int mpl_usac_rand_stream(unsigned seed, int count, int* out);
 /* mpl_get_pose_triang_pts_api mirrors poselib::getPoseTriangPts(E, p1, p2, R, t, Q, mask, dist, translatE)
  *   (MP/poselib/source/pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338, decomposeEssentialMat :340-352):
  *   E 3x3 row-major, p1/p2 n x 2 doubles (camera-normalised).  mask (may be NULL): n bytes; mask_given != 0 -> its

@@ -86,6 +86,9 @@ SIGNATURES = {
     "mpl_estimate_essential_api": (c_int, [c_void_p, c_void_p, c_int, c_char_p, c_double, c_int, c_void_p, c_void_p, c_void_p]),
     "mpl_arrsac_set_seed": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong]),
     "mpl_arrsac5pt": (c_int, [c_void_p, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_usac_params_default": (None, [c_void_p, c_double]),
+    "mpl_usac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_usac_rand_stream": (c_int, [ctypes.c_uint, c_int, c_void_p]),
     "mpl_match_pose_pair": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_void_p, c_void_p, c_char_p, c_int,
                                     c_double, c_int, c_double, c_int, ctypes.c_ulonglong, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -95,6 +98,22 @@ SIGNATURES = {
     "mpl_ransac_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_ransac_score_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p]),
 }
+
+class UsacParams(ctypes.Structure):
+    """mpl_usac_params (include/mplb200.h)."""
+    _fields_ = [("th", c_double), ("conf", c_double), ("max_hypotheses", c_int), ("prevalidate_sample", c_int),
+                ("prosac_beta", c_double), ("prosac_non_rand_conf", c_double), ("prosac_max_samples", c_int), ("prosac_min_stop_len", c_int),
+                ("sprt_delta", c_double), ("sprt_epsilon", c_double), ("sprt_tM", c_double), ("sprt_mS", c_double),
+                ("lo_inner_sample_size", c_int), ("lo_inner_reps", c_int), ("lo_num_steps", c_int), ("lo_threshold_multiplier", c_double),
+                ("estimator", c_int), ("refine", c_int), ("degeneracy", c_int), ("seed", ctypes.c_uint)]
+
+
+class UsacResult(ctypes.Structure):
+    """mpl_usac_result (include/mplb200.h)."""
+    _fields_ = [("ok", c_int), ("hyp_count", ctypes.c_uint), ("model_count", ctypes.c_uint), ("rejected_sample_count", ctypes.c_uint),
+                ("rejected_model_count", ctypes.c_uint), ("total_points_verified", ctypes.c_uint), ("num_local_optimizations", ctypes.c_uint),
+                ("best_inlier_count", ctypes.c_uint), ("sprt_delta", c_double), ("sprt_epsilon", c_double), ("n_batches", c_int), ("n_launches", c_int)]
+
 
 _lib = None
 

@@ -87,6 +87,45 @@ def arrsac5pt(p1, p2, threshold, refine=True, seed=None):
     return dict(ok=cnt.value > 0, E=E.reshape(3, 3), mask=mask, count=cnt.value, n_hypotheses=nh.value, n_batches=nb.value)
 
 
+def usac5pt(p1, p2, threshold, sorted_idx=None, seed=1, estimator="NISTER", **overrides):
+    """estimateEssentialMatUsac (usac/usac_estimations.cpp:283-735) through mpl_usac5pt: USAC with SPRT verification, LOSAC local
+    optimisation (8-point with Torr weights) and uniform (sorted_idx=None) or PROSAC sampling (sorted_idx = correspondence
+    indices by increasing match distance).  `overrides` set fields of mpl_usac_params (sprt_delta, sprt_epsilon, prosac_beta,
+    sprt_mS, ...).  Returns dict(ok, E, mask, count, hyp_count, model_count, rejected_sample_count, rejected_model_count,
+    total_points_verified, num_local_optimizations, sprt_delta, sprt_epsilon, n_batches, n_launches)."""
+    lib = _lib.load()
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if p2.shape[0] != n:
+        raise AssertionError("CV_Assert((p1.cols == 2) && (p2.cols == 2) && (p1.rows == p2.rows))")
+    prm = _lib.UsacParams()
+    lib.mpl_usac_params_default(ctypes.byref(prm), float(threshold))
+    est = {"NISTER": 0, "STEWENIUS": 2}.get(str(estimator).upper())
+    if est is None:
+        raise _lib.MplError("usac5pt: estimator %r is not built (NISTER / STEWENIUS only; no CPU fallback)" % (estimator,))
+    prm.estimator = est
+    if est == 2:
+        prm.sprt_tM, prm.sprt_mS = 2736.0, 6.0                     # usac_estimations.cpp:392-421 (first call: avgModels = 6)
+    prm.seed = int(seed) & 0xffffffff
+    for k, v in overrides.items():
+        if not hasattr(prm, k):
+            raise TypeError("usac5pt: unknown parameter %r" % (k,))
+        setattr(prm, k, v)
+    idx = None
+    if sorted_idx is not None:
+        idx = np.ascontiguousarray(np.asarray(sorted_idx, np.uint32).reshape(-1))
+        if idx.shape[0] != n:
+            raise AssertionError("CV_Assert(sortedMatchIdx.empty() || (p1.rows == (int)sortedMatchIdx.size()))")
+    E = np.zeros(9); mask = np.zeros(max(n, 1), np.uint8)
+    res = _lib.UsacResult()
+    _lib.check(lib.mpl_usac5pt(_lib.ptr(p1), _lib.ptr(p2), n, _lib.ptr(idx) if idx is not None else None, ctypes.byref(prm),
+                               _lib.ptr(E), _lib.ptr(mask), ctypes.byref(res)), "mpl_usac5pt")
+    out = dict(ok=bool(res.ok), E=E.reshape(3, 3), mask=mask[:n], count=int(res.best_inlier_count))
+    for k, _t in _lib.UsacResult._fields_[1:]:
+        out.setdefault(k, getattr(res, k))
+    return out
+
+
 def getPoseTriangPts(E, p1, p2, mask=None, dist=50.0, translatE=False):
     """poselib::getPoseTriangPts (pose_estim.h:192-200, pose_estim.cpp:913-946 -> recoverPose, five-point.cpp:150-338).
     Returns (n_valid, R 3x3, t 3x1, Q n x 3, mask 1 x n uint8).  `mask` (optional, 1 x n or n) is the inlier mask
