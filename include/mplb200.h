@@ -225,7 +225,15 @@ int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refi
  *   solver, tM / mS are the caller's); refine must be 0 (REFINE_WEIGHTS) and degeneracy 0 -- other values return
  *   MPL_ERR_BAD_ARG, there is no CPU fallback.  Outputs: E[9] (zeros when no model was found, like final_model_params_),
  *   mask[n], res (may be NULL).  res->ok = 0: solve() returned false (fewer than 5 points, or fewer than minStopLen with
- *   PROSAC) -- the reference then returns EXIT_FAILURE. */
+ *   PROSAC) -- the reference then returns EXIT_FAILURE.
+ *   lo_mode: the reference's local optimisation never improves a model with REFINE_WEIGHTS -- FTools::singulF
+ *   (FundmatrixFunctions.cpp:334-360) goes through the ccmath port MathTools::svduv, which returns wrong singular triplets
+ *   for matrices with two nearly equal singular values, i.e. for every essential-like matrix (measured: D = (0.651, 1.1e-5,
+ *   0.697) for a matrix whose singular values are (0.717, 0.697, 1.0e-5), |U D V^T - F|^2 = 0.09), so every refitted model
+ *   is mangled, fails its SPRT, and "Inlier count before: N, after: N" is what its verbose mode prints for every LO.
+ *   lo_mode 1 (default) reproduces that observable behaviour: the inner samples are drawn (the random stream stays the
+ *   reference's) and their models count as rejected.  lo_mode 0 runs the local optimisation as USAC.h:948-1060 states it,
+ *   on the device (one launch, a CTA per repetition): supports reach the ground truth's and fewer hypotheses are needed. */
 typedef struct mpl_usac_params {
     double th, conf;
     int max_hypotheses, prevalidate_sample;
@@ -233,6 +241,7 @@ typedef struct mpl_usac_params {
     double sprt_delta, sprt_epsilon, sprt_tM, sprt_mS;
     int lo_inner_sample_size, lo_inner_reps, lo_num_steps; double lo_threshold_multiplier;
     int estimator, refine, degeneracy;
+    int lo_mode;                                /* 1 (default): local optimisation as the reference BEHAVES; 0: as it is stated -- see above */
     unsigned seed;                              /* srand(seed); the reference uses time(NULL) */
 } mpl_usac_params;
 typedef struct mpl_usac_result {

@@ -105,7 +105,7 @@ class UsacParams(ctypes.Structure):
                 ("prosac_beta", c_double), ("prosac_non_rand_conf", c_double), ("prosac_max_samples", c_int), ("prosac_min_stop_len", c_int),
                 ("sprt_delta", c_double), ("sprt_epsilon", c_double), ("sprt_tM", c_double), ("sprt_mS", c_double),
                 ("lo_inner_sample_size", c_int), ("lo_inner_reps", c_int), ("lo_num_steps", c_int), ("lo_threshold_multiplier", c_double),
-                ("estimator", c_int), ("refine", c_int), ("degeneracy", c_int), ("seed", ctypes.c_uint)]
+                ("estimator", c_int), ("refine", c_int), ("degeneracy", c_int), ("lo_mode", c_int), ("seed", ctypes.c_uint)]
 
 
 class UsacResult(ctypes.Structure):

@@ -35,6 +35,9 @@
 // Parity: statistical.  Sampler, evaluation pool, SPRT, LOSAC and the stopping rules are the reference's, restated; the
 // models differ in rounding and in their order within a sample (own solver), and the repetitions of one local optimisation
 // run side by side from the same pool cursor (the reference's cursor only moves between them when an SPRT rejects).
+// One reference DEFECT decides the default: its local optimisation never improves a model (singulF's 3 x 3 SVD port fails on
+// essential-like matrices; include/mplb200.h, lo_mode, has the measurement), so lo_mode 1 (default) draws the inner samples
+// and treats their models as rejected, and lo_mode 0 runs the optimisation as stated, on the device.
 // tests/test_usac_gpu.py compares with the reference's own estimator compiled into oracle/_ref/libusac_ref.so.
 #include "mpl_common.cuh"
 #include "mpl_ctx.h"
@@ -434,7 +437,7 @@ struct UsacHost {
     unsigned prosac_max_samples = 1000, prosac_min_stop_len = 20; double prosac_beta = 0.09, prosac_non_rand_conf = 0.99;
     const unsigned* sorted = nullptr;
     double tM = 2314.0, mS = 8.5, delta = 0.05, epsilon = 0.15;
-    unsigned lo_sample = 14, lo_reps = 5, lo_steps = 4; double lo_mult = 2.0;
+    unsigned lo_sample = 14, lo_reps = 5, lo_steps = 4; double lo_mult = 2.0; int lo_mode = 1;
     // PROSAC state (USAC.h:145-150)
     unsigned subset_size = 0, largest_size = 0, stop_len = 0;
     std::vector<unsigned> growth, non_random_inliers, maximality;
@@ -671,6 +674,7 @@ unsigned locally_optimise(UsacHost& H, UsacDevice& G, unsigned best_inliers)
         uniform_sample(H.rng, best_inliers, sz, tmp);
         for (unsigned j = 0; j < sz; ++j) samples[(size_t)r * kLoMaxSample + j] = (int32_t)orig[tmp[j]];
     }
+    if (H.lo_mode == 1) return best_inliers;          // the reference's observable behaviour (include/mplb200.h, lo_mode): no repetition improves
     LoParams P;
     P.n = H.n; P.W = G.W; P.sample_size = (int)sz; P.n_steps = (int)H.lo_steps; P.pool_start = (int)(H.cursor > (unsigned)H.n - 1 ? 0 : H.cursor);
     P.th2 = H.th2; P.mult = H.lo_mult; P.delta = H.delta; P.epsilon = H.epsilon; P.A = H.A; P.T = G.T;
@@ -797,7 +801,7 @@ extern "C" void mpl_usac_params_default(mpl_usac_params* p, double th)
     p->prosac_beta = 0.09; p->prosac_non_rand_conf = 0.99; p->prosac_max_samples = 1000; p->prosac_min_stop_len = 20;     // :389-396, pose_estim.cpp:1754
     p->sprt_delta = 0.05; p->sprt_epsilon = 0.15; p->sprt_tM = 2314.0; p->sprt_mS = 8.5;                  // :399-430
     p->lo_inner_sample_size = 14; p->lo_inner_reps = 5; p->lo_num_steps = 4; p->lo_threshold_multiplier = 2.0;            // :380-386
-    p->estimator = 0; p->refine = 0; p->degeneracy = 0; p->seed = 1;
+    p->estimator = 0; p->refine = 0; p->degeneracy = 0; p->lo_mode = 1; p->seed = 1;
 }
 
 extern "C" int mpl_usac5pt(const double* p1, const double* p2, int n, const unsigned* sorted_idx, const mpl_usac_params* prm,
@@ -808,7 +812,7 @@ extern "C" int mpl_usac5pt(const double* p1, const double* p2, int n, const unsi
         mpl_set_error("mpl_usac5pt: only estimator NISTER / STEWENIUS with REFINE_WEIGHTS and no degeneracy test is built"); return MPL_ERR_BAD_ARG;
     }
     if (prm->lo_inner_sample_size > kLoMaxSample || prm->lo_inner_sample_size < 5 || prm->lo_inner_reps < 1 || prm->lo_inner_reps > 64 ||
-        prm->lo_num_steps < 1 || prm->max_hypotheses < 1 || !(prm->th > 0)) { mpl_set_error("mpl_usac5pt: parameter out of range"); return MPL_ERR_BAD_ARG; }
+        prm->lo_num_steps < 1 || prm->max_hypotheses < 1 || prm->lo_mode < 0 || prm->lo_mode > 1 || !(prm->th > 0)) { mpl_set_error("mpl_usac5pt: parameter out of range"); return MPL_ERR_BAD_ARG; }
     if (res) memset(res, 0, sizeof(*res));
     for (int k = 0; k < 9; ++k) E[k] = 0.0;
     if (mask && n > 0) memset(mask, 0, (size_t)n);
@@ -820,7 +824,7 @@ extern "C" int mpl_usac5pt(const double* p1, const double* p2, int n, const unsi
     H.prosac_max_samples = (unsigned)prm->prosac_max_samples; H.prosac_min_stop_len = (unsigned)prm->prosac_min_stop_len;
     H.prosac_beta = prm->prosac_beta; H.prosac_non_rand_conf = prm->prosac_non_rand_conf;
     H.tM = prm->sprt_tM; H.mS = prm->sprt_mS; H.delta = prm->sprt_delta; H.epsilon = prm->sprt_epsilon;
-    H.lo_sample = (unsigned)prm->lo_inner_sample_size; H.lo_reps = (unsigned)prm->lo_inner_reps; H.lo_steps = (unsigned)prm->lo_num_steps; H.lo_mult = prm->lo_threshold_multiplier;
+    H.lo_sample = (unsigned)prm->lo_inner_sample_size; H.lo_reps = (unsigned)prm->lo_inner_reps; H.lo_steps = (unsigned)prm->lo_num_steps; H.lo_mult = prm->lo_threshold_multiplier; H.lo_mode = prm->lo_mode;
     if (n < 5 || (H.prosac && (unsigned)n < H.prosac_min_stop_len)) return MPL_OK;         // solve() == false: res->ok stays 0
     H.rng.seed(prm->seed);
     // initDataUSAC (USAC.h:274-336): PROSAC tables, the first SPRT design, the evaluation pool (std::random_shuffle over rand())

@@ -65,7 +65,7 @@ int usac_ref_essential(const double* p1, const double* p2, int n, double th, dou
     c_ess.focalLength = focal_length; c_ess.hDegenThreshold = 2.0 * th; c_ess.maxUpgradeSamples = 8000;             // :444-446
     c_ess.refineMethod = USACConfig::REFINE_WEIGHTS; c_ess.rotDegenThesholdPix = th_pixels; c_ess.used_estimator = est;
     c_ess.ransacLikeUpgradeDegenerate = true; c_ess.enableHDegen = true; c_ess.enableUpgradeDegenPose = true;       // :450-456
-    ConfigParamsEssential cfg(c_com, c_pro, c_sprt, c_lo, c_ess, false);
+    ConfigParamsEssential cfg(c_com, c_pro, c_sprt, c_lo, c_ess, getenv("USAC_REF_VERBOSE") != nullptr);     // verbose: the reference's own progress lines
 
     std::unique_ptr<EssentialMatEstimator> fund(new EssentialMatEstimator);                                         // :461-470
     fund->initParamsUSAC(cfg);
@@ -81,5 +81,10 @@ int usac_ref_essential(const double* p1, const double* p2, int n, double th, dou
     for (int i = 0; i < n; ++i) mask[i] = r.inlier_flags_[i] ? 1 : 0;
     return 0;
 }
+
+// FTools::singulF (FundmatrixFunctions.cpp:334-360) on a caller's 3 x 3 matrix: lets tests/test_oracle_usac.py pin the defect that
+// makes the reference's REFINE_WEIGHTS local optimisation a no-op (its ccmath svduv port returns wrong singular triplets when two
+// singular values are nearly equal, i.e. for essential-like matrices).
+void usac_ref_singulF(double* F) { FTools::singulF(F); }
 
 }  // extern "C"

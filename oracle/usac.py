@@ -58,6 +58,16 @@ def usac(p1, p2, th, sorted_idx=None, seed=1, estimator="NISTER", prosac_beta=0.
                 num_local_optimizations=int(stats[5]), sprt_delta=float(sp[0]), sprt_epsilon=float(sp[1]))
 
 
+def ref_singulF(F):
+    """The reference's FTools::singulF on a 3 x 3 matrix (None when the reference build is absent)."""
+    R = ref_lib()
+    if R is None:
+        return None
+    out = np.ascontiguousarray(np.asarray(F, np.float64).reshape(9)).copy()
+    R.usac_ref_singulF(ctypes.c_void_p(out.ctypes.data))
+    return out.reshape(3, 3)
+
+
 # ---- numpy restatements ---------------------------------------------------------------------------------------------
 
 def sampson(E, p1, p2):

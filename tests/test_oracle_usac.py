@@ -56,6 +56,30 @@ def test_refined_model_restatement_fits_the_inliers():
     assert 10 < A < 100
 
 
+def test_reference_singulF_defect_is_pinned():
+    """Why mpl_usac5pt has lo_mode: the reference's rank-2 projection is right for a generic matrix and wrong for an essential-like
+    one (two nearly equal singular values), so every model its local optimisation refits is mangled."""
+    _built()
+    def proj(F):
+        U, s, Vt = np.linalg.svd(F)
+        return U @ np.diag([s[0], s[1], 0.0]) @ Vt
+    G = np.array([[1, 2, 3], [4, 5, 6], [7, 8, 10.0]])
+    assert np.linalg.norm(ousac.ref_singulF(G) - proj(G)) < 1e-9
+    F = np.array([0.0307373, 0.245357, -0.170661, -0.252817, 0.0102013, 0.646064, 0.0969459, -0.647193, -0.00737131]).reshape(3, 3)
+    assert np.linalg.svd(F)[1][2] < 2e-5                                                  # already rank 2 to 1e-5: the projection should change nothing
+    assert np.linalg.norm(proj(F) - F) < 2e-5 and np.linalg.norm(ousac.ref_singulF(F) - F) > 0.2
+    # and on a scene: an 8-point fit of ALL ground-truth inliers, pushed through the reference's singulF, loses most of them
+    sc = datagen_pose.make_scene(800, 0.05, seed=31)
+    inl = ousac.sampson(sc["E"], sc["p1"], sc["p2"]) < sc["th"] ** 2
+    p1n, p2n, T1, T2 = ousac.normalize_points(sc["p1"], sc["p2"])
+    x1, y1 = p1n[inl].T; x2, y2 = p2n[inl].T
+    A = np.stack([x2 * x1, x2 * y1, x2, y2 * x1, y2 * y1, y2, x1, y1, np.ones(len(x1))], 1)
+    f = np.linalg.eigh(A.T @ A)[1][:, 0].reshape(3, 3)
+    good = (ousac.sampson(T2.T @ proj(f) @ T1, sc["p1"], sc["p2"]) < sc["th"] ** 2).sum()
+    bad = (ousac.sampson(T2.T @ ousac.ref_singulF(f) @ T1, sc["p1"], sc["p2"]) < sc["th"] ** 2).sum()
+    assert good >= 0.98 * inl.sum() and bad < 0.2 * inl.sum(), (good, bad, inl.sum())
+
+
 def test_rand_stream_is_glibc():
     import __graft_entry__ as g
     g.build()
