@@ -25,8 +25,9 @@ if len(sys.argv) > 1 and sys.argv[1] == "detail":
         print("scene n=%d outl=%.2f prosac=%s truth=%d" % (n, outl, prosac, truth))
         for seed in range(1, 9):
             g = poselib.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=seed)
+            g0 = poselib.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=seed, lo_mode=0)
             o = ousac.usac(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=seed)
-            print("  seed %d GPU %s sprt (%.4f %.4f)" % (seed, [g[k] for k in keys], g["sprt_delta"], g["sprt_epsilon"]))
+            print("  seed %d GPU %s sprt (%.4f %.4f)   [lo_mode 0: %s]" % (seed, [g[k] for k in keys], g["sprt_delta"], g["sprt_epsilon"], [g0[k] for k in keys[:2]]))
             print("         REF %s sprt (%.4f %.4f)" % ([o[k] for k in keys], o["sprt_delta"], o["sprt_epsilon"]))
     sys.exit(0)
 
