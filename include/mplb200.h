@@ -226,14 +226,16 @@ int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refi
  *   MPL_ERR_BAD_ARG, there is no CPU fallback.  Outputs: E[9] (zeros when no model was found, like final_model_params_),
  *   mask[n], res (may be NULL).  res->ok = 0: solve() returned false (fewer than 5 points, or fewer than minStopLen with
  *   PROSAC) -- the reference then returns EXIT_FAILURE.
- *   lo_mode: the reference's local optimisation never improves a model with REFINE_WEIGHTS -- FTools::singulF
- *   (FundmatrixFunctions.cpp:334-360) goes through the ccmath port MathTools::svduv, which returns wrong singular triplets
- *   for matrices with two nearly equal singular values, i.e. for every essential-like matrix (measured: D = (0.651, 1.1e-5,
- *   0.697) for a matrix whose singular values are (0.717, 0.697, 1.0e-5), |U D V^T - F|^2 = 0.09), so every refitted model
- *   is mangled, fails its SPRT, and "Inlier count before: N, after: N" is what its verbose mode prints for every LO.
- *   lo_mode 1 (default) reproduces that observable behaviour: the inner samples are drawn (the random stream stays the
- *   reference's) and their models count as rejected.  lo_mode 0 runs the local optimisation as USAC.h:948-1060 states it,
- *   on the device (one launch, a CTA per repetition): supports reach the ground truth's and fewer hypotheses are needed. */
+ *   lo_mode: the reference's local optimisation is data dependent in a way its code does not state -- FTools::singulF
+ *   (FundmatrixFunctions.cpp:334-360) goes through the ccmath port MathTools::svduv, which for SOME matrices with two nearly
+ *   equal singular values (essential-like ones) returns wrong singular triplets (measured: D = (0.651, 1.1e-5, 0.697) for a
+ *   matrix whose singular values are (0.717, 0.697, 1.0e-5), |U D V^T - F|^2 = 0.09).  In scenes where that happens every
+ *   refitted model is mangled, fails its SPRT, and the reference's verbose mode prints "Inlier count before: N, after: N"
+ *   for every local optimisation; in other scenes its local optimisation works.  That 200-line third-party routine is not
+ *   restated here, so there are two modes and the reference behaves like one or the other, scene by scene
+ *   (tests/test_usac_gpu.py reports which):  lo_mode 0 (default) runs the local optimisation as USAC.h:948-1060 states it,
+ *   on the device (one launch, a CTA per repetition);  lo_mode 1 draws the inner samples (the random stream stays the
+ *   reference's) and counts their models as rejected -- what the reference does where its singulF fails. */
 typedef struct mpl_usac_params {
     double th, conf;
     int max_hypotheses, prevalidate_sample;
@@ -241,7 +243,7 @@ typedef struct mpl_usac_params {
     double sprt_delta, sprt_epsilon, sprt_tM, sprt_mS;
     int lo_inner_sample_size, lo_inner_reps, lo_num_steps; double lo_threshold_multiplier;
     int estimator, refine, degeneracy;
-    int lo_mode;                                /* 1 (default): local optimisation as the reference BEHAVES; 0: as it is stated -- see above */
+    int lo_mode;                                /* 0 (default): local optimisation as stated; 1: its models count as rejected -- see above */
     unsigned seed;                              /* srand(seed); the reference uses time(NULL) */
 } mpl_usac_params;
 typedef struct mpl_usac_result {

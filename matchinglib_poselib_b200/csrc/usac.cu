@@ -35,9 +35,10 @@
 // Parity: statistical.  Sampler, evaluation pool, SPRT, LOSAC and the stopping rules are the reference's, restated; the
 // models differ in rounding and in their order within a sample (own solver), and the repetitions of one local optimisation
 // run side by side from the same pool cursor (the reference's cursor only moves between them when an SPRT rejects).
-// One reference DEFECT decides the default: its local optimisation never improves a model (singulF's 3 x 3 SVD port fails on
-// essential-like matrices; include/mplb200.h, lo_mode, has the measurement), so lo_mode 1 (default) draws the inner samples
-// and treats their models as rejected, and lo_mode 0 runs the optimisation as stated, on the device.
+// One reference DEFECT is not restated: in some scenes its local optimisation never improves a model (singulF's 3 x 3 SVD
+// port fails on some essential-like matrices; include/mplb200.h, lo_mode, has the measurement).  lo_mode 0 (default) runs the
+// optimisation as stated, on the device; lo_mode 1 draws the inner samples and treats their models as rejected, which is
+// what the reference does in those scenes.  Scene by scene the reference's runs equal one mode or the other.
 // tests/test_usac_gpu.py compares with the reference's own estimator compiled into oracle/_ref/libusac_ref.so.
 #include "mpl_common.cuh"
 #include "mpl_ctx.h"
@@ -437,7 +438,7 @@ struct UsacHost {
     unsigned prosac_max_samples = 1000, prosac_min_stop_len = 20; double prosac_beta = 0.09, prosac_non_rand_conf = 0.99;
     const unsigned* sorted = nullptr;
     double tM = 2314.0, mS = 8.5, delta = 0.05, epsilon = 0.15;
-    unsigned lo_sample = 14, lo_reps = 5, lo_steps = 4; double lo_mult = 2.0; int lo_mode = 1;
+    unsigned lo_sample = 14, lo_reps = 5, lo_steps = 4; double lo_mult = 2.0; int lo_mode = 0;
     // PROSAC state (USAC.h:145-150)
     unsigned subset_size = 0, largest_size = 0, stop_len = 0;
     std::vector<unsigned> growth, non_random_inliers, maximality;
@@ -674,7 +675,7 @@ unsigned locally_optimise(UsacHost& H, UsacDevice& G, unsigned best_inliers)
         uniform_sample(H.rng, best_inliers, sz, tmp);
         for (unsigned j = 0; j < sz; ++j) samples[(size_t)r * kLoMaxSample + j] = (int32_t)orig[tmp[j]];
     }
-    if (H.lo_mode == 1) return best_inliers;          // the reference's observable behaviour (include/mplb200.h, lo_mode): no repetition improves
+    if (H.lo_mode == 1) return best_inliers;          // what the reference does where its singulF fails (include/mplb200.h, lo_mode): no repetition improves
     LoParams P;
     P.n = H.n; P.W = G.W; P.sample_size = (int)sz; P.n_steps = (int)H.lo_steps; P.pool_start = (int)(H.cursor > (unsigned)H.n - 1 ? 0 : H.cursor);
     P.th2 = H.th2; P.mult = H.lo_mult; P.delta = H.delta; P.epsilon = H.epsilon; P.A = H.A; P.T = G.T;
@@ -801,7 +802,7 @@ extern "C" void mpl_usac_params_default(mpl_usac_params* p, double th)
     p->prosac_beta = 0.09; p->prosac_non_rand_conf = 0.99; p->prosac_max_samples = 1000; p->prosac_min_stop_len = 20;     // :389-396, pose_estim.cpp:1754
     p->sprt_delta = 0.05; p->sprt_epsilon = 0.15; p->sprt_tM = 2314.0; p->sprt_mS = 8.5;                  // :399-430
     p->lo_inner_sample_size = 14; p->lo_inner_reps = 5; p->lo_num_steps = 4; p->lo_threshold_multiplier = 2.0;            // :380-386
-    p->estimator = 0; p->refine = 0; p->degeneracy = 0; p->lo_mode = 1; p->seed = 1;
+    p->estimator = 0; p->refine = 0; p->degeneracy = 0; p->lo_mode = 0; p->seed = 1;
 }
 
 extern "C" int mpl_usac5pt(const double* p1, const double* p2, int n, const unsigned* sorted_idx, const mpl_usac_params* prm,

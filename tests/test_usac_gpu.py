@@ -6,9 +6,11 @@ GPU path (both draw from glibc's rand()).
 Parity is statistical for this randomised, adaptive algorithm -- the 5-point solvers differ in rounding and in the order of a
 sample's models, and the evaluation-pool cursor drifts apart after a local optimisation -- but with the same seed most runs are
 IDENTICAL in (support, hypotheses, models, rejected models, local optimisations), which pins sampler, pool, SPRT, PROSAC and
-stopping rules.  The bars: identical runs in at least half of the seeds of every scene, medians of support and hypotheses within
+stopping rules.  The reference's local optimisation works in some scenes and is a no-op in others (a defect of its 3 x 3 SVD
+port, include/mplb200.h lo_mode, pinned in tests/test_oracle_usac.py), so every scene is run in both lo_modes and must match the
+reference in one of them.  The bars: identical runs in at least half of the seeds, medians of support and hypotheses within
 10 % / a factor 1.5, and -- exact -- the returned mask is the inlier set of the returned model under evaluateModel's own error.
-lo_mode 0 (local optimisation as stated, see include/mplb200.h) must reach the ground truth's support."""
+lo_mode 0 (the default: local optimisation as stated) must also reach the ground truth's support."""
 import numpy as np
 import pytest
 
@@ -51,26 +53,31 @@ def test_usac_vs_reference_per_seed(P, n, outl, seed, prosac):
     sc = datagen_pose.make_scene(n, outl, seed=seed)
     truth = int((ousac.sampson(sc["E"], sc["p1"], sc["p2"]) < sc["th"] ** 2).sum())
     idx = _order(sc, seed) if prosac else None
-    gc, oc, gh, oh, same = [], [], [], [], 0
+    gc, gh, same = {0: [], 1: []}, {0: [], 1: []}, {0: 0, 1: 0}
+    oc, oh = [], []
     for s in range(1, 11):
-        g = P.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=s)
-        assert g["ok"] and g["count"] >= 0.5 * truth, (g["count"], truth)
-        # exact: mask == {evaluateModel error of the returned model < th^2}, count == its size (storeSolution, USAC.h:1208-1228)
-        omask = ousac.sampson(g["E"], sc["p1"], sc["p2"]) < sc["th"] ** 2
-        assert np.array_equal(omask, g["mask"].astype(bool)) and int(omask.sum()) == g["count"]
-        assert _ed(g["E"], sc["E"]) < 0.15
-        gc.append(g["count"]); gh.append(g["hyp_count"])
         o = ousac.usac(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=s)
         if o is not None:
             assert o["ok"]
             oc.append(o["count"]); oh.append(o["hyp_count"])
-            same += int(all(o[k] == g[k] for k in KEYS))
-    print("n=%d outliers %.0f%% %s, ground truth %d: GPU inliers %s hypotheses %s | reference inliers %s hypotheses %s | identical runs %d/10" %
-          (n, 100 * outl, "PROSAC" if prosac else "uniform", truth, gc, gh, oc, oh, same))
+        for mode in (0, 1):
+            g = P.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=s, lo_mode=mode)
+            assert g["ok"] and g["count"] >= 0.5 * truth, (g["count"], truth)
+            # exact: mask == {evaluateModel error of the returned model < th^2}, count == its size (storeSolution, USAC.h:1208-1228)
+            omask = ousac.sampson(g["E"], sc["p1"], sc["p2"]) < sc["th"] ** 2
+            assert np.array_equal(omask, g["mask"].astype(bool)) and int(omask.sum()) == g["count"]
+            assert _ed(g["E"], sc["E"]) < 0.15
+            gc[mode].append(g["count"]); gh[mode].append(g["hyp_count"])
+            if o is not None:
+                same[mode] += int(all(o[k] == g[k] for k in KEYS))
+    m = 0 if same[0] >= same[1] else 1
+    print("n=%d outliers %.0f%% %s, ground truth %d: reference inliers %s hypotheses %s | lo_mode 0 inliers %s hypotheses %s identical runs %d/10 | "
+          "lo_mode 1 inliers %s hypotheses %s identical runs %d/10 -> the reference behaves like lo_mode %d here" %
+          (n, 100 * outl, "PROSAC" if prosac else "uniform", truth, oc, oh, gc[0], gh[0], same[0], gc[1], gh[1], same[1], m))
     if oc:
-        assert same >= 5, same
-        assert abs(np.median(gc) - np.median(oc)) <= 0.1 * truth, (gc, oc, truth)
-        assert 1 / 1.5 <= (np.median(gh) + 1) / (np.median(oh) + 1) <= 1.5, (gh, oh)
+        assert same[m] >= 5, same
+        assert abs(np.median(gc[m]) - np.median(oc)) <= 0.1 * truth, (gc[m], oc, truth)
+        assert 1 / 1.5 <= (np.median(gh[m]) + 1) / (np.median(oh) + 1) <= 1.5, (gh[m], oh)
 
 
 @pytest.mark.parametrize("n,outl,seed,prosac", SCENES[:8] + SCENES[9:])
@@ -111,7 +118,7 @@ def test_usac_too_few_points_and_noise(P):
 def test_usac_deterministic_and_parameter_checks(P):
     from matchinglib_poselib_b200 import _lib
     sc = datagen_pose.make_scene(1200, 0.4, seed=51)
-    for mode in (0, 1):
+    for mode in (1, 0):
         a = P.usac5pt(sc["p1"], sc["p2"], sc["th"], seed=9, lo_mode=mode)
         b = P.usac5pt(sc["p1"], sc["p2"], sc["th"], seed=9, lo_mode=mode)
         assert a["hyp_count"] == b["hyp_count"] and a["count"] == b["count"] and np.array_equal(a["mask"], b["mask"]) and np.array_equal(a["E"], b["E"])
