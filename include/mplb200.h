@@ -154,6 +154,20 @@ int    mpl_merge_top2_dev(const void* d_keys_parts, int n_parts, int nq, int k, 
 int    mpl_knn2_hamming_batch_dev(const void* d_q, const void* d_t, int n_pairs, int nq, int nt, int w16,
                                   void* d_keys_out, void* stream);
 
+/* mpl_knn2_hamming_static_dev: mpl_knn2_hamming_dev without a scratch argument and WITHOUT ANY ALLOCATION.  It has no
+ * counterpart in the reference; it was added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The partial keys of the train-split
+ * path live in a file-scope device array of MPL_KNN_STATIC_SCRATCH_BYTES (4 MiB) that every GPU loading the library holds
+ * until the process exits (csrc/knn_hamming_static.cu).  Same inputs, outputs and results as mpl_knn2_hamming_dev.  When the
+ * preferred split count x nq x 16 bytes exceeds the array, fewer splits are used (same keys, less parallelism); when even the
+ * minimum, ceil(nt / 2^20) >= 2 splits, does not fit, the call returns MPL_ERR_LIMIT with a message and launches nothing.  All calls
+ * on a device share the array; nothing in it needs clearing between calls, but calls that OVERLAP on the GPU (two streams,
+ * two threads) race on it -- serialise them or use mpl_knn2_hamming_dev with a scratch buffer per stream. */
+#define MPL_KNN_STATIC_SCRATCH_BYTES (4u << 20)
+size_t mpl_knn_hamming_static_max_bytes(void);
+int    mpl_knn2_hamming_static_dev(const void* d_q, int nq, const void* d_t, int nt, int w16, long long train_offset,
+                                   void* d_keys_out, void* stream);
+
 /* d_scratch of the float path must be 256-byte aligned.  mpl_knn_l2_last_stats reads back (synchronising the stream) how
  * many queries of the last tensor-core call on that scratch buffer failed certification and went through the exact
  * scan, and whether the operands were bf16-exact (tf32_mode = 0) or ranked in tf32 (1).  *_host: same for the last

@@ -71,6 +71,8 @@ SIGNATURES = {
     "mpl_gms_filter": (c_int, [c_void_p, c_int, c_size_t, c_int, c_int, c_void_p, c_int, c_size_t, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_knn_hamming_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mpl_pack_rows_u8_dev": (c_int, [c_void_p, c_int, c_size_t, c_int, c_void_p, c_int, c_void_p]),
+    "mpl_knn_hamming_static_max_bytes": (c_size_t, []),
+    "mpl_knn2_hamming_static_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p]),
     "mpl_knn2_hamming_dev": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_ll, c_void_p, c_size_t, c_void_p, c_void_p]),
     "mpl_merge_top2_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_knn2_hamming_batch_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
