@@ -20,7 +20,10 @@
 #  endif
 #endif
 #include <opencv2/core.hpp>
+#include <opencv2/imgproc.hpp>      // convexHull, contourArea (estimateSprtDeltaInit)
 
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <iostream>
 #include <string>
@@ -134,6 +137,81 @@ inline bool estimateEssentialMat(cv::OutputArray E, cv::InputArray p1, cv::Input
     if (mask.needed()) cv::Mat(1, npoints, CV_8U, m.data()).copyTo(mask);        // :130-135
     cv::Mat(3 * (npoints == 5 ? n_E : 1), 3, CV_64F, e_buf).copyTo(E);           // :137-141
     return true;
+}
+
+// poselib::estimateEssentialOrPoseUSAC (pose_estim.h:212-223; pose_estim.cpp:1737-2262 -> estimateEssentialMatUsac,
+// usac/usac_estimations.cpp:283-735) for the configurations mpl_usac5pt serves: estimator POSE_NISTER / POSE_STEWENIUS, refinealg
+// REF_WEIGHTS, degeneracyCheck DEGEN_NO_CHECK (poselib-test: cfgUSAC digits 4-6 = 0, 0|2, 0).  Any other value prints and returns
+// -1 like the reference does for values it does not know -- nothing falls back to the CPU.  The SPRT / PROSAC start values follow
+// the reference's first call (:1810-1976); its cross-call running statistics (function statics) are not kept.
+enum UsacChkDegenType { DEGEN_NO_CHECK, DEGEN_QDEGSAC, DEGEN_USAC_INTERNAL };                    // pose_estim.h:61
+enum PoseEstimator { POSE_NISTER, POSE_EIG_KNEIP, POSE_STEWENIUS };                              // :64
+enum RefineAlg { REF_WEIGHTS, REF_8PT_PSEUDOHUBER, REF_EIG_KNEIP, REF_EIG_KNEIP_WEIGHTS, REF_STEWENIUS, REF_STEWENIUS_WEIGHTS, REF_NISTER, REF_NISTER_WEIGHTS };   // :67-76
+enum SprtInit { SPRT_DEFAULT_INIT = 0x0, SPRT_DELTA_AUTOM_INIT = 0x1, SPRT_EPSILON_AUTOM_INIT = 0x2 };       // :91
+struct ConfigUSAC {                                                                              // :94-132, same defaults
+    double focalLength = 800; double th_pixels = 0.8;
+    UsacChkDegenType degeneracyCheck = DEGEN_USAC_INTERNAL; PoseEstimator estimator = POSE_STEWENIUS; RefineAlg refinealg = REF_STEWENIUS_WEIGHTS;
+    bool prevalidateSample = false, noAutomaticProsacParamters = false;
+    int automaticSprtInit = SPRT_DELTA_AUTOM_INIT | SPRT_EPSILON_AUTOM_INIT;
+    std::vector<cv::DMatch>* matches = nullptr; std::vector<cv::KeyPoint>* keypoints1 = nullptr; std::vector<cv::KeyPoint>* keypoints2 = nullptr;
+    unsigned int nrMatchesVfcFiltered = 0; cv::Size imgSize = cv::Size(800, 600); double degenDecisionTh = 0.85;
+    unsigned seed = 1; int lo_mode = 0;                                                          // this library's additions (mpl_usac_params)
+};
+
+inline int estimateEssentialOrPoseUSAC(const cv::Mat& p1, const cv::Mat& p2, cv::OutputArray E, double th, ConfigUSAC& cfg, bool& isDegenerate,
+                                       cv::OutputArray inliers = cv::noArray(), cv::OutputArray R_degenerate = cv::noArray(),
+                                       cv::OutputArray inliers_degenerate_R = cv::noArray(), cv::OutputArray R = cv::noArray(),
+                                       cv::OutputArray t = cv::noArray(), bool verbose = false)
+{
+    if (cfg.estimator != POSE_NISTER && cfg.estimator != POSE_STEWENIUS) { std::cout << "Estimator not supported!" << std::endl; return -1; }     // :1776-1778
+    if (cfg.refinealg != REF_WEIGHTS) { std::cout << "Refinement algorithm not supported!" << std::endl; return -1; }                            // :1806-1808
+    if (cfg.degeneracyCheck != DEGEN_NO_CHECK) { std::cout << "Mothod for checking degeneracy not available!" << std::endl; return -1; }         // :2218-2222
+    if (cfg.automaticSprtInit < 0 || cfg.automaticSprtInit > 3) { std::cout << "Method for SPRT initialization not supported!" << std::endl; return -1; }
+    CV_Assert(p1.cols == 2 && p2.cols == 2 && p1.rows == p2.rows && p1.type() == CV_64FC1 && p2.type() == CV_64FC1);   // usac_estimations.cpp:315
+    CV_Assert(!cfg.matches || p1.rows == (int)cfg.matches->size());
+    mpl_usac_params prm;
+    mpl_usac_params_default(&prm, th);
+    if (cfg.automaticSprtInit & SPRT_DELTA_AUTOM_INIT) {                           // estimateSprtDeltaInit, pose_helper.cpp:2830-2867
+        CV_Assert(cfg.matches && cfg.keypoints1 && cfg.keypoints2);
+        std::vector<cv::Point2f> pts1, pts2, h1, h2;
+        for (const cv::DMatch& m : *cfg.matches) { pts1.push_back((*cfg.keypoints1)[m.queryIdx].pt); pts2.push_back((*cfg.keypoints2)[m.trainIdx].pt); }
+        cv::convexHull(pts1, h1); cv::convexHull(pts2, h2);
+        double area = std::min(cv::contourArea(h1), cv::contourArea(h2));
+        const double maxEpi = std::sqrt((double)(cfg.imgSize.width * cfg.imgSize.width + cfg.imgSize.height * cfg.imgSize.height)) * 2 * cfg.th_pixels;
+        area = std::max(area, 6 * maxEpi);
+        prm.sprt_delta = std::max(maxEpi / area, 0.001);
+    }
+    if (cfg.automaticSprtInit & SPRT_EPSILON_AUTOM_INIT) {                         // estimateSprtEpsilonInit, pose_helper.cpp:2881-2889
+        CV_Assert(cfg.matches);
+        prm.sprt_epsilon = std::min(std::max(0.8 * (double)cfg.nrMatchesVfcFiltered / (double)cfg.matches->size(), 0.1), 0.4);
+    }
+    if (!cfg.noAutomaticProsacParamters) prm.prosac_beta = prm.sprt_delta;         // pose_estim.cpp:1972-1975
+    std::vector<unsigned> sorted;
+    if (cfg.matches) {                                                             // getSortedMatchIdx, pose_helper.cpp:2902-2926
+        sorted.resize(cfg.matches->size());
+        for (size_t i = 0; i < sorted.size(); ++i) sorted[i] = (unsigned)i;
+        const std::vector<cv::DMatch>& mm = *cfg.matches;
+        std::stable_sort(sorted.begin(), sorted.end(), [&mm](unsigned a, unsigned b) { return mm[a].distance < mm[b].distance; });
+    }
+    prm.estimator = cfg.estimator == POSE_STEWENIUS ? 2 : 0;
+    if (cfg.estimator == POSE_STEWENIUS) { prm.sprt_tM = 2736.0; prm.sprt_mS = 6.0; }                // usac_estimations.cpp:392-421, first call
+    prm.seed = cfg.seed; prm.lo_mode = cfg.lo_mode;
+    cv::Mat a = p1.isContinuous() ? p1 : p1.clone(), b = p2.isContinuous() ? p2 : p2.clone();
+    double e_buf[9];
+    std::vector<uchar> m((size_t)std::max(a.rows, 1));
+    mpl_usac_result res;
+    const int rc = mpl_usac5pt(a.ptr<double>(), b.ptr<double>(), a.rows, cfg.matches ? sorted.data() : nullptr, &prm, e_buf, m.data(), &res);
+    if (rc < 0) { std::cout << mpl_last_error() << std::endl; return -2; }
+    if (!res.ok) { std::cout << "USAC failed!" << std::endl; return -2; }                           // pose_estim.cpp:2018-2022
+    if (verbose) std::cout << "Number of hypotheses/models: " << res.hyp_count << "/" << res.model_count << std::endl
+                           << "Max inliers/total points: " << res.best_inlier_count << "/" << a.rows << std::endl;
+    isDegenerate = false;                                                          // :2023
+    if (E.needed()) cv::Mat(3, 3, CV_64F, e_buf).copyTo(E);
+    if (inliers.needed()) cv::Mat(1, a.rows, CV_8U, m.data()).copyTo(inliers);
+    if (R.needed() && !R.empty()) R.clear();                                       // :2036-2042: R, t only come from Kneip's solver
+    if (t.needed() && !t.empty()) t.clear();
+    (void)R_degenerate; (void)inliers_degenerate_R;
+    return 0;
 }
 
 // poselib::getPoseTriangPts (pose_estim.h:192-200; pose_estim.cpp:913-946 -> recoverPose five-point.cpp:150-338)

@@ -126,6 +126,108 @@ def usac5pt(p1, p2, threshold, sorted_idx=None, seed=1, estimator="NISTER", **ov
     return out
 
 
+# enums of poselib/pose_estim.h:61-91
+DEGEN_NO_CHECK, DEGEN_QDEGSAC, DEGEN_USAC_INTERNAL = 0, 1, 2
+POSE_NISTER, POSE_EIG_KNEIP, POSE_STEWENIUS = 0, 1, 2
+(REF_WEIGHTS, REF_8PT_PSEUDOHUBER, REF_EIG_KNEIP, REF_EIG_KNEIP_WEIGHTS, REF_STEWENIUS, REF_STEWENIUS_WEIGHTS, REF_NISTER,
+ REF_NISTER_WEIGHTS) = range(8)
+SPRT_DEFAULT_INIT, SPRT_DELTA_AUTOM_INIT, SPRT_EPSILON_AUTOM_INIT = 0, 1, 2
+
+
+class ConfigUSAC:
+    """poselib::ConfigUSAC (pose_estim.h:94-132) with the reference's defaults.  Served: estimator POSE_NISTER / POSE_STEWENIUS,
+    refinealg REF_WEIGHTS, degeneracyCheck DEGEN_NO_CHECK (poselib-test's cfgUSAC digits 4-6 = 0, 0|2, 0); every other value makes
+    estimateEssentialOrPoseUSAC raise -- there is no CPU fallback.  `matches` is the DMatch record array getMatches returns (or
+    None: uniform sampling instead of PROSAC), keypoints1/2 are (n, 2) pixel coordinates (only read for SPRT_DELTA_AUTOM_INIT).
+    seed / lo_mode are this library's additions (the reference seeds with time(); see mpl_usac_params in include/mplb200.h)."""
+
+    def __init__(self, **kw):
+        self.focalLength = 800.0; self.th_pixels = 0.8
+        self.degeneracyCheck = DEGEN_USAC_INTERNAL; self.estimator = POSE_STEWENIUS; self.refinealg = REF_STEWENIUS_WEIGHTS
+        self.prevalidateSample = False; self.noAutomaticProsacParamters = False
+        self.automaticSprtInit = SPRT_DELTA_AUTOM_INIT | SPRT_EPSILON_AUTOM_INIT
+        self.matches = None; self.keypoints1 = None; self.keypoints2 = None
+        self.nrMatchesVfcFiltered = 0; self.imgSize = (800, 600); self.degenDecisionTh = 0.85
+        self.seed = 1; self.lo_mode = 0
+        for k, v in kw.items():
+            if not hasattr(self, k):
+                raise TypeError("ConfigUSAC has no field %r" % (k,))
+            setattr(self, k, v)
+
+
+def _convex_hull_area(pts):
+    """cv::contourArea(cv::convexHull(points)) (pose_helper.cpp:2848-2853): monotone chain + shoelace."""
+    p = np.unique(np.asarray(pts, np.float64).reshape(-1, 2), axis=0)
+    if len(p) < 3:
+        return 0.0
+    p = p[np.lexsort((p[:, 1], p[:, 0]))]
+
+    def half(seq):
+        h = []
+        for q in seq:
+            while len(h) >= 2 and (h[-1][0] - h[-2][0]) * (q[1] - h[-2][1]) - (h[-1][1] - h[-2][1]) * (q[0] - h[-2][0]) <= 0:
+                h.pop()
+            h.append(q)
+        return h
+    hull = np.array(half(p)[:-1] + half(p[::-1])[:-1])
+    x, y = hull[:, 0], hull[:, 1]
+    return 0.5 * abs(float(np.dot(x, np.roll(y, -1)) - np.dot(y, np.roll(x, -1))))
+
+
+def estimateSprtDeltaInit(matches, kp1, kp2, th, imgSize):
+    """poselib::estimateSprtDeltaInit (pose_helper.cpp:2830-2867): area around the longest possible epipolar line over the smaller
+    convex-hull area of the matched keypoints, at least 0.001."""
+    kp1 = np.asarray(kp1, np.float64).reshape(-1, 2); kp2 = np.asarray(kp2, np.float64).reshape(-1, 2)
+    area = min(_convex_hull_area(kp1[matches["queryIdx"]]), _convex_hull_area(kp2[matches["trainIdx"]]))
+    max_epi = float(np.sqrt(float(imgSize[0]) ** 2 + float(imgSize[1]) ** 2)) * 2 * th
+    area = max(area, 6 * max_epi)
+    return max(max_epi / area, 0.001)
+
+
+def estimateSprtEpsilonInit(matches, nrMatchesVfcFiltered):
+    """poselib::estimateSprtEpsilonInit (pose_helper.cpp:2881-2889)."""
+    return float(min(max(0.8 * float(nrMatchesVfcFiltered) / float(len(matches)), 0.1), 0.4))
+
+
+def getSortedMatchIdx(matches):
+    """poselib::getSortedMatchIdx (pose_helper.cpp:2902-2926): positions of the matches by ascending distance (std::sort is not
+    stable; ties are broken by position here)."""
+    return np.argsort(np.asarray(matches["distance"]), kind="stable").astype(np.uint32)
+
+
+def estimateEssentialOrPoseUSAC(p1, p2, th, cfg, verbose=False):
+    """poselib::estimateEssentialOrPoseUSAC (pose_estim.h:212-223, pose_estim.cpp:1737-2262) for the configurations ConfigUSAC's
+    docstring lists.  Returns (code, E 3x3 or None, isDegenerate, inliers 1 x n uint8, info): code 0 success, -1 unsupported
+    estimator / refinement (raised instead: no fallback), -2 "USAC failed!".  The SPRT / PROSAC start values follow the reference's
+    first call (:1810-1976); its cross-call running statistics (function statics, :1752-1758, 2226-2259) are not kept -- every call
+    starts like the first."""
+    if cfg.estimator not in (POSE_NISTER, POSE_STEWENIUS):
+        raise _lib.MplError("estimateEssentialOrPoseUSAC: estimator %r is not built (POSE_NISTER / POSE_STEWENIUS only)" % (cfg.estimator,))
+    if cfg.refinealg != REF_WEIGHTS:
+        raise _lib.MplError("estimateEssentialOrPoseUSAC: refinealg %r is not built (REF_WEIGHTS only)" % (cfg.refinealg,))
+    if cfg.degeneracyCheck != DEGEN_NO_CHECK:
+        raise _lib.MplError("estimateEssentialOrPoseUSAC: degeneracyCheck %r is not built (DEGEN_NO_CHECK only)" % (cfg.degeneracyCheck,))
+    if cfg.automaticSprtInit not in (0, 1, 2, 3):
+        print("Method for SPRT initialization not supported!")
+        return -1, None, False, None, {}
+    sprt_delta, sprt_epsilon, prosac_beta = 0.05, 0.15, 0.09                       # :1748
+    if cfg.automaticSprtInit & SPRT_DELTA_AUTOM_INIT:
+        sprt_delta = estimateSprtDeltaInit(cfg.matches, cfg.keypoints1, cfg.keypoints2, cfg.th_pixels, cfg.imgSize)
+    if cfg.automaticSprtInit & SPRT_EPSILON_AUTOM_INIT:
+        sprt_epsilon = estimateSprtEpsilonInit(cfg.matches, cfg.nrMatchesVfcFiltered)
+    if not cfg.noAutomaticProsacParamters:
+        prosac_beta = sprt_delta                                                   # :1972-1975
+    idx = getSortedMatchIdx(cfg.matches) if cfg.matches is not None else None     # :1977-1981
+    r = usac5pt(p1, p2, th, sorted_idx=idx, seed=cfg.seed, estimator="NISTER" if cfg.estimator == POSE_NISTER else "STEWENIUS",
+                sprt_delta=float(sprt_delta), sprt_epsilon=float(sprt_epsilon), prosac_beta=float(prosac_beta), lo_mode=int(cfg.lo_mode))
+    if not r["ok"]:
+        print("USAC failed!")
+        return -2, None, False, None, r
+    if verbose:
+        print("Number of hypotheses/models: %d/%d\nMax inliers/total points: %d/%d" % (r["hyp_count"], r["model_count"], r["count"], len(r["mask"])))
+    return 0, r["E"], False, r["mask"].reshape(1, -1), r
+
+
 def getPoseTriangPts(E, p1, p2, mask=None, dist=50.0, translatE=False):
     """poselib::getPoseTriangPts (pose_estim.h:192-200, pose_estim.cpp:913-946 -> recoverPose, five-point.cpp:150-338).
     Returns (n_valid, R 3x3, t 3x1, Q n x 3, mask 1 x n uint8).  `mask` (optional, 1 x n or n) is the inlier mask
