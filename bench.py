@@ -884,7 +884,7 @@ def measure_tf32_peak(torch, dev):
 def bench_next_rows(g):
     import datagen_gms, datagen_pose
     from matchinglib_poselib_b200 import matchinglib, poselib
-    from oracle import gms as ogms, arrsac as oarrsac
+    from oracle import gms as ogms, arrsac as oarrsac, usac as ousac
     torch = g.torch
     out = {}
     k1, k2, mt, sz = datagen_gms.scene(n=8000, seed=1, border=True)
@@ -919,6 +919,29 @@ def bench_next_rows(g):
                          ms_per_call=float(np.median(ts) * 1e3), inliers=int(res["count"]), hypotheses=int(res["n_hypotheses"]), device_batches=int(res["n_batches"]),
                          note="latency-bound: every device batch waits for one 5-point solve (~1.2 ms of dependent fp64 work); parity with the reference is statistical",
                          cpu_baseline=cb)
+    # USAC: uniform sampling needs a few hundred hypotheses on this scene, PROSAC a handful
+    sc = datagen_pose.make_scene(10000, 0.5, seed=2)
+    outl = ousac.sampson(sc["E"], sc["p1"], sc["p2"]) >= sc["th"] ** 2
+    order = np.argsort(outl + 0.6 * np.random.default_rng(2).random(len(outl)), kind="stable").astype(np.uint32)
+    for name, idx in (("usac_uniform", None), ("usac_prosac", order)):
+        ts, tc, res, ref = [], [], None, None
+        for i in range(9):
+            torch.cuda.synchronize(); t0 = time.perf_counter()
+            res = poselib.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=i + 1)
+            if i >= 2:
+                ts.append(time.perf_counter() - t0)
+            if ousac.ref_lib() is not None:
+                t0 = time.perf_counter(); ref = ousac.usac(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=i + 1)
+                if i >= 2:
+                    tc.append(time.perf_counter() - t0)
+        cb = None
+        if tc:
+            cb = dict(value=1.0 / float(np.median(tc)), unit="calls/s", cores=1, kind="reference", inliers=int(ref["count"]), hypotheses=int(ref["hyp_count"]),
+                      sample="the reference's own USAC.h + EssentialMatEstimator.h + opengv (oracle/_ref/libusac_ref.so) on the same scene and seeds, median %.1f ms" % (np.median(tc) * 1e3))
+        out[name] = dict(workload="estimateEssentialMatUsac (NISTER, REF_WEIGHTS, no degeneracy test, %s sampling), 10000 correspondences, 50 %% outliers, host buffers in and out" %
+                         ("PROSAC" if idx is not None else "uniform"), value=1.0 / float(np.median(ts)), unit="calls/s", ms_per_call=float(np.median(ts) * 1e3),
+                         inliers=int(res["count"]), hypotheses=int(res["hyp_count"]), device_batches=int(res["n_batches"]), launches=int(res["n_launches"]),
+                         note="latency-bound like ARRSAC: each device batch costs one 5-point solve latency; parity per seed in tests/test_usac_gpu.py", cpu_baseline=cb)
     return out
 
 

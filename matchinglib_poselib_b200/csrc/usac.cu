@@ -140,7 +140,9 @@ usac_solve_kernel(const double4* __restrict__ corr, int n, const int32_t* __rest
     }
     double ee[4][9], tmp[90];
     fivept::null_space_5x9(x1, y1, x2, y2, ee);
-    const int cnt = fivept::solve_from_basis(ee, tmp);
+    // Durand-Kerner with the early exit (every root moved < 2^-40 relative): 0 differing root sets in 10^6 samples
+    // (profiles/r2_solver_early_exit.json), 1.3x less latency -- and latency is what a batch of this schedule costs
+    const int cnt = fivept::solve_from_basis<true>(ee, tmp);
     double* out = models + (size_t)s * 90;
     int valid = 0;
     for (int m = 0; m < cnt; ++m) {
@@ -707,7 +709,10 @@ bool usac_solve(UsacHost& H, UsacDevice& G)
     const unsigned max2 = H.max_hyp / 2, max3 = 2 * H.max_hyp / 3;
     struct Snap { GlibcRand rng; unsigned subset, largest; };
     std::vector<int32_t> samples; std::vector<Snap> snaps;
-    unsigned batch_cap = H.prosac ? 16 : 32;
+    // A batch costs one solver latency (~1.2 ms) whatever its size, so batches are as large as the stopping count allows, bounded
+    // by the size of the inlier bit matrix that comes back (8 MiB) and, before a first model exists, by what is plausibly needed.
+    const unsigned cap_bytes = std::max(16u, (unsigned)((8u << 20) / ((size_t)40 * ((N + 31) / 32))));
+    unsigned batch_cap = std::min(H.prosac ? 64u : 512u, cap_bytes);
     while (H.hyp_count < adaptive && H.hyp_count < H.max_hyp) {
         const unsigned next = H.hyp_count + 1;
         if (next == max2 && H.best == 0) H.th2 *= 1.33;                                   // :367-373 (a batch never runs across these counts)
@@ -779,7 +784,7 @@ bool usac_solve(UsacHost& H, UsacDevice& G)
                 if (usac_trace()) fprintf(stderr, "hyp %u: SPRT stopping count %u\n", H.hyp_count, adaptive);
             }
         }
-        batch_cap = H.best ? 256u : std::min(batch_cap * 2, 512u);
+        batch_cap = std::min(H.best ? 1024u : 512u, cap_bytes);
     }
     return true;
 }
