@@ -175,8 +175,9 @@ usac_bits_kernel(const double* __restrict__ models, const int32_t* __restrict__ 
 }
 
 // ---- local optimisation (USAC::locallyOptimizeSolution, USAC.h:948-1060): one CTA per inner-RANSAC repetition -------------
-constexpr int kLoThreads = 256;
+constexpr int kLoThreads = 512;
 constexpr int kLoWarps = kLoThreads / 32;
+constexpr int kLoGroups = kLoThreads / 45;          // 11 groups of 45 threads: thread (g, k) sums product k of the covariance over a tile's rows g, g + 11, ...
 constexpr int kLoMaxSample = 16;
 
 struct LoParams {
@@ -185,79 +186,126 @@ struct LoParams {
     double delta, epsilon, A;              // the SPRT in force (evaluateModel uses, never updates, them)
     NormT T;
 };
-struct LoOut { double E[9]; int status, count, shift, n_eval; };     // status 0: the repetition reached its final evaluation and passed
-
-// Cyclic two-sided Jacobi on a symmetric 9 x 9 matrix (the covariance FTools::formCovMat builds): eigenvector of the
-// smallest eigenvalue, which is what generateRefinedModel takes from MathTools::svdu1v (EssentialMatEstimator.h:566-583).
-__device__ void sym9_smallest_eigvec(double (&C)[9][9], double (&x)[9])
-{
-    double V[9][9];
-    for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) V[i][j] = i == j ? 1.0 : 0.0;
-    for (int sweep = 0; sweep < 30; ++sweep) {
-        double off = 0, diag = 0;
-        for (int i = 0; i < 9; ++i) { diag += C[i][i] * C[i][i]; for (int j = i + 1; j < 9; ++j) off += C[i][j] * C[i][j]; }
-        if (off <= 1e-32 * diag) break;
-        for (int p = 0; p < 8; ++p)
-            for (int q = p + 1; q < 9; ++q) {
-                const double apq = C[p][q];
-                if (apq == 0.0) continue;
-                const double theta = (C[q][q] - C[p][p]) / (2.0 * apq);
-                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
-                for (int k = 0; k < 9; ++k) { const double akp = C[k][p], akq = C[k][q]; C[k][p] = c * akp - s * akq; C[k][q] = s * akp + c * akq; }
-                for (int k = 0; k < 9; ++k) { const double apk = C[p][k], aqk = C[q][k]; C[p][k] = c * apk - s * aqk; C[q][k] = s * apk + c * aqk; }
-                for (int k = 0; k < 9; ++k) { const double vkp = V[k][p], vkq = V[k][q]; V[k][p] = c * vkp - s * vkq; V[k][q] = s * vkp + c * vkq; }
-            }
-    }
-    int j = 0;
-    for (int i = 1; i < 9; ++i) if (C[i][i] < C[j][j]) j = i;                             // :570-577
-    for (int i = 0; i < 9; ++i) x[i] = V[i][j];
-}
+struct LoOut { double E[9]; int status, count, shift, n_eval; long long clk[4]; };     // status 0: the repetition reached its final evaluation and passed
 
 struct LoShared {
     double E[9], F[9];                     // models_denorm_[0], models_[0]
-    double acc[kLoWarps][45];
+    double part[kLoGroups][45];
+    double C[45];                          // upper triangle of the 9 x 9 covariance, row-major
     int cnt[kLoWarps];
     int flag, tested;
+    double pa[33], pb[33];                 // (delta / epsilon)^i, ((1 - delta) / (1 - epsilon))^o
+    long long clk[4];                      // phase clocks (thread 0): fit accumulation, eigen + projection, errors, SPRT walk
 };
+
+__host__ __device__ constexpr int tri9(int a, int b) { return a * 9 - (a * (a - 1)) / 2 + (b - a); }     // a <= b
+
+__device__ __forceinline__ double half_warp_sum(double v)     // called by lanes 0..15 only; identical in all of them (control flow stays uniform)
+{
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) v += __shfl_xor_sync(0x0000ffffu, v, o);
+    return v;
+}
+
+// Eigenvector of the smallest eigenvalue of the symmetric 9 x 9 covariance in S.C -- what generateRefinedModel takes from
+// MathTools::svdu1v (EssentialMatEstimator.h:566-583) -- by a one-sided Jacobi SVD run by lanes 0..15 of a warp: lane i holds row i of every
+// column (a symmetric positive semi-definite matrix' right singular vectors are its eigenvectors).  Result in S.F (unnormalised F).
+__device__ void warp_smallest_eigvec(LoShared& S)
+{
+    const int lane = threadIdx.x & 31;
+    double U[9], V[9];
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {
+        U[j] = lane < 9 ? S.C[lane <= j ? tri9(lane, j) : tri9(j, lane)] : 0.0;
+        V[j] = lane == j ? 1.0 : 0.0;
+    }
+    // Round-robin ordering: in round r the four disjoint column pairs ((r + k) mod 9, (r - k) mod 9), k = 1..4, are rotated
+    // together -- their twelve reductions and four chains of scalar fp64 (a divide, a square root, a reciprocal square root
+    // each) overlap instead of queueing behind one another; 9 rounds visit all 36 pairs once.
+    for (int sweep = 0; sweep < 40; ++sweep) {
+        bool rotated = false;
+#pragma unroll
+        for (int r = 0; r < 9; ++r) {
+            double a[4], b[4], c[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int p = (r + k + 1) % 9, q = (r + 8 - k) % 9;
+                a[k] = U[p] * U[p]; b[k] = U[q] * U[q]; c[k] = U[p] * U[q];
+            }
+#pragma unroll
+            for (int o = 8; o >= 1; o >>= 1)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    a[k] += __shfl_xor_sync(0x0000ffffu, a[k], o); b[k] += __shfl_xor_sync(0x0000ffffu, b[k], o); c[k] += __shfl_xor_sync(0x0000ffffu, c[k], o);
+                }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int p = (r + k + 1) % 9, q = (r + 8 - k) % 9;
+                const bool skip = c[k] * c[k] <= 4.930380657631324e-32 * (a[k] * b[k]) || fabs(c[k]) <= 1e-300;      // |c| <= eps * sqrt(a b)
+                rotated |= !skip;
+                const double tau = b[k] - a[k];
+                const double t = skip ? 0.0 : (tau >= 0 ? 2.0 : -2.0) * c[k] / (fabs(tau) + sqrt(tau * tau + 4.0 * c[k] * c[k]));
+                const double cs = rsqrt(1.0 + t * t), sn = cs * t;
+                const double up = U[p], uq = U[q], vp = V[p], vq = V[q];
+                U[p] = cs * up - sn * uq; U[q] = sn * up + cs * uq;
+                V[p] = cs * vp - sn * vq; V[q] = sn * vp + cs * vq;
+            }
+        }
+        if (!rotated) break;
+    }
+    double wbest = 0; int best = 0;
+#pragma unroll
+    for (int j = 0; j < 9; ++j) { const double w = half_warp_sum(U[j] * U[j]); if (j == 0 || w < wbest) { wbest = w; best = j; } }     // :570-577
+    double x = 0;
+#pragma unroll
+    for (int j = 0; j < 9; ++j) if (j == best) x = V[j];
+    if (lane < 9) S.F[lane] = x;
+}
 
 // covariance of the (weighted) data-matrix rows of the selected correspondences -> models_[0], models_denorm_[0]
 // (generateRefinedModel, REFINE_WEIGHTS).  Selection: sample list (sel_n > 0), else the first `limit` correspondences in
 // index order with err < thr (USAC.h:1019-1021 passes temp_inliers, the count at the inlier threshold, as numPoints for a
 // list found at a looser threshold).  Returns the number of points used; < 5 leaves the model untouched (:535-537).
-__device__ int lo_fit(LoShared& S, const LoParams& P, const double4* __restrict__ corr, const double* __restrict__ err,
+// A tile of kLoThreads rows goes through shared memory (`rows`); thread (g, k) accumulates product k over the tile.
+__device__ int lo_fit(LoShared& S, const LoParams& P, const double4* __restrict__ corr, const double* __restrict__ err, double* rows,
                       const int32_t* sel, int sel_n, double thr, int limit, bool weighted)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    double acc[45];
-#pragma unroll
-    for (int k = 0; k < 45; ++k) acc[k] = 0.0;
+    const int g = tid / 45, k = tid - g * 45;
+    const bool summer = g < kLoGroups;
+    int ka = 0, kb = 0;
+    { int r = k; for (ka = 0; ka < 9; ++ka) { if (r < 9 - ka) { kb = ka + r; break; } r -= 9 - ka; } }
     double F[9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) F[k] = S.F[k];
-    int used = 0;
-    auto add = [&](int i) {
-        double x1, y1, x2, y2;
-        normalise_pt(P.T, corr[i], x1, y1, x2, y2);
-        double w = 1.0;
-        if (weighted) {                                                                    // findWeights (EssentialMatEstimator.h:2376-2389)
-            const double rxc = F[0] * x2 + F[3] * y2 + F[6], ryc = F[1] * x2 + F[4] * y2 + F[7];
-            const double rx = F[0] * x1 + F[1] * y1 + F[2], ry = F[3] * x1 + F[4] * y1 + F[5];
-            w = 1.0 / sqrt(rxc * rxc + ryc * ryc + rx * rx + ry * ry);
+    for (int j = 0; j < 9; ++j) F[j] = S.F[j];
+    double acc = 0.0;
+    auto put_row = [&](int i, bool take) {
+        double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        if (take) {
+            double x1, y1, x2, y2;
+            normalise_pt(P.T, corr[i], x1, y1, x2, y2);
+            double w = 1.0;
+            if (weighted) {                                                                // findWeights (EssentialMatEstimator.h:2376-2389)
+                const double rxc = F[0] * x2 + F[3] * y2 + F[6], ryc = F[1] * x2 + F[4] * y2 + F[7];
+                const double rx = F[0] * x1 + F[1] * y1 + F[2], ry = F[3] * x1 + F[4] * y1 + F[5];
+                w = 1.0 / sqrt(rxc * rxc + ryc * ryc + rx * rx + ry * ry);
+            }
+            r[0] = x2 * x1 * w; r[1] = x2 * y1 * w; r[2] = x2 * w; r[3] = y2 * x1 * w; r[4] = y2 * y1 * w; r[5] = y2 * w; r[6] = x1 * w; r[7] = y1 * w; r[8] = w;   // computeDataMatrix
         }
-        const double r[9] = {x2 * x1 * w, x2 * y1 * w, x2 * w, y2 * x1 * w, y2 * y1 * w, y2 * w, x1 * w, y1 * w, w};   // computeDataMatrix
-        int k = 0;
 #pragma unroll
-        for (int a = 0; a < 9; ++a)
-#pragma unroll
-            for (int b = a; b < 9; ++b) acc[k++] += r[a] * r[b];
+        for (int j = 0; j < 9; ++j) rows[tid * 9 + j] = r[j];
     };
+    int used = 0;
+    const long long c0 = clock64();
     if (sel_n > 0) {
-        if (tid < sel_n) add(sel[tid]);
+        put_row(tid < sel_n ? sel[tid] : 0, tid < sel_n);
+        __syncthreads();
+        if (summer) for (int pp = g; pp < sel_n; pp += kLoGroups) acc += rows[pp * 9 + ka] * rows[pp * 9 + kb];
+        __syncthreads();
         used = sel_n;
     } else {
         int base = 0;
-        for (int t0 = 0; t0 < P.n; t0 += kLoThreads) {
+        for (int t0 = 0; t0 < P.n && base < limit; t0 += kLoThreads) {
             const int i = t0 + tid;
             const bool p = i < P.n && err[i] < thr;
             const unsigned m = __ballot_sync(0xffffffffu, p);
@@ -267,34 +315,33 @@ __device__ int lo_fit(LoShared& S, const LoParams& P, const double4* __restrict_
 #pragma unroll
             for (int w = 0; w < kLoWarps; ++w) { const int c = S.cnt[w]; total += c; if (w < warp) before += c; }
             const int rank = base + before + __popc(m & ((1u << lane) - 1u));
-            if (p && rank < limit) add(i);
+            put_row(i, p && rank < limit);
             base += total;
+            __syncthreads();
+            const int tile_n = min(kLoThreads, P.n - t0);
+            if (summer) for (int pp = g; pp < tile_n; pp += kLoGroups) acc += rows[pp * 9 + ka] * rows[pp * 9 + kb];
             __syncthreads();
         }
         used = min(base, limit);
     }
     if (used < 5) return used;
-#pragma unroll
-    for (int k = 0; k < 45; ++k) {
-        double v = acc[k];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) S.acc[warp][k] = v;
-    }
+    const long long c1 = clock64();
+    if (summer) S.part[g][k] = acc;
+    __syncthreads();
+    if (tid < 45) { double v = 0; for (int gg = 0; gg < kLoGroups; ++gg) v += S.part[gg][tid]; S.C[tid] = v; }
+    __syncthreads();
+    if (tid < 16) warp_smallest_eigvec(S);
     __syncthreads();
     if (tid == 0) {
-        double C[9][9], f[9];
-        int k = 0;
-        for (int a = 0; a < 9; ++a) for (int b = a; b < 9; ++b) { double v = 0; for (int w = 0; w < kLoWarps; ++w) v += S.acc[w][k]; C[a][b] = C[b][a] = v; ++k; }
-        sym9_smallest_eigvec(C, f);
         // FTools::singulF (FundmatrixFunctions.cpp:334-360): drop the smallest singular value, F - (F v3) v3^T
         double F0[3][3], v[3];
-        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) F0[a][b] = f[3 * a + b];
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) F0[a][b] = S.F[3 * a + b];
         jacobi_null_vector<3>(F0, v);
         double Fv[3];
         for (int a = 0; a < 3; ++a) Fv[a] = F0[a][0] * v[0] + F0[a][1] * v[1] + F0[a][2] * v[2];
         for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) S.F[3 * a + b] = F0[a][b] - Fv[a] * v[b];
         denormalise_model(P.T, S.F, S.E);
+        S.clk[0] += c1 - c0; S.clk[1] += clock64() - c1;
     }
     __syncthreads();
     return used;
@@ -309,6 +356,7 @@ __device__ bool lo_eval(LoShared& S, const LoParams& P, const double4* __restric
     double E[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) E[k] = S.E[k];
+    const long long c0 = clock64();
     int c = 0;
     for (int i = tid; i < P.n; i += kLoThreads) { const double e = usac_err(E, corr[i]); err[i] = e; c += e < P.th2 ? 1 : 0; }
 #pragma unroll
@@ -324,20 +372,42 @@ __device__ bool lo_eval(LoShared& S, const LoParams& P, const double4* __restric
     }
     __syncthreads();
     if (tid == 0) {
+        const long long c1 = clock64();
         const double fa = P.delta / P.epsilon, fb = (1 - P.delta) / (1 - P.epsilon), floor_v = DBL_EPSILON * 10;
+        // The bit-serial walk of evaluateModel for the first words (where lam starts at 1 and most rejections happen), then a
+        // word-level pass: with i inliers and o outliers in a word, no value inside the word exceeds lam_in * fb^o and the value
+        // after it is at most max(lam_in * fa^i * fb^o, floor * fb^o) (a clamp inside restarts from the floor).  If that bound
+        // never passes A the test accepts -- the common case for a refitted model -- at W steps instead of n; if it does,
+        // the bit-serial walk resumes from where it stopped.
         double lam = 1.0;
         int tested = P.n, good = 1;
-        for (int w = 0; w < P.W && good; ++w) {
-            unsigned word = sseq[w];
-            const int nb = min(32, P.n - 32 * w);
-            if (lam == floor_v && fa <= 0.1 && nb == 32 && word == 0xffffffffu) continue;   // floor * fa <= DBL_EPSILON: 32 inliers leave it at the floor
-            for (int b = 0; b < nb; ++b, word >>= 1) {
-                lam *= (word & 1u) ? fa : fb;
-                if (lam <= DBL_EPSILON) lam = floor_v;
-                if (lam > P.A) { good = 0; tested = 32 * w + b + 1; break; }
+        auto walk = [&](int w0, int w1) {
+            for (int w = w0; w < w1 && good; ++w) {
+                unsigned word = sseq[w];
+                const int nb = min(32, P.n - 32 * w);
+                for (int b = 0; b < nb; ++b, word >>= 1) {
+                    lam *= (word & 1u) ? fa : fb;
+                    if (lam <= DBL_EPSILON) lam = floor_v;
+                    if (lam > P.A) { good = 0; tested = 32 * w + b + 1; break; }
+                }
             }
+        };
+        const int head = min(P.W, 4);
+        walk(0, head);
+        if (good && head < P.W) {
+            double ub = lam;
+            bool sure = true;
+            for (int w = head; w < P.W; ++w) {
+                const int nb = min(32, P.n - 32 * w);
+                const int o = nb - __popc(sseq[w]), i = nb - o;
+                const double up = S.pb[o];
+                if (ub * up * 1.000001 > P.A) { sure = false; break; }
+                ub = fmax(ub * S.pa[i] * up, floor_v * up) * 1.000001;
+            }
+            if (!sure) walk(head, P.W);
         }
         S.flag = good; S.tested = tested;
+        S.clk[2] += c1 - c0; S.clk[3] += clock64() - c1;
     }
     __syncthreads();
     ++n_eval;
@@ -355,22 +425,26 @@ __global__ void __launch_bounds__(kLoThreads)
 usac_lo_kernel(const double4* __restrict__ corr, const int32_t* __restrict__ pool, const int32_t* __restrict__ samples /* [reps][kLoMaxSample] */,
                LoParams P, double* __restrict__ err_all /* [reps][n] */, LoOut* __restrict__ out, uint32_t* __restrict__ bits_out /* [reps][W] */)
 {
-    extern __shared__ uint32_t sseq[];
+    extern __shared__ double lo_smem[];                 // kLoThreads x 9 row tile, then W words of SPRT bits
+    double* rows = lo_smem;
+    uint32_t* sseq = (uint32_t*)(lo_smem + kLoThreads * 9);
     __shared__ LoShared S;
     const int rep = blockIdx.x, tid = threadIdx.x;
     double* err = err_all + (size_t)rep * P.n;
     const int32_t* sel = samples + rep * kLoMaxSample;
     int cursor = P.pool_start, n_eval = 0, status = 0, cnt = 0;
     if (tid < 9) { S.E[tid] = 0; S.F[tid] = 0; }
+    if (tid < 4) S.clk[tid] = 0;
+    if (tid < 33) { S.pa[tid] = pow(P.delta / P.epsilon, (double)tid); S.pb[tid] = pow((1 - P.delta) / (1 - P.epsilon), (double)tid); }
     __syncthreads();
     const double thr_lo = P.mult * P.th2, step = (thr_lo - P.th2) / P.n_steps;           // USAC.h:989-990
     do {
-        lo_fit(S, P, corr, err, sel, P.sample_size, 0.0, 0, false);                       // :999 (sample_size >= 5 is the caller's check)
+        lo_fit(S, P, corr, err, rows, sel, P.sample_size, 0.0, 0, false);                       // :999 (sample_size >= 5 is the caller's check)
         if (!lo_eval(S, P, corr, pool, err, sseq, cursor, &cnt, n_eval)) { status = 1; break; }     // :1004-1007
-        if (lo_fit(S, P, corr, err, nullptr, 0, thr_lo, INT_MAX, false) < 5) { status = 2; break; } // :1008-1018
+        if (lo_fit(S, P, corr, err, rows, nullptr, 0, thr_lo, INT_MAX, false) < 5) { status = 2; break; } // :1008-1018
         for (int j = 0; j < P.n_steps; ++j) {                                              // :1022-1036
             if (!lo_eval(S, P, corr, pool, err, sseq, cursor, &cnt, n_eval)) continue;
-            lo_fit(S, P, corr, err, nullptr, 0, thr_lo - (j + 1) * step, cnt, true);
+            lo_fit(S, P, corr, err, rows, nullptr, 0, thr_lo - (j + 1) * step, cnt, true);
         }
         if (!lo_eval(S, P, corr, pool, err, sseq, cursor, &cnt, n_eval)) { status = 3; break; }     // :1039-1043
     } while (false);
@@ -385,6 +459,7 @@ usac_lo_kernel(const double4* __restrict__ corr, const int32_t* __restrict__ poo
         for (int k = 0; k < 9; ++k) o.E[k] = S.E[k];
         int shift = cursor - P.pool_start; if (shift < 0) shift += P.n;
         o.status = status; o.count = cnt; o.shift = shift; o.n_eval = n_eval;
+        for (int k = 0; k < 4; ++k) o.clk[k] = S.clk[k];
         out[rep] = o;
     }
 }
@@ -648,9 +723,11 @@ struct UsacDevice {
         char* Hs = nullptr;
         const size_t h_total = 1024 + (total - o_o);
         if ((err = mpl_stage2_ensure(h_total, (void**)&Hs))) return;
+        const size_t lo_smem_bytes = (size_t)kLoThreads * 9 * 8 + (size_t)W * 4;
+        ck(cudaFuncSetAttribute(usac_lo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lo_smem_bytes));
         memcpy(Hs, samples, (size_t)reps * kLoMaxSample * 4);
         ck(cudaMemcpyAsync(D + o_s, Hs, (size_t)reps * kLoMaxSample * 4, cudaMemcpyHostToDevice, st));
-        usac_lo_kernel<<<reps, kLoThreads, (size_t)W * 4, st>>>(d_corr, d_pool, (const int32_t*)(D + o_s), P, (double*)(D + o_e), (LoOut*)(D + o_o), (uint32_t*)(D + o_b));
+        usac_lo_kernel<<<reps, kLoThreads, lo_smem_bytes, st>>>(d_corr, d_pool, (const int32_t*)(D + o_s), P, (double*)(D + o_e), (LoOut*)(D + o_o), (uint32_t*)(D + o_b));
         ck(cudaGetLastError()); mpl_count_launch();
         ck(cudaMemcpyAsync(Hs + 1024, D + o_o, total - o_o, cudaMemcpyDeviceToHost, st));
         ck(cudaStreamSynchronize(st));
@@ -687,7 +764,7 @@ unsigned locally_optimise(UsacHost& H, UsacDevice& G, unsigned best_inliers)
     unsigned lo_inliers = best_inliers, shift = 0;
     for (int r = 0; r < reps; ++r) {
         shift += (unsigned)out[r].shift;
-        if (usac_trace()) fprintf(stderr, "  LO rep %d: status %d count %d evals %d shift %d\n", r, out[r].status, out[r].count, out[r].n_eval, out[r].shift);
+        if (usac_trace()) fprintf(stderr, "  LO rep %d: status %d count %d evals %d shift %d; clocks fit %lld eig %lld err %lld sprt %lld\n", r, out[r].status, out[r].count, out[r].n_eval, out[r].shift, out[r].clk[0], out[r].clk[1], out[r].clk[2], out[r].clk[3]);
         if (out[r].status == 0 && (unsigned)out[r].count > lo_inliers) {                   // :1045-1050 storeSolution(0, lo_inliers)
             lo_inliers = (unsigned)out[r].count;
             H.best = lo_inliers;
@@ -831,6 +908,7 @@ extern "C" int mpl_usac5pt(const double* p1, const double* p2, int n, const unsi
     H.prosac_beta = prm->prosac_beta; H.prosac_non_rand_conf = prm->prosac_non_rand_conf;
     H.tM = prm->sprt_tM; H.mS = prm->sprt_mS; H.delta = prm->sprt_delta; H.epsilon = prm->sprt_epsilon;
     H.lo_sample = (unsigned)prm->lo_inner_sample_size; H.lo_reps = (unsigned)prm->lo_inner_reps; H.lo_steps = (unsigned)prm->lo_num_steps; H.lo_mult = prm->lo_threshold_multiplier; H.lo_mode = prm->lo_mode;
+    if (n > (1 << 20)) { mpl_set_error("mpl_usac5pt: at most 2^20 correspondences"); return MPL_ERR_LIMIT; }
     if (n < 5 || (H.prosac && (unsigned)n < H.prosac_min_stop_len)) return MPL_OK;         // solve() == false: res->ok stays 0
     H.rng.seed(prm->seed);
     // initDataUSAC (USAC.h:274-336): PROSAC tables, the first SPRT design, the evaluation pool (std::random_shuffle over rand())
