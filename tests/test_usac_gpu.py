@@ -131,3 +131,41 @@ def test_usac_deterministic_and_parameter_checks(P):
         P.usac5pt(sc["p1"], sc["p2"], sc["th"], degeneracy=2)
     with pytest.raises(_lib.MplError):
         P.usac5pt(sc["p1"], sc["p2"], sc["th"], estimator="EIG_KNEIP")
+
+
+def test_estimateEssentialOrPoseUSAC_mirror(P):
+    """The host mirror of poselib::estimateEssentialOrPoseUSAC: SPRT / PROSAC start values from matches and keypoints
+    (pose_estim.cpp:1810-1981), PROSAC order from the match distances, the served configurations only."""
+    from matchinglib_poselib_b200 import _lib, matchinglib
+    sc = datagen_pose.make_scene(2000, 0.4, seed=61)
+    n = 2000
+    inl = ousac.sampson(sc["E"], sc["p1"], sc["p2"]) < sc["th"] ** 2
+    rng = np.random.default_rng(61)
+    m = np.zeros(n, matchinglib.DMATCH_DTYPE)
+    m["queryIdx"] = np.arange(n); m["trainIdx"] = np.arange(n); m["imgIdx"] = -1
+    m["distance"] = np.where(inl, rng.uniform(10, 60, n), rng.uniform(30, 90, n)).astype(np.float32)     # inliers tend to match better
+    kp1 = sc["p1"] * 800.0 + np.array([696.0, 256.0]); kp2 = sc["p2"] * 800.0 + np.array([696.0, 256.0])
+    cfg = P.ConfigUSAC(estimator=P.POSE_NISTER, refinealg=P.REF_WEIGHTS, degeneracyCheck=P.DEGEN_NO_CHECK, matches=m, keypoints1=kp1,
+                       keypoints2=kp2, th_pixels=1.6, imgSize=(1392, 512), nrMatchesVfcFiltered=int(0.55 * n), seed=4)
+    d = P.estimateSprtDeltaInit(m, kp1, kp2, 1.6, (1392, 512))
+    assert 0.001 <= d <= 1.0 / 6 + 1e-12 and P.estimateSprtEpsilonInit(m, cfg.nrMatchesVfcFiltered) == 0.4
+    order = P.getSortedMatchIdx(m)
+    assert np.all(np.diff(m["distance"][order]) >= 0)
+    code, E, degenerate, inliers, info = P.estimateEssentialOrPoseUSAC(sc["p1"], sc["p2"], sc["th"], cfg)
+    assert code == 0 and not degenerate and inliers.shape == (1, n) and inliers.sum() == info["count"] >= 0.95 * inl.sum()
+    assert _ed(E, sc["E"]) < 5e-2 and abs(info["sprt_delta"]) > 0
+    o = ousac.usac(sc["p1"], sc["p2"], sc["th"], sorted_idx=order, seed=4, prosac_beta=d, sprt_delta=d, sprt_epsilon=0.4)
+    if o is not None:
+        g1 = P.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=order, seed=4, prosac_beta=d, sprt_delta=d, sprt_epsilon=0.4, lo_mode=1)
+        assert (o["count"], o["hyp_count"]) in ((info["count"], info["hyp_count"]), (g1["count"], g1["hyp_count"])) or \
+            abs(o["count"] - info["count"]) <= 0.15 * inl.sum()
+    cfg.matches = None; cfg.automaticSprtInit = P.SPRT_DEFAULT_INIT                        # no matches: uniform sampling, default start values
+    code, E, _, inliers, info = P.estimateEssentialOrPoseUSAC(sc["p1"], sc["p2"], sc["th"], cfg)
+    assert code == 0 and inliers.sum() >= 0.95 * inl.sum()
+    for bad in (dict(estimator=P.POSE_EIG_KNEIP), dict(refinealg=P.REF_8PT_PSEUDOHUBER), dict(degeneracyCheck=P.DEGEN_USAC_INTERNAL)):
+        c = P.ConfigUSAC(estimator=P.POSE_NISTER, refinealg=P.REF_WEIGHTS, degeneracyCheck=P.DEGEN_NO_CHECK, automaticSprtInit=0)
+        for k, v in bad.items():
+            setattr(c, k, v)
+        with pytest.raises(_lib.MplError):
+            P.estimateEssentialOrPoseUSAC(sc["p1"], sc["p2"], sc["th"], c)
+    assert P.estimateEssentialOrPoseUSAC(sc["p1"][:4], sc["p2"][:4], sc["th"], cfg)[0] == -2      # "USAC failed!"
