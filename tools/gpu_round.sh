@@ -10,12 +10,13 @@ head -c 1500 gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 fi
 if [ -n "$NCU" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-for k in l2_tc_rank_kernel "hamming_top2_kernel<2>" "hamming_top2_kernel<4>" sampson_score_kernel fivept_solve_kernel score_slots_kernel solve_chunk_kernel pair_gather_kernel refit_basis_kernel gms_filter_kernel arrsac_bits_kernel; do
+# kernel names are matched on the demangled name (template arguments included); NCU_KERNELS overrides the list
+for k in ${NCU_KERNELS:-"hamming_top2_kernel<2>" "hamming_top2_kernel<4>" l2_tc_rank_kernel sampson_score_kernel score_slots_kernel usac_lo_kernel usac_solve_kernel usac_bits_kernel}; do
   f=$(echo $k | tr -d '<>')
-  timeout 600 ncu --set full --clock-control none --import-source on -k "regex:$k" -s 1 -c 1 -f -o gpurun_out/full_$f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_$f.log 2>&1; echo "ncu full $k rc=$?"
+  timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:$k" -s 1 -c 1 -f -o gpurun_out/full_$f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_$f.log 2>&1; echo "ncu full $k rc=$?"
 done
 # the tf32 mode of the ranking kernel: the 3rd .. launches of l2_tc_rank_kernel belong to parts.l2_tf32_c2 (after the C2 headline's)
-timeout 600 ncu --set full --clock-control none --import-source on -k "regex:l2_tc_rank_kernel" -s 40 -c 1 -f -o gpurun_out/full_l2_tc_rank_kernel_tf32 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_tc_tf32.log 2>&1; echo "ncu full tf32 rc=$?"
+[ -n "$NCU_TF32" ] && timeout 600 ncu --set full --clock-control none --import-source on -k "regex:l2_tc_rank_kernel" -s 40 -c 1 -f -o gpurun_out/full_l2_tc_rank_kernel_tf32 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_tc_tf32.log 2>&1; echo "ncu full tf32 rc=$?"
 fi
 if [ -n "$REF" ]; then
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "reference arm rc=$?"
