@@ -224,6 +224,17 @@ int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const 
 int mpl_arrsac_set_seed(unsigned long long prosac_state, unsigned long long random_state);
 int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refine, double* E, uint8_t* mask, int* n_inl,
                   int* n_hypotheses, int* n_batches);
+/* mpl_vfc_filter replaces filterWithVFC (MP/matchinglib/source/vfcMatches.cpp:49-86 -> class VFC, source/vfc.cpp, SparseVFC), the
+ *   post-filter matchinglib::getMatches applies with VFCrefine = true (source/matchers.cpp:721-733).  kp1 / kp2: keypoint records
+ *   with the cv::Point2f pt at offset 0 (cv::KeyPoint: stride 28); matches: cv::DMatch records.  Outputs: keep[n_matches] (1 = the
+ *   match is in matches_out), *n_keep, *vfc_code = filterWithVFC's return value (0 ok, -1 fewer than 5 matches -- nothing kept,
+ *   -2 fewer than 10 % kept: "Maybe VFC failed"), *n_iterations (may be NULL) = EM iterations run.  The set-up (normalisation,
+ *   the rand()-driven choice of 16 control points) runs on the host as written, the kernel matrix and the EM iterations in one
+ *   kernel launch.  Results agree with the reference within float tolerance (csrc/vfc.cu).  mpl_vfc_set_seed restarts the
+ *   calling thread's rand() stream (the reference draws from the process' state; a fresh process is srand(1)). */
+int mpl_vfc_set_seed(unsigned seed);
+int mpl_vfc_filter(const void* kp1, int n1, size_t kp_stride1, const void* kp2, int n2, size_t kp_stride2, const mpl_dmatch* matches,
+                   int n_matches, uint8_t* keep, int* n_keep, int* vfc_code, int* n_iterations);
 /* mpl_usac5pt replaces estimateEssentialMatUsac (MP/poselib/source/usac/usac_estimations.cpp:283-735) -- the robust
  *   estimator behind poselib::estimateEssentialOrPoseUSAC (pose_estim.cpp:1737), the default RobMethod of poselib-test:
  *   USAC<EssentialMatEstimator>::solve (MP/poselib/include/usac/estimators/USAC.h:345-612; uniform or PROSAC sampling,

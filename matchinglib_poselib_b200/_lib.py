@@ -88,6 +88,8 @@ SIGNATURES = {
     "mpl_estimate_essential_api": (c_int, [c_void_p, c_void_p, c_int, c_char_p, c_double, c_int, c_void_p, c_void_p, c_void_p]),
     "mpl_arrsac_set_seed": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong]),
     "mpl_arrsac5pt": (c_int, [c_void_p, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "mpl_vfc_set_seed": (c_int, [ctypes.c_uint]),
+    "mpl_vfc_filter": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_usac_params_default": (None, [c_void_p, c_double]),
     "mpl_usac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_usac_rand_stream": (c_int, [ctypes.c_uint, c_int, c_void_p]),

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libmplb200.so")
-SOURCES = ["capi.cu", "knn_hamming.cu", "knn_hamming_static.cu", "knn_l2_exact.cu", "knn_l2_tc.cu", "ransac5pt.cu", "ransac_batch.cu", "pose_host.cu", "recover_pose.cu", "pipeline.cu", "gms.cu", "arrsac.cu", "usac.cu"]
+SOURCES = ["capi.cu", "knn_hamming.cu", "knn_hamming_static.cu", "knn_l2_exact.cu", "knn_l2_tc.cu", "ransac5pt.cu", "ransac_batch.cu", "pose_host.cu", "recover_pose.cu", "pipeline.cu", "gms.cu", "arrsac.cu", "usac.cu", "vfc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",            # fp contraction is opted into per expression (__fma_rn / fma()); parity code relies on it being off

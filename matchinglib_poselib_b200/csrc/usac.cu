@@ -45,6 +45,7 @@
 #include "mpl_ransac.h"
 #include "small_svd.cuh"
 #include "fivept_device.cuh"
+#include "glibc_rand.h"
 #include "../../include/mplb200.h"
 
 #include <algorithm>
@@ -467,34 +468,6 @@ usac_lo_kernel(const double4* __restrict__ corr, const int32_t* __restrict__ poo
 // ------------------------------------------------------------------------------------------------------------------
 // host side: the reference's random stream, samplers, SPRT, stopping rules and USAC::solve over device batches
 // ------------------------------------------------------------------------------------------------------------------
-
-// glibc's srand() / rand() (TYPE_3 additive feedback generator, x^31 + x^3 + 1): the reference seeds it in
-// estimateEssentialMatUsac (usac_estimations.cpp:328) and draws every sample and the evaluation-pool shuffle from it.
-struct GlibcRand {
-    uint32_t st[31]; int f = 3, r = 0;
-    void seed(unsigned s)
-    {
-        if (s == 0) s = 1;
-        int32_t word = (int32_t)s;
-        st[0] = (uint32_t)word;
-        for (int i = 1; i < 31; ++i) {
-            const long hi = word / 127773, lo = word % 127773;
-            long w = 16807 * lo - 2836 * hi;
-            if (w < 0) w += 2147483647;
-            word = (int32_t)w; st[i] = (uint32_t)word;
-        }
-        f = 3; r = 0;
-        for (int i = 0; i < 310; ++i) next();
-    }
-    int next()
-    {
-        st[f] += st[r];
-        const int res = (int)(st[f] >> 1);
-        if (++f >= 31) f = 0;
-        if (++r >= 31) r = 0;
-        return res;
-    }
-};
 
 // generateUniformRandomSample (USAC.h:620-636)
 void uniform_sample(GlibcRand& g, unsigned data_size, unsigned sample_size, unsigned* sample)
