@@ -32,6 +32,23 @@
 
 #include "mplb200.h"
 
+// matchinglib/include/matchinglib/vfcMatches.h (global namespace in the reference), source/vfcMatches.cpp:49-86 -> class VFC
+// (source/vfc.cpp, SparseVFC): 0 ok, -1 too few matches for refinement, -2 "maybe VFC failed" (fewer than 10 % kept).
+inline int filterWithVFC(std::vector<cv::KeyPoint> const& keypL, std::vector<cv::KeyPoint> const& keypR,
+                         std::vector<cv::DMatch> const& matches_in, std::vector<cv::DMatch>& matches_out)
+{
+    static_assert(sizeof(cv::DMatch) == sizeof(mpl_dmatch), "cv::DMatch layout");
+    matches_out.clear();
+    std::vector<uchar> keep(matches_in.size() + 1);
+    int n_keep = 0, code = 0;
+    const int rc = mpl_vfc_filter(keypL.data(), (int)keypL.size(), sizeof(cv::KeyPoint), keypR.data(), (int)keypR.size(), sizeof(cv::KeyPoint),
+                                  reinterpret_cast<const mpl_dmatch*>(matches_in.data()), (int)matches_in.size(), keep.data(), &n_keep, &code, nullptr);
+    if (rc < 0) CV_Error(cv::Error::StsError, mpl_last_error());
+    if (code == -1) { std::cout << "Too less matches for refinement with VFC!" << std::endl; return -1; }
+    for (size_t i = 0; i < matches_in.size(); ++i) if (keep[i]) matches_out.push_back(matches_in[i]);
+    return code;
+}
+
 namespace matchinglib {
 
 // matchers.cpp:115-736, LINEAR (:525-714) and BRUTEFORCENMS (:476-519) branches.
@@ -45,10 +62,6 @@ inline int getMatches(const std::vector<cv::KeyPoint>& keypoints1, const std::ve
     (void)imgSi; (void)descriptor_name; (void)idxPars_NMSLIB; (void)queryPars_NMSLIB;
     CV_Assert(descriptors1.type() == descriptors2.type());                      // matchers.cpp:119
     finalMatches.clear();                                                        // matchers.cpp:135
-    if (VFCrefine) {                                                             // :722-733 optional post-filter, not on the hot path
-        std::cout << "VFC refinement is not served by the B200 hot path." << std::endl;
-        return -2;
-    }
     static_assert(sizeof(cv::DMatch) == sizeof(mpl_dmatch), "cv::DMatch layout");
     std::vector<cv::DMatch> out(descriptors1.rows > 0 ? (size_t)descriptors1.rows : 1);
     int n_out = 0;
@@ -62,6 +75,11 @@ inline int getMatches(const std::vector<cv::KeyPoint>& keypoints1, const std::ve
     if (err == MPL_ERR_ASSERT) CV_Error(cv::Error::StsAssert, mpl_last_error());
     if (err != 0) std::cout << mpl_last_error() << std::endl;                    // the reference prints its diagnostics to cout
     if (err == 0 || err == -3) finalMatches.assign(out.begin(), out.begin() + n_out);
+    if (err == 0 && VFCrefine) {                                                 // matchers.cpp:721-733 (the early returns skip it there too)
+        std::vector<cv::DMatch> vfcfilteredMatches;
+        if (!filterWithVFC(keypoints1, keypoints2, finalMatches, vfcfilteredMatches))
+            if (vfcfilteredMatches.size() > 8 || finalMatches.size() < 24) finalMatches = vfcfilteredMatches;
+    }
     return err;
 }
 

@@ -60,9 +60,6 @@ def getMatchesArray(keypoints1, keypoints2, descriptors1, descriptors2, imgSi=No
                     nr_threads=0):
     """Returns (err, matches) with matches a numpy array of DMATCH_DTYPE (cv::DMatch layout)."""
     lib = _lib.load()
-    if VFCrefine:
-        # matchers.cpp:722-733: optional VFC post-filter, outside the hot path (SURVEY section 2: out of scope)
-        raise NotImplementedError("VFCrefine is outside the B200 hot path")
     a1, r1, c1, s1, t1 = _mat_fields(descriptors1)
     a2, r2, c2, s2, t2 = _mat_fields(descriptors2)
     out = np.empty(max(r1, 1), dtype=DMATCH_DTYPE)        # the library fills the first n_out records
@@ -72,7 +69,28 @@ def getMatchesArray(keypoints1, keypoints2, descriptors1, descriptors2, imgSi=No
                                   int(nr_threads), _lib.ptr(out), ctypes.byref(n_out))
     if err == -103:
         raise AssertionError(_lib.last_error())          # cv::Exception from CV_Assert in the reference
-    return err, out[: n_out.value]
+    final = out[: n_out.value]
+    if VFCrefine and err == 0:                            # matchers.cpp:721-733 (the early returns above skip it, as there)
+        code, kept = filterWithVFC(keypoints1, keypoints2, final)
+        if code == 0 and (len(kept) > 8 or len(final) < 24):
+            final = kept
+    return err, final
+
+
+def filterWithVFC(keypL, keypR, matches_in, seed=None):
+    """filterWithVFC (matchinglib/source/vfcMatches.cpp:49-86 -> class VFC, SparseVFC) through mpl_vfc_filter.  Returns
+    (code, matches_out): code 0 ok, -1 fewer than 5 matches (matches_out empty), -2 fewer than 10 % kept.  seed restarts the rand()
+    stream the control points are drawn from (None: it keeps running, like the reference's process-wide rand())."""
+    lib = _lib.load()
+    k1, k2 = _kp_xy(keypL), _kp_xy(keypR)
+    m = np.ascontiguousarray(matches_in, DMATCH_DTYPE)
+    if seed is not None:
+        lib.mpl_vfc_set_seed(int(seed) & 0xffffffff)
+    keep = np.zeros(max(len(m), 1), np.uint8)
+    nk, code, it = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+    _lib.check(lib.mpl_vfc_filter(_lib.ptr(k1), len(k1), 8, _lib.ptr(k2), len(k2), 8, _lib.ptr(m), len(m), _lib.ptr(keep), ctypes.byref(nk),
+                                  ctypes.byref(code), ctypes.byref(it)), "mpl_vfc_filter")
+    return code.value, m[keep[: len(m)].astype(bool)]
 
 
 def getMatches(keypoints1, keypoints2, descriptors1, descriptors2, imgSi, finalMatches, matcher_name="GMBSOF",
@@ -130,12 +148,13 @@ def getCorrespondences(img1, img2, featuretype="FAST", extractortype="FREAK", ma
     -3 descriptor error, -4 incompatible detector/matcher, -6 incompatible detector/descriptor, and a getMatches failure e
     as -4 + e (:356-359), i.e. -5 wrong input, -6 matcher not served by this build, -7 too few matches, -8 too few keypoints.
     `detector` / `extractor` (objects with detect(img) / compute(img, kps)) replace the cv2 factories when given.
-    GMSrefine runs the GMS grid filter on the GPU (mpl_gms_filter; :378-396); the other post-filters (VFC, SOF, sub-pixel
-    refinement; :415-506) are outside the B200 hot path."""
+    GMSrefine runs the GMS grid filter (mpl_gms_filter; :378-396) and VFCrefine the vector-field-consensus filter inside
+    getMatches (mpl_vfc_filter; matchers.cpp:721-733) on the GPU; SOF and sub-pixel refinement (:415-506) are outside the B200
+    hot path."""
     if img1 is None or img2 is None or np.size(img1) == 0 or np.size(img2) == 0:
         return -1, [], [], []
-    if VFCrefine or SOFrefine or subPixRefine:
-        raise NotImplementedError("VFC / SOF / sub-pixel refinement are outside the B200 hot path")
+    if SOFrefine or subPixRefine:
+        raise NotImplementedError("SOF / sub-pixel refinement are outside the B200 hot path")
     if featuretype in ("MSER", "SimpleBlob") and matchertype == "GMBSOF":
         return -4, [], [], []
     if (featuretype != "KAZE" and extractortype == "KAZE") or (featuretype != "AKAZE" and extractortype == "AKAZE") or \
@@ -152,7 +171,7 @@ def getCorrespondences(img1, img2, featuretype="FAST", extractortype="FREAK", ma
     kp2, d2 = ext.compute(img2, kp2)
     if d1 is None or d2 is None or len(kp1) != len(d1) or len(kp2) != len(d2):
         return -3, [], list(kp1 or []), list(kp2 or [])
-    err, matches = getMatchesArray(kp1, kp2, d1, d2, None, matchertype, False, ratioTest, extractortype,
+    err, matches = getMatchesArray(kp1, kp2, d1, d2, None, matchertype, VFCrefine, ratioTest, extractortype,
                                    idxPars_NMSLIB, queryPars_NMSLIB)
     if err != 0:
         return -4 + err, [], list(kp1), list(kp2)

@@ -1,0 +1,86 @@
+"""GPU: filterWithVFC (mpl_vfc_filter: host set-up as written, kernel matrix + EM iterations in one kernel launch) against the
+reference's OWN vfc.cpp / vfcMatches.cpp compiled into oracle/_ref/libvfc_ref.so, seeded alike (both draw the control points
+from glibc's rand()).  Float tolerance, not bitwise (csrc/vfc.cu says why): the bars are the same return code, kept sets that
+differ in at most 0.2 % of the matches (a posterior within ~1e-4 of the 0.75 threshold), and -- on scenes with a clear margin --
+identical sets; plus getMatches(VFCrefine = true)'s replacement rule (matchers.cpp:721-733)."""
+import numpy as np
+import pytest
+
+import datagen_vfc
+from oracle import vfc as ovfc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def M():
+    import __graft_entry__ as g
+    g.build()
+    from matchinglib_poselib_b200 import matchinglib, _lib
+    _lib.check(_lib.load().mpl_init(0), "mpl_init")
+    return matchinglib
+
+
+def _dm(M, mt, rng=None):
+    m = np.zeros(len(mt), M.DMATCH_DTYPE)
+    m["queryIdx"] = mt[:, 0]; m["trainIdx"] = mt[:, 1]; m["imgIdx"] = -1
+    m["distance"] = 1.0 if rng is None else rng.uniform(5, 90, len(mt))
+    return m
+
+
+@pytest.mark.parametrize("n,outl,seed", [(3000, 0.4, 1), (500, 0.2, 2), (10000, 0.6, 3), (30, 0.1, 4), (1500, 0.0, 5), (2000, 0.85, 6), (12, 0.0, 7), (6000, 0.5, 8)])
+def test_vfc_vs_reference(M, n, outl, seed):
+    k1, k2, mt, inl = datagen_vfc.scene(n, outl, seed=seed)
+    dm = _dm(M, mt)
+    same, worst = 0, 0
+    for s in (1, 7, 1234):
+        code, kept = M.filterWithVFC(k1, k2, dm, seed=s)
+        keep = np.zeros(n, bool); keep[np.searchsorted(dm["queryIdx"], kept["queryIdx"])] = True
+        r = ovfc.filter_with_vfc(k1, k2, mt, seed=s)
+        if outl <= 0.6:
+            assert code == 0 and (keep & inl).sum() >= 0.98 * inl.sum() and (keep & ~inl).sum() <= 0.02 * n + 2, (code, keep.sum(), inl.sum())
+        if r is not None:
+            assert code == r[0]
+            diff = int((keep != r[1].astype(bool)).sum())
+            worst = max(worst, diff); same += int(diff == 0)
+            assert diff <= max(1, int(0.002 * n)), (n, outl, s, diff, keep.sum(), r[1].sum())
+    print("n=%d outliers %.0f%%: kept sets identical to the reference's in %d/3 seeds, worst difference %d matches" % (n, 100 * outl, same, worst))
+
+
+def test_vfc_edge_cases(M):
+    k1, k2, mt, inl = datagen_vfc.scene(40, 0.1, seed=9)
+    dm = _dm(M, mt)
+    code, kept = M.filterWithVFC(k1, k2, dm[:4], seed=1)                       # setData: fewer than 5 matches
+    assert code == -1 and len(kept) == 0
+    same = np.tile(k1[:1], (40, 1))                                             # zero spread: normalize() fails, optimize() returns, everything is kept
+    code, kept = M.filterWithVFC(same, k2, dm, seed=1)
+    r = ovfc.filter_with_vfc(same, k2, mt, seed=1)
+    assert code == 0 and len(kept) == 40 and (r is None or (r[0] == 0 and r[1].sum() == 40))
+    code, kept = M.filterWithVFC(k1, k2, dm[:0], seed=1)
+    assert code == -1 and len(kept) == 0
+    with pytest.raises(Exception):
+        bad = dm.copy(); bad["trainIdx"][3] = 4000
+        M.filterWithVFC(k1, k2, bad, seed=1)
+    # two calls with the same seed are identical; without a seed the stream keeps running (another control-point choice)
+    k1, k2, mt, inl = datagen_vfc.scene(2000, 0.5, seed=10)
+    dm = _dm(M, mt)
+    a = M.filterWithVFC(k1, k2, dm, seed=5); b = M.filterWithVFC(k1, k2, dm, seed=5); c = M.filterWithVFC(k1, k2, dm)
+    assert a[0] == b[0] == c[0] == 0 and np.array_equal(a[1], b[1]) and abs(len(c[1]) - len(a[1])) <= 20
+
+
+def test_getMatches_with_VFCrefine(M):
+    """getMatches(..., VFCrefine = true): match, then filterWithVFC, then the replacement rule of matchers.cpp:726-731."""
+    rng = np.random.default_rng(11)
+    n = 1500
+    k1, k2, mt, inl = datagen_vfc.scene(n, 0.3, seed=11)
+    t = rng.integers(0, 256, (n, 32), dtype=np.uint8)                           # train descriptors; query i is a noisy copy of its partner's
+    q = t[mt[:, 1]] ^ np.packbits(rng.random((n, 256)) < 0.03, axis=1)
+    M._lib.load().mpl_vfc_set_seed(3)
+    err0, plain = M.getMatchesArray(k1, k2, q, t, None, "LINEAR", False, True)
+    M._lib.load().mpl_vfc_set_seed(3)
+    err1, refined = M.getMatchesArray(k1, k2, q, t, None, "LINEAR", True, True)
+    assert err0 == 0 and err1 == 0 and len(plain) > 0.95 * n
+    code, kept = M.filterWithVFC(k1, k2, plain, seed=3)
+    assert code == 0 and np.array_equal(refined, kept)
+    keep_q = np.zeros(n, bool); keep_q[refined["queryIdx"]] = True
+    assert (keep_q & inl).sum() >= 0.97 * inl.sum() and (keep_q & ~inl).sum() <= 0.02 * n
