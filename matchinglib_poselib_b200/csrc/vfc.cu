@@ -13,14 +13,17 @@
 // Split: the O(n) set-up that fixes the problem -- match -> point pairs, normalize() with its sequential float sums, the
 // rand()-driven choice of the (at most 16) control points and their 16 x 16 kernel -- runs on the host exactly as written
 // (glibc's rand() restated, glibc_rand.h).  Everything that is O(n) PER EM ITERATION runs in ONE kernel launch of one CTA:
-// the 16 x n kernel matrix U, and up to 50 iterations of E-step (posterior P), the 168 weighted sums U diag(P) U^T and
-// U diag(P) Y, the 16 x 16 LU solve, V = U^T C, sigma^2, gamma, with the loop's exit tests (iterations, energy change rate,
-// sigma^2) evaluated on the device.
+// the 16 x n kernel matrix U, and up to 50 iterations of E-step (posterior P; per match, spread over the CTA), the 168
+// weighted sums U diag(P) U^T and U diag(P) Y plus the four scalar sums (172 threads, each one sum, sequential in match order),
+// the 16 x 16 LU solve, V = U^T C, sigma^2, gamma, with the loop's exit tests evaluated on the device.
 //
-// Parity: float tolerance, not bitwise -- the reference accumulates its float sums sequentially over the n matches, the device in
-// a fixed tree, and expf differs in the last ulp; multiplications and additions are kept separate (no FMA contraction) and in
-// the reference's order within a term.  A match whose posterior ends within ~1e-4 of the 0.75 threshold can flip;
-// tests/test_vfc_gpu.py measures it against the reference's own vfc.cpp (oracle/_ref/libvfc_ref.so).
+// Parity: the kept set is the reference's for the same rand() seed.  The EM iteration is numerically chaotic (sigma^2 settles near
+// 1e-5, the energy keeps jumping, all 50 iterations run -- also in the reference), so "close" arithmetic gives kept sets that
+// differ in up to 2 % of the matches; the device therefore does the reference's ARITHMETIC: float sums sequential in match order
+// (one thread per sum), multiplications and additions separate and in the written order (no FMA contraction), pow(x, 2) in
+// double, expf / logf as the once-rounded double results glibc returns.  What can still differ: glibc's expf is not correctly
+// rounded for about one argument in 10^8.  tests/test_vfc_gpu.py compares with the reference's own vfc.cpp
+// (oracle/_ref/libvfc_ref.so, built with -ffp-contract=off like an x86-64 baseline build).
 #include "mpl_common.cuh"
 #include "mpl_ctx.h"
 #include "glibc_rand.h"
@@ -37,34 +40,42 @@ namespace {
 constexpr int kCtrl = 16;                      // _numCtrlPts (vfc.cpp:51)
 constexpr int kVfcThreads = 1024;
 constexpr int kSums = kCtrl * (kCtrl + 1) / 2 + 2 * kCtrl;     // 136 entries of U diag(P) U^T + 32 of U diag(P) Y
-constexpr int kGroups = kVfcThreads / kSums;   // 6 groups of 168 threads share the n matches of a sum
 
 struct VfcJob {
     const float2* X; const float2* Y;          // normalised left points, displacement vectors
     int n, m;                                  // matches, control points actually chosen (<= 16)
     float ctrl[kCtrl][2];
     float K[kCtrl][kCtrl];                     // intra-kernel of the control points (host)
-    float* Ut;                                 // [n][16] inter-kernel, point-major
-    float* P; float2* V;
+    float* U;                                  // [16][n] inter-kernel, row j = control point j (the reference's _U)
+    float* P; float* Praw; float* T; float2* V;
     uint8_t* keep; int* out;                   // out[0] = kept, out[1] = iterations
+    unsigned long long exp_tab[32];            // glibc's __exp2f_data.tab: bits of 2^(i/32) minus (i << 47), filled on the host
 };
 
 __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
-
-// sum over the CTA, identical in every thread (fixed tree: warp butterflies, then the 32 warp sums in order)
-__device__ float block_sum(float v, float* red)
+// expf as glibc computes it (sysdeps/ieee754/flt-32/e_expf.c, the algorithm of ARM's optimized routines): x * 32 / ln 2 = k + r,
+// 2^(k/32) from a 32-entry table, a cubic in r, all in double, ONE rounding to float at the end.  That last value is not always
+// the correctly rounded one (6 of 10^4 arguments differ from (float)exp((double)x)), and the EM iteration amplifies single ulps,
+// so the algorithm is restated; against the host's expf it agreed on 2 * 10^7 of 2 * 10^7 random arguments in [-60, 0].
+// Arguments here are never positive; below -103.97 glibc returns 0.
+__device__ __forceinline__ float expf_glibc(float x, const unsigned long long* __restrict__ tab)
 {
-#pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) v = fadd(v, __shfl_xor_sync(0xffffffffu, v, o));
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-    __syncthreads();
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < kVfcThreads / 32; ++w) s = fadd(s, red[w]);
-    return s;
+    if (!(x >= -0x1.9fe368p6f)) return x != x ? x : 0.0f;
+    const double N = 32.0, InvLn2N = 0x1.71547652b82fep+0 * N, SHIFT = 0x1.8p+52;
+    const double C0 = 0x1.c6af84b912394p-5 / N / N / N, C1 = 0x1.ebfce50fac4f3p-3 / N / N, C2 = 0x1.62e42ff0c52d6p-1 / N;
+    const double z = __dmul_rn(InvLn2N, (double)x);
+    double kd = __dadd_rn(z, SHIFT);
+    const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd = __dsub_rn(kd, SHIFT);
+    const double r = __dsub_rn(z, kd);
+    const double sc = __longlong_as_double((long long)(tab[ki & 31] + (ki << 47)));
+    const double zz = __fma_rn(C0, r, C1), r2 = __dmul_rn(r, r);
+    double y = __fma_rn(C2, r, 1.0);
+    y = __fma_rn(zz, r2, y);
+    return (float)__dmul_rn(y, sc);
 }
+__device__ __forceinline__ float logf_like_glibc(float x) { return (float)log((double)x); }     // only feeds the energy change rate
 
 // |a - b|^2 as the reference writes it: pow(float, int) promotes to double, the sum is narrowed to float (vfc.cpp:386, 494, 551)
 __device__ __forceinline__ float sqdist(float ax, float ay, float bx, float by)
@@ -73,137 +84,197 @@ __device__ __forceinline__ float sqdist(float ax, float ay, float bx, float by)
     return (float)__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
 }
 
+// The reference's float sums run sequentially over the n matches; float addition is not associative and the EM iteration
+// amplifies every rounding difference (sigma^2 settles near 1e-5 and the energy keeps jumping: all 50 iterations run), so the
+// sums here are sequential too -- one THREAD per sum, 172 sums side by side, fed through shared-memory tiles that the whole CTA
+// loads -- and only the per-match work (posteriors, V, the kernel matrix) is spread over the CTA.
+// acc += term(0) + term(1) + ... strictly in order, with the (independent) terms of eight elements formed before their adds so
+// that only the add chain is serial
+template <class F>
+__device__ __forceinline__ float seq_sum(float acc, int len, F term)
+{
+    int k = 0;
+    for (; k + 8 <= len; k += 8) {
+        const float x0 = term(k), x1 = term(k + 1), x2 = term(k + 2), x3 = term(k + 3), x4 = term(k + 4), x5 = term(k + 5), x6 = term(k + 6), x7 = term(k + 7);
+        acc = fadd(acc, x0); acc = fadd(acc, x1); acc = fadd(acc, x2); acc = fadd(acc, x3); acc = fadd(acc, x4); acc = fadd(acc, x5); acc = fadd(acc, x6); acc = fadd(acc, x7);
+    }
+    for (; k < len; ++k) acc = fadd(acc, term(k));
+    return acc;
+}
+
+constexpr int kTile = 256, kTileLd = kTile + 1;          // row stride 257: the 16 rows of a tile fall into distinct banks
+
 __global__ void __launch_bounds__(kVfcThreads)
 vfc_sparse_kernel(const VfcJob* __restrict__ job)
 {
-    __shared__ float red[32];
-    __shared__ float part[kGroups][kSums];
+    __shared__ float sU[kCtrl][kTileLd], sP[kTile], sA[kTile], sB[kTile], sC[kTile], sD[kTile];
     __shared__ float A[kCtrl][kCtrl], Bm[kCtrl][2], C[kCtrl][2], Ks[kCtrl][kCtrl], ctrl[kCtrl][2];
-    __shared__ float s_sigma2, s_gamma, s_E, s_tecr;
-    __shared__ int s_iter, s_go;
+    __shared__ float s_sigma2, s_gamma, s_E, s_tecr, s_sumP, s_Esum, s_trace, s_sg, s_sp;
+    __shared__ int s_iter, s_go, s_cnt, s_ok;
+    __shared__ unsigned long long tab[32];
     const VfcJob& J = *job;
     const int tid = threadIdx.x, n = J.n, m = J.m;
     const float beta = 0.1f, lambda = 3.0f, theta = 0.75f, a_par = 10.0f, ecr = 1e-5f, minP = 1e-5f;      // vfc.cpp:43-50
     if (tid < kCtrl * kCtrl) Ks[tid / kCtrl][tid % kCtrl] = J.K[tid / kCtrl][tid % kCtrl];
     if (tid < kCtrl * 2) { ctrl[tid / 2][tid & 1] = J.ctrl[tid / 2][tid & 1]; C[tid / 2][tid & 1] = 0.f; }
+    if (tid < 32) tab[tid] = J.exp_tab[tid];
     __syncthreads();
     // constructInterKernel(_ctrlPts, _X) (:545-558) and initialize() (:507-526): V = 0, P = 1, sigma^2 from them
-    float sg = 0.f, sp = 0.f;
     for (int i = tid; i < n; i += kVfcThreads) {
         const float2 x = J.X[i], y = J.Y[i];
-        for (int j = 0; j < kCtrl; ++j)
-            J.Ut[(size_t)i * kCtrl + j] = j < m ? expf(fmul(-beta, sqdist(ctrl[j][0], ctrl[j][1], x.x, x.y))) : 0.f;
+        for (int j = 0; j < m; ++j) J.U[(size_t)j * n + i] = expf_glibc(fmul(-beta, sqdist(ctrl[j][0], ctrl[j][1], x.x, x.y)), tab);
         J.V[i] = make_float2(0.f, 0.f); J.P[i] = 1.f;
-        sg = fadd(sg, sqdist(y.x, y.y, 0.f, 0.f)); sp = fadd(sp, 1.f);
+        J.T[i] = sqdist(y.x, y.y, 0.f, 0.f);
     }
-    sg = block_sum(sg, red); sp = block_sum(sp, red);
-    if (tid == 0) { s_sigma2 = sg / fmul(sp, 2.f); s_gamma = 0.9f; s_E = 1.f; s_tecr = 1.f; s_iter = 0; }
+    if (tid == 0) { s_gamma = 0.9f; s_E = 1.f; s_tecr = 1.f; s_iter = 0; }
     __syncthreads();
-    // which of the 168 sums this thread owns
-    const int g = tid / kSums, o = tid - g * kSums;
-    int oi = 0, oj = 0;                                       // o < 136: (oi, oj), oi <= oj; else row oi = (o - 136) / 2, column oj = (o - 136) & 1 of U diag(P) Y
-    if (o < kSums - 2 * kCtrl) { int r = o; for (oi = 0; oi < kCtrl; ++oi) { if (r < kCtrl - oi) { oj = oi + r; break; } r -= kCtrl - oi; } }
-    else { oi = (o - (kSums - 2 * kCtrl)) >> 1; oj = (o - (kSums - 2 * kCtrl)) & 1; }
-    const bool is_y = o >= kSums - 2 * kCtrl;
+    // which of the 168 M-step sums this thread owns: tid < 136: (oi, oj), oi <= oj; tid < 168: row oi, column oj of U diag(P) Y
+    int oi = 0, oj = 0;
+    if (tid < kSums - 2 * kCtrl) { int r = tid; for (oi = 0; oi < kCtrl; ++oi) { if (r < kCtrl - oi) { oj = oi + r; break; } r -= kCtrl - oi; } }
+    else if (tid < kSums) { oi = (tid - (kSums - 2 * kCtrl)) >> 1; oj = (tid - (kSums - 2 * kCtrl)) & 1; }
+    const bool is_y = tid >= kSums - 2 * kCtrl;
+    const bool live = tid < kSums && oi < m && (is_y || oj < m);
+    bool first = true;                                         // the first pass only computes sigma^2 of initialize()
     for (;;) {
-        if (tid == 0) s_go = (s_iter < 50 && s_tecr > ecr && (double)s_sigma2 > 1e-8) ? 1 : 0;      // :106
-        __syncthreads();
-        if (!s_go) break;
-        const float sigma2 = s_sigma2, gamma = s_gamma, E_old = s_E;
-        // ---- E-step: getP (:490-505)
-        const float temp2 = fmul(fmul(6.283185f, sigma2), (1.f - gamma)) / fmul(gamma, a_par);      // pow(x, 1.0f) == x
-        float sumP = 0.f, E = 0.f;
-        for (int i = tid; i < n; i += kVfcThreads) {
-            const float2 y = J.Y[i], v = J.V[i];
-            const float t = sqdist(y.x, y.y, v.x, v.y);
-            const float temp1 = expf(-t / fmul(2.f, sigma2));
-            const float p = temp1 / fadd(temp1, temp2);
-            J.P[i] = fmaxf(minP, p);
-            sumP = fadd(sumP, p); E = fadd(E, fmul(p, t));
+        if (!first) {
+            if (tid == 0) { s_go = (s_iter < 50 && s_tecr > ecr && (double)s_sigma2 > 1e-8) ? 1 : 0; s_cnt = 0; }      // :106
+            __syncthreads();
+            if (!s_go) break;
         }
-        sumP = block_sum(sumP, red); E = block_sum(E, red);
-        E = E / fmul(2.f, sigma2);
-        E = fadd(E, fmul(fmul(sumP, logf(sigma2)), 2.f) / 2.f);
-        // ---- calculateTraceCKC (:468-488), energy change rate (:111-112)
-        if (tid == 0) {
-            float tr = 0.f;
-            for (int i = 0; i < m; ++i) {
-                float t1 = 0.f, t2 = 0.f;
-                for (int j = 0; j < m; ++j) { t1 = fadd(t1, fmul(Ks[i][j], C[j][0])); t2 = fadd(t2, fmul(Ks[i][j], C[j][1])); }
-                tr = fadd(tr, fadd(fmul(C[i][0], t1), fmul(C[i][1], t2)));
+        const float sigma2 = first ? 1.f : s_sigma2, gamma = s_gamma, E_old = s_E;
+        if (!first) {
+            // ---- E-step, per match: getP (:490-505)
+            const float temp2 = fmul(fmul(6.283185f, sigma2), (1.f - gamma)) / fmul(gamma, a_par);      // pow(x, 1.0f) == x
+            for (int i = tid; i < n; i += kVfcThreads) {
+                const float2 y = J.Y[i], v = J.V[i];
+                const float t = sqdist(y.x, y.y, v.x, v.y);
+                const float temp1 = expf_glibc(-t / fmul(2.f, sigma2), tab);
+                const float p = temp1 / fadd(temp1, temp2);
+                J.Praw[i] = p; J.P[i] = fmaxf(minP, p); J.T[i] = t;
             }
-            const float En = fadd(E, fmul(lambda / 2.f, tr));
-            s_E = En; s_tecr = fabsf((En - E_old) / En);
-        }
-        // ---- M-step: calculateC_SparseVFC (:152-189).  Thread (g, o) sums its term over matches g, g + 6, ...
-        float acc = 0.f;
-        if (g < kGroups && oi < m && (is_y || oj < m))
-            for (int k = g; k < n; k += kGroups) {
-                const float pu = fmul(J.P[k], J.Ut[(size_t)k * kCtrl + oi]);
-                const float w = is_y ? (oj ? J.Y[k].y : J.Y[k].x) : J.Ut[(size_t)k * kCtrl + oj];
-                acc = fadd(acc, fmul(pu, w));
-            }
-        if (g < kGroups) part[g][o] = acc;
-        __syncthreads();
-        if (tid < kSums) {
-            float s = 0.f;
-            for (int gg = 0; gg < kGroups; ++gg) s = fadd(s, part[gg][tid]);
-            if (!is_y) { s = fadd(s, fmul(fmul(lambda, sigma2), Ks[oi][oj])); A[oi][oj] = s; A[oj][oi] = s; }
-            else Bm[oi][oj] = s;
-        }
-        __syncthreads();
-        if (tid == 0) {                                        // cv::solve(K, Y, C, DECOMP_LU): LUImpl, float
-            bool ok = true;
-            for (int i = 0; i < m && ok; i++) {
-                int k = i;
-                for (int j = i + 1; j < m; j++) if (fabsf(A[j][i]) > fabsf(A[k][i])) k = j;
-                if (fabsf(A[k][i]) < FLT_EPSILON * 10) { ok = false; break; }
-                if (k != i) {
-                    for (int j = i; j < m; j++) { const float t = A[i][j]; A[i][j] = A[k][j]; A[k][j] = t; }
-                    for (int j = 0; j < 2; j++) { const float t = Bm[i][j]; Bm[i][j] = Bm[k][j]; Bm[k][j] = t; }
+            __syncthreads();
+            // ---- the sequential sums of this half: 168 of calculateC_SparseVFC (:152-178), sum p and sum p t of getP, calculateTraceCKC
+            float acc = 0.f;
+            for (int t0 = 0; t0 < n; t0 += kTile) {
+                const int len = min(kTile, n - t0);
+                for (int e = tid; e < m * kTile; e += kVfcThreads) { const int r = e / kTile, c = e - r * kTile; if (c < len) sU[r][c] = J.U[(size_t)r * n + t0 + c]; }
+                if (tid < len) { sP[tid] = J.P[t0 + tid]; const float2 y = J.Y[t0 + tid]; sA[tid] = y.x; sB[tid] = y.y; }
+                else if (tid >= kTile && tid - kTile < len) { sC[tid - kTile] = J.Praw[t0 + tid - kTile]; sD[tid - kTile] = J.T[t0 + tid - kTile]; }
+                __syncthreads();
+                if (live) {
+                    const float* ui = sU[oi];
+                    const float* w = is_y ? (oj ? sB : sA) : sU[oj];
+                    acc = seq_sum(acc, len, [&](int k) { return fmul(fmul(sP[k], ui[k]), w[k]); });
+                } else if (tid == 192) {
+                    acc = seq_sum(acc, len, [&](int k) { return sC[k]; });
+                } else if (tid == 224) {
+                    acc = seq_sum(acc, len, [&](int k) { return fmul(sC[k], sD[k]); });
                 }
-                const float d = -1.f / A[i][i];
-                for (int j = i + 1; j < m; j++) {
-                    const float alpha = fmul(A[j][i], d);
-                    for (int kk = i + 1; kk < m; kk++) A[j][kk] = fadd(A[j][kk], fmul(alpha, A[i][kk]));
-                    for (int kk = 0; kk < 2; kk++) Bm[j][kk] = fadd(Bm[j][kk], fmul(alpha, Bm[i][kk]));
-                }
+                __syncthreads();
             }
-            if (ok)
-                for (int i = m - 1; i >= 0; i--)
-                    for (int j = 0; j < 2; j++) {
-                        float s = Bm[i][j];
-                        for (int k = i + 1; k < m; k++) s = __fsub_rn(s, fmul(A[i][k], Bm[k][j]));
-                        Bm[i][j] = s / A[i][i];
+            if (tid < kSums) {
+                if (!is_y) { if (live) { acc = fadd(acc, fmul(fmul(lambda, sigma2), Ks[oi][oj])); A[oi][oj] = acc; A[oj][oi] = acc; } }
+                else if (live) Bm[oi][oj] = acc;
+            } else if (tid == 192) s_sumP = acc;
+            else if (tid == 224) s_Esum = acc;
+            else if (tid == 256) {
+                float tr = 0.f;
+                for (int i = 0; i < m; ++i) {
+                    float t1 = 0.f, t2 = 0.f;
+                    for (int j = 0; j < m; ++j) { t1 = fadd(t1, fmul(Ks[i][j], C[j][0])); t2 = fadd(t2, fmul(Ks[i][j], C[j][1])); }
+                    tr = fadd(tr, fadd(fmul(C[i][0], t1), fmul(C[i][1], t2)));
+                }
+                s_trace = tr;
+            }
+            __syncthreads();
+            if (tid == 64) {                                   // energy (:501-502, :110-112)
+                float E = s_Esum / fmul(2.f, sigma2);
+                E = fadd(E, fmul(fmul(s_sumP, logf_like_glibc(sigma2)), 2.f) / 2.f);
+                const float En = fadd(E, fmul(lambda / 2.f, s_trace));
+                s_E = En; s_tecr = fabsf((En - E_old) / En);
+            }
+            // ---- cv::solve(K, Y, C, DECOMP_LU): OpenCV's LUImpl in float; lane j of warp 0 owns row j (every element sees the same
+            //      operations in the same order as in the serial loop)
+            if (tid < 32) {
+                const int lane = tid;
+                if (lane == 0) s_ok = 1;
+                __syncwarp();
+                for (int i = 0; i < m; i++) {
+                    float best = (lane >= i && lane < m) ? fabsf(A[lane][i]) : -1.f;
+                    int k = lane;
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) {
+                        const float ob = __shfl_xor_sync(0xffffffffu, best, off); const int ok2 = __shfl_xor_sync(0xffffffffu, k, off);
+                        if (ob > best || (ob == best && ok2 < k)) { best = ob; k = ok2; }      // the FIRST largest |a| (strict > in the reference)
                     }
-            for (int i = 0; i < kCtrl; ++i) for (int j = 0; j < 2; ++j) C[i][j] = (ok && i < m) ? Bm[i][j] : 0.f;      // a singular system leaves cv::solve's output zero
+                    if (best < FLT_EPSILON * 10) { if (lane == 0) s_ok = 0; break; }
+                    if (k != i) {
+                        if (lane >= i && lane < m) { const float t = A[i][lane]; A[i][lane] = A[k][lane]; A[k][lane] = t; }
+                        if (lane < 2) { const float t = Bm[i][lane]; Bm[i][lane] = Bm[k][lane]; Bm[k][lane] = t; }
+                    }
+                    __syncwarp();
+                    const float d = -1.f / A[i][i];
+                    if (lane > i && lane < m) {
+                        const float alpha = fmul(A[lane][i], d);
+                        for (int kk = i + 1; kk < m; kk++) A[lane][kk] = fadd(A[lane][kk], fmul(alpha, A[i][kk]));
+                        for (int kk = 0; kk < 2; kk++) Bm[lane][kk] = fadd(Bm[lane][kk], fmul(alpha, Bm[i][kk]));
+                    }
+                    __syncwarp();
+                }
+                __syncwarp();
+                if (s_ok && lane < 2)
+                    for (int i = m - 1; i >= 0; i--) {
+                        float sv = Bm[i][lane];
+                        for (int k = i + 1; k < m; k++) sv = __fsub_rn(sv, fmul(A[i][k], Bm[k][lane]));
+                        Bm[i][lane] = sv / A[i][i];
+                    }
+                __syncwarp();
+                if (lane < kCtrl) { C[lane][0] = (s_ok && lane < m) ? Bm[lane][0] : 0.f; C[lane][1] = (s_ok && lane < m) ? Bm[lane][1] : 0.f; }   // singular: cv::solve zeroes its output
+            }
+            __syncthreads();
+            // ---- per match: calculateV (:432-444), the terms of calculateSigmaSquare (:383-392), calculateGamma's count (:369-381)
+            int cnt = 0;
+            for (int i = tid; i < n; i += kVfcThreads) {
+                float t1 = 0.f, t2 = 0.f;
+                for (int j = 0; j < m; ++j) { const float u = J.U[(size_t)j * n + i]; t1 = fadd(t1, fmul(u, C[j][0])); t2 = fadd(t2, fmul(u, C[j][1])); }
+                J.V[i] = make_float2(t1, t2);
+                const float2 y = J.Y[i];
+                J.T[i] = sqdist(y.x, y.y, t1, t2);
+                cnt += J.P[i] > theta ? 1 : 0;
+            }
+            if (cnt) atomicAdd(&s_cnt, cnt);
+            __syncthreads();
         }
+        // ---- calculateSigmaSquare's two sequential sums (:383-392), 1024 matches per tile
+        float a1 = 0.f;
+        for (int t0 = 0; t0 < n; t0 += kVfcThreads) {
+            const int len = min(kVfcThreads, n - t0);
+            float* sPP = &sU[0][0]; float* sTT = &sU[0][0] + kVfcThreads;                  // 2 x 1024 floats of the (idle) U tile
+            if (tid < len) { sPP[tid] = J.P[t0 + tid]; sTT[tid] = J.T[t0 + tid]; }
+            __syncthreads();
+            if (tid == 0) a1 = seq_sum(a1, len, [&](int k) { return fmul(sPP[k], sTT[k]); });
+            else if (tid == 32) a1 = seq_sum(a1, len, [&](int k) { return sPP[k]; });
+            __syncthreads();
+        }
+        if (tid == 0) s_sg = a1; else if (tid == 32) s_sp = a1;
         __syncthreads();
-        // ---- calculateV (:432-444), calculateSigmaSquare (:383-392), calculateGamma (:369-381)
-        float sg2 = 0.f, sp2 = 0.f, cnt = 0.f;
-        for (int i = tid; i < n; i += kVfcThreads) {
-            float t1 = 0.f, t2 = 0.f;
-            for (int j = 0; j < m; ++j) { const float u = J.Ut[(size_t)i * kCtrl + j]; t1 = fadd(t1, fmul(u, C[j][0])); t2 = fadd(t2, fmul(u, C[j][1])); }
-            J.V[i] = make_float2(t1, t2);
-            const float2 y = J.Y[i];
-            const float p = J.P[i];
-            sg2 = fadd(sg2, fmul(p, sqdist(y.x, y.y, t1, t2))); sp2 = fadd(sp2, p);
-            cnt += p > theta ? 1.f : 0.f;
-        }
-        sg2 = block_sum(sg2, red); sp2 = block_sum(sp2, red); cnt = block_sum(cnt, red);
         if (tid == 0) {
-            s_sigma2 = sg2 / fmul(sp2, 2.f);
-            s_gamma = fmaxf(fminf(cnt / (float)n, 0.95f), 0.05f);
-            s_iter = s_iter + 1;
+            s_sigma2 = s_sg / fmul(s_sp, 2.f);
+            if (!first) { s_gamma = fmaxf(fminf((float)s_cnt / (float)n, 0.95f), 0.05f); s_iter = s_iter + 1; }
         }
+        first = false;
         __syncthreads();
     }
     // obtainCorrectMatch: the P > theta set of the last calculateGamma; all matches when no iteration ran (:66-68)
     const bool none = s_iter == 0;
-    float kept = 0.f;
-    for (int i = tid; i < n; i += kVfcThreads) { const bool k = none || J.P[i] > theta; J.keep[i] = k ? 1 : 0; kept += k ? 1.f : 0.f; }
-    kept = block_sum(kept, red);
-    if (tid == 0) { J.out[0] = (int)kept; J.out[1] = s_iter; }
+    __syncthreads();
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    int kept = 0;
+    for (int i = tid; i < n; i += kVfcThreads) { const bool k = none || J.P[i] > theta; J.keep[i] = k ? 1 : 0; kept += k ? 1 : 0; }
+    if (kept) atomicAdd(&s_cnt, kept);
+    __syncthreads();
+    if (tid == 0) { J.out[0] = s_cnt; J.out[1] = s_iter; }
 }
 
 thread_local GlibcRand t_vfc_rng;
@@ -266,6 +337,7 @@ extern "C" int mpl_vfc_filter(const void* kp1, int n1, size_t kp_stride1, const 
         iter++;
     }
     J.n = n; J.m = cnt;
+    for (int i = 0; i < 32; ++i) { const double v = exp2(i / 32.0); unsigned long long u; memcpy(&u, &v, 8); J.exp_tab[i] = u - ((unsigned long long)i << 47); }
     for (int i = 0; i < cnt; i++) {
         J.K[i][i] = 1;
         for (int j = i + 1; j < cnt; j++) {
@@ -283,13 +355,13 @@ extern "C" int mpl_vfc_filter(const void* kp1, int n1, size_t kp_stride1, const 
     MplCtx* ctx = mpl_ctx(); cudaStream_t st = ctx->stream; MplBuf* B = ctx->bufs;
     auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
     const size_t nn = (size_t)n;
-    const size_t o_job = 0, o_x = al(sizeof(VfcJob)), o_y = o_x + al(nn * 8), o_u = o_y + al(nn * 8), o_p = o_u + al(nn * kCtrl * 4), o_v = o_p + al(nn * 4),
-                 o_keep = o_v + al(nn * 8), o_out = o_keep + al(nn), total = o_out + 256;
+    const size_t o_job = 0, o_x = al(sizeof(VfcJob)), o_y = o_x + al(nn * 8), o_u = o_y + al(nn * 8), o_p = o_u + al(nn * kCtrl * 4), o_pr = o_p + al(nn * 4),
+                 o_t = o_pr + al(nn * 4), o_v = o_t + al(nn * 4), o_keep = o_v + al(nn * 8), o_out = o_keep + al(nn), total = o_out + 256;
     if ((rc = B[MPL_BUF_RAW].ensure(total))) return rc;
     char* D = (char*)B[MPL_BUF_RAW].ptr;
     char* hs = nullptr;
     if ((rc = mpl_stage_ensure(o_u + al(nn) + 256, (void**)&hs))) return rc;
-    J.X = (const float2*)(D + o_x); J.Y = (const float2*)(D + o_y); J.Ut = (float*)(D + o_u); J.P = (float*)(D + o_p); J.V = (float2*)(D + o_v);
+    J.X = (const float2*)(D + o_x); J.Y = (const float2*)(D + o_y); J.U = (float*)(D + o_u); J.P = (float*)(D + o_p); J.Praw = (float*)(D + o_pr); J.T = (float*)(D + o_t); J.V = (float2*)(D + o_v);
     J.keep = (uint8_t*)(D + o_keep); J.out = (int*)(D + o_out);
     memcpy(hs + o_job, &J, sizeof(J)); memcpy(hs + o_x, X.data(), nn * 8); memcpy(hs + o_y, Y.data(), nn * 8);
     MPL_CUDA_CHECK(cudaMemcpyAsync(D, hs, o_u, cudaMemcpyHostToDevice, st));

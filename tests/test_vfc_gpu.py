@@ -1,8 +1,9 @@
 """GPU: filterWithVFC (mpl_vfc_filter: host set-up as written, kernel matrix + EM iterations in one kernel launch) against the
 reference's OWN vfc.cpp / vfcMatches.cpp compiled into oracle/_ref/libvfc_ref.so, seeded alike (both draw the control points
-from glibc's rand()).  Float tolerance, not bitwise (csrc/vfc.cu says why): the bars are the same return code, kept sets that
-differ in at most 0.2 % of the matches (a posterior within ~1e-4 of the 0.75 threshold), and -- on scenes with a clear margin --
-identical sets; plus getMatches(VFCrefine = true)'s replacement rule (matchers.cpp:721-733)."""
+from glibc's rand()).  The EM iteration is numerically chaotic, so the device does the reference's arithmetic (sequential float
+sums, glibc's expf restated, csrc/vfc.cu) and the bar is EQUALITY: same return code, same kept set for the same seed -- also
+where the reference's result is poor (it keeps 40 wrong matches of 3000 for one seed; so does the device).  Plus
+getMatches(VFCrefine = true)'s replacement rule (matchers.cpp:721-733)."""
 import numpy as np
 import pytest
 
@@ -28,7 +29,7 @@ def _dm(M, mt, rng=None):
     return m
 
 
-@pytest.mark.parametrize("n,outl,seed", [(3000, 0.4, 1), (500, 0.2, 2), (10000, 0.6, 3), (30, 0.1, 4), (1500, 0.0, 5), (2000, 0.85, 6), (12, 0.0, 7), (6000, 0.5, 8)])
+@pytest.mark.parametrize("n,outl,seed", [(3000, 0.4, 1), (500, 0.2, 2), (10000, 0.6, 3), (30, 0.1, 4), (1500, 0.0, 5), (2000, 0.85, 6), (12, 0.0, 7), (6000, 0.5, 8), (20000, 0.5, 9), (257, 0.3, 10), (1025, 0.95, 11)])
 def test_vfc_vs_reference(M, n, outl, seed):
     k1, k2, mt, inl = datagen_vfc.scene(n, outl, seed=seed)
     dm = _dm(M, mt)
@@ -38,12 +39,12 @@ def test_vfc_vs_reference(M, n, outl, seed):
         keep = np.zeros(n, bool); keep[np.searchsorted(dm["queryIdx"], kept["queryIdx"])] = True
         r = ovfc.filter_with_vfc(k1, k2, mt, seed=s)
         if outl <= 0.6:
-            assert code == 0 and (keep & inl).sum() >= 0.98 * inl.sum() and (keep & ~inl).sum() <= 0.02 * n + 2, (code, keep.sum(), inl.sum())
+            assert code == 0 and (keep & inl).sum() >= 0.98 * inl.sum() and (keep & ~inl).sum() <= 0.03 * n + 2, (code, keep.sum(), inl.sum())
         if r is not None:
             assert code == r[0]
             diff = int((keep != r[1].astype(bool)).sum())
             worst = max(worst, diff); same += int(diff == 0)
-            assert diff <= max(1, int(0.002 * n)), (n, outl, s, diff, keep.sum(), r[1].sum())
+            assert diff == 0, (n, outl, s, diff, keep.sum(), r[1].sum())
     print("n=%d outliers %.0f%%: kept sets identical to the reference's in %d/3 seeds, worst difference %d matches" % (n, 100 * outl, same, worst))
 
 
