@@ -884,7 +884,8 @@ def measure_tf32_peak(torch, dev):
 def bench_next_rows(g):
     import datagen_gms, datagen_pose
     from matchinglib_poselib_b200 import matchinglib, poselib
-    from oracle import gms as ogms, arrsac as oarrsac, usac as ousac
+    from oracle import gms as ogms, arrsac as oarrsac, usac as ousac, vfc as ovfc
+    import datagen_vfc
     torch = g.torch
     out = {}
     k1, k2, mt, sz = datagen_gms.scene(n=8000, seed=1, border=True)
@@ -919,6 +920,26 @@ def bench_next_rows(g):
                          ms_per_call=float(np.median(ts) * 1e3), inliers=int(res["count"]), hypotheses=int(res["n_hypotheses"]), device_batches=int(res["n_batches"]),
                          note="latency-bound: every device batch waits for one 5-point solve (~1.2 ms of dependent fp64 work); parity with the reference is statistical",
                          cpu_baseline=cb)
+    # VFC post-filter (second half): getMatches(VFCrefine = true)
+    v1, v2, vmt, vinl = datagen_vfc.scene(8000, 0.5, seed=3)
+    vdm = np.zeros(len(vmt), matchinglib.DMATCH_DTYPE); vdm["queryIdx"] = vmt[:, 0]; vdm["trainIdx"] = vmt[:, 1]; vdm["distance"] = 1
+    ts, kept = [], None
+    for i in range(8):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        code, kept = matchinglib.filterWithVFC(v1, v2, vdm, seed=1)
+        if i >= 2:
+            ts.append(time.perf_counter() - t0)
+    cb = None
+    if ovfc.ref_lib() is not None:
+        t0 = time.perf_counter(); rr = ovfc.filter_with_vfc(v1, v2, vmt, seed=1); dt_cpu = time.perf_counter() - t0
+        keep = np.zeros(len(vmt), bool); keep[np.searchsorted(vdm["queryIdx"], kept["queryIdx"])] = True
+        if rr[0] != code or not np.array_equal(keep, rr[1].astype(bool)):
+            raise RuntimeError("VFC: GPU kept set differs from the reference's")
+        cb = dict(value=len(vmt) / dt_cpu, unit="matches/s", cores=1, kind="reference", sample="the same call through the reference's vfc.cpp / vfcMatches.cpp (oracle/_ref/libvfc_ref.so), %.1f ms" % (dt_cpu * 1e3))
+    out["vfc_filter"] = dict(workload="filterWithVFC (SparseVFC, 16 control points, 50 EM iterations), %d matches, 50 %% outliers, host buffers in and out" % len(vmt),
+                             value=len(vmt) / float(np.median(ts)), unit="matches/s", ms_per_call=float(np.median(ts) * 1e3), kept=int(len(kept)),
+                             check="kept set identical to the reference's own vfc.cpp for the same rand() seed",
+                             note="bound by the reference's sequential float sums: 172 single-thread add chains per iteration, kept to reproduce its (numerically chaotic) result", cpu_baseline=cb)
     # USAC: uniform sampling needs a few hundred hypotheses on this scene, PROSAC a handful
     sc = datagen_pose.make_scene(10000, 0.5, seed=2)
     outl = ousac.sampson(sc["E"], sc["p1"], sc["p2"]) >= sc["th"] ** 2

@@ -230,8 +230,9 @@ int mpl_arrsac5pt(const double* p1, const double* p2, int n, double th, int refi
  *   match is in matches_out), *n_keep, *vfc_code = filterWithVFC's return value (0 ok, -1 fewer than 5 matches -- nothing kept,
  *   -2 fewer than 10 % kept: "Maybe VFC failed"), *n_iterations (may be NULL) = EM iterations run.  The set-up (normalisation,
  *   the rand()-driven choice of 16 control points) runs on the host as written, the kernel matrix and the EM iterations in one
- *   kernel launch.  Results agree with the reference within float tolerance (csrc/vfc.cu).  mpl_vfc_set_seed restarts the
- *   calling thread's rand() stream (the reference draws from the process' state; a fresh process is srand(1)). */
+ *   kernel launch that does the reference's float arithmetic in the reference's order (sequential sums, glibc's expf restated):
+ *   the kept set equals the reference's for the same rand() state (csrc/vfc.cu, tests/test_vfc_gpu.py).  mpl_vfc_set_seed
+ *   restarts the calling thread's rand() stream (the reference draws from the process' state; a fresh process is srand(1)). */
 int mpl_vfc_set_seed(unsigned seed);
 int mpl_vfc_filter(const void* kp1, int n1, size_t kp_stride1, const void* kp2, int n2, size_t kp_stride2, const mpl_dmatch* matches,
                    int n_matches, uint8_t* keep, int* n_keep, int* vfc_code, int* n_iterations);

@@ -102,15 +102,42 @@ __device__ __forceinline__ float seq_sum(float acc, int len, F term)
     return acc;
 }
 
-constexpr int kTile = 256, kTileLd = kTile + 1;          // row stride 257: the 16 rows of a tile fall into distinct banks
+// the same, with the operands of four consecutive matches fetched by one 16-byte shared-memory load per array (the sums are
+// bound by shared-memory wavefronts: six warps read the same tiles)
+template <class F4, class F1>
+__device__ __forceinline__ float seq_sum4(float acc, int len, F4 term4, F1 term1)
+{
+    int k = 0;
+    if (len >= 8) {
+        float4 a = term4(0), b = term4(4);                     // the terms of the NEXT eight matches are formed while the adds of these eight queue up
+        for (; k + 16 <= len; k += 8) {
+            const float4 na = term4(k + 8), nb = term4(k + 12);
+            acc = fadd(acc, a.x); acc = fadd(acc, a.y); acc = fadd(acc, a.z); acc = fadd(acc, a.w);
+            acc = fadd(acc, b.x); acc = fadd(acc, b.y); acc = fadd(acc, b.z); acc = fadd(acc, b.w);
+            a = na; b = nb;
+        }
+        acc = fadd(acc, a.x); acc = fadd(acc, a.y); acc = fadd(acc, a.z); acc = fadd(acc, a.w);
+        acc = fadd(acc, b.x); acc = fadd(acc, b.y); acc = fadd(acc, b.z); acc = fadd(acc, b.w);
+        k += 8;
+    }
+    for (; k < len; ++k) acc = fadd(acc, term1(k));
+    return acc;
+}
+__device__ __forceinline__ float4 ld4(const float* p, int k) { return *reinterpret_cast<const float4*>(p + k); }
+__device__ __forceinline__ float4 mul3(float4 p, float4 u, float4 w) { return make_float4(fmul(fmul(p.x, u.x), w.x), fmul(fmul(p.y, u.y), w.y), fmul(fmul(p.z, u.z), w.z), fmul(fmul(p.w, u.w), w.w)); }
+__device__ __forceinline__ float4 mul2(float4 p, float4 t) { return make_float4(fmul(p.x, t.x), fmul(p.y, t.y), fmul(p.z, t.z), fmul(p.w, t.w)); }
+
+constexpr int kSig = 960;                                 // matches per tile of the two sigma^2 sums (960 loader threads)
+constexpr int kTile = 256, kTileLd = kTile + 4;          // row stride 260: 16-byte aligned rows, a warp's 16 rows x 16 bytes = two wavefronts
 
 __global__ void __launch_bounds__(kVfcThreads)
 vfc_sparse_kernel(const VfcJob* __restrict__ job)
 {
-    __shared__ float sU[kCtrl][kTileLd], sP[kTile], sA[kTile], sB[kTile], sC[kTile], sD[kTile];
+    __shared__ __align__(16) float sU[2][kCtrl][kTileLd], sP[2][kTile], sA[2][kTile], sB[2][kTile], sC[2][kTile], sD[2][kTile];     // two tile buffers: warps 8.. load tile t + 1 while warps 0..7 sum tile t
     __shared__ float A[kCtrl][kCtrl], Bm[kCtrl][2], C[kCtrl][2], Ks[kCtrl][kCtrl], ctrl[kCtrl][2];
     __shared__ float s_sigma2, s_gamma, s_E, s_tecr, s_sumP, s_Esum, s_trace, s_sg, s_sp;
     __shared__ int s_iter, s_go, s_cnt, s_ok;
+    __shared__ long long s_clk[5];                  // thread 0's clocks per phase: posteriors, M-step sums, energy + solve, V, sigma^2 sums
     __shared__ unsigned long long tab[32];
     const VfcJob& J = *job;
     const int tid = threadIdx.x, n = J.n, m = J.m;
@@ -126,7 +153,7 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
         J.V[i] = make_float2(0.f, 0.f); J.P[i] = 1.f;
         J.T[i] = sqdist(y.x, y.y, 0.f, 0.f);
     }
-    if (tid == 0) { s_gamma = 0.9f; s_E = 1.f; s_tecr = 1.f; s_iter = 0; }
+    if (tid == 0) { s_gamma = 0.9f; s_E = 1.f; s_tecr = 1.f; s_iter = 0; for (int k = 0; k < 5; ++k) s_clk[k] = 0; }
     __syncthreads();
     // which of the 168 M-step sums this thread owns: tid < 136: (oi, oj), oi <= oj; tid < 168: row oi, column oj of U diag(P) Y
     int oi = 0, oj = 0;
@@ -142,6 +169,8 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
             if (!s_go) break;
         }
         const float sigma2 = first ? 1.f : s_sigma2, gamma = s_gamma, E_old = s_E;
+        long long c0 = clock64(), c1;
+        auto lap = [&](int k) { c1 = clock64(); if (tid == 0) s_clk[k] += c1 - c0; c0 = c1; };
         if (!first) {
             // ---- E-step, per match: getP (:490-505)
             const float temp2 = fmul(fmul(6.283185f, sigma2), (1.f - gamma)) / fmul(gamma, a_par);      // pow(x, 1.0f) == x
@@ -153,38 +182,66 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
                 J.Praw[i] = p; J.P[i] = fmaxf(minP, p); J.T[i] = t;
             }
             __syncthreads();
+            lap(0);
             // ---- the sequential sums of this half: 168 of calculateC_SparseVFC (:152-178), sum p and sum p t of getP, calculateTraceCKC
             float acc = 0.f;
-            for (int t0 = 0; t0 < n; t0 += kTile) {
+            auto load_tile = [&](int buf, int t0, int first_thread, int n_threads) {     // every global load is issued before the first shared store
+                const int len = min(kTile, n - t0), lt = tid - first_thread;
+                float v[6]; int idx[6];
+#pragma unroll
+                for (int q = 0; q < 6; ++q) {
+                    const int e = lt + q * n_threads, r = e / kTile, c = e - r * kTile;
+                    const bool ok = e < m * kTile && c < len;
+                    idx[q] = ok ? r * kTileLd + c : -1;
+                    v[q] = ok ? J.U[(size_t)r * n + t0 + c] : 0.f;
+                }
+                float p0 = 0.f, p1 = 0.f; float2 y = make_float2(0.f, 0.f);
+                const int c = lt & (kTile - 1);
+                const bool okA = lt < kTile && c < len, okB = lt >= kTile && lt < 2 * kTile && c < len;
+                if (okA) { p0 = J.P[t0 + c]; y = J.Y[t0 + c]; }
+                if (okB) { p0 = J.Praw[t0 + c]; p1 = J.T[t0 + c]; }
+#pragma unroll
+                for (int q = 0; q < 6; ++q) if (idx[q] >= 0) (&sU[buf][0][0])[idx[q]] = v[q];
+                if (okA) { sP[buf][c] = p0; sA[buf][c] = y.x; sB[buf][c] = y.y; }
+                if (okB) { sC[buf][c] = p0; sD[buf][c] = p1; }
+            };
+            load_tile(0, 0, 0, kVfcThreads);
+            __syncthreads();
+            int buf = 0;
+            for (int t0 = 0; t0 < n; t0 += kTile, buf ^= 1) {
                 const int len = min(kTile, n - t0);
-                for (int e = tid; e < m * kTile; e += kVfcThreads) { const int r = e / kTile, c = e - r * kTile; if (c < len) sU[r][c] = J.U[(size_t)r * n + t0 + c]; }
-                if (tid < len) { sP[tid] = J.P[t0 + tid]; const float2 y = J.Y[t0 + tid]; sA[tid] = y.x; sB[tid] = y.y; }
-                else if (tid >= kTile && tid - kTile < len) { sC[tid - kTile] = J.Praw[t0 + tid - kTile]; sD[tid - kTile] = J.T[t0 + tid - kTile]; }
-                __syncthreads();
-                if (live) {
-                    const float* ui = sU[oi];
-                    const float* w = is_y ? (oj ? sB : sA) : sU[oj];
-                    acc = seq_sum(acc, len, [&](int k) { return fmul(fmul(sP[k], ui[k]), w[k]); });
+                if (tid >= 256) { if (t0 + kTile < n) load_tile(buf ^ 1, t0 + kTile, 256, kVfcThreads - 256); }
+                else if (live) {
+                    const float* ui = sU[buf][oi];
+                    const float* w = is_y ? (oj ? sB[buf] : sA[buf]) : sU[buf][oj];
+                    const float* pp = sP[buf];
+                    acc = seq_sum4(acc, len, [&](int k) { return mul3(ld4(pp, k), ld4(ui, k), ld4(w, k)); }, [&](int k) { return fmul(fmul(pp[k], ui[k]), w[k]); });
                 } else if (tid == 192) {
-                    acc = seq_sum(acc, len, [&](int k) { return sC[k]; });
+                    const float* c = sC[buf];
+                    acc = seq_sum4(acc, len, [&](int k) { return ld4(c, k); }, [&](int k) { return c[k]; });
                 } else if (tid == 224) {
-                    acc = seq_sum(acc, len, [&](int k) { return fmul(sC[k], sD[k]); });
+                    const float* c = sC[buf]; const float* d = sD[buf];
+                    acc = seq_sum4(acc, len, [&](int k) { return mul2(ld4(c, k), ld4(d, k)); }, [&](int k) { return fmul(c[k], d[k]); });
                 }
                 __syncthreads();
             }
+            lap(1);
             if (tid < kSums) {
                 if (!is_y) { if (live) { acc = fadd(acc, fmul(fmul(lambda, sigma2), Ks[oi][oj])); A[oi][oj] = acc; A[oj][oi] = acc; } }
                 else if (live) Bm[oi][oj] = acc;
             } else if (tid == 192) s_sumP = acc;
             else if (tid == 224) s_Esum = acc;
-            else if (tid == 256) {
-                float tr = 0.f;
-                for (int i = 0; i < m; ++i) {
+            else if (tid >= 256 && tid < 288) {                // calculateTraceCKC: lane i forms row i's term, lane 0 adds the terms in row order
+                const int i = tid - 256;
+                float term = 0.f;
+                if (i < m) {
                     float t1 = 0.f, t2 = 0.f;
                     for (int j = 0; j < m; ++j) { t1 = fadd(t1, fmul(Ks[i][j], C[j][0])); t2 = fadd(t2, fmul(Ks[i][j], C[j][1])); }
-                    tr = fadd(tr, fadd(fmul(C[i][0], t1), fmul(C[i][1], t2)));
+                    term = fadd(fmul(C[i][0], t1), fmul(C[i][1], t2));
                 }
-                s_trace = tr;
+                float tr = 0.f;
+                for (int r = 0; r < m; ++r) { const float tv = __shfl_sync(0xffffffffu, term, r); tr = fadd(tr, tv); }
+                if (i == 0) s_trace = tr;
             }
             __syncthreads();
             if (tid == 64) {                                   // energy (:501-502, :110-112)
@@ -232,11 +289,16 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
                 if (lane < kCtrl) { C[lane][0] = (s_ok && lane < m) ? Bm[lane][0] : 0.f; C[lane][1] = (s_ok && lane < m) ? Bm[lane][1] : 0.f; }   // singular: cv::solve zeroes its output
             }
             __syncthreads();
+            lap(2);
             // ---- per match: calculateV (:432-444), the terms of calculateSigmaSquare (:383-392), calculateGamma's count (:369-381)
             int cnt = 0;
             for (int i = tid; i < n; i += kVfcThreads) {
                 float t1 = 0.f, t2 = 0.f;
-                for (int j = 0; j < m; ++j) { const float u = J.U[(size_t)j * n + i]; t1 = fadd(t1, fmul(u, C[j][0])); t2 = fadd(t2, fmul(u, C[j][1])); }
+                float u[kCtrl];
+#pragma unroll
+                for (int j = 0; j < kCtrl; ++j) u[j] = j < m ? J.U[(size_t)j * n + i] : 0.f;
+#pragma unroll
+                for (int j = 0; j < kCtrl; ++j) if (j < m) { t1 = fadd(t1, fmul(u[j], C[j][0])); t2 = fadd(t2, fmul(u[j], C[j][1])); }
                 J.V[i] = make_float2(t1, t2);
                 const float2 y = J.Y[i];
                 J.T[i] = sqdist(y.x, y.y, t1, t2);
@@ -244,20 +306,31 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
             }
             if (cnt) atomicAdd(&s_cnt, cnt);
             __syncthreads();
+            lap(3);
         }
         // ---- calculateSigmaSquare's two sequential sums (:383-392), 1024 matches per tile
         float a1 = 0.f;
-        for (int t0 = 0; t0 < n; t0 += kVfcThreads) {
-            const int len = min(kVfcThreads, n - t0);
-            float* sPP = &sU[0][0]; float* sTT = &sU[0][0] + kVfcThreads;                  // 2 x 1024 floats of the (idle) U tile
-            if (tid < len) { sPP[tid] = J.P[t0 + tid]; sTT[tid] = J.T[t0 + tid]; }
+        {
+            float* base = &sU[0][0][0];                                    // 2 x (1024 + 1024) floats of the (idle) U tile buffers
+            auto load2 = [&](int b, int t0, int first_thread) {
+                const int i = t0 + tid - first_thread;
+                if (tid >= first_thread && tid - first_thread < kVfcThreads - 64 && i < n && tid - first_thread < kSig) { base[b * 2 * kSig + tid - first_thread] = J.P[i]; base[b * 2 * kSig + kSig + tid - first_thread] = J.T[i]; }
+            };
+            load2(0, 0, 0);
             __syncthreads();
-            if (tid == 0) a1 = seq_sum(a1, len, [&](int k) { return fmul(sPP[k], sTT[k]); });
-            else if (tid == 32) a1 = seq_sum(a1, len, [&](int k) { return sPP[k]; });
-            __syncthreads();
+            int b = 0;
+            for (int t0 = 0; t0 < n; t0 += kSig, b ^= 1) {
+                const int len = min(kSig, n - t0);
+                const float* sPP = base + b * 2 * kSig; const float* sTT = sPP + kSig;
+                if (tid >= 64) { if (t0 + kSig < n) load2(b ^ 1, t0 + kSig, 64); }
+                else if (tid == 0) a1 = seq_sum4(a1, len, [&](int k) { return mul2(ld4(sPP, k), ld4(sTT, k)); }, [&](int k) { return fmul(sPP[k], sTT[k]); });
+                else if (tid == 32) a1 = seq_sum4(a1, len, [&](int k) { return ld4(sPP, k); }, [&](int k) { return sPP[k]; });
+                __syncthreads();
+            }
         }
         if (tid == 0) s_sg = a1; else if (tid == 32) s_sp = a1;
         __syncthreads();
+        lap(4);
         if (tid == 0) {
             s_sigma2 = s_sg / fmul(s_sp, 2.f);
             if (!first) { s_gamma = fmaxf(fminf((float)s_cnt / (float)n, 0.95f), 0.05f); s_iter = s_iter + 1; }
@@ -274,7 +347,7 @@ vfc_sparse_kernel(const VfcJob* __restrict__ job)
     for (int i = tid; i < n; i += kVfcThreads) { const bool k = none || J.P[i] > theta; J.keep[i] = k ? 1 : 0; kept += k ? 1 : 0; }
     if (kept) atomicAdd(&s_cnt, kept);
     __syncthreads();
-    if (tid == 0) { J.out[0] = s_cnt; J.out[1] = s_iter; }
+    if (tid == 0) { J.out[0] = s_cnt; J.out[1] = s_iter; for (int k = 0; k < 5; ++k) J.out[2 + k] = (int)(s_clk[k] >> 10); }
 }
 
 thread_local GlibcRand t_vfc_rng;
@@ -369,11 +442,12 @@ extern "C" int mpl_vfc_filter(const void* kp1, int n1, size_t kp_stride1, const 
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     char* h_keep = hs + o_u; int* h_out = (int*)(h_keep + al(nn));
     MPL_CUDA_CHECK(cudaMemcpyAsync(h_keep, D + o_keep, nn, cudaMemcpyDeviceToHost, st));
-    MPL_CUDA_CHECK(cudaMemcpyAsync(h_out, D + o_out, 8, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(h_out, D + o_out, 32, cudaMemcpyDeviceToHost, st));
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
     memcpy(keep, h_keep, nn);
     *n_keep = h_out[0];
     if (n_iterations) *n_iterations = h_out[1];
+    if (getenv("MPL_VFC_TRACE")) fprintf(stderr, "vfc: n %d, %d iterations, kilo-clocks: posteriors %d, M-step sums %d, energy + solve %d, V %d, sigma sums %d\n", n, h_out[1], h_out[2], h_out[3], h_out[4], h_out[5], h_out[6]);
     if ((double)*n_keep / (double)n < 0.1) *vfc_code = -2;                               // vfcMatches.cpp:82-83 "Maybe VFC failed"
     return MPL_OK;
 }
