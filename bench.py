@@ -881,6 +881,17 @@ def measure_tf32_peak(torch, dev):
 # the "next" rows of SURVEY 8(f) that are built: GMS post-filter (N4) and ARRSAC (N2), each next to the REFERENCE's own code
 # compiled into oracle/_ref (MatchGMS.cpp; the theia::Arrsac template)
 # ------------------------------------------------------------------------------------------------
+def _threaded_rate(fn, n_calls, n_threads):
+    """calls/s of fn(i) issued from a pool of host threads (the library keeps one context -- stream, scratch -- per host thread, so
+    independent calls overlap on the GPU; ctypes releases the GIL inside the call)."""
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(n_threads) as ex:
+        list(ex.map(fn, range(n_threads)))                      # first call of every thread creates its context
+        t0 = time.perf_counter()
+        list(ex.map(fn, range(n_calls)))
+        return n_calls / (time.perf_counter() - t0)
+
+
 def bench_next_rows(g):
     import datagen_gms, datagen_pose
     from matchinglib_poselib_b200 import matchinglib, poselib
@@ -940,6 +951,9 @@ def bench_next_rows(g):
                              value=len(vmt) / float(np.median(ts)), unit="matches/s", ms_per_call=float(np.median(ts) * 1e3), kept=int(len(kept)),
                              check="kept set identical to the reference's own vfc.cpp for the same rand() seed",
                              note="bound by the reference's sequential float sums: 172 single-thread add chains per iteration, kept to reproduce its (numerically chaotic) result", cpu_baseline=cb)
+    r32 = _threaded_rate(lambda i: matchinglib.filterWithVFC(v1, v2, vdm, seed=1), 128, 32)
+    out["vfc_filter"]["calls_per_s_32_host_threads"] = r32
+    out["vfc_filter"]["matches_per_s_32_host_threads"] = r32 * len(vmt)
     # USAC: uniform sampling needs a few hundred hypotheses on this scene, PROSAC a handful
     sc = datagen_pose.make_scene(10000, 0.5, seed=2)
     outl = ousac.sampson(sc["E"], sc["p1"], sc["p2"]) >= sc["th"] ** 2
@@ -963,6 +977,7 @@ def bench_next_rows(g):
                          ("PROSAC" if idx is not None else "uniform"), value=1.0 / float(np.median(ts)), unit="calls/s", ms_per_call=float(np.median(ts) * 1e3),
                          inliers=int(res["count"]), hypotheses=int(res["hyp_count"]), device_batches=int(res["n_batches"]), launches=int(res["n_launches"]),
                          note="latency-bound like ARRSAC: each device batch costs one 5-point solve latency; parity per seed in tests/test_usac_gpu.py", cpu_baseline=cb)
+        out[name]["calls_per_s_16_host_threads"] = _threaded_rate(lambda i: poselib.usac5pt(sc["p1"], sc["p2"], sc["th"], sorted_idx=idx, seed=i + 1), 128, 16)
     return out
 
 

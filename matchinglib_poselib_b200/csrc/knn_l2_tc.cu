@@ -49,7 +49,9 @@ constexpr int BN = 128;              // train rows per tile = UMMA N
 constexpr int SLAB_BYTES = 128;      // K extent of one smem slab in bytes (= swizzle width)
 constexpr int A_SLAB = BM * SLAB_BYTES;      // 32 KB
 constexpr int B_SLAB = BN * SLAB_BYTES;      // 16 KB
-constexpr int MAX_A_SLABS = 4;       // dim <= 128 floats (tf32) / 256 bf16
+constexpr int MAX_A_SLABS = 4;       // query block of BM rows: dim <= 128 floats (tf32) / 256 bf16
+constexpr int MAX_DIM = 256;         // wider rows (128 < dim <= 256) run with query blocks of UM rows: 8 tf32 slabs of 16 KB, one
+                                     // UMMA M block (issuer warp 3 and the m = 1 epilogue warps idle), same rings and lists
 constexpr int AUG_BYTES = 32;        // one extra K step per row: |t|^2 split in three exact pieces (B), ones (A)
 constexpr int A_AUG = BM * AUG_BYTES;                        //  8 KB
 constexpr int STAGE_BYTES = B_SLAB + BN * AUG_BYTES;         // 20 KB: one B slab (+ the tile's aug slab beside slab 0)
@@ -289,9 +291,10 @@ struct TcParams {
     int nq, nt, NT;                  // NT = train tiles of BN rows
     long long U;                     // work units = query blocks x train tiles
     int max_slots;                   // candidate slots per query block
+    int rq;                          // query rows per block: BM, or UM for 128 < dim <= MAX_DIM (one UMMA M block per CTA)
     int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
-    uint4* cand;                     // [qblock][slot][LPS][BM rows][2 x uint4] = 4 scores + 4 train indices
-    uint32_t* gthr;                  // [NQB * BM] per query: smallest list threshold any CTA has published (order-preserving uint)
+    uint4* cand;                     // [qblock][slot][LPS][rq rows][2 x uint4] = 4 scores + 4 train indices
+    uint32_t* gthr;                  // [NQB * rq] per query: smallest list threshold any CTA has published (order-preserving uint)
     const TcHeader* hdr;
 };
 
@@ -517,7 +520,7 @@ __device__ __forceinline__ unsigned group_mask32(const uint32_t (&r)[32], float 
 // Accumulators are handed over per M block: t_full / t_empty index = accumulator buffer * 2 + m; a B slab is released
 // when BOTH issuers' MMAs on it have retired (b_empty counts 2 commits), likewise the resident A block (a_empty).
 template <int MODE, int SPS>   // MODE 0 = bf16 (kind::f16), 1 = tf32; SPS = K slabs per B ring stage (one barrier round trip per stage)
-__device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_addr, uint32_t aa_addr,
+__device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_slab16, uint32_t a_addr, uint32_t aa_addr,
                                                uint32_t b_addr, uint32_t tmem_base, uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full,
                                                uint64_t* b_empty, uint64_t* t_full, uint64_t* t_empty)
 {
@@ -561,7 +564,7 @@ __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1
 #pragma unroll
                 for (int j = 0; j < SPS; ++j) {
                     const uint64_t bd = hi128 | (uint64_t)((sb + j * B_SLAB) >> 4);
-                    const uint64_t ad = ad0 + (uint64_t)((s + j) * (A_SLAB >> 4));
+                    const uint64_t ad = ad0 + (uint64_t)((uint32_t)(s + j) * a_slab16);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {                                // 4 x 32 bytes of K per slab row
                         if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
@@ -602,14 +605,14 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
     const uint32_t partner = share_s + 8u * (uint32_t)((hf ^ 1) * BM + m * UM + row);
     int tile = (int)(u0 - (u0 / p.NT) * p.NT);
     S.qb = (int)(u0 / p.NT);
-    S.gq = p.gthr + (size_t)S.qb * BM + m * UM + row;
+    S.gq = p.gthr + (size_t)S.qb * p.rq + m * UM + row;
     unsigned it = 0;
     auto flush = [&]() {
         epi_drain(S);
         const int slot = (int)blockIdx.x - tc_owner((long long)S.qb * p.NT, p.U, G);
-        S.L.store(p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * BM + m * UM + row) * 2);
+        S.L.store(p.cand + ((((size_t)S.qb * p.max_slots + slot) * LPS + hf) * p.rq + m * UM + row) * 2);
         S.L.reset(); S.thr = INFINITY; S.ext = INFINITY; S.gpub = INFINITY;
-        S.gq += BM;                                                              // flush() ends a query block
+        S.gq += p.rq;                                                            // flush() ends a query block
     };
     const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + m * 128 + hf * 64;
 #ifdef MPL_TC_TRACE
@@ -719,12 +722,14 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     const CUtensorMap* mapB = tf32 ? &maps.b32 : &maps.b16;
     const CUtensorMap* mapAa = tf32 ? &maps.aa32 : &maps.aa16;
     const CUtensorMap* mapBa = tf32 ? &maps.ba32 : &maps.ba16;
-    unsigned char* sA = smem;                                    // n_slabs x 32 KB
-    unsigned char* sAa = smem + n_slabs * A_SLAB;                // 8 KB
-    unsigned char* sB = sAa + A_AUG;                             // ring of n_stages x 20 KB
+    const bool wide = p.rq == UM;                                // 128 < dim <= 256: query blocks of one UMMA M block
+    const int a_slab = p.rq * SLAB_BYTES, a_aug = p.rq * AUG_BYTES;
+    unsigned char* sA = smem;                                    // n_slabs x 32 KB (wide: 16 KB)
+    unsigned char* sAa = smem + n_slabs * a_slab;                // 8 KB (wide: 4 KB)
+    unsigned char* sB = sAa + a_aug;                             // ring of n_stages x 20 KB
     // B ring stage = `sps` K slabs of one train tile + the tile's aug slab; two slabs per stage (a whole tile at dim <= 128
     // in bf16 mode) when at least 3 such stages fit: half the barrier round trips and commits on the issuers' critical path
-    const int ring_bytes = SMEM_DATA - n_slabs * A_SLAB - A_AUG;
+    const int ring_bytes = SMEM_DATA - n_slabs * a_slab - a_aug;
     const int sps = ((n_slabs & 1) == 0 && ring_bytes / (2 * B_SLAB + BN * AUG_BYTES) >= 3) ? 2 : 1;
     const int stage_bytes = sps * B_SLAB + BN * AUG_BYTES;
     int n_stages = ring_bytes / stage_bytes;
@@ -739,8 +744,9 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
         asm volatile("prefetch.tensormap [%0];" ::"l"(mapBa) : "memory");
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(a_full, 1); mbar_init(a_empty, 2);                 // *_empty: one commit per MMA issuer warp
-        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 2); }
+        const uint32_t n_issuers = wide ? 1u : 2u;
+        mbar_init(a_full, 1); mbar_init(a_empty, n_issuers);         // *_empty: one commit per MMA issuer warp
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], n_issuers); }
         for (int b = 0; b < 4; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], EPI_WARPS / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -764,9 +770,9 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
             if (qb != cur_qb) {
                 mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));                 // MMAs of the previous query block are done
                 if (elect_one()) {
-                    mbar_expect_tx(a_full, (uint32_t)(n_slabs * A_SLAB + A_AUG));
-                    for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * A_SLAB, mapA, s * KS, qb * BM, a_full);
-                    tma_load_2d(sAa, mapAa, 0, qb * BM, a_full);
+                    mbar_expect_tx(a_full, (uint32_t)(n_slabs * a_slab + a_aug));
+                    for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * a_slab, mapA, s * KS, qb * p.rq, a_full);
+                    tma_load_2d(sAa, mapAa, 0, qb * p.rq, a_full);
                 }
                 __syncwarp();
                 ++a_cnt; cur_qb = qb;
@@ -783,16 +789,16 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
                 if (++stage == n_stages) { stage = 0; sphase ^= 1; }
             }
         }
-    } else if (warp == 1 || warp == 3) {
+    } else if (warp == 1 || (warp == 3 && !wide)) {
         // ===== MMA issuers: warp 1 -> UMMA M block 0, warp 3 -> M block 1 =====
         const int m = warp >> 1;
-#define MPL_ISSUE(MODE, SPS) mma_issue_loop<MODE, SPS>(m, u0, u1, p.NT, n_slabs, n_stages, smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base, \
+#define MPL_ISSUE(MODE, SPS) mma_issue_loop<MODE, SPS>(m, u0, u1, p.NT, n_slabs, n_stages, (uint32_t)(a_slab >> 4), smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base, \
                                                        a_full, a_empty, b_full, b_empty, t_full, t_empty)
         if (tf32) { if (sps == 2) MPL_ISSUE(1, 2); else MPL_ISSUE(1, 1); }
         else      { if (sps == 2) MPL_ISSUE(0, 2); else MPL_ISSUE(0, 1); }
 #undef MPL_ISSUE
-    } else if (warp >= 4) {
-        // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile =====
+    } else if (warp >= 4 && !(wide && (((warp - 4) >> 2) & 1))) {
+        // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile (wide: m = 0 only) =====
         // Exact-integer mode (bf16-exact integer data, e.g. OpenCV SIFT): the scores are exact, so sorted top-2 lists give
         // the exact answer and no certificate margin is needed -- half as many insertions as the general top-4 lists.
         if (!tf32 && p.hdr->not_integer == 0)
@@ -847,7 +853,7 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float* __restrict__ t, int nt, size_t t_ld, int dim,
                   const float* __restrict__ qnorm, const uint4* __restrict__ cand, int NT, long long U, int G, int max_slots,
-                  long long train_offset, TcHeader* hdr, mpl_key64* __restrict__ keys_out, int* __restrict__ fallback_list)
+                  long long train_offset, TcHeader* hdr, mpl_key64* __restrict__ keys_out, int* __restrict__ fallback_list, int rq)
 {
     if (hdr->not_bf16_exact == 0 && hdr->not_integer == 0) {
         // Exact-integer mode (the ranking kernel kept top-2 lists): every value is an integer that bf16 holds exactly.  If
@@ -858,14 +864,14 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         // records.  A query outside the bound cannot be certified from top-2 lists and takes the exact scan.
         const int q1 = blockIdx.x * blockDim.x + threadIdx.x;
         if (q1 >= nq) return;
-        const int qb1 = q1 / BM, row1 = q1 - qb1 * BM;
+        const int qb1 = q1 / rq, row1 = q1 - qb1 * rq;
         const int f1 = tc_owner((long long)qb1 * NT, U, G), l1 = tc_owner((long long)qb1 * NT + NT - 1, U, G);
         const float qq1 = qnorm[q1];
         const float sq1 = sqrtf(qq1), st1 = sqrtf(__uint_as_float(hdr->max_tnorm_bits));
         if (!((sq1 + st1) * (sq1 + st1) < 16777216.f * 0.999f)) { fallback_list[atomicAdd(&hdr->fallback_count, 1u)] = q1; return; }
         mpl_key64 k0 = MPL_KEY_INVALID, k1 = MPL_KEY_INVALID;
         for (int sl = 0; sl < (l1 - f1 + 1) * LPS; ++sl) {
-            const uint4* rec = cand + (((size_t)qb1 * max_slots * LPS + sl) * BM + row1) * 2;
+            const uint4* rec = cand + (((size_t)qb1 * max_slots * LPS + sl) * rq + row1) * 2;
             const uint4 sc = rec[0], id = rec[1];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
@@ -884,7 +890,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
-    const int qb = qi / BM, row = qi - qb * BM;
+    const int qb = qi / rq, row = qi - qb * rq;
     const int first = tc_owner((long long)qb * NT, U, G), last = tc_owner((long long)qb * NT + NT - 1, U, G);
     const int n_cand = (last - first + 1) * LPS * NC;          // lists of this query block are contiguous: (slot, half)
     const float qq = qnorm[qi];
@@ -899,7 +905,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
     float s_a = INFINITY, s_b = INFINITY, tau = INFINITY;
     for (int c = lane; c < n_cand; c += 32) {
         const int slot = c / NC, e = c - slot * NC;
-        const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
+        const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * rq + row) * 2;
         const uint4 sc = rec[0];
         const float s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
         if (e == nc - 1) tau = fminf(tau, s);
@@ -922,7 +928,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         int ti = -1; float s = INFINITY;
         if (c < n_cand) {
             const int slot = c / NC, e = c - slot * NC;
-            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * BM + row) * 2;
+            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + slot) * rq + row) * 2;
             const uint4 sc = rec[0], id = rec[1];
             s = __uint_as_float(e == 0 ? sc.x : e == 1 ? sc.y : e == 2 ? sc.z : sc.w);
             ti = (int)(e == 0 ? id.x : e == 1 ? id.y : e == 2 ? id.z : id.w);
@@ -954,7 +960,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
 
 // ---- host side ------------------------------------------------------------------------------------------
 struct TcPlan {
-    int NQB, NT, G, max_slots, kp16, kp32;
+    int NQB, NT, G, max_slots, kp16, kp32, rq;
     long long U;
     size_t off_tnorm, off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_list, off_part, off_gthr, total;
 };
@@ -964,7 +970,8 @@ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 TcPlan make_plan(int nq, int nt, int dim, int sm_count)
 {
     TcPlan P;
-    P.NQB = (nq + BM - 1) / BM;
+    P.rq = dim > 128 ? UM : BM;
+    P.NQB = (nq + P.rq - 1) / P.rq;
     P.NT = (nt + BN - 1) / BN;
     P.U = (long long)P.NQB * P.NT;
     P.G = (int)(P.U < sm_count ? P.U : sm_count);
@@ -977,15 +984,15 @@ TcPlan make_plan(int nq, int nt, int dim, int sm_count)
     }
     size_t o = 256;
     P.off_tnorm = o; o = align256(o + (size_t)P.NT * BN * 4);
-    P.off_qnorm = o; o = align256(o + (size_t)P.NQB * BM * 4);
+    P.off_qnorm = o; o = align256(o + (size_t)P.NQB * P.rq * 4);
     P.off_tp = o;    o = align256(o + (size_t)nt * P.kp32 * 4);
     P.off_qp = o;    o = align256(o + (size_t)nq * P.kp32 * 4);
     P.off_taug = o;  o = align256(o + (size_t)P.NT * BN * AUG_BYTES);
     P.off_qaug = o;  o = align256(o + (size_t)nq * AUG_BYTES);
-    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * BM * 32);
+    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * P.rq * 32);
     P.off_list = o;  o = align256(o + (size_t)nq * 4);
     P.off_part = o;  o = align256(o + mpl_l2_list_scratch_entries(nq, sm_count) * 16);
-    P.off_gthr = o;  o = align256(o + (size_t)P.NQB * BM * 4);
+    P.off_gthr = o;  o = align256(o + (size_t)P.NQB * P.rq * 4);
     P.total = o;
     return P;
 }
@@ -1018,7 +1025,7 @@ int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int elt_bytes, void* ba
 
 }  // namespace
 
-bool mpl_l2tc_supported(int nq, int nt, int dim) { return nq >= 1 && nt >= 2 && dim >= 1 && dim <= 128; }
+bool mpl_l2tc_supported(int nq, int nt, int dim) { return nq >= 1 && nt >= 2 && dim >= 1 && dim <= MAX_DIM; }
 
 size_t mpl_l2tc_scratch_bytes(int nq, int nt, int dim, int sm_count)
 {
@@ -1049,13 +1056,13 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     alignas(64) TcMaps maps;
     int rc;
     const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, F32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
-    if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, BM))) return rc;
+    if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, P.rq))) return rc;
     if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, nt, 64, BN))) return rc;
-    if ((rc = encode_map(&maps.a32, F32, 4, qp, P.kp32, nq, 32, BM))) return rc;
+    if ((rc = encode_map(&maps.a32, F32, 4, qp, P.kp32, nq, 32, P.rq))) return rc;
     if ((rc = encode_map(&maps.b32, F32, 4, tp, P.kp32, nt, 32, BN))) return rc;
-    if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
     if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, P.NT * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
-    if ((rc = encode_map(&maps.aa32, F32, 4, qaug, 8, nq, 8, BM, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_map(&maps.aa32, F32, 4, qaug, 8, nq, 8, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
     if ((rc = encode_map(&maps.ba32, F32, 4, taug, 8, P.NT * BN, 8, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
 
     MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
@@ -1063,7 +1070,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MplProfScope prof(MPL_PROF_L2_PREP, st);
         const int rows = P.NT * BN + nq;
         int blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;      // 4 rows per warp and iteration
-        l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr, gthr, P.NQB * BM);
+        l2_prep_bf16_kernel<<<blocks, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp16, tnorm, P.NT * BN, qnorm, taug, qaug, hdr, gthr, P.NQB * P.rq);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         l2_prep_tf32_kernel<<<sm_count * 8, 256, 0, st>>>(d_t, nt, t_ld, d_q, nq, q_ld, dim, tp, qp, P.kp32, tnorm, P.NT * BN, taug, qaug, hdr);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
@@ -1071,7 +1078,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     {
         MplProfScope prof(MPL_PROF_L2_TC, st);
         TcParams prm;
-        prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots;
+        prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
         prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
         l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
@@ -1079,8 +1086,8 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     {
         MplProfScope prof(MPL_PROF_L2_RERANK, st);
         const int blocks = (nq + 7) / 8;
-        if (sqrt_out) l2_certify_kernel<1><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist);
-        else          l2_certify_kernel<0><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist);
+        if (sqrt_out) l2_certify_kernel<1><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist, P.rq);
+        else          l2_certify_kernel<0><<<blocks, 256, 0, st>>>(d_q, nq, q_ld, d_t, nt, t_ld, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots, train_offset, hdr, d_keys_out, flist, P.rq);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
     return mpl_launch_l2_exact_list(d_q, flist, &hdr->fallback_count, q_ld, d_t, nt, t_ld, dim, sqrt_out ? 1 : 0, train_offset, part,

@@ -156,7 +156,10 @@ def _tc(m, q, t, sqrt_out=False):
 
 @pytest.mark.parametrize("nq,nt,d,kind", [(5, 2, 128, "sift"), (256, 128, 128, "sift"), (257, 129, 128, "sift"), (300, 40000, 128, "sift"),
                                            (5000, 5000, 128, "sift"), (700, 9000, 64, "sift"), (640, 3000, 120, "signed"),
-                                           (1000, 20000, 128, "signed"), (513, 2050, 33, "signed"), (400, 1111, 7, "signed")])
+                                           (1000, 20000, 128, "signed"), (513, 2050, 33, "signed"), (400, 1111, 7, "signed"),
+                                           # 128 < dim <= 256 (DAISY is 200-d): query blocks of 128 rows, up to 8 tf32 K slabs
+                                           (129, 300, 129, "signed"), (700, 6000, 200, "signed"), (1000, 9000, 256, "signed"),
+                                           (5, 2, 200, "sift"), (300, 5000, 192, "sift"), (1100, 7000, 256, "sift"), (257, 1000, 130, "sift")])
 def test_l2_tc_path(m, nq, nt, d, kind):
     q, t = datagen.sift_like(nq, nt, d, seed=nq + nt) if kind == "sift" else datagen.signed_float(nq, nt, d, seed=nq + nt)
     idx, dist, fb, mode = _tc(m, q, t)
@@ -165,6 +168,19 @@ def test_l2_tc_path(m, nq, nt, d, kind):
     assert np.array_equal(dist.view(np.int32), od.view(np.int32)), (nq, nt, d)
     assert np.array_equal(idx, oi)
     assert fb <= max(4, nq // 20), "certificate failed for %d of %d queries" % (fb, nq)
+
+
+def test_l2_wide_rows_take_the_tensor_core_path_by_default(m):
+    """DAISY-like 200-d rows, large enough for the default path to choose the tensor cores: LINEAR and BRUTEFORCENMS order vs the oracle."""
+    q, t = datagen.signed_float(3000, 4000, 200, seed=200)
+    for mode in (0, 1):
+        import ctypes
+        idx, dist = m.knn2_l2(q, t, 2, bool(mode))
+        fb, tf = ctypes.c_uint(0), ctypes.c_uint(0)
+        m._lib.check(m._lib.load().mpl_knn_l2_last_stats_host(ctypes.byref(fb), ctypes.byref(tf)), "stats")
+        assert tf.value == 1 and fb.value <= 150
+        oi, od = orc.knn_l2(q, t, 2, mode, threads=8)
+        assert np.array_equal(dist.view(np.int32), od.view(np.int32)) and np.array_equal(idx, oi)
 
 
 def test_l2_tc_sqrt_mode(m):
