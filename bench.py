@@ -931,6 +931,22 @@ def bench_next_rows(g):
                          ms_per_call=float(np.median(ts) * 1e3), inliers=int(res["count"]), hypotheses=int(res["n_hypotheses"]), device_batches=int(res["n_batches"]),
                          note="latency-bound: every device batch waits for one 5-point solve (~1.2 ms of dependent fp64 work); parity with the reference is statistical",
                          cpu_baseline=cb)
+    # LMedS: the third method of estimateEssentialMat (134 fixed samples, per-model median of all errors)
+    from oracle import ransac as oransac
+    sc = datagen_pose.make_scene(10000, 0.35, seed=4)
+    smp = datagen_pose.draw_samples_fast(10000, oransac.lmeds_niters(0.999, 2000), 9)
+    ts, res = [], None
+    for i in range(7):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        res = poselib.lmeds5pt(sc["p1"], sc["p2"], smp)
+        if i >= 2:
+            ts.append(time.perf_counter() - t0)
+    t0 = time.perf_counter(); o = oransac.lmeds5pt(sc["p1"], sc["p2"], smp); dt_cpu = time.perf_counter() - t0
+    out["lmeds"] = dict(workload="estimateEssentialMat(method = LMEDS): 134 samples, 10000 correspondences, 35 % outliers, host buffers in and out",
+                        value=1.0 / float(np.median(ts)), unit="calls/s", ms_per_call=float(np.median(ts) * 1e3), inliers=int(res["count"]),
+                        check="same sample selected as the oracle: %s; inliers %d vs %d" % (abs(res["min_median"] - o["min_median"]) <= 1e-6 * o["min_median"], res["count"], o["count"]),
+                        cpu_baseline=dict(value=1.0 / dt_cpu, unit="calls/s", cores=1, kind="port",
+                                          sample="the C restatement of runLMeDS on the same samples, single thread as the reference runs it, %.1f ms" % (dt_cpu * 1e3)))
     # VFC post-filter (second half): getMatches(VFCrefine = true)
     v1, v2, vmt, vinl = datagen_vfc.scene(8000, 0.5, seed=3)
     vdm = np.zeros(len(vmt), matchinglib.DMATCH_DTYPE); vdm["queryIdx"] = vmt[:, 0]; vdm["trainIdx"] = vmt[:, 1]; vdm["distance"] = 1

@@ -120,7 +120,7 @@ inline int filterMatchesGMS(const std::vector<cv::KeyPoint>& keypoints1, const c
 namespace poselib {
 
 // pose_estim.cpp:857-890 -> findEssentialMat (five-point-nister/five-point.cpp:69-148), methods "ARRSAC" (the default;
-// runARRSAC + robustEssentialRefine on the GPU, mpl_arrsac5pt) and "RANSAC".
+// runARRSAC + robustEssentialRefine on the GPU, mpl_arrsac5pt), "RANSAC" and "LMEDS" (runLMeDS, mpl_lmeds5pt; no refinement, :874-877).
 // p1, p2: n x 2 (or n x 1 2-channel) camera-normalised points of any depth; E: 3 x 3 CV_64F (stacked 3k x 3 when
 // n == 5); mask: 1 x n CV_8U.
 inline bool estimateEssentialMat(cv::OutputArray E, cv::InputArray p1, cv::InputArray p2, const std::string& method = "ARRSAC",
@@ -130,11 +130,9 @@ inline bool estimateEssentialMat(cv::OutputArray E, cv::InputArray p1, cv::Input
         std::cout << "USAC must be executed by function estimateEssentialOrPoseUSAC as it needs additional paramters! Exiting." << std::endl;
         std::exit(1);
     }
-    if (method != "RANSAC" && method != "ARRSAC") {
-        // :883-887 exits for unknown strings; LMEDS is served by the reference but not by this library -- fail the call
-        // instead of terminating the caller's process
-        std::cout << "Method " << method << " is not served by the B200 hot path (ARRSAC, RANSAC)." << std::endl;
-        return false;
+    if (method != "RANSAC" && method != "ARRSAC" && method != "LMEDS") {         // :883-887
+        std::cout << "Either there is a typo in the specified robust estimation method or the method is not supported. Exiting." << std::endl;
+        std::exit(1);
     }
     cv::Mat points1 = p1.getMat().clone(), points2 = p2.getMat().clone();        // five-point.cpp:77-78 deep copies
     const int npoints = points1.checkVector(2);

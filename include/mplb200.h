@@ -196,9 +196,18 @@ int    mpl_knn2_l2f32_dev(const void* d_q, int nq, size_t q_ld, const void* d_t,
  *   n_models[h], counts[<=10h], errsums[<=10h].
  * mpl_estimate_essential_api mirrors poselib::estimateEssentialMat(E, p1, p2, "RANSAC", threshold, refine, mask)
  *   (MP/poselib/source/pose_estim.cpp:857-890 -> findEssentialMat five-point.cpp:69-148): returns 1/0 like the
- *   reference's bool (negative MPL_ERR_* on failure; MPL_ERR_ASSERT where CV_Assert would throw).  method "RANSAC" or
- *   "ARRSAC" (the reference's default, mpl_arrsac5pt); "LMEDS" / "USAC" / anything else is refused -- no CPU fallback.
- *   n == 5: solver only, *n_E models stacked in E_out. */
+ *   reference's bool (negative MPL_ERR_* on failure; MPL_ERR_ASSERT where CV_Assert would throw).  method "RANSAC",
+ *   "ARRSAC" (the reference's default, mpl_arrsac5pt) or "LMEDS" (mpl_lmeds5pt; refine is ignored like in the reference,
+ *   pose_estim.cpp:874-877); "USAC" (the reference exits, pose_estim.cpp:878-887; use mpl_usac5pt) / anything else is
+ *   refused -- no CPU fallback.  n == 5: solver only, *n_E models stacked in E_out.
+ * mpl_lmeds5pt replaces CvModelEstimator3::runLMeDS (modelest.cpp:483-564) as findEssentialMat calls it
+ *   (five-point.cpp:124-128: prob 0.999, maxIters 2000): a fixed number of minimal samples (round(log(1 - conf) /
+ *   log(1 - 0.55^5)) in [3, max_iters] = 134; samples: h x 5 PRE-DRAWN, or NULL to draw that many inside like getSubset),
+ *   per model the median of the n float Sampson errors (sorted through their bit patterns as ints, even n: float sum of
+ *   the two middle values times 0.5), strict '<' keeps the first minimal model, sigma = 2.5 * 1.4826 * (1 + 5 / (n - 5)) *
+ *   sqrt(min median), at least 0.001, and findInliers with sigma.  No refit.  Outputs: E[9], mask[n], *n_inl (the reference's
+ *   result is n_inl >= 5; 0 with *min_median = DBL_MAX: no model had a finite median), optional *min_median, *sigma,
+ *   medians[<= 10 h] in evaluation order, n_models[h].  n > 5 (n == 5 is findEssentialMat's solver-only branch). */
 int mpl_ransac_set_seed(unsigned long long seed);
 /* Experiment switch, default 0 = the reference's 300 Durand-Kerner sweeps (cv::solvePoly, five-point.cpp:430).  1: the
  * minimal solver stops once a sweep moved every root by less than 2^-40 relative (DESIGN.md 4.4 reports the measured
@@ -210,6 +219,8 @@ int mpl_ransac5pt(const double* p1, const double* p2, int n, const int32_t* samp
                   double* models, int32_t* n_models, int32_t* counts, double* errsums);
 int mpl_estimate_essential_api(const double* p1, const double* p2, int n, const char* method, double threshold,
                                int refine, double* E_out, int* n_E, uint8_t* mask);
+int mpl_lmeds5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double conf, int max_iters,
+                 double* E, uint8_t* mask, int* n_inl, double* min_median, double* sigma, double* medians, int32_t* n_models);
 /* mpl_arrsac5pt replaces CvModelEstimator3::runARRSAC (MP/poselib/source/five-point-nister/modelest.cpp:197-341) -- what
  *   poselib::estimateEssentialMat runs for its DEFAULT method "ARRSAC" (pose_estim.cpp:866-869): theia::Arrsac
  *   (MP/poselib/include/arrsac/arrsac.h:206-545: PROSAC-ordered initial hypotheses verified by SPRT on the first block of

@@ -8,6 +8,6 @@ Everything computes in lib/libmplb200.so (hand-written CUDA, C ABI in include/mp
 """
 from . import _lib, matchinglib, poselib  # noqa: F401
 from .matchinglib import filterMatchesGMS, getCorrespondences, getMatches, getMatchesArray, knn2_hamming, knn2_l2, pinned_array  # noqa: F401
-from .poselib import estimateEssentialMat, ransac5pt  # noqa: F401
+from .poselib import estimateEssentialMat, lmeds5pt, ransac5pt  # noqa: F401
 
-__all__ = ["filterMatchesGMS", "getCorrespondences", "pinned_array", "getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib", "poselib", "estimateEssentialMat", "ransac5pt"]
+__all__ = ["filterMatchesGMS", "getCorrespondences", "pinned_array", "getMatches", "getMatchesArray", "knn2_hamming", "knn2_l2", "matchinglib", "poselib", "estimateEssentialMat", "ransac5pt", "lmeds5pt"]

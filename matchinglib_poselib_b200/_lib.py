@@ -86,6 +86,8 @@ SIGNATURES = {
     "mpl_ransac5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_double, c_int,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_estimate_essential_api": (c_int, [c_void_p, c_void_p, c_int, c_char_p, c_double, c_int, c_void_p, c_void_p, c_void_p]),
+    "mpl_lmeds5pt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                             c_void_p, c_void_p]),
     "mpl_arrsac_set_seed": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong]),
     "mpl_arrsac5pt": (c_int, [c_void_p, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpl_vfc_set_seed": (c_int, [ctypes.c_uint]),

@@ -12,6 +12,9 @@ int mpl_launch_compact_models(const double* models, const int32_t* n_models, int
 int mpl_launch_sampson_score(const double* models, int m, const void* corr, int n, double th, int32_t* counts,
                              double* errsums /* may be null */, cudaStream_t st);
 
+// LMedS: median of the n float Sampson errors of every model (modelest.cpp:537-542); inlier mask + count of one model
+int mpl_launch_lmeds_medians(const double* models, int m, const void* corr, int n, double* medians, cudaStream_t st);
+int mpl_launch_inlier_mask(const double* model, const void* corr, int n, double th, uint8_t* mask, int* count, cudaStream_t st);
 
 // ---- ransac_batch.cu: device-driven RANSAC for a batch of pairs (no host round trip) -----------------------------------
 // One record per pair.  Written by the gather kernel (pipeline.cu) or by the host (mpl_ransac5pt's refit), advanced by the

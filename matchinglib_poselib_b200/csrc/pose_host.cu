@@ -249,6 +249,82 @@ int mpl_ransac_run_locked(MplCtx* ctx, int n, int h_use, double th, int max_iter
     return MPL_OK;
 }
 
+// ---- runLMeDS (modelest.cpp:483-564) ------------------------------------------------------------------
+// niters = round(log(1 - conf) / log(1 - (1 - 0.45)^5)) clamped to [3, max_iters] (:518-519; 134 for the 0.999 / 2000 that
+// findEssentialMat passes, five-point.cpp:126): a FIXED number of minimal samples, each model's median of the n float errors,
+// strict '<' keeps the first minimal model, then sigma = 2.5 * 1.4826 * (1 + 5 / (n - 5)) * sqrt(minMedian) (>= 0.001) and
+// findInliers with it; result = count >= 5.  No refit.  One solve launch, one median launch (CTA per model), one mask launch.
+static int lmeds_niters(double conf, int max_iters)
+{
+    int niters = (int)std::round(std::log(1. - conf) / std::log(1. - std::pow(1. - 0.45, 5.0)));
+    niters = std::max(niters, 3);
+    return std::min(niters, max_iters);
+}
+
+extern "C" int mpl_lmeds5pt(const double* p1, const double* p2, int n, const int32_t* samples, int h, double conf, int max_iters,
+                            double* E, uint8_t* mask, int* n_inl, double* min_median, double* sigma_out, double* medians_out,
+                            int32_t* n_models_out)
+{
+    if (!p1 || !p2 || n < 5 || h < 0 || !E || !n_inl || max_iters < 0) { mpl_set_error("mpl_lmeds5pt: bad argument"); return MPL_ERR_BAD_ARG; }
+    *n_inl = 0;
+    if (min_median) *min_median = DBL_MAX;
+    if (n == 5) { mpl_set_error("mpl_lmeds5pt: n == 5 is the solver-only case of findEssentialMat (mpl_estimate_essential_api)"); return MPL_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> g(mpl_ctx_mutex());
+    int rc = mpl_ensure_ctx_locked();
+    if (rc) return rc;
+    MplCtx* ctx = mpl_ctx();
+    cudaStream_t st = ctx->stream;
+    std::vector<int32_t> drawn;
+    if (!samples) {
+        h = lmeds_niters(conf, max_iters);
+        drawn.resize((size_t)5 * (h > 0 ? h : 1));
+        int nd = 0;
+        if ((rc = mpl_ransac_draw_samples(p1, p2, n, h, drawn.data(), &nd))) return rc;
+        h = nd; samples = drawn.data();
+    }
+    if (h == 0) return MPL_OK;
+    RansacBufs R;
+    if ((rc = ransac_bufs_locked(ctx, n, h, R))) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_p1, p1, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_p2, p2, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(R.d_samples, samples, (size_t)h * 20, cudaMemcpyHostToDevice, st));
+    if ((rc = mpl_launch_pack_corr(R.d_p1, R.d_p2, n, R.d_corr, st))) return rc;
+    const size_t m_max = (size_t)10 * h;
+    const size_t o_med = (((size_t)h + 1) * 4 + 15) & ~(size_t)15;
+    char* h_stage = nullptr;
+    if ((rc = mpl_stage_ensure(o_med + m_max * 8 + 64, (void**)&h_stage))) return rc;
+    int32_t* off = (int32_t*)h_stage; double* med = (double*)(h_stage + o_med);
+    if ((rc = mpl_launch_fivept_solve(R.d_corr, n, R.d_samples, h, R.d_models, R.d_nm, st))) return rc;
+    if ((rc = mpl_launch_compact_models(R.d_models, R.d_nm, h, R.d_off, R.d_dense, st))) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(off, R.d_off, ((size_t)h + 1) * 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    const int m = off[h];
+    if (m < 0 || (size_t)m > m_max) { mpl_set_error("lmeds: model count %d out of range", m); return MPL_ERR_CUDA; }
+    if (n_models_out) for (int s = 0; s < h; ++s) n_models_out[s] = off[s + 1] - off[s];
+    if (m == 0) return MPL_OK;
+    double* d_med = R.d_errsums;                                     // m doubles: the slot the RANSAC path keeps its error sums in
+    if ((rc = mpl_launch_lmeds_medians(R.d_dense, m, R.d_corr, n, d_med, st))) return rc;
+    MPL_CUDA_CHECK(cudaMemcpyAsync(med, d_med, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (medians_out) memcpy(medians_out, med, (size_t)m * 8);
+    double minMedian = DBL_MAX; int best = -1;
+    for (int i = 0; i < m; ++i) if (med[i] < minMedian) { minMedian = med[i]; best = i; }      // modelest.cpp:544-548
+    if (min_median) *min_median = minMedian;
+    if (best < 0) return MPL_OK;                                     // every median NaN / inf: runLMeDS returns false
+    double sigma = 2.5 * 1.4826 * (1 + 5. / (n - 5)) * std::sqrt(minMedian);                   // :553-554
+    if (!(sigma > 0.001)) sigma = 0.001;
+    if (sigma_out) *sigma_out = sigma;
+    int* d_count = (int*)R.d_misc;
+    if ((rc = mpl_launch_inlier_mask(R.d_dense + (size_t)best * 9, R.d_corr, n, sigma, R.d_mask, d_count, st))) return rc;
+    int* h_count = (int*)(h_stage + o_med + m_max * 8);
+    MPL_CUDA_CHECK(cudaMemcpyAsync(h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaMemcpyAsync(E, R.d_dense + (size_t)best * 9, 72, cudaMemcpyDeviceToHost, st));
+    if (mask) MPL_CUDA_CHECK(cudaMemcpyAsync(mask, R.d_mask, (size_t)n, cudaMemcpyDeviceToHost, st));
+    MPL_CUDA_CHECK(cudaStreamSynchronize(st));
+    *n_inl = *h_count;                                               // the caller applies result = count >= 5 (:557)
+    return MPL_OK;
+}
+
 // poselib::estimateEssentialMat (pose_estim.cpp:857-890) -> findEssentialMat (five-point.cpp:69-148), method "RANSAC".
 // Returns 1 (true) / 0 (false) like the reference's bool, or a negative MPL_ERR_*.  E_out holds 9 doubles, or
 // 9 * (*n_E) doubles (up to 90) when n == 5 (solver only, mask all ones, five-point.cpp:108-114).
@@ -257,9 +333,9 @@ extern "C" int mpl_estimate_essential_api(const double* p1, const double* p2, in
 {
     if (!method) { mpl_set_error("estimateEssentialMat: null method"); return MPL_ERR_BAD_ARG; }
     const std::string m(method);
-    if (m != "RANSAC" && m != "ARRSAC") {
-        // pose_estim.cpp:878-887: USAC / unknown methods print and exit(1); LMEDS is another algorithm (not served).
-        mpl_set_error("estimateEssentialMat: method %s is not served by the B200 hot path (RANSAC, ARRSAC; no CPU fallback)", method);
+    if (m != "RANSAC" && m != "ARRSAC" && m != "LMEDS") {
+        // pose_estim.cpp:878-887: USAC / unknown methods print and exit(1)
+        mpl_set_error("estimateEssentialMat: method %s is not served here (RANSAC, ARRSAC, LMEDS; USAC has its own entry point mpl_usac5pt; no CPU fallback)", method);
         return MPL_ERR_BAD_ARG;
     }
     if (n < 5 || !p1 || !p2) { mpl_set_error("CV_Assert(npoints >= 5 && points2.checkVector(2) == npoints)"); return MPL_ERR_ASSERT; }
@@ -294,6 +370,11 @@ extern "C" int mpl_estimate_essential_api(const double* p1, const double* p2, in
         int rc = mpl_arrsac5pt(p1, p2, n, threshold, refine, E_out, mask, &n_inl, nullptr, nullptr);
         if (rc) return rc;
         return n_inl > 0 ? 1 : 0;
+    }
+    if (m == "LMEDS") {                                        // pose_estim.cpp:874-877 -> five-point.cpp:124-128: runLMeDS(prob 0.999, 2000), no refit
+        int rc = mpl_lmeds5pt(p1, p2, n, nullptr, 0, 0.999, 2000, E_out, mask, &n_inl, nullptr, nullptr, nullptr, nullptr);
+        if (rc) return rc;
+        return n_inl >= 5 ? 1 : 0;
     }
     int rc = mpl_ransac5pt(p1, p2, n, nullptr, 0, threshold, 1000, 0.999, refine, E_out, mask, &n_inl, &iters,
                            nullptr, nullptr, nullptr, nullptr);

@@ -202,6 +202,98 @@ sampson_score_kernel(const double* __restrict__ models, int m, const double4* __
     if (mi < m) { counts[mi] = good; if (errsums) errsums[mi] = esum; }
 }
 
+// ---- LMedS (runLMeDS, modelest.cpp:483-564) ------------------------------------------------------------
+// The reference sorts the n float errors of a model through their bit patterns as ints (icvSortDistances over
+// (int*)err.data, modelest.cpp:477-480, 539) and takes the middle one / the float sum of the two middle ones times 0.5.
+// Here one CTA per model finds the order statistics lo = (n-1)/2 and hi = n/2 of the same keys by a 4-pass radix select
+// (8 bits per pass, per-warp histograms in shared memory); the errors are recomputed in every pass from the
+// L2-resident correspondences (44 fp64 issue slots each) instead of being stored.  A NaN error (0/0) is the x86
+// default NaN 0xFFC00000 in the reference, a negative int that sorts first; the key mapping reproduces that.
+constexpr int kMedThreads = 256;
+__device__ __forceinline__ uint32_t lmeds_key(float e)
+{
+    const uint32_t b = (e != e) ? 0xFFC00000u : __float_as_uint(e);
+    return b ^ 0x80000000u;                                               // signed int order -> unsigned order
+}
+__device__ __forceinline__ float lmeds_unkey(uint32_t k) { return __uint_as_float(k ^ 0x80000000u); }
+
+__global__ void __launch_bounds__(kMedThreads)
+lmeds_median_kernel(const double* __restrict__ models, int m, const double4* __restrict__ corr, int n, double* __restrict__ medians)
+{
+    __shared__ unsigned hist[kMedThreads / 32][256];
+    __shared__ unsigned s_prefix, s_rank, s_eq;
+    __shared__ unsigned s_min[kMedThreads / 32];
+    const int mi = blockIdx.x, tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    if (mi >= m) return;
+    double E[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) E[k] = models[(size_t)mi * 9 + k];
+    const unsigned lo = (unsigned)(n - 1) / 2, hi = (unsigned)n / 2;
+    if (tid == 0) { s_prefix = 0; s_rank = lo; }
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        for (int i = tid; i < (kMedThreads / 32) * 256; i += kMedThreads) (&hist[0][0])[i] = 0;
+        __syncthreads();
+        const unsigned prefix = s_prefix;
+        for (int i = tid; i < n; i += kMedThreads) {
+            const uint32_t k = lmeds_key(sampson_err(E, corr[i]));
+            if (pass == 0 || (k >> (shift + 8)) == prefix) atomicAdd(&hist[wid][(k >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        unsigned c = 0;                                                   // thread = bin
+#pragma unroll
+        for (int w = 0; w < kMedThreads / 32; ++w) c += hist[w][tid];
+        // exclusive scan over the 256 bins: warp scan + warp totals
+        unsigned incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        __syncthreads();                                                  // all reads of hist[][] done before it is reused
+        if (lane == 31) hist[0][wid] = incl;
+        __syncthreads();
+        unsigned base = 0;
+        for (int w = 0; w < wid; ++w) base += hist[0][w];
+        const unsigned excl = base + incl - c, r = s_rank;
+        __syncthreads();
+        if (c > 0 && r >= excl && r < excl + c) { s_prefix = (prefix << 8) | (unsigned)tid; s_rank = r - excl; s_eq = c; }
+        __syncthreads();
+    }
+    const uint32_t k_lo = s_prefix;
+    uint32_t k_hi = k_lo;
+    // elements <= k_lo: (lo - s_rank) strictly smaller + s_eq equal ones; rank hi lies beyond them -> the smallest larger key
+    if (hi != lo && (lo - s_rank) + s_eq <= hi) {
+        unsigned mn = 0xFFFFFFFFu;
+        for (int i = tid; i < n; i += kMedThreads) {
+            const uint32_t k = lmeds_key(sampson_err(E, corr[i]));
+            if (k > k_lo) mn = min(mn, k);
+        }
+        mn = __reduce_min_sync(0xffffffffu, mn);
+        if (lane == 0) s_min[wid] = mn;
+        __syncthreads();
+        if (tid == 0) { for (int w = 1; w < kMedThreads / 32; ++w) mn = min(mn, s_min[w]); s_min[0] = mn; }
+        __syncthreads();
+        k_hi = s_min[0];
+    }
+    if (tid == 0) {
+        const float f_lo = lmeds_unkey(k_lo), f_hi = lmeds_unkey(k_hi);
+        medians[mi] = (n & 1) ? (double)f_lo : __dmul_rn((double)__fadd_rn(f_lo, f_hi), 0.5);     // modelest.cpp:541-542
+    }
+}
+
+// findInliers (modelest.cpp:69-83) of one model: mask + count
+__global__ void __launch_bounds__(256)
+inlier_mask_kernel(const double* __restrict__ model, const double4* __restrict__ corr, int n, double th2, uint8_t* __restrict__ mask,
+                   int* __restrict__ count)
+{
+    double E[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) E[k] = model[k];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = i < n && (double)sampson_err(E, corr[i]) <= th2;
+    if (i < n) mask[i] = in ? 1 : 0;
+    const unsigned b = __ballot_sync(0xffffffffu, in);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(count, __popc(b));
+}
+
 }  // namespace
 
 // ---- launch wrappers (declared in mpl_ransac.h) ------------------------------------------------------
@@ -253,6 +345,23 @@ int mpl_launch_sampson_score(const double* models, int m, const void* corr, int 
     at[0].val.clusterDim.x = (unsigned)S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     MPL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampson_score_kernel, models, m, (const double4*)corr, n, th * th, counts, errsums, S));
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_lmeds_medians(const double* models, int m, const void* corr, int n, double* medians, cudaStream_t st)
+{
+    if (m <= 0) return MPL_OK;
+    MplProfScope prof(MPL_PROF_SCORE, st);
+    lmeds_median_kernel<<<m, kMedThreads, 0, st>>>(models, m, (const double4*)corr, n, medians);
+    MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+    return MPL_OK;
+}
+
+int mpl_launch_inlier_mask(const double* model, const void* corr, int n, double th, uint8_t* mask, int* count, cudaStream_t st)
+{
+    MPL_CUDA_CHECK(cudaMemsetAsync(count, 0, sizeof(int), st));
+    inlier_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(model, (const double4*)corr, n, th * th, mask, count);
     MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     return MPL_OK;
 }

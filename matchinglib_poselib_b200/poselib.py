@@ -48,9 +48,34 @@ def ransac5pt(p1, p2, samples, threshold, max_iters=1000, confidence=0.999, refi
     return out
 
 
+def lmeds5pt(p1, p2, samples=None, confidence=0.999, max_iters=2000, trace=False):
+    """runLMeDS (modelest.cpp:483-564) through mpl_lmeds5pt; samples: PRE-DRAWN h x 5 int32, or None to draw the reference's fixed
+    iteration count inside.  Returns dict(ok, E, mask, count, min_median, sigma[, medians, n_models])."""
+    lib = _lib.load()
+    p1, p2 = _pts(p1), _pts(p2)
+    n = p1.shape[0]
+    if p2.shape[0] != n:
+        raise AssertionError("CV_Assert(m1.size() == m2.size() && m1.cols == mask.cols)")
+    s = None if samples is None else np.ascontiguousarray(samples, np.int32)
+    h = 0 if s is None else s.shape[0]
+    hh = h if s is not None else max_iters
+    E = np.zeros(9); mask = np.zeros(n, np.uint8); cnt = ctypes.c_int(0)
+    mm, sg = ctypes.c_double(0), ctypes.c_double(0)
+    med = np.zeros(10 * max(hh, 1)) if trace else None
+    nm = np.zeros(max(hh, 1), np.int32) if trace else None
+    _lib.check(lib.mpl_lmeds5pt(_lib.ptr(p1), _lib.ptr(p2), n, _lib.ptr(s), h, float(confidence), int(max_iters), _lib.ptr(E),
+                                _lib.ptr(mask), ctypes.byref(cnt), ctypes.byref(mm), ctypes.byref(sg), _lib.ptr(med), _lib.ptr(nm)),
+               "mpl_lmeds5pt")
+    out = dict(ok=cnt.value >= 5, E=E.reshape(3, 3), mask=mask, count=cnt.value, min_median=mm.value, sigma=sg.value)
+    if trace:
+        out.update(n_models=nm, medians=med[: int(nm.sum())])
+    return out
+
+
 def estimateEssentialMat(p1, p2, method="ARRSAC", threshold=1.6, refine=True, want_mask=True):
-    """poselib::estimateEssentialMat.  Returns (ok, E, mask).  Methods "ARRSAC" (the reference's default; mpl_arrsac5pt)
-    and "RANSAC" are served; "LMEDS" / "USAC" raise (no CPU fallback)."""
+    """poselib::estimateEssentialMat.  Returns (ok, E, mask).  Methods "ARRSAC" (the reference's default; mpl_arrsac5pt),
+    "RANSAC" and "LMEDS" (no refinement, like the reference) are served; "USAC" has its own function
+    (estimateEssentialOrPoseUSAC), anything else raises (no CPU fallback)."""
     lib = _lib.load()
     p1, p2 = _pts(p1), _pts(p2)
     n = p1.shape[0]

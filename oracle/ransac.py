@@ -25,6 +25,10 @@ def lib():
                                        ctypes.c_double, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 8 + [ctypes.c_int]
         _lib.orc_sampson.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        _lib.orc_lmeds_niters.argtypes = [ctypes.c_double, ctypes.c_int]
+        _lib.orc_lmeds5pt.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 2 + \
+                                     [ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                      ctypes.c_void_p, ctypes.c_void_p]
     return _lib
 
 
@@ -74,6 +78,25 @@ def ransac5pt(p1, p2, samples, th, conf=0.999, max_iters=1000, refine=False, tra
         tot = int(nm.sum())
         out.update(models=tm[:tot], counts=tc[:tot], errsums=te[:tot])
     return out
+
+
+def lmeds_niters(conf=0.999, max_iters=2000):
+    """Iteration count of runLMeDS (modelest.cpp:518-519): fixed, from an assumed outlier ratio of 0.45."""
+    return int(lib().orc_lmeds_niters(ctypes.c_double(conf), int(max_iters)))
+
+
+def lmeds5pt(p1, p2, samples):
+    """runLMeDS over pre-drawn samples (modelest.cpp:483-564).  Returns dict(ok, E, mask, count, min_median, sigma, medians, n_models)."""
+    p1 = np.ascontiguousarray(p1, np.float64); p2 = np.ascontiguousarray(p2, np.float64)
+    samples = np.ascontiguousarray(samples, np.int32)
+    n, h = p1.shape[0], samples.shape[0]
+    E = np.zeros(9); mask = np.zeros(n, np.uint8); cnt = ctypes.c_int(0)
+    mm = ctypes.c_double(0); sg = ctypes.c_double(0)
+    med = np.zeros(10 * max(h, 1)); nm = np.zeros(max(h, 1), np.int32)
+    ok = lib().orc_lmeds5pt(_p(p1), _p(p2), n, _p(samples), h, _p(E), _p(mask), ctypes.byref(cnt), ctypes.byref(mm), ctypes.byref(sg),
+                            _p(med), _p(nm))
+    return dict(ok=bool(ok), E=E.reshape(3, 3), mask=mask, count=cnt.value, min_median=mm.value, sigma=sg.value,
+                medians=med[:int(nm[:h].sum())], n_models=nm[:h])
 
 
 def match_models(a, b):

@@ -411,3 +411,48 @@ int orc_ransac5pt(const double *p1, const double *p2, int n, const int32_t *samp
     free(mask); free(bestmask);
     return best > 0;
 }
+
+/* runLMeDS (modelest.cpp:483-564) over pre-drawn samples[h][5]; the caller passes h = the reference's fixed iteration count
+ * (orc_lmeds_niters).  Errors are floats sorted through their bit patterns as ints (icvSortDistances over (int*)err.data,
+ * modelest.cpp:477-480, 539); the median of an even count is the FLOAT sum of the two middle values times 0.5 (:541-542);
+ * strict '<' keeps the first minimal model (:544); sigma and the final findInliers as :553-559.  medians (optional): one
+ * value per model in evaluation order.  Returns 1 when count >= 5 (result), E_out / mask_out written whenever a model had a
+ * finite median (like the reference writes model and mask before it decides result). */
+static int cmp_i32(const void *a, const void *b) { int32_t x = *(const int32_t *)a, y = *(const int32_t *)b; return x < y ? -1 : x > y; }
+int orc_lmeds_niters(double conf, int max_iters)
+{
+    int niters = (int)round(log(1. - conf) / log(1. - pow(1. - 0.45, 5.0)));
+    if (niters < 3) niters = 3;
+    return niters < max_iters ? niters : max_iters;
+}
+int orc_lmeds5pt(const double *p1, const double *p2, int n, const int32_t *samples, int h, double *E_out, uint8_t *mask_out,
+                 int *n_inl, double *min_median, double *sigma_out, double *medians, int32_t *n_models)
+{
+    double minMedian = DBL_MAX, models[90];
+    float *err = (float *)malloc(sizeof(float) * n);
+    int nt = 0;
+    if (n_inl) *n_inl = 0;
+    for (int it = 0; it < h; ++it) {
+        double s1[10], s2[10];
+        for (int j = 0; j < 5; ++j) { int id = samples[5 * it + j]; s1[2*j] = p1[2*id]; s1[2*j+1] = p1[2*id+1]; s2[2*j] = p2[2*id]; s2[2*j+1] = p2[2*id+1]; }
+        int nm = orc_run5point(s1, s2, 5, models);
+        if (n_models) n_models[it] = nm;
+        for (int m = 0; m < nm; ++m) {
+            orc_sampson(models + 9 * m, p1, p2, n, 0.0, err, NULL, NULL);
+            qsort(err, n, sizeof(float), cmp_i32);
+            double median = n % 2 != 0 ? (double)err[n / 2] : (double)(err[n / 2 - 1] + err[n / 2]) * 0.5;
+            if (medians) medians[nt] = median;
+            ++nt;
+            if (median < minMedian) { minMedian = median; memcpy(E_out, models + 9 * m, 72); }
+        }
+    }
+    free(err);
+    if (min_median) *min_median = minMedian;
+    if (!(minMedian < DBL_MAX)) return 0;
+    double sigma = 2.5 * 1.4826 * (1 + 5. / (n - 5)) * sqrt(minMedian);
+    if (!(sigma > 0.001)) sigma = 0.001;                    /* MAX(sigma, 0.001): NaN -> 0.001 like the macro */
+    if (sigma_out) *sigma_out = sigma;
+    int count = orc_sampson(E_out, p1, p2, n, sigma, NULL, mask_out, NULL);
+    if (n_inl) *n_inl = count;
+    return count >= 5;
+}

@@ -65,3 +65,23 @@ def test_ransac_end_to_end(gold, name, refine):
     assert np.array_equal(res["mask"], gold[tag + "_mask"])
     E = gold[tag + "_E"].reshape(3, 3)
     assert min(np.linalg.norm(res["E"] - E), np.linalg.norm(res["E"] + E)) < 1e-6
+
+
+def test_lmeds_oracle_recovers_scene_and_follows_the_formulae():
+    """runLMeDS restatement (modelest.cpp:483-564): 134 fixed iterations for (0.999, 2000), median / sigma / inlier rule."""
+    import datagen_pose
+    assert orc.lmeds_niters(0.999, 2000) == 134 and orc.lmeds_niters(0.999, 50) == 50 and orc.lmeds_niters(0.1, 2000) == 3
+    for n in (1000, 1001):                                           # even and odd counts take different median branches
+        sc = datagen_pose.make_scene(n, 0.35, seed=n)
+        s = datagen_pose.draw_samples_fast(n, 134, 5)
+        r = orc.lmeds5pt(sc["p1"], sc["p2"], s)
+        assert r["ok"] and r["count"] > 0.9 * 0.65 * n
+        assert min(np.linalg.norm(r["E"] - sc["E"]), np.linalg.norm(r["E"] + sc["E"])) < 5e-2
+        # the winning model's median recomputed with numpy from the float errors
+        _, _, err, _ = orc.sampson(r["E"], sc["p1"], sc["p2"], 1.0)
+        e = np.sort(err.astype(np.float32).view(np.int32)).view(np.float32)
+        med = float(e[n // 2]) if n % 2 else float(np.float32(e[n // 2 - 1] + e[n // 2])) * 0.5
+        assert med == r["min_median"] == r["medians"].min()
+        sigma = max(2.5 * 1.4826 * (1 + 5.0 / (n - 5)) * np.sqrt(med), 0.001)
+        assert sigma == r["sigma"]
+        assert np.array_equal(r["mask"], (err.astype(np.float32).astype(np.float64) <= sigma * sigma).astype(np.uint8))
