@@ -424,6 +424,36 @@ def e2e_l2(g, q, t, reps):
     return float(np.median(ts)), len(mt), hq.nbytes + ht.nbytes, len(hq) * 2 * 8
 
 
+def hamming_kernel_roofline(g, nb, pairs, long_step, per="per GPU"):
+    """Roofline of the Hamming kernel the profiled step(s) just ran, from the library's per-class CUDA-event timers: the tensor-core
+    path (bits as bf16 on l2_tc_rank_kernel: 2 * bits flop per pair against the measured cuBLAS bf16 rate) or the popc scan
+    (executed alu-pipe instructions against the measured issue rate).  Returns (roofline dict, kernel ms, path)."""
+    tc_ms, tc_n = g.prof_read(PROF["l2_tc"]); pr_ms, pr_n = g.prof_read(PROF["l2_prep"]); rr_ms, rr_n = g.prof_read(PROF["l2_rerank"])
+    k_ms, k_n = g.prof_read(PROF["hamming"])
+    pk, pp = peaks(), pipe_peaks()
+    if tc_n > 0:
+        bits = ((nb + 15) // 16) * 128
+        flops = 2.0 * bits * pairs
+        # denominator: the burst cuBLAS rate also for the long C5 step -- on 0 / 1 operands the power-limited tensor pipe runs
+        # ABOVE the sustained rate cuBLAS reaches on random bf16 data (frac_of_sustained > 1), so the sustained figure is no ceiling here
+        peak = pk["bf16_tflops"]
+        return dict(bound="tensor", achieved=flops / (tc_ms * 1e-3) / 1e12, peak=peak, unit="TFLOP/s " + per, frac=flops / (tc_ms * 1e-3) / 1e12 / peak,
+                    frac_of_sustained=(flops / (tc_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"]) if long_step and "bf16_tflops_sustained" in pk else None,
+                    kernel="l2_tc_rank_kernel (tcgen05 kind::f16 on bits unpacked to bf16, exact-integer mode)", kernel_ms=tc_ms, rank_launches=int(tc_n),
+                    prep_ms=pr_ms, certify_ms=rr_ms, flops_per_step=flops, traffic=ncu_traffic("l2_tc_rank_kernel_hamming"),
+                    peak_src="%s: bf16_tflops (cuBLAS bf16 on random data, burst)" % pk["_src"],
+                    note="hamming = |q| + |t| - 2 q.t: 2 x bits flop per pair; scores are exact integers, keys identical to the popc kernel's"), tc_ms, "tensor cores"
+    kern_ms = k_ms / max(k_n, 1)
+    alu = HAMMING_ALU_PER_PAIR[nb]
+    # SURVEY 8(d) counts ceil(B/4) POPC per pair (the reference's scalar form); the kernel folds 8 XOR words through 3 carry-save
+    # adders and EXECUTES 5 POPC + 19 alu-pipe instructions (15 LOP3 + 3 VIMNMX + 1 IADD3) per pair: the binding pipe is the alu
+    return dict(bound="int alu issue (executed LOP3 + VIMNMX + IADD3 per pair)", achieved=pairs * alu / (kern_ms * 1e-3) / 1e9, peak=pp.get("shf_funnel_ginst"),
+                unit="G alu instr/s " + per, frac=(pairs * alu / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"]) if "shf_funnel_ginst" in pp else None,
+                alu_instr_per_pair=alu, popc_executed_per_pair=5, popc_frac_executed=pairs * 5 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
+                popc_frac_algorithmic_8_per_pair=pairs * (nb // 4) / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], traffic=ncu_traffic("hamming_top2_kernel"),
+                kernel="hamming_top2_kernel<%d>" % ((nb + 15) // 16), kernel_ms=kern_ms, peak_src=pp["_src"]), kern_ms, "popc scan"
+
+
 # ------------------------------------------------------------------------------------------------
 # C1: Hamming k-NN (ORB 8192 x 8192 x 32 B)
 # ------------------------------------------------------------------------------------------------
@@ -446,15 +476,26 @@ def bench_hamming(g, steps, warmup):
                                               d_keys.data_ptr(), st), "knn2_hamming_dev")
         m._lib.check(lib.mpl_merge_top2_dev(d_keys.data_ptr(), 1, nq, 2, 0, d_idx.data_ptr(), d_dist.data_ptr(), None, st), "merge")
 
-    ms = g.time_steps(step, steps, warmup)
-    lib.mpl_prof_enable(1)
-    for _ in range(5):
-        g.flush_l2()
-        step()
-    torch.cuda.synchronize()
-    lib.mpl_prof_enable(0)
-    k_ms, k_n = g.prof_read(PROF["hamming"])
-    g.prof_read(PROF["merge"])
+    pairs = float(nq) * nt
+
+    def measure():
+        ms = g.time_steps(step, steps, warmup)
+        for cls in ("hamming", "merge", "l2_tc", "l2_prep", "l2_rerank"):
+            g.prof_read(PROF[cls])
+        lib.mpl_prof_enable(1)
+        g.flush_l2(); step()
+        torch.cuda.synchronize()
+        lib.mpl_prof_enable(0)
+        roof, kern_ms, path = hamming_kernel_roofline(g, nb, pairs, long_step=False, per="")
+        g.prof_read(PROF["merge"])
+        return float(np.mean(ms)), roof, path
+
+    step_ms, roof, path = measure()                              # the library's default path (auto rule: tensor cores at this size)
+    lib.mpl_set_hamming_path(1)                                  # the popc scan beside it
+    try:
+        popc_ms, popc_roof, _ = measure()
+    finally:
+        lib.mpl_set_hamming_path(0)
     # end to end through getMatches("LINEAR") with pinned host buffers
     (_, hq), (_, ht) = pinned(q, torch), pinned(t, torch)
     kp = range(nq)
@@ -466,27 +507,12 @@ def bench_hamming(g, steps, warmup):
         t0 = time.perf_counter()
         err, mt = m.getMatchesArray(kp, range(nt), hq, ht, None, "LINEAR", False, True)
         ts.append(time.perf_counter() - t0)
-    pairs = float(nq) * nt
-    step_ms = float(np.mean(ms))
-    kern_ms = k_ms / max(k_n, 1)
-    pk = peaks()
-    pp = pipe_peaks()
-    bytes_alg = (nq + nt) * nb + nq * 16
-    popc = pairs * (nb // 4)
     return dict(
         workload="C1: ORB 8192x8192x32B Hamming k=2 + ratio (LINEAR)", value=pairs / (step_ms * 1e-3), unit="pairs/s", ms_per_step=step_ms,
-        dtype="u32 popc",
-        # Bound = the integer pipes, not HBM (algorithmic bytes are 0.65 MB).  SURVEY 8(d) counts ceil(B/4) POPC per pair (the
-        # reference's scalar form); the kernel folds 8 XOR words through 3 carry-save adders and EXECUTES 5 POPC + 19 alu-pipe
-        # instructions (15 LOP3 + 3 VIMNMX + 1 IADD3) per pair: the binding pipe is the alu (64 lanes/clk/SM, measured as the SHF rate).
-        roofline=dict(bound="int alu issue (executed instructions)", achieved=pairs * HAMMING_ALU_PER_PAIR[nb] / (kern_ms * 1e-3) / 1e9,
-                      peak=pp.get("shf_funnel_ginst"), unit="G alu instr/s",
-                      frac=(pairs * HAMMING_ALU_PER_PAIR[nb] / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"]) if "shf_funnel_ginst" in pp else None,
-                      alu_instr_per_pair=HAMMING_ALU_PER_PAIR[nb], popc_executed_per_pair=5,
-                      popc_frac_executed=pairs * 5 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
-                      popc_frac_algorithmic_8_per_pair=popc / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
-                      hbm_gbs_algorithmic=bytes_alg / (kern_ms * 1e-3) / 1e9, hbm_peak_gbs=pk["hbm_gbs"], traffic=ncu_traffic("hamming_top2_kernel"),
-                      kernel="hamming_top2_kernel<2>", kernel_ms=kern_ms, peak_src=pp["_src"]),
+        dtype="bits as bf16 0/1 on tcgen05 (exact integers)" if path == "tensor cores" else "u32 popc", path=path,
+        roofline=roof,
+        popc_path=dict(value=pairs / (popc_ms * 1e-3), unit="pairs/s", ms_per_step=popc_ms, roofline=popc_roof,
+                       note="mpl_set_hamming_path(1): the carry-save popc scan, same keys bit for bit"),
         cpu_baseline=cpu_hamming_c1(q, t),
         e2e=dict(value=pairs / float(np.median(ts)), unit="pairs/s", h2d_bytes_per_step=int(hq.nbytes + ht.nbytes), d2h_bytes_per_step=int(nq * 16),
                  matches=int(len(mt))))
@@ -643,8 +669,24 @@ def bench_database_c5(g, steps, world=1, rank=0, dist=None, peers_factory=None):
     torch.cuda.synchronize()
     launches = g.launches() - l0
     ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    for cls in ("hamming", "merge", "l2_tc", "l2_prep", "l2_rerank"):
+        g.prof_read(PROF[cls])
     lib.mpl_prof_enable(1); step(); torch.cuda.synchronize(); lib.mpl_prof_enable(0)
-    k_ms, k_n = g.prof_read(PROF["hamming"]); mg_ms, mg_n = g.prof_read(PROF["merge"])
+    roof, kern_ms, path = hamming_kernel_roofline(g, NB, float(NQ) * ROWS, long_step=True)
+    mg_ms, mg_n = g.prof_read(PROF["merge"])
+    # the popc scan on the same shard, for comparison (mpl_set_hamming_path(1)); the exchange is the same
+    lib.mpl_set_hamming_path(1)
+    try:
+        step(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); step(); e1.record(); torch.cuda.synchronize()
+        popc_ms = float(e0.elapsed_time(e1))
+        keys_popc = keys.clone()
+    finally:
+        lib.mpl_set_hamming_path(0)
+    step(); torch.cuda.synchronize()                             # the checked results below come from the default path
+    paths_equal = bool(torch.equal(keys, keys_popc))
+    del keys_popc
     if peers is not None:
         to = ctypes.c_int(0)
         m._lib.check(lib.mpl_peer_status(peers[1][rank], ctypes.byref(to), g.stream()), "peer_status")
@@ -664,7 +706,12 @@ def bench_database_c5(g, steps, world=1, rank=0, dist=None, peers_factory=None):
     probe = torch.randint(0, 256, (n_probe, NB), dtype=torch.uint8, device=dev, generator=torch.Generator(device=dev).manual_seed(99))
     pk = torch.empty((n_probe, 2), dtype=torch.int64, device=dev); pi = torch.empty((n_probe, 2), dtype=torch.int32, device=dev); pd = torch.empty((n_probe, 2), dtype=torch.int32, device=dev)
     pscr_b = int(lib.mpl_knn_hamming_scratch_bytes(n_probe, ROWS, w16)); pscr = torch.empty(max(pscr_b, 16), dtype=torch.uint8, device=dev)
-    m._lib.check(lib.mpl_knn2_hamming_dev(probe.data_ptr(), n_probe, t.data_ptr(), ROWS, w16, rank * ROWS, pscr.data_ptr(), pscr_b, pk.data_ptr(), g.stream()), "hamming probe")
+    if path == "tensor cores":
+        lib.mpl_set_hamming_path(2)                              # 48 queries would take the popc scan by the auto rule: check the path the step ran
+    try:
+        m._lib.check(lib.mpl_knn2_hamming_dev(probe.data_ptr(), n_probe, t.data_ptr(), ROWS, w16, rank * ROWS, pscr.data_ptr(), pscr_b, pk.data_ptr(), g.stream()), "hamming probe")
+    finally:
+        lib.mpl_set_hamming_path(0)
     if world > 1:
         allk = torch.empty((world, n_probe, 2), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(allk.view(-1, 2), pk)
@@ -685,28 +732,24 @@ def bench_database_c5(g, steps, world=1, rank=0, dist=None, peers_factory=None):
     merged = np.sort(allo.permute(1, 0, 2).reshape(n_probe, -1).cpu().numpy(), axis=1)[:, :2]
     gi, gd = pi.cpu().numpy(), pd.cpu().numpy()
     oracle_ok = bool(np.array_equal(merged & 0xFFFFFFFF, gi.astype(np.int64)) and np.array_equal(merged >> 32, gd.astype(np.int64)))
-    ok_all = torch.tensor([1 if (planted and oracle_ok) else 0], device=dev)
+    ok_all = torch.tensor([1 if (planted and oracle_ok and paths_equal) else 0], device=dev)
     if dist is not None:
         dist.all_reduce(ok_all, op=dist.ReduceOp.MIN)
     if int(ok_all.item()) == 0:
-        raise RuntimeError("rank %d: C5 check failed (planted %s, oracle %s)" % (rank, planted, oracle_ok))
+        raise RuntimeError("rank %d: C5 check failed (planted %s, oracle %s, popc == tensor-core keys %s)" % (rank, planted, oracle_ok, paths_equal))
     out = None
     if rank == 0:
         pairs = float(NQ) * ROWS * world
-        pp = pipe_peaks()
-        kern_ms = k_ms / max(k_n, 1)
-        per_gpu = float(NQ) * ROWS
-        alu = HAMMING_ALU_PER_PAIR[NB]
         out = dict(workload="C5: %d ORB queries x %d train rows per rank (%d rows on %d GPU%s), Hamming k=2, train sharded, top-2 merged over NVLink" %
                             (NQ, ROWS, ROWS * world, world, "s" if world > 1 else ""),
-                   value=pairs / (ms * 1e-3), unit="pairs/s", n_gpus=world, scaling="weak", ms_per_step=ms, dtype="u32 popc", gpu_launches=int(launches),
+                   value=pairs / (ms * 1e-3), unit="pairs/s", n_gpus=world, scaling="weak", ms_per_step=ms,
+                   dtype="bits as bf16 0/1 on tcgen05 (exact integers)" if path == "tensor cores" else "u32 popc", path=path, gpu_launches=int(launches),
                    exchange="NVLink peer memory inside the merge kernel (mpl_allgather_merge_top2_dev)" if world > 1 else "none (one shard)",
-                   kernels=dict(hamming_top2_ms=kern_ms, merge_or_exchange_ms=mg_ms / max(mg_n, 1)),
-                   roofline=dict(bound="int alu issue (executed LOP3 + VIMNMX + IADD3 per pair)", achieved=per_gpu * alu / (kern_ms * 1e-3) / 1e9,
-                                 peak=pp.get("shf_funnel_ginst"), unit="G alu instr/s per GPU", frac=per_gpu * alu / (kern_ms * 1e-3) / 1e9 / pp["shf_funnel_ginst"] if "shf_funnel_ginst" in pp else None,
-                                 popc_frac_executed=per_gpu * 5 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"], popc_frac_algorithmic_8_per_pair=per_gpu * 8 / (kern_ms * 1e-3) / 1e9 / pp["popc_gops"],
-                                 hbm_gbs=(ROWS * NB) / (kern_ms * 1e-3) / 1e9, kernel="hamming_top2_kernel<2>", kernel_ms=kern_ms, peak_src=pp["_src"]),
-                   checks=dict(planted_neighbours_found=planted, oracle_probe_queries=n_probe, oracle_merged_equal=oracle_ok),
+                   kernels=dict(hamming_kernel_ms=kern_ms, merge_or_exchange_ms=mg_ms / max(mg_n, 1)),
+                   roofline=roof,
+                   popc_path=dict(ms_per_step=popc_ms, value_rank0=float(NQ) * ROWS / (popc_ms * 1e-3), unit="pairs/s per GPU",
+                                  note="mpl_set_hamming_path(1): hamming_top2_kernel<2> on rank 0's shard, same keys bit for bit"),
+                   checks=dict(planted_neighbours_found=planted, oracle_probe_queries=n_probe, oracle_merged_equal=oracle_ok, popc_and_tensor_core_keys_identical=paths_equal),
                    cpu_baseline=dict(value=float(n_probe) * ROWS / cpu_s, unit="pairs/s", cores=max(1, (os.cpu_count() or 1) // world), kind="port",
                                      sample="%d probe queries x %d rows (this rank's shard), oracle cvflann-order Hamming scan; the full config is %d x that work (extrapolate linearly)" %
                                             (n_probe, ROWS, (NQ * world) // n_probe)))

@@ -82,6 +82,10 @@ int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt
                    int dim, int sqrt_out, int k, int32_t* idx, float* dist);
 /* force a float path: 0 = auto, 1 = exact SIMT scan only, 2 = tensor-core ranking + exact re-rank */
 int mpl_set_l2_path(int path);
+/* Hamming k-NN path of mpl_knn2_hamming / mpl_knn2_hamming_dev / getMatches on CV_8U descriptors: 0 = auto, 1 = popc scan
+ * (hamming_top2_kernel), 2 = tensor cores (bits unpacked to bf16, hamming = |q| + |t| - 2 q.t on the float ranking kernel in its
+ * exact-integer mode; rows of 16 / 32 / 64 bytes only).  Both give the same keys bit for bit; process-wide. */
+int mpl_set_hamming_path(int path);
 
 /* Lowe ratio test + cv::DMatch emission (matchers.cpp:601-625, 677-701; nmslib_matchers.h:399-415):
  * keep q iff d0 < 0.75f*d1 (ratio_test != 0; needs k == 2), emit every query otherwise.

@@ -64,6 +64,7 @@ SIGNATURES = {
     "mpl_knn2_hamming": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_knn2_l2f32": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_set_l2_path": (c_int, [c_int]),
+    "mpl_set_hamming_path": (c_int, [c_int]),
     "mpl_ratio_matches_i32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_ratio_matches_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "mpl_get_matches_api": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_size_t, c_int,

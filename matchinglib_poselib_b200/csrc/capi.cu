@@ -294,12 +294,32 @@ static int round_w16(int nbytes_used)
     return r;     // 1,2,4,8,16
 }
 
+// Hamming k-NN path: 0 = auto, 1 = popc scan (hamming_top2_kernel), 2 = tensor cores (bits as bf16, knn_l2_tc.cu).
+// auto rule of the Hamming path, from measurements (tools/hamming_tc_time.py): the tensor-core path is 1.4x
+// (5000 x 5000 x 64 B) to 3.4x (10 000 x 12.5 M x 32 B) faster once the scan hides its four launches and fills the 256-row query
+// blocks; few queries (a tile computes 256 rows whatever nq is) and small scans stay on the popc kernel
+#ifndef MPL_HAMMING_TC_AUTO
+#define MPL_HAMMING_TC_AUTO(nq, nt, w16) ((nq) >= 128 && (long long)(nq) * (nt) >= (1ll << 24))
+#endif
+static std::atomic<int> g_hamming_path{0};
+extern "C" int mpl_set_hamming_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_hamming_path.store(path, std::memory_order_relaxed); return MPL_OK; }
+static bool hamming_wants_tc(int nq, int nt, int w16)
+{
+    const int path = g_hamming_path.load(std::memory_order_relaxed);
+    if (path == 1 || !mpl_hamming_tc_supported(nq, nt, w16)) return false;
+    if (path == 2) return true;
+    return MPL_HAMMING_TC_AUTO(nq, nt, w16);
+}
+
 extern "C" size_t mpl_knn_hamming_scratch_bytes(int nq, int nt, int w16)
 {
     if (nq <= 0 || nt <= 0) return 16;
     int sm = g_ctx.ready ? g_ctx.sm_count : 148;
     int splits = mpl_hamming_pick_splits(nq, nt, w16, sm);
-    return (size_t)splits * nq * 2 * sizeof(mpl_key64);
+    const size_t popc = (size_t)splits * nq * 2 * sizeof(mpl_key64);
+    // sized for either path, so that a buffer obtained here serves whatever mpl_set_hamming_path selects later
+    const size_t tc = mpl_hamming_tc_supported(nq, nt, w16) ? mpl_hamming_tc_scratch_bytes(nq, nt, w16, sm) : 0;
+    return popc > tc ? popc : tc;
 }
 
 extern "C" int mpl_pack_rows_u8_dev(const void* d_src, int n, size_t src_step, int nbytes_used, void* d_dst, int w16, void* stream)
@@ -314,6 +334,11 @@ extern "C" int mpl_knn2_hamming_dev(const void* d_q, int nq, const void* d_t, in
     cudaStream_t st = (cudaStream_t)stream;
     if (nt <= 0) { MPL_CUDA_CHECK(cudaMemsetAsync(d_keys_out, 0xFF, (size_t)nq * 2 * sizeof(mpl_key64), st)); return MPL_OK; }
     int sm = g_ctx.ready ? g_ctx.sm_count : 148;
+    if (hamming_wants_tc(nq, nt, w16) && d_scratch && ((uintptr_t)d_scratch & 255) == 0 &&
+        scratch_bytes >= mpl_hamming_tc_scratch_bytes(nq, nt, w16, sm))
+        return mpl_hamming_tc_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, train_offset, d_scratch, scratch_bytes,
+                                   (mpl_key64*)d_keys_out, sm, st);
+    if (g_hamming_path.load(std::memory_order_relaxed) == 2) { mpl_set_error("hamming_dev: tensor-core path forced but shape / scratch do not allow it (w16=%d, scratch %zu bytes)", w16, scratch_bytes); return MPL_ERR_BAD_ARG; }
     const int splits = mpl_hamming_pick_splits(nq, nt, w16, sm);
     if (splits == 1)
         return mpl_launch_hamming_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, 1, 1, train_offset,
@@ -444,6 +469,14 @@ int mpl_hamming_keys_locked(const uint8_t* q, int nq, size_t q_step, const uint8
     const int splits = mpl_hamming_pick_splits(nq, nt, w16, g_ctx.sm_count);
     MplBuf &bpart = g_ctx.bufs[MPL_BUF_PART], &bkeys = g_ctx.bufs[MPL_BUF_KEYS];
     if ((rc = bkeys.ensure((size_t)nq * 2 * sizeof(mpl_key64)))) return rc;
+    if (hamming_wants_tc(nq, nt, w16)) {
+        const size_t need = mpl_hamming_tc_scratch_bytes(nq, nt, w16, g_ctx.sm_count);
+        if ((rc = bpart.ensure(need))) return rc;
+        rc = mpl_hamming_tc_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, 0, bpart.ptr, need, (mpl_key64*)bkeys.ptr, g_ctx.sm_count, st);
+        if (rc) return rc;
+        *d_keys = (mpl_key64*)bkeys.ptr;
+        return MPL_OK;
+    }
     if ((rc = bpart.ensure((size_t)splits * nq * 2 * sizeof(mpl_key64)))) return rc;
     rc = mpl_launch_hamming_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, splits, 1, 0, (mpl_key64*)bpart.ptr, st);
     if (rc) return rc;

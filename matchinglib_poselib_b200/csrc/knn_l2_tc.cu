@@ -286,6 +286,56 @@ l2_prep_tf32_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
     }
 }
 
+// Binary descriptors (Hamming distance as a contraction, section "Hamming on the tensor cores" below): rows of w16 x 16 bytes ->
+// bf16 operand rows of 128 w16 elements, train bits as 0 / 1, query bits as 0 / -2; |x|^2 = popcount.  8 lanes per row: lane sl
+// unpacks bytes [2 w16 sl, 2 w16 (sl + 1)) into 16 w16 elements (element 8 b + i = bit i of byte b).
+__global__ void __launch_bounds__(256)
+hamming_prep_kernel(const uint8_t* __restrict__ t, int nt, const uint8_t* __restrict__ q, int nq, int w16, void* __restrict__ tp,
+                    void* __restrict__ qp, float* __restrict__ tnorm, int nt_pad, float* __restrict__ qnorm, uint4* __restrict__ taug,
+                    uint4* __restrict__ qaug, TcHeader* hdr, uint32_t* __restrict__ gthr, int n_gthr)
+{
+    const int lane = threadIdx.x & 31, sub = lane >> 3, sl = lane & 7;
+    const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
+    const int total = nt_pad + nq;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = 0xFFFFFFFFu;
+    const int lane_bytes = 2 * w16;
+    unsigned tmax = 0;
+    for (int base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4; base < total; base += warps_per_grid * 4) {
+        const int row = base + sub;
+        const bool live = row < total, is_t = row < nt_pad;
+        const int r = is_t ? row : row - nt_pad;
+        const bool pad = live && is_t && r >= nt;
+        unsigned pc = 0;
+        if (live && !pad) {
+            const uint8_t* x = (is_t ? t : q) + (size_t)r * 16 * w16 + (size_t)sl * lane_bytes;
+            const uint32_t one = is_t ? 0x3F80u : 0xC000u;                       // bf16 1.0 / -2.0
+            uint4* dst = reinterpret_cast<uint4*>((char*)(is_t ? tp : qp) + (size_t)r * 256 * w16 + (size_t)sl * 16 * lane_bytes);
+            for (int b = 0; b < lane_bytes; ++b) {
+                const unsigned v = x[b];
+                pc += __popc(v);
+                uint4 o;
+                o.x = ((v & 1u) ? one : 0u) | ((v & 2u) ? one << 16 : 0u);
+                o.y = ((v & 4u) ? one : 0u) | ((v & 8u) ? one << 16 : 0u);
+                o.z = ((v & 16u) ? one : 0u) | ((v & 32u) ? one << 16 : 0u);
+                o.w = ((v & 64u) ? one : 0u) | ((v & 128u) ? one << 16 : 0u);
+                dst[b] = o;
+            }
+        }
+#pragma unroll
+        for (int o = 4; o >= 1; o >>= 1) pc += __shfl_xor_sync(0xffffffffu, pc, o);
+        if (live && sl == 0) {
+            if (pad) { tnorm[r] = INFINITY; write_aug(taug + 2 * (size_t)r, true, INFINITY, true); }
+            else {
+                (is_t ? tnorm : qnorm)[r] = (float)pc;
+                write_aug((is_t ? taug : qaug) + 2 * (size_t)r, is_t, (float)pc, true);
+            }
+        }
+        if (live && is_t && !pad) tmax = max(tmax, pc);
+    }
+    tmax = __reduce_max_sync(0xffffffffu, tmax);
+    if (lane == 0 && tmax) atomicMax(&hdr->max_tnorm_bits, __float_as_uint((float)tmax));
+}
+
 // ---- 3. tensor-core ranking kernel ----------------------------------------------------------------------
 struct TcParams {
     int nq, nt, NT;                  // NT = train tiles of BN rows
@@ -879,7 +929,9 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
                 if (ti < 0 || ti >= nt) continue;
                 float d = __fadd_rn(__uint_as_float(e == 0 ? sc.x : sc.y), qq1);
                 if (MODE == 1) d = sqrtf(d);
-                const mpl_key64 key = ((mpl_key64)__float_as_uint(d) << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
+                // MODE 2 (binary descriptors): d = |t| + |q| - 2 q.t is the Hamming distance, an exact integer; integer key like the popc kernel's
+                const uint32_t dbits = MODE == 2 ? __float2uint_rn(d) : __float_as_uint(d);
+                const mpl_key64 key = ((mpl_key64)dbits << 32) | (mpl_key64)(uint32_t)(train_offset + ti);
                 const mpl_key64 hi = max(k0, key);
                 k0 = min(k0, key); k1 = min(k1, hi);
             }
@@ -887,6 +939,7 @@ l2_certify_kernel(const float* __restrict__ q, int nq, size_t q_ld, const float*
         reinterpret_cast<ulonglong2*>(keys_out)[q1] = make_ulonglong2(k0, k1);
         return;
     }
+    if (MODE == 2) return;                                       // 0 / 1 data is always in exact-integer mode
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
@@ -967,10 +1020,10 @@ struct TcPlan {
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-TcPlan make_plan(int nq, int nt, int dim, int sm_count)
+TcPlan make_plan(int nq, int nt, int dim, int sm_count, bool bf16_only = false)
 {
     TcPlan P;
-    P.rq = dim > 128 ? UM : BM;
+    P.rq = (bf16_only ? dim > 256 : dim > 128) ? UM : BM;     // resident A block: 4 slabs of BM rows, or 8 of UM rows
     P.NQB = (nq + P.rq - 1) / P.rq;
     P.NT = (nt + BN - 1) / BN;
     P.U = (long long)P.NQB * P.NT;
@@ -985,8 +1038,9 @@ TcPlan make_plan(int nq, int nt, int dim, int sm_count)
     size_t o = 256;
     P.off_tnorm = o; o = align256(o + (size_t)P.NT * BN * 4);
     P.off_qnorm = o; o = align256(o + (size_t)P.NQB * P.rq * 4);
-    P.off_tp = o;    o = align256(o + (size_t)nt * P.kp32 * 4);
-    P.off_qp = o;    o = align256(o + (size_t)nq * P.kp32 * 4);
+    const size_t row_bytes = bf16_only ? (size_t)P.kp16 * 2 : (size_t)P.kp32 * 4;
+    P.off_tp = o;    o = align256(o + (size_t)nt * row_bytes);
+    P.off_qp = o;    o = align256(o + (size_t)nq * row_bytes);
     P.off_taug = o;  o = align256(o + (size_t)P.NT * BN * AUG_BYTES);
     P.off_qaug = o;  o = align256(o + (size_t)nq * AUG_BYTES);
     P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * P.rq * 32);
@@ -1102,5 +1156,85 @@ int mpl_l2tc_last_fallbacks(const void* d_scratch, unsigned* count, unsigned* tf
     MPL_CUDA_CHECK(cudaStreamSynchronize(st));
     if (count) *count = h.fallback_count;
     if (tf32_mode) *tf32_mode = h.not_bf16_exact;
+    return MPL_OK;
+}
+
+// ---- Hamming on the tensor cores ------------------------------------------------------------------------------------------
+// For bit vectors q, t:  hamming(q, t) = |q| + |t| - 2 q.t  (popcounts and a dot product of 0 / 1 values).  With the bits unpacked
+// to bf16 (0 / 1 train, 0 / -2 query) the ranking kernel above computes score = |t| - 2 q.t exactly (integers far below 2^24) in
+// its exact-integer mode: sorted top-2 lists, ties kept by lowest train index, no certificate and no re-read of any row; the
+// certify kernel adds |q| and emits the same integer keys (distance << 32 | train index) as hamming_top2_kernel.  256 bits are
+// K = 256 (four bf16 slabs, BM = 256 rows resident), 512 bits K = 512 (eight slabs, 128-row query blocks).
+// A train set whose bf16 image exceeds the L2 is walked in chunks of ~48 MB (every chunk's tiles are then read from HBM once and
+// re-read by the other query blocks out of L2), each chunk leaving partial keys that one merge launch folds.
+bool mpl_hamming_tc_supported(int nq, int nt, int w16) { return nq >= 1 && nt >= 2 && (w16 == 1 || w16 == 2 || w16 == 4); }
+
+static int hamming_tc_chunk_rows(int w16) { return std::max(BN, (int)(((size_t)48 << 20) / ((size_t)w16 * 256)) / BN * BN); }
+
+size_t mpl_hamming_tc_scratch_bytes(int nq, int nt, int w16, int sm_count)
+{
+    if (!mpl_hamming_tc_supported(nq, nt, w16)) return 16;
+    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16));
+    const int n_chunks = (nt + chunk - 1) / chunk;
+    const size_t plan = make_plan(nq, chunk, w16 * 128, sm_count, true).total;
+    return plan + (n_chunks > 1 ? align256((size_t)n_chunks * nq * 2 * sizeof(mpl_key64)) : 0);
+}
+
+int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int w16, long long train_offset, void* d_scratch,
+                        size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st)
+{
+    if (!mpl_hamming_tc_supported(nq, nt, w16)) { mpl_set_error("hamming tensor-core path: unsupported shape (w16=%d, nt=%d)", w16, nt); return MPL_ERR_BAD_ARG; }
+    const size_t need = mpl_hamming_tc_scratch_bytes(nq, nt, w16, sm_count);
+    if (!d_scratch || scratch_bytes < need) { mpl_set_error("hamming tensor-core path: scratch %zu < %zu bytes", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
+    if (((uintptr_t)d_scratch & 255) != 0) { mpl_set_error("hamming tensor-core path: scratch must be 256-byte aligned"); return MPL_ERR_BAD_ARG; }
+    const int dim = w16 * 128;
+    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16));
+    const int n_chunks = (nt + chunk - 1) / chunk;
+    const size_t plan_bytes = make_plan(nq, chunk, dim, sm_count, true).total;
+    char* base = (char*)d_scratch;
+    mpl_key64* parts = n_chunks > 1 ? (mpl_key64*)(base + plan_bytes) : d_keys_out;
+    MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    for (int c = 0; c < n_chunks; ++c) {
+        const int t0 = c * chunk, ntc = std::min(chunk, nt - t0);
+        const TcPlan P = make_plan(nq, ntc, dim, sm_count, true);                     // <= the first chunk's plan
+        TcHeader* hdr = (TcHeader*)base;
+        float* tnorm = (float*)(base + P.off_tnorm); float* qnorm = (float*)(base + P.off_qnorm);
+        void* tp = base + P.off_tp; void* qp = base + P.off_qp;
+        uint4* cand = (uint4*)(base + P.off_cand); int* flist = (int*)(base + P.off_list);
+        uint32_t* gthr = (uint32_t*)(base + P.off_gthr);
+        uint4* taug = (uint4*)(base + P.off_taug); uint4* qaug = (uint4*)(base + P.off_qaug);
+        alignas(64) TcMaps maps;
+        memset(&maps, 0, sizeof(maps));
+        int rc;
+        if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, P.rq))) return rc;
+        if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, ntc, 64, BN))) return rc;
+        if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, P.NT * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
+        {
+            MplProfScope prof(MPL_PROF_L2_PREP, st);
+            const int rows = P.NT * BN + nq;
+            int blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;
+            hamming_prep_kernel<<<blocks, 256, 0, st>>>(d_t + (size_t)t0 * 16 * w16, ntc, d_q, nq, w16, tp, qp, tnorm, P.NT * BN, qnorm, taug, qaug,
+                                                        hdr, gthr, P.NQB * P.rq);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+        {
+            MplProfScope prof(MPL_PROF_L2_TC, st);
+            TcParams prm;
+            prm.nq = nq; prm.nt = ntc; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
+            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
+            l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+        {
+            MplProfScope prof(MPL_PROF_L2_RERANK, st);
+            l2_certify_kernel<2><<<(nq + 7) / 8, 256, 0, st>>>(nullptr, nq, 0, nullptr, ntc, 0, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots,
+                                                               train_offset + t0, hdr, parts + (size_t)c * nq * 2, flist, P.rq);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+    }
+    if (n_chunks > 1) return mpl_launch_merge_top2(parts, n_chunks, nq, 2, nullptr, nullptr, -1, d_keys_out, st);
     return MPL_OK;
 }

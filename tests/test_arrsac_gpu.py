@@ -63,7 +63,7 @@ def test_arrsac_is_the_default_method(P):
     assert ok and E.shape == (3, 3) and mask.shape == (1, 800) and mask.sum() > 400 and _ed(E, sc["E"]) < 5e-2
     from matchinglib_poselib_b200 import _lib
     with pytest.raises(_lib.MplError):
-        P.estimateEssentialMat(sc["p1"], sc["p2"], "LMEDS", sc["th"])
+        P.estimateEssentialMat(sc["p1"], sc["p2"], "MLESAC", sc["th"])                       # unknown method strings are refused
 
 
 def test_arrsac_rejects_noise_and_small_sets(P):

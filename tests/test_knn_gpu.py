@@ -50,6 +50,36 @@ def test_hamming_vs_oracle(m, nq, nt, nb):
             assert np.array_equal(idx, oi), (nq, nt, nb, k, mode)
 
 
+@pytest.mark.parametrize("nq,nt,nb", [(1, 2, 32), (17, 5000, 32), (1500, 3000, 32), (1025, 257, 64), (300, 4097, 61), (64, 700, 16),
+                                      (257, 129, 32), (700, 70000, 32), (200, 250000, 32), (300, 60000, 64), (8192, 8192, 32)])
+def test_hamming_tensor_core_path_vs_oracle(m, nq, nt, nb):
+    """mpl_set_hamming_path(2): the bits as bf16 on the float ranking kernel's exact-integer mode (hamming = |q| + |t| - 2 q.t); the
+    last three shapes walk the train set in chunks / use 128-row query blocks (512-bit rows).  Same keys as the popc kernel."""
+    q, t = datagen.binary_descriptors(nq, nt, nb, seed=nq * 7 + nt)
+    if nt >= 5000:
+        t[nt // 2] = t[3]; t[nt - 1] = t[3]; q[0] = t[3]                # exact duplicates in different tiles / chunks: ties by index
+    import ctypes
+    lib = m._lib.load()
+    lib.mpl_set_hamming_path(2)
+    lib.mpl_prof_enable(1)
+    ms, cnt = ctypes.c_double(0), ctypes.c_longlong(0)
+    lib.mpl_prof_read(2, ctypes.byref(ms), ctypes.byref(cnt))               # reading clears the ranking kernel's timer
+    try:
+        for k in (1, 2):
+            for mode, ign in ((0, 0), (1, 1 if nb & 1 else 2)):
+                if mode == 1 and nt > 100000:
+                    continue
+                idx, dist = m.knn2_hamming(q, t, k, ign)
+                oi, od = orc.knn_hamming(q, t, k, mode, threads=8)
+                assert np.array_equal(dist, od), (nq, nt, nb, k, mode)
+                assert np.array_equal(idx, oi), (nq, nt, nb, k, mode)
+        lib.mpl_prof_read(2, ctypes.byref(ms), ctypes.byref(cnt))
+        assert cnt.value >= 2, "the tensor-core ranking kernel did not run"
+    finally:
+        lib.mpl_set_hamming_path(0)
+        lib.mpl_prof_enable(0)
+
+
 def test_hamming_strided_and_empty(m):
     q, t = datagen.binary_descriptors(100, 300, 32, seed=9)
     big_q = np.zeros((100, 48), np.uint8); big_q[:, :32] = q
