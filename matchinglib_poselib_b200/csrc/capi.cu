@@ -303,6 +303,7 @@ static int round_w16(int nbytes_used)
 #endif
 static std::atomic<int> g_hamming_path{0};
 extern "C" int mpl_set_hamming_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_hamming_path.store(path, std::memory_order_relaxed); return MPL_OK; }
+int mpl_hamming_path() { return g_hamming_path.load(std::memory_order_relaxed); }
 static bool hamming_wants_tc(int nq, int nt, int w16)
 {
     const int path = g_hamming_path.load(std::memory_order_relaxed);

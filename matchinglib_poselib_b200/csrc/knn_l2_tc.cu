@@ -342,6 +342,9 @@ struct TcParams {
     long long U;                     // work units = query blocks x train tiles
     int max_slots;                   // candidate slots per query block
     int rq;                          // query rows per block: BM, or UM for 128 < dim <= MAX_DIM (one UMMA M block per CTA)
+    // batch of independent pairs in one launch (Hamming path): query block qb belongs to pair qb / NQBp; a pair's operand rows start
+    // at pair * q_pair_rows / pair * t_pair_rows, its aug rows are padded per block / per tile.  NQBp = 0: one problem.
+    int NQBp, q_pair_rows, t_pair_rows;
     int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
     uint4* cand;                     // [qblock][slot][LPS][rq rows][2 x uint4] = 4 scores + 4 train indices
     uint32_t* gthr;                  // [NQB * rq] per query: smallest list threshold any CTA has published (order-preserving uint)
@@ -813,15 +816,17 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
 
     if (warp == 0) {
         // ===== TMA producer: the whole warp runs the loop (uniform control flow), one elected lane issues =====
-        int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1;
+        int stage = 0; uint32_t sphase = 0; int a_cnt = 0, cur_qb = -1, b_row0 = 0, ba_row0 = 0;
         int qb = (int)(u0 / p.NT), tile = (int)(u0 - (long long)qb * p.NT) - 1;
         for (long long u = u0; u < u1; ++u) {
             if (++tile == p.NT) { tile = 0; ++qb; }
             if (qb != cur_qb) {
                 mbar_wait(a_empty, (uint32_t)((a_cnt & 1) ^ 1));                 // MMAs of the previous query block are done
+                int a_row = qb * p.rq;
+                if (p.NQBp) { const int pair = qb / p.NQBp; a_row = pair * p.q_pair_rows + (qb - pair * p.NQBp) * p.rq; b_row0 = pair * p.t_pair_rows; ba_row0 = pair * p.NT * BN; }
                 if (elect_one()) {
                     mbar_expect_tx(a_full, (uint32_t)(n_slabs * a_slab + a_aug));
-                    for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * a_slab, mapA, s * KS, qb * p.rq, a_full);
+                    for (int s = 0; s < n_slabs; ++s) tma_load_2d(sA + s * a_slab, mapA, s * KS, a_row, a_full);
                     tma_load_2d(sAa, mapAa, 0, qb * p.rq, a_full);
                 }
                 __syncwarp();
@@ -832,8 +837,8 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
                 if (elect_one()) {
                     unsigned char* dst = sB + stage * stage_bytes;
                     mbar_expect_tx(&b_full[stage], (uint32_t)(sps * B_SLAB + (s == 0 ? BN * AUG_BYTES : 0)));
-                    for (int j = 0; j < sps; ++j) tma_load_2d(dst + j * B_SLAB, mapB, (s + j) * KS, tile * BN, &b_full[stage]);
-                    if (s == 0) tma_load_2d(dst + sps * B_SLAB, mapBa, 0, tile * BN, &b_full[stage]);
+                    for (int j = 0; j < sps; ++j) tma_load_2d(dst + j * B_SLAB, mapB, (s + j) * KS, b_row0 + tile * BN, &b_full[stage]);
+                    if (s == 0) tma_load_2d(dst + sps * B_SLAB, mapBa, 0, ba_row0 + tile * BN, &b_full[stage]);
                 }
                 __syncwarp();
                 if (++stage == n_stages) { stage = 0; sphase ^= 1; }
@@ -1132,7 +1137,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
     {
         MplProfScope prof(MPL_PROF_L2_TC, st);
         TcParams prm;
-        prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
+        prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq; prm.NQBp = 0; prm.q_pair_rows = 0; prm.t_pair_rows = 0;
         prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
         l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
@@ -1223,7 +1228,7 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
         {
             MplProfScope prof(MPL_PROF_L2_TC, st);
             TcParams prm;
-            prm.nq = nq; prm.nt = ntc; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
+            prm.nq = nq; prm.nt = ntc; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq; prm.NQBp = 0; prm.q_pair_rows = 0; prm.t_pair_rows = 0;
             prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
             l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
@@ -1236,5 +1241,206 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
         }
     }
     if (n_chunks > 1) return mpl_launch_merge_top2(parts, n_chunks, nq, 2, nullptr, nullptr, -1, d_keys_out, st);
+    return MPL_OK;
+}
+
+// ---- a batch of independent pairs in ONE ranking launch (the pair-batch pipeline, C4) --------------------------------------
+// Pairs share the geometry (strides nq_stride / nt_stride rows, real sizes in dims[pair] = (n1, n2) like the popc batch kernel):
+// work units run over (pair, query block, train tile), operand rows keep the pipeline's pair-strided layout, aug rows / norms /
+// thresholds / lists are padded per query block and per train tile, and a train row beyond n2 -- padding or, when the stride is not
+// a multiple of the tile, the next pair's first rows -- carries |t|^2 = +inf in its aug row so that it never enters a list.
+namespace {
+
+__device__ __forceinline__ unsigned unpack_bits_row(const uint8_t* __restrict__ x, int lane_bytes, uint32_t one, uint4* __restrict__ dst)
+{
+    unsigned pc = 0;
+    for (int b = 0; b < lane_bytes; ++b) {
+        const unsigned v = x[b];
+        pc += __popc(v);
+        uint4 o;
+        o.x = ((v & 1u) ? one : 0u) | ((v & 2u) ? one << 16 : 0u);
+        o.y = ((v & 4u) ? one : 0u) | ((v & 8u) ? one << 16 : 0u);
+        o.z = ((v & 16u) ? one : 0u) | ((v & 32u) ? one << 16 : 0u);
+        o.w = ((v & 64u) ? one : 0u) | ((v & 128u) ? one << 16 : 0u);
+        dst[b] = o;
+    }
+    return pc;
+}
+
+// rows [0, nb * NTp * BN): padded train rows, then nb * NQBp * rq padded query rows; 8 lanes per row
+__global__ void __launch_bounds__(256)
+hamming_prep_batch_kernel(const uint8_t* __restrict__ t, int nt_stride, const uint8_t* __restrict__ q, int nq_stride, int w16, int nb,
+                          const int2* __restrict__ dims, int NTp, int NQBp, int rq, void* __restrict__ tp, void* __restrict__ qp,
+                          float* __restrict__ qnorm, uint4* __restrict__ taug, uint4* __restrict__ qaug, TcHeader* hdr,
+                          uint32_t* __restrict__ gthr, int n_gthr)
+{
+    const int lane = threadIdx.x & 31, sub = lane >> 3, sl = lane & 7;
+    const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
+    const int t_rows = NTp * BN, q_rows = NQBp * rq;
+    const long long total_t = (long long)nb * t_rows, total = total_t + (long long)nb * q_rows;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = 0xFFFFFFFFu;
+    const int lane_bytes = 2 * w16;
+    unsigned tmax = 0;
+    for (long long base = (long long)(blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4; base < total; base += (long long)warps_per_grid * 4) {
+        const long long R = base + sub;
+        const bool live = R < total, is_t = R < total_t;
+        const long long Rl = is_t ? R : R - total_t;
+        const int per = is_t ? t_rows : q_rows, stride = is_t ? nt_stride : nq_stride;
+        const int pr = live ? (int)(Rl / per) : 0, r = live ? (int)(Rl - (long long)pr * per) : 0;
+        const int n_real = live ? (is_t ? dims[pr].y : dims[pr].x) : 0;
+        const size_t row = (size_t)pr * stride + r;                              // operand row in the pair-strided layout
+        unsigned pc = 0;
+        if (live && r < stride) {
+            uint4* dst = reinterpret_cast<uint4*>((char*)(is_t ? tp : qp) + row * 256 * w16 + (size_t)sl * 16 * lane_bytes);
+            if (r < n_real) pc = unpack_bits_row((is_t ? t : q) + row * 16 * w16 + (size_t)sl * lane_bytes, lane_bytes, is_t ? 0x3F80u : 0xC000u, dst);
+            else for (int b = 0; b < lane_bytes; ++b) dst[b] = make_uint4(0, 0, 0, 0);          // padding inside the stride: finite operands
+        }
+#pragma unroll
+        for (int o = 4; o >= 1; o >>= 1) pc += __shfl_xor_sync(0xffffffffu, pc, o);
+        if (live && sl == 0) {
+            if (is_t) write_aug(taug + 2 * (size_t)Rl, true, r < n_real ? (float)pc : INFINITY, true);
+            else { qnorm[Rl] = (float)pc; write_aug(qaug + 2 * (size_t)Rl, false, 0.f, true); }
+        }
+        if (live && is_t && r < n_real) tmax = max(tmax, pc);
+    }
+    tmax = __reduce_max_sync(0xffffffffu, tmax);
+    if (lane == 0 && tmax) atomicMax(&hdr->max_tnorm_bits, __float_as_uint((float)tmax));
+}
+
+// thread per (pair, query): union of the block's exact top-2 lists -> integer Hamming keys, local train indices
+__global__ void __launch_bounds__(256)
+hamming_certify_batch_kernel(int nb, int nq_stride, const int2* __restrict__ dims, int NQBp, int rq, const float* __restrict__ qnorm,
+                             const uint4* __restrict__ cand, int NT, long long U, int G, int max_slots, mpl_key64* __restrict__ keys_out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)nb * nq_stride) return;
+    const int pr = (int)(i / nq_stride), q = (int)(i - (long long)pr * nq_stride);
+    const int2 d = dims[pr];
+    mpl_key64 k0 = MPL_KEY_INVALID, k1 = MPL_KEY_INVALID;
+    if (q < d.x) {
+        const int qb = pr * NQBp + q / rq, row = q % rq;
+        const int f1 = tc_owner((long long)qb * NT, U, G), l1 = tc_owner((long long)qb * NT + NT - 1, U, G);
+        const float qq = qnorm[(size_t)qb * rq + row];
+        for (int sl = 0; sl < (l1 - f1 + 1) * LPS; ++sl) {
+            const uint4* rec = cand + (((size_t)qb * max_slots * LPS + sl) * rq + row) * 2;
+            const uint4 sc = rec[0], id = rec[1];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int ti = (int)(e == 0 ? id.x : id.y);
+                if (ti < 0 || ti >= d.y) continue;
+                const float dd = __fadd_rn(__uint_as_float(e == 0 ? sc.x : sc.y), qq);
+                const mpl_key64 key = ((mpl_key64)__float2uint_rn(dd) << 32) | (mpl_key64)(uint32_t)ti;
+                const mpl_key64 hi = max(k0, key);
+                k0 = min(k0, key); k1 = min(k1, hi);
+            }
+        }
+    }
+    reinterpret_cast<ulonglong2*>(keys_out)[i] = make_ulonglong2(k0, k1);
+}
+
+struct TcBatchPlan { int rq, NQBp, NTp, NQB, G, max_slots, kp16; long long U; size_t off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_gthr, total; };
+
+TcBatchPlan make_batch_plan(int nq_stride, int nt_stride, int w16, int nb, int sm_count)
+{
+    TcBatchPlan P;
+    const int dim = w16 * 128;
+    P.kp16 = dim;
+    P.rq = dim > 256 ? UM : BM;
+    P.NQBp = (nq_stride + P.rq - 1) / P.rq; P.NTp = (nt_stride + BN - 1) / BN;
+    P.NQB = nb * P.NQBp;
+    P.U = (long long)P.NQB * P.NTp;
+    P.G = (int)(P.U < sm_count ? P.U : sm_count);
+    P.max_slots = 1;
+    for (int qb = 0; qb < P.NQB; ++qb) {
+        const int s = tc_owner((long long)qb * P.NTp + P.NTp - 1, P.U, P.G) - tc_owner((long long)qb * P.NTp, P.U, P.G) + 1;
+        if (s > P.max_slots) P.max_slots = s;
+    }
+    size_t o = 256;
+    P.off_qnorm = o; o = align256(o + (size_t)P.NQB * P.rq * 4);
+    P.off_tp = o;    o = align256(o + (size_t)nb * nt_stride * dim * 2);
+    P.off_qp = o;    o = align256(o + (size_t)nb * nq_stride * dim * 2);
+    P.off_taug = o;  o = align256(o + (size_t)nb * P.NTp * BN * AUG_BYTES);
+    P.off_qaug = o;  o = align256(o + (size_t)P.NQB * P.rq * AUG_BYTES);
+    P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * P.rq * 32);
+    P.off_gthr = o;  o = align256(o + (size_t)P.NQB * P.rq * 4);
+    P.total = o;
+    return P;
+}
+
+// pairs per ranking launch: the train operands of the pairs in flight should stay L2-resident (every query block of a pair
+// re-reads the pair's train tiles), and one launch should still hold a few thousand work units
+int hamming_tc_group(int nt_stride, int w16, int nb)
+{
+    const size_t per_pair = (size_t)nt_stride * w16 * 256;
+    int g = (int)std::max<size_t>(1, ((size_t)80 << 20) / std::max<size_t>(per_pair, 1));
+    return std::min(std::min(g, 64), nb);
+}
+
+}  // namespace
+
+bool mpl_hamming_tc_batch_supported(int nq_stride, int nt_stride, int w16)
+{
+    return (w16 == 1 || w16 == 2 || w16 == 4) && nq_stride >= 1 && nt_stride >= 2;
+}
+
+size_t mpl_hamming_tc_batch_scratch_bytes(int nq_stride, int nt_stride, int w16, int nb, int sm_count)
+{
+    if (!mpl_hamming_tc_batch_supported(nq_stride, nt_stride, w16) || nb <= 0) return 16;
+    return make_batch_plan(nq_stride, nt_stride, w16, hamming_tc_group(nt_stride, w16, nb), sm_count).total;
+}
+
+int mpl_hamming_tc_top2_batch(const uint8_t* d_q, int nq_stride, const uint8_t* d_t, int nt_stride, int w16, int nb, const int2* d_dims,
+                              void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st)
+{
+    if (nb <= 0) return MPL_OK;
+    if (!mpl_hamming_tc_batch_supported(nq_stride, nt_stride, w16)) { mpl_set_error("hamming tensor-core batch: unsupported shape (w16=%d)", w16); return MPL_ERR_BAD_ARG; }
+    const int group = hamming_tc_group(nt_stride, w16, nb);
+    const size_t need = make_batch_plan(nq_stride, nt_stride, w16, group, sm_count).total;
+    if (!d_scratch || scratch_bytes < need || ((uintptr_t)d_scratch & 255) != 0) { mpl_set_error("hamming tensor-core batch: scratch %zu < %zu bytes or not 256-byte aligned", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
+    MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    char* base = (char*)d_scratch;
+    const size_t rowb = (size_t)w16 * 16;
+    for (int g0 = 0; g0 < nb; g0 += group) {
+        const int gn = std::min(group, nb - g0);
+        const TcBatchPlan P = make_batch_plan(nq_stride, nt_stride, w16, gn, sm_count);
+        TcHeader* hdr = (TcHeader*)base;
+        float* qnorm = (float*)(base + P.off_qnorm);
+        void* tp = base + P.off_tp; void* qp = base + P.off_qp;
+        uint4* taug = (uint4*)(base + P.off_taug); uint4* qaug = (uint4*)(base + P.off_qaug);
+        uint4* cand = (uint4*)(base + P.off_cand); uint32_t* gthr = (uint32_t*)(base + P.off_gthr);
+        alignas(64) TcMaps maps;
+        memset(&maps, 0, sizeof(maps));
+        int rc;
+        if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, gn * nq_stride, 64, P.rq))) return rc;
+        if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, gn * nt_stride, 64, BN))) return rc;
+        if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, P.NQB * P.rq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, gn * P.NTp * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
+        {
+            MplProfScope prof(MPL_PROF_L2_PREP, st);
+            const long long rows = (long long)gn * P.NTp * BN + (long long)P.NQB * P.rq;
+            long long blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;
+            hamming_prep_batch_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_t + (size_t)g0 * nt_stride * rowb, nt_stride, d_q + (size_t)g0 * nq_stride * rowb, nq_stride,
+                                                                        w16, gn, d_dims + g0, P.NTp, P.NQBp, P.rq, tp, qp, qnorm, taug, qaug, hdr, gthr, P.NQB * P.rq);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+        {
+            MplProfScope prof(MPL_PROF_L2_TC, st);
+            TcParams prm;
+            prm.nq = gn * nq_stride; prm.nt = nt_stride; prm.NT = P.NTp; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
+            prm.NQBp = P.NQBp; prm.q_pair_rows = nq_stride; prm.t_pair_rows = nt_stride;
+            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
+            l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+        {
+            MplProfScope prof(MPL_PROF_L2_RERANK, st);
+            const long long n = (long long)gn * nq_stride;
+            hamming_certify_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(gn, nq_stride, d_dims + g0, P.NQBp, P.rq, qnorm, cand, P.NTp, P.U, P.G,
+                                                                                      P.max_slots, d_keys_out + (size_t)g0 * nq_stride * 2);
+            MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
+        }
+    }
     return MPL_OK;
 }

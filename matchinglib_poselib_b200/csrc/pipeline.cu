@@ -209,6 +209,7 @@ struct BatchPlan {
     int is_float, sqrt_out, ignore_tail;
     int nq_stride, nt_stride, h, bs;
     int splits;                                     // train splits of the Hamming scan (> 1 only for batches too small to fill the GPU)
+    int use_tc;                                     // Hamming scan on the tensor cores (mpl_hamming_tc_top2_batch): one ranking launch per group of pairs
     size_t pe;                                      // bytes per keypoint
     size_t l2_scratch;
     CamParams cam;
@@ -300,7 +301,10 @@ int enqueue_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, 
         pack_pairs_kernel<<<dim3(blocks, 2 * nb), 256, 0, st>>>((const uint8_t*)(D + A.raw), (const unsigned long long*)(D + A.offs), d_dims,
                                                                  P.cols, P.used, P.row_bytes, P.nq_stride, P.nt_stride, (uint8_t*)(D + A.dq), (uint8_t*)(D + A.dt));
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
-        if (P.splits > 1) {
+        if (P.use_tc) {
+            if ((rc = mpl_hamming_tc_top2_batch((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, nb, d_dims,
+                                                D + A.l2scr, P.l2_scratch, d_keys, mpl_ctx()->sm_count, st))) return rc;
+        } else if (P.splits > 1) {
             // a batch of a few pairs cannot fill the GPU with one CTA row per pair: split the train rows as the single-pair
             // matcher does and merge the per-split keys (one merge launch per pair; only taken for nb <= 8)
             mpl_key64* d_part = (mpl_key64*)(D + A.part);
@@ -458,7 +462,15 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
     if (n_pairs >= 16 && n_pairs <= bs) bs = (n_pairs + 1) / 2;
     P.bs = bs;
     P.splits = 1;
-    if (!P.is_float && bs <= 8) {
+    // Hamming scan: tensor cores (bits as bf16, knn_l2_tc.cu) when the rows are 16 / 32 / 64 bytes and the pairs are big enough to
+    // fill the 256 x 128 tiles; the popc batch kernel otherwise (mpl_set_hamming_path: 1 forces popc, 2 the tensor cores)
+    P.use_tc = 0;
+    if (!P.is_float && mpl_hamming_tc_batch_supported(P.nq_stride, P.nt_stride, P.w16)) {
+        const int path = mpl_hamming_path();
+        if (path == 2 || (path == 0 && P.nq_stride >= 512 && P.nt_stride >= 512)) P.use_tc = 1;
+    }
+    if (P.use_tc) P.l2_scratch = mpl_hamming_tc_batch_scratch_bytes(P.nq_stride, P.nt_stride, P.w16, bs, ctx->sm_count) + 256;
+    if (!P.is_float && !P.use_tc && bs <= 8) {
         const int sp = mpl_hamming_pick_splits(P.nq_stride, P.nt_stride, P.w16, std::max(1, ctx->sm_count / bs));
         if (sp > 1 && (P.nt_stride + sp - 1) / sp >= 32) P.splits = sp;
     }

@@ -108,6 +108,33 @@ def test_batch_equals_oracle_and_host_replay(P, matcher):
                 assert np.array_equal(hr["E"], r["E"])               # same kernels from the selection on: bit-identical
 
 
+@pytest.mark.parametrize("nb", [16, 32, 61])
+def test_batch_hamming_paths_identical(P, nb):
+    """The batch's Hamming scan on the tensor cores (one ranking launch per group of pairs; bits as bf16) and the popc batch kernel
+    give the same matches, hence the same everything; pairs of different sizes, strides that are no multiple of the tiles."""
+    from matchinglib_poselib_b200 import _lib
+    shapes = [(1500, 1700), (1700, 1500), (130, 1650), (1650, 129), (5, 900), (1111, 1333), (257, 255), (1700, 1700), (0, 100), (640, 2)]
+    pairs, th = [], None
+    for i, (n1, n2) in enumerate(shapes):
+        q, t, p1, p2, th = make_pair(n1, n2, nb, seed=300 + i)
+        if n2 > 300:
+            t[n2 - 1] = t[7]; t[n2 // 2] = t[7]                             # duplicates: ties must resolve to the lowest train index
+        pairs.append((q, t, p1, p2))
+    lib = _lib.load()
+    out = {}
+    for path in (1, 2):
+        lib.mpl_set_hamming_path(path)
+        try:
+            out[path] = P.matchAndEstimatePoseBatch(pairs * 3, "LINEAR", True, th, 64, 0.999, True, seeds=list(range(len(pairs) * 3)))
+        finally:
+            lib.mpl_set_hamming_path(0)
+    for a, b in zip(out[1], out[2]):
+        assert np.array_equal(a["matches"], b["matches"]) and np.array_equal(a["mask"], b["mask"]) and a["count"] == b["count"]
+        assert np.array_equal(a["E"], b["E"])
+    for r, (q, t, p1, p2) in zip(out[2][:4], pairs[:4]):
+        assert np.array_equal(r["matches"], oracle_matches(q, t, "LINEAR"))
+
+
 def test_c4_unit_vs_oracle(P):
     """The unit of BASELINE config C4 at its own size: AKAZE-like 61-byte descriptors 5000 x 5000 + RANSAC 1000 samples + refit."""
     q, t, p1, p2, th = make_pair(5000, 5000, 61, seed=1004)
