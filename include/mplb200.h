@@ -82,9 +82,11 @@ int mpl_knn2_l2f32(const float* q, int nq, size_t q_step, const float* t, int nt
                    int dim, int sqrt_out, int k, int32_t* idx, float* dist);
 /* force a float path: 0 = auto, 1 = exact SIMT scan only, 2 = tensor-core ranking + exact re-rank */
 int mpl_set_l2_path(int path);
-/* Hamming k-NN path of mpl_knn2_hamming / mpl_knn2_hamming_dev / getMatches on CV_8U descriptors: 0 = auto, 1 = popc scan
- * (hamming_top2_kernel), 2 = tensor cores (bits unpacked to bf16, hamming = |q| + |t| - 2 q.t on the float ranking kernel in its
- * exact-integer mode; rows of 16 / 32 / 64 bytes only).  Both give the same keys bit for bit; process-wide. */
+/* Hamming k-NN path of mpl_knn2_hamming / mpl_knn2_hamming_dev / getMatches / mpl_match_pose_batch on CV_8U descriptors: 0 = auto
+ * (tensor cores for large scans), 1 = popc scan (hamming_top2_kernel), 2 = tensor cores: bits unpacked to e4m3 bytes (0 / 1 train,
+ * 0 / -2 query), hamming = |q| + |t| - 2 q.t on the float ranking kernel in its exact-integer mode (tcgen05 kind::f8f6f4; rows of
+ * 16 / 32 / 64 bytes only), 3 = the same with bf16 operands (kind::f16; kept for comparison).  All give the same keys bit for bit;
+ * process-wide. */
 int mpl_set_hamming_path(int path);
 
 /* Lowe ratio test + cv::DMatch emission (matchers.cpp:601-625, 677-701; nmslib_matchers.h:399-415):

@@ -294,7 +294,8 @@ static int round_w16(int nbytes_used)
     return r;     // 1,2,4,8,16
 }
 
-// Hamming k-NN path: 0 = auto, 1 = popc scan (hamming_top2_kernel), 2 = tensor cores (bits as bf16, knn_l2_tc.cu).
+// Hamming k-NN path: 0 = auto, 1 = popc scan (hamming_top2_kernel), 2 = tensor cores (bits as e4m3 bytes, knn_l2_tc.cu), 3 = tensor cores
+// with bf16 operands (the first form; kept for comparison).
 // auto rule of the Hamming path, from measurements (tools/hamming_tc_time.py): the tensor-core path is 1.4x
 // (5000 x 5000 x 64 B) to 3.4x (10 000 x 12.5 M x 32 B) faster once the scan hides its four launches and fills the 256-row query
 // blocks; few queries (a tile computes 256 rows whatever nq is) and small scans stay on the popc kernel
@@ -302,13 +303,13 @@ static int round_w16(int nbytes_used)
 #define MPL_HAMMING_TC_AUTO(nq, nt, w16) ((nq) >= 128 && (long long)(nq) * (nt) >= (1ll << 24))
 #endif
 static std::atomic<int> g_hamming_path{0};
-extern "C" int mpl_set_hamming_path(int path) { if (path < 0 || path > 2) return MPL_ERR_BAD_ARG; g_hamming_path.store(path, std::memory_order_relaxed); return MPL_OK; }
+extern "C" int mpl_set_hamming_path(int path) { if (path < 0 || path > 3) return MPL_ERR_BAD_ARG; g_hamming_path.store(path, std::memory_order_relaxed); return MPL_OK; }
 int mpl_hamming_path() { return g_hamming_path.load(std::memory_order_relaxed); }
 static bool hamming_wants_tc(int nq, int nt, int w16)
 {
     const int path = g_hamming_path.load(std::memory_order_relaxed);
     if (path == 1 || !mpl_hamming_tc_supported(nq, nt, w16)) return false;
-    if (path == 2) return true;
+    if (path >= 2) return true;
     return MPL_HAMMING_TC_AUTO(nq, nt, w16);
 }
 
@@ -338,8 +339,8 @@ extern "C" int mpl_knn2_hamming_dev(const void* d_q, int nq, const void* d_t, in
     if (hamming_wants_tc(nq, nt, w16) && d_scratch && ((uintptr_t)d_scratch & 255) == 0 &&
         scratch_bytes >= mpl_hamming_tc_scratch_bytes(nq, nt, w16, sm))
         return mpl_hamming_tc_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, train_offset, d_scratch, scratch_bytes,
-                                   (mpl_key64*)d_keys_out, sm, st);
-    if (g_hamming_path.load(std::memory_order_relaxed) == 2) { mpl_set_error("hamming_dev: tensor-core path forced but shape / scratch do not allow it (w16=%d, scratch %zu bytes)", w16, scratch_bytes); return MPL_ERR_BAD_ARG; }
+                                   (mpl_key64*)d_keys_out, sm, st, mpl_hamming_path() == 3 ? 1 : 2);
+    if (g_hamming_path.load(std::memory_order_relaxed) >= 2) { mpl_set_error("hamming_dev: tensor-core path forced but shape / scratch do not allow it (w16=%d, scratch %zu bytes)", w16, scratch_bytes); return MPL_ERR_BAD_ARG; }
     const int splits = mpl_hamming_pick_splits(nq, nt, w16, sm);
     if (splits == 1)
         return mpl_launch_hamming_top2((const uint8_t*)d_q, nq, (const uint8_t*)d_t, nt, w16, 1, 1, train_offset,
@@ -473,7 +474,7 @@ int mpl_hamming_keys_locked(const uint8_t* q, int nq, size_t q_step, const uint8
     if (hamming_wants_tc(nq, nt, w16)) {
         const size_t need = mpl_hamming_tc_scratch_bytes(nq, nt, w16, g_ctx.sm_count);
         if ((rc = bpart.ensure(need))) return rc;
-        rc = mpl_hamming_tc_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, 0, bpart.ptr, need, (mpl_key64*)bkeys.ptr, g_ctx.sm_count, st);
+        rc = mpl_hamming_tc_top2((const uint8_t*)bq.ptr, nq, (const uint8_t*)bt.ptr, nt, w16, 0, bpart.ptr, need, (mpl_key64*)bkeys.ptr, g_ctx.sm_count, st, mpl_hamming_path() == 3 ? 1 : 2);
         if (rc) return rc;
         *d_keys = (mpl_key64*)bkeys.ptr;
         return MPL_OK;

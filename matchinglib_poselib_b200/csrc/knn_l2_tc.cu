@@ -124,6 +124,12 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
                  "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// e4m3 x e4m3 -> f32, K = 32 per instruction (32 bytes of a K-major row, like the other kinds)
+__device__ __forceinline__ void tc_mma_f8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 // 32 lanes x 32 consecutive columns of 32-bit accumulators -> 32 registers per thread (thread = lane = row)
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -144,7 +150,7 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 [[maybe_unused]] __device__ __forceinline__ uint64_t umma_desc_sw32(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);
 }
-// instruction descriptor: D = f32, A/B format (1 = bf16, 2 = tf32), both K-major, N = 128, M = 128
+// instruction descriptor: D = f32, A/B format (kind::f16: 1 = bf16; kind::tf32: 2; kind::f8f6f4: 0 = e4m3), both K-major, N = 128, M = 128
 __host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(UM >> 4) << 24);
 }
@@ -287,8 +293,63 @@ l2_prep_tf32_kernel(const float* __restrict__ t, int nt, size_t t_ld, const floa
 }
 
 // Binary descriptors (Hamming distance as a contraction, section "Hamming on the tensor cores" below): rows of w16 x 16 bytes ->
-// bf16 operand rows of 128 w16 elements, train bits as 0 / 1, query bits as 0 / -2; |x|^2 = popcount.  8 lanes per row: lane sl
-// unpacks bytes [2 w16 sl, 2 w16 (sl + 1)) into 16 w16 elements (element 8 b + i = bit i of byte b).
+// operand rows of 128 w16 elements, train bits as 0 / 1, query bits as 0 / -2, in e4m3 (one byte per bit, kind::f8f6f4) or bf16;
+// |x|^2 = popcount.  8 lanes per row, lane sl takes bytes sl, sl + 8, ...: the 8 lanes of a row write 64 (e4m3) / 128 (bf16)
+// contiguous bytes per step.  Element 8 b + i = bit i of byte b.
+template <bool FP8>
+__device__ __forceinline__ unsigned unpack_bits_row(const uint8_t* __restrict__ x, int row_bytes, int sl, bool is_t, bool real, char* __restrict__ dst)
+{
+    unsigned pc = 0;
+    for (int b = sl; b < row_bytes; b += 8) {
+        const unsigned v = real ? x[b] : 0u;                                     // padding rows: finite (zero) operands
+        pc += __popc(v);
+        if (FP8) {
+            const uint32_t one = is_t ? 0x38u : 0xC0u;                           // e4m3 1.0 / -2.0
+            uint2 o;
+            o.x = (((v & 0xFu) * 0x00204081u) & 0x01010101u) * one;
+            o.y = (((v >> 4) * 0x00204081u) & 0x01010101u) * one;
+            reinterpret_cast<uint2*>(dst)[b] = o;
+        } else {
+            const uint32_t one = is_t ? 0x3F80u : 0xC000u;                       // bf16 1.0 / -2.0
+            uint4 o;
+            o.x = ((v & 1u) ? one : 0u) | ((v & 2u) ? one << 16 : 0u);
+            o.y = ((v & 4u) ? one : 0u) | ((v & 8u) ? one << 16 : 0u);
+            o.z = ((v & 16u) ? one : 0u) | ((v & 32u) ? one << 16 : 0u);
+            o.w = ((v & 64u) ? one : 0u) | ((v & 128u) ? one << 16 : 0u);
+            reinterpret_cast<uint4*>(dst)[b] = o;
+        }
+    }
+    return pc;
+}
+
+// e4m3 code of an integer with at most four significant bits (<= 448)
+__device__ __forceinline__ uint32_t e4m3_int(unsigned v)
+{
+    if (v == 0) return 0;
+    const int e = 31 - __clz(v);
+    const unsigned m = e >= 3 ? (v >> (e - 3)) & 7u : (v << (3 - e)) & 7u;
+    return ((uint32_t)(e + 7) << 3) | m;
+}
+
+// aug row (32 bytes) of a bit-vector row with popcount pc (<= 512).  bf16: write_aug.  e4m3 has four significant bits, a maximum of
+// 448 and no infinity: |t|^2 = pc goes into six exact pieces (bit 9 as 256 + 256, bits 5-8 as two halves of 16 m, bits 1-4, bit 0)
+// against eight ones in the query row; a padding row gets 8 x 448 = 3584, above every real score (<= 512 + 0).
+template <bool FP8>
+__device__ __forceinline__ void write_aug_bits(uint4* dst, bool is_t, unsigned pc, bool pad)
+{
+    if (!FP8) { write_aug(dst, is_t, pad ? INFINITY : (float)pc, true); return; }
+    uint4 w = make_uint4(0, 0, 0, 0);
+    if (!is_t) { w.x = 0x38383838u; w.y = 0x38383838u; }
+    else if (pad) { w.x = 0x7E7E7E7Eu; w.y = 0x7E7E7E7Eu; }
+    else {
+        const uint32_t h9 = (pc & 0x200u) ? e4m3_int(256) : 0u, h5 = e4m3_int((pc & 0x1E0u) >> 1);
+        w.x = h9 | (h9 << 8) | (h5 << 16) | (h5 << 24);
+        w.y = e4m3_int(pc & 0x1Eu) | (e4m3_int(pc & 1u) << 8);
+    }
+    dst[0] = w; dst[1] = make_uint4(0, 0, 0, 0);
+}
+
+template <bool FP8>
 __global__ void __launch_bounds__(256)
 hamming_prep_kernel(const uint8_t* __restrict__ t, int nt, const uint8_t* __restrict__ q, int nq, int w16, void* __restrict__ tp,
                     void* __restrict__ qp, float* __restrict__ tnorm, int nt_pad, float* __restrict__ qnorm, uint4* __restrict__ taug,
@@ -298,7 +359,8 @@ hamming_prep_kernel(const uint8_t* __restrict__ t, int nt, const uint8_t* __rest
     const int warps_per_grid = gridDim.x * (blockDim.x >> 5);
     const int total = nt_pad + nq;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = 0xFFFFFFFFu;
-    const int lane_bytes = 2 * w16;
+    const int row_bytes = 16 * w16;
+    const size_t out_row = (size_t)row_bytes * (FP8 ? 8 : 16);
     unsigned tmax = 0;
     for (int base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4; base < total; base += warps_per_grid * 4) {
         const int row = base + sub;
@@ -306,29 +368,12 @@ hamming_prep_kernel(const uint8_t* __restrict__ t, int nt, const uint8_t* __rest
         const int r = is_t ? row : row - nt_pad;
         const bool pad = live && is_t && r >= nt;
         unsigned pc = 0;
-        if (live && !pad) {
-            const uint8_t* x = (is_t ? t : q) + (size_t)r * 16 * w16 + (size_t)sl * lane_bytes;
-            const uint32_t one = is_t ? 0x3F80u : 0xC000u;                       // bf16 1.0 / -2.0
-            uint4* dst = reinterpret_cast<uint4*>((char*)(is_t ? tp : qp) + (size_t)r * 256 * w16 + (size_t)sl * 16 * lane_bytes);
-            for (int b = 0; b < lane_bytes; ++b) {
-                const unsigned v = x[b];
-                pc += __popc(v);
-                uint4 o;
-                o.x = ((v & 1u) ? one : 0u) | ((v & 2u) ? one << 16 : 0u);
-                o.y = ((v & 4u) ? one : 0u) | ((v & 8u) ? one << 16 : 0u);
-                o.z = ((v & 16u) ? one : 0u) | ((v & 32u) ? one << 16 : 0u);
-                o.w = ((v & 64u) ? one : 0u) | ((v & 128u) ? one << 16 : 0u);
-                dst[b] = o;
-            }
-        }
+        if (live && !pad) pc = unpack_bits_row<FP8>((is_t ? t : q) + (size_t)r * row_bytes, row_bytes, sl, is_t, true, (char*)(is_t ? tp : qp) + (size_t)r * out_row);
 #pragma unroll
         for (int o = 4; o >= 1; o >>= 1) pc += __shfl_xor_sync(0xffffffffu, pc, o);
         if (live && sl == 0) {
-            if (pad) { tnorm[r] = INFINITY; write_aug(taug + 2 * (size_t)r, true, INFINITY, true); }
-            else {
-                (is_t ? tnorm : qnorm)[r] = (float)pc;
-                write_aug((is_t ? taug : qaug) + 2 * (size_t)r, is_t, (float)pc, true);
-            }
+            if (is_t) tnorm[r] = pad ? INFINITY : (float)pc; else qnorm[r] = (float)pc;
+            write_aug_bits<FP8>((is_t ? taug : qaug) + 2 * (size_t)r, is_t, pc, pad);
         }
         if (live && is_t && !pad) tmax = max(tmax, pc);
     }
@@ -346,6 +391,7 @@ struct TcParams {
     // at pair * q_pair_rows / pair * t_pair_rows, its aug rows are padded per block / per tile.  NQBp = 0: one problem.
     int NQBp, q_pair_rows, t_pair_rows;
     int slabs16, slabs32;            // K slabs of 128 bytes in bf16 / tf32 mode
+    int slabs8;                      // > 0: e4m3 operands (bits of binary descriptors as 0 / 1 bytes), K slabs of 128 elements; exact-integer mode
     uint4* cand;                     // [qblock][slot][LPS][rq rows][2 x uint4] = 4 scores + 4 train indices
     uint32_t* gthr;                  // [NQB * rq] per query: smallest list threshold any CTA has published (order-preserving uint)
     const TcHeader* hdr;
@@ -572,12 +618,12 @@ __device__ __forceinline__ unsigned group_mask32(const uint32_t (&r)[32], float 
 // the tile's MMAs, so it is split).  The whole warp runs the loop (uniform control flow), one elected lane issues.
 // Accumulators are handed over per M block: t_full / t_empty index = accumulator buffer * 2 + m; a B slab is released
 // when BOTH issuers' MMAs on it have retired (b_empty counts 2 commits), likewise the resident A block (a_empty).
-template <int MODE, int SPS>   // MODE 0 = bf16 (kind::f16), 1 = tf32; SPS = K slabs per B ring stage (one barrier round trip per stage)
+template <int MODE, int SPS>   // MODE 0 = bf16 (kind::f16), 1 = tf32, 2 = e4m3 (kind::f8f6f4); SPS = K slabs per B ring stage (one barrier round trip per stage)
 __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1, int NT, int n_slabs, int n_stages, uint32_t a_slab16, uint32_t a_addr, uint32_t aa_addr,
                                                uint32_t b_addr, uint32_t tmem_base, uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full,
                                                uint64_t* b_empty, uint64_t* t_full, uint64_t* t_empty)
 {
-    constexpr uint32_t idesc = umma_idesc(MODE == 1 ? 2u : 1u);
+    constexpr uint32_t idesc = umma_idesc(MODE == 1 ? 2u : MODE == 2 ? 0u : 1u);
     constexpr uint64_t hi128 = ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);     // see umma_desc()
     constexpr uint64_t hi32 = ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);       // see umma_desc_sw32()
     const uint64_t ada = hi32 | (uint64_t)((aa_addr + m * (UM * AUG_BYTES)) >> 4);
@@ -612,7 +658,7 @@ __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1
                 const uint32_t sb = b_addr + stage * (SPS * B_SLAB + BN * AUG_BYTES);
                 if (s == 0) {                                                    // aug K step first: D = |t|^2 (overwrites)
                     const uint64_t bda = hi32 | (uint64_t)((sb + SPS * B_SLAB) >> 4);
-                    if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
+                    if (MODE == 1) tc_mma_tf32(d, ada, bda, idesc, 0u); else if (MODE == 2) tc_mma_f8(d, ada, bda, idesc, 0u); else tc_mma_f16(d, ada, bda, idesc, 0u);
                 }
 #pragma unroll
                 for (int j = 0; j < SPS; ++j) {
@@ -620,7 +666,9 @@ __device__ __forceinline__ void mma_issue_loop(int m, long long u0, long long u1
                     const uint64_t ad = ad0 + (uint64_t)((uint32_t)(s + j) * a_slab16);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {                                // 4 x 32 bytes of K per slab row
-                        if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u); else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                        if (MODE == 1) tc_mma_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                        else if (MODE == 2) tc_mma_f8(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
+                        else tc_mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1u);
                     }
                 }
                 tc_commit(&b_empty[stage]);                                      // stage free once both issuers' MMAs retire
@@ -752,7 +800,7 @@ __device__ __forceinline__ void epilogue_loop(const TcParams& p, long long u0, l
 #endif
 }
 
-struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
+struct TcMaps { CUtensorMap a16, b16, a32, b32, aa16, ba16, aa32, ba32, a8, b8, aa8, ba8; };   // main slabs (128B swizzle) and aug slabs (32B swizzle)
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
@@ -768,13 +816,14 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
     const uint32_t pend_s = share_s + SMEM_SHARE;                    // [PEND_CAP][epilogue threads] x (score, train index)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const bool tf32 = p.hdr->not_bf16_exact != 0;
-    const int n_slabs = tf32 ? p.slabs32 : p.slabs16;
-    const int KS = tf32 ? 32 : 64;                               // elements per 128-byte slab row
-    const CUtensorMap* mapA = tf32 ? &maps.a32 : &maps.a16;
-    const CUtensorMap* mapB = tf32 ? &maps.b32 : &maps.b16;
-    const CUtensorMap* mapAa = tf32 ? &maps.aa32 : &maps.aa16;
-    const CUtensorMap* mapBa = tf32 ? &maps.ba32 : &maps.ba16;
+    const bool fp8 = p.slabs8 > 0;
+    const bool tf32 = !fp8 && p.hdr->not_bf16_exact != 0;
+    const int n_slabs = fp8 ? p.slabs8 : tf32 ? p.slabs32 : p.slabs16;
+    const int KS = fp8 ? 128 : tf32 ? 32 : 64;                   // elements per 128-byte slab row
+    const CUtensorMap* mapA = fp8 ? &maps.a8 : tf32 ? &maps.a32 : &maps.a16;
+    const CUtensorMap* mapB = fp8 ? &maps.b8 : tf32 ? &maps.b32 : &maps.b16;
+    const CUtensorMap* mapAa = fp8 ? &maps.aa8 : tf32 ? &maps.aa32 : &maps.aa16;
+    const CUtensorMap* mapBa = fp8 ? &maps.ba8 : tf32 ? &maps.ba32 : &maps.ba16;
     const bool wide = p.rq == UM;                                // 128 < dim <= 256: query blocks of one UMMA M block
     const int a_slab = p.rq * SLAB_BYTES, a_aug = p.rq * AUG_BYTES;
     unsigned char* sA = smem;                                    // n_slabs x 32 KB (wide: 16 KB)
@@ -849,8 +898,9 @@ l2_tc_rank_kernel(const __grid_constant__ TcMaps maps, const TcParams p)
         const int m = warp >> 1;
 #define MPL_ISSUE(MODE, SPS) mma_issue_loop<MODE, SPS>(m, u0, u1, p.NT, n_slabs, n_stages, (uint32_t)(a_slab >> 4), smem_u32(sA), smem_u32(sAa), smem_u32(sB), tmem_base, \
                                                        a_full, a_empty, b_full, b_empty, t_full, t_empty)
-        if (tf32) { if (sps == 2) MPL_ISSUE(1, 2); else MPL_ISSUE(1, 1); }
-        else      { if (sps == 2) MPL_ISSUE(0, 2); else MPL_ISSUE(0, 1); }
+        if (fp8)       { if (sps == 2) MPL_ISSUE(2, 2); else MPL_ISSUE(2, 1); }
+        else if (tf32) { if (sps == 2) MPL_ISSUE(1, 2); else MPL_ISSUE(1, 1); }
+        else           { if (sps == 2) MPL_ISSUE(0, 2); else MPL_ISSUE(0, 1); }
 #undef MPL_ISSUE
     } else if (warp >= 4 && !(wide && (((warp - 4) >> 2) & 1))) {
         // ===== epilogue: thread = one query row of UMMA block m, one half (64 columns) of the tile (wide: m = 0 only) =====
@@ -1025,10 +1075,10 @@ struct TcPlan {
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-TcPlan make_plan(int nq, int nt, int dim, int sm_count, bool bf16_only = false)
+TcPlan make_plan(int nq, int nt, int dim, int sm_count, int bits_fmt = 0)   // bits_fmt: 0 float rows; binary rows as 1 = bf16, 2 = e4m3
 {
     TcPlan P;
-    P.rq = (bf16_only ? dim > 256 : dim > 128) ? UM : BM;     // resident A block: 4 slabs of BM rows, or 8 of UM rows
+    P.rq = dim > (bits_fmt == 2 ? 512 : bits_fmt == 1 ? 256 : 128) ? UM : BM;     // resident A block: 4 slabs of BM rows, or 8 of UM rows
     P.NQB = (nq + P.rq - 1) / P.rq;
     P.NT = (nt + BN - 1) / BN;
     P.U = (long long)P.NQB * P.NT;
@@ -1043,7 +1093,7 @@ TcPlan make_plan(int nq, int nt, int dim, int sm_count, bool bf16_only = false)
     size_t o = 256;
     P.off_tnorm = o; o = align256(o + (size_t)P.NT * BN * 4);
     P.off_qnorm = o; o = align256(o + (size_t)P.NQB * P.rq * 4);
-    const size_t row_bytes = bf16_only ? (size_t)P.kp16 * 2 : (size_t)P.kp32 * 4;
+    const size_t row_bytes = bits_fmt == 2 ? (size_t)dim : bits_fmt == 1 ? (size_t)P.kp16 * 2 : (size_t)P.kp32 * 4;
     P.off_tp = o;    o = align256(o + (size_t)nt * row_bytes);
     P.off_qp = o;    o = align256(o + (size_t)nq * row_bytes);
     P.off_taug = o;  o = align256(o + (size_t)P.NT * BN * AUG_BYTES);
@@ -1138,7 +1188,7 @@ int mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, int n
         MplProfScope prof(MPL_PROF_L2_TC, st);
         TcParams prm;
         prm.nq = nq; prm.nt = nt; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq; prm.NQBp = 0; prm.q_pair_rows = 0; prm.t_pair_rows = 0;
-        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
+        prm.slabs16 = P.kp16 / 64; prm.slabs32 = P.kp32 / 32; prm.slabs8 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
         l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
     }
@@ -1174,35 +1224,41 @@ int mpl_l2tc_last_fallbacks(const void* d_scratch, unsigned* count, unsigned* tf
 // re-read by the other query blocks out of L2), each chunk leaving partial keys that one merge launch folds.
 bool mpl_hamming_tc_supported(int nq, int nt, int w16) { return nq >= 1 && nt >= 2 && (w16 == 1 || w16 == 2 || w16 == 4); }
 
-static int hamming_tc_chunk_rows(int w16) { return std::max(BN, (int)(((size_t)48 << 20) / ((size_t)w16 * 256)) / BN * BN); }
+static int hamming_tc_chunk_rows(int w16, int fmt) { return std::max(BN, (int)(((size_t)48 << 20) / ((size_t)w16 * (fmt == 2 ? 128 : 256))) / BN * BN); }
 
+static size_t hamming_tc_scratch_fmt(int nq, int nt, int w16, int sm_count, int fmt)
+{
+    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16, fmt));
+    const int n_chunks = (nt + chunk - 1) / chunk;
+    const size_t plan = make_plan(nq, chunk, w16 * 128, sm_count, fmt).total;
+    return plan + (n_chunks > 1 ? align256((size_t)n_chunks * nq * 2 * sizeof(mpl_key64)) : 0);
+}
+// sized for either operand format (fmt 1 = bf16, 2 = e4m3)
 size_t mpl_hamming_tc_scratch_bytes(int nq, int nt, int w16, int sm_count)
 {
     if (!mpl_hamming_tc_supported(nq, nt, w16)) return 16;
-    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16));
-    const int n_chunks = (nt + chunk - 1) / chunk;
-    const size_t plan = make_plan(nq, chunk, w16 * 128, sm_count, true).total;
-    return plan + (n_chunks > 1 ? align256((size_t)n_chunks * nq * 2 * sizeof(mpl_key64)) : 0);
+    return std::max(hamming_tc_scratch_fmt(nq, nt, w16, sm_count, 1), hamming_tc_scratch_fmt(nq, nt, w16, sm_count, 2));
 }
 
 int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int w16, long long train_offset, void* d_scratch,
-                        size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st)
+                        size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st, int fmt)
 {
+    if (fmt != 1) fmt = 2;
     if (!mpl_hamming_tc_supported(nq, nt, w16)) { mpl_set_error("hamming tensor-core path: unsupported shape (w16=%d, nt=%d)", w16, nt); return MPL_ERR_BAD_ARG; }
-    const size_t need = mpl_hamming_tc_scratch_bytes(nq, nt, w16, sm_count);
+    const size_t need = hamming_tc_scratch_fmt(nq, nt, w16, sm_count, fmt);
     if (!d_scratch || scratch_bytes < need) { mpl_set_error("hamming tensor-core path: scratch %zu < %zu bytes", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
     if (((uintptr_t)d_scratch & 255) != 0) { mpl_set_error("hamming tensor-core path: scratch must be 256-byte aligned"); return MPL_ERR_BAD_ARG; }
     const int dim = w16 * 128;
-    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16));
+    const int chunk = std::min(nt, hamming_tc_chunk_rows(w16, fmt));
     const int n_chunks = (nt + chunk - 1) / chunk;
-    const size_t plan_bytes = make_plan(nq, chunk, dim, sm_count, true).total;
+    const size_t plan_bytes = make_plan(nq, chunk, dim, sm_count, fmt).total;
     char* base = (char*)d_scratch;
     mpl_key64* parts = n_chunks > 1 ? (mpl_key64*)(base + plan_bytes) : d_keys_out;
     MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, U8 = CU_TENSOR_MAP_DATA_TYPE_UINT8;
     for (int c = 0; c < n_chunks; ++c) {
         const int t0 = c * chunk, ntc = std::min(chunk, nt - t0);
-        const TcPlan P = make_plan(nq, ntc, dim, sm_count, true);                     // <= the first chunk's plan
+        const TcPlan P = make_plan(nq, ntc, dim, sm_count, fmt);                      // <= the first chunk's plan
         TcHeader* hdr = (TcHeader*)base;
         float* tnorm = (float*)(base + P.off_tnorm); float* qnorm = (float*)(base + P.off_qnorm);
         void* tp = base + P.off_tp; void* qp = base + P.off_qp;
@@ -1212,16 +1268,24 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
         alignas(64) TcMaps maps;
         memset(&maps, 0, sizeof(maps));
         int rc;
-        if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, P.rq))) return rc;
-        if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, ntc, 64, BN))) return rc;
-        if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
-        if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, P.NT * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        if (fmt == 2) {
+            if ((rc = encode_map(&maps.a8, U8, 1, qp, dim, nq, 128, P.rq))) return rc;
+            if ((rc = encode_map(&maps.b8, U8, 1, tp, dim, ntc, 128, BN))) return rc;
+            if ((rc = encode_map(&maps.aa8, U8, 1, qaug, 32, nq, 32, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+            if ((rc = encode_map(&maps.ba8, U8, 1, taug, 32, P.NT * BN, 32, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        } else {
+            if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, nq, 64, P.rq))) return rc;
+            if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, ntc, 64, BN))) return rc;
+            if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, nq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+            if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, P.NT * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        }
         MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
         {
             MplProfScope prof(MPL_PROF_L2_PREP, st);
             const int rows = P.NT * BN + nq;
             int blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;
-            hamming_prep_kernel<<<blocks, 256, 0, st>>>(d_t + (size_t)t0 * 16 * w16, ntc, d_q, nq, w16, tp, qp, tnorm, P.NT * BN, qnorm, taug, qaug,
+            auto prep = fmt == 2 ? hamming_prep_kernel<true> : hamming_prep_kernel<false>;
+            prep<<<blocks, 256, 0, st>>>(d_t + (size_t)t0 * 16 * w16, ntc, d_q, nq, w16, tp, qp, tnorm, P.NT * BN, qnorm, taug, qaug,
                                                         hdr, gthr, P.NQB * P.rq);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         }
@@ -1229,7 +1293,7 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
             MplProfScope prof(MPL_PROF_L2_TC, st);
             TcParams prm;
             prm.nq = nq; prm.nt = ntc; prm.NT = P.NT; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq; prm.NQBp = 0; prm.q_pair_rows = 0; prm.t_pair_rows = 0;
-            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
+            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.slabs8 = fmt == 2 ? dim / 128 : 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
             l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         }
@@ -1251,23 +1315,8 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
 // a multiple of the tile, the next pair's first rows -- carries |t|^2 = +inf in its aug row so that it never enters a list.
 namespace {
 
-__device__ __forceinline__ unsigned unpack_bits_row(const uint8_t* __restrict__ x, int lane_bytes, uint32_t one, uint4* __restrict__ dst)
-{
-    unsigned pc = 0;
-    for (int b = 0; b < lane_bytes; ++b) {
-        const unsigned v = x[b];
-        pc += __popc(v);
-        uint4 o;
-        o.x = ((v & 1u) ? one : 0u) | ((v & 2u) ? one << 16 : 0u);
-        o.y = ((v & 4u) ? one : 0u) | ((v & 8u) ? one << 16 : 0u);
-        o.z = ((v & 16u) ? one : 0u) | ((v & 32u) ? one << 16 : 0u);
-        o.w = ((v & 64u) ? one : 0u) | ((v & 128u) ? one << 16 : 0u);
-        dst[b] = o;
-    }
-    return pc;
-}
-
 // rows [0, nb * NTp * BN): padded train rows, then nb * NQBp * rq padded query rows; 8 lanes per row
+template <bool FP8>
 __global__ void __launch_bounds__(256)
 hamming_prep_batch_kernel(const uint8_t* __restrict__ t, int nt_stride, const uint8_t* __restrict__ q, int nq_stride, int w16, int nb,
                           const int2* __restrict__ dims, int NTp, int NQBp, int rq, void* __restrict__ tp, void* __restrict__ qp,
@@ -1279,7 +1328,8 @@ hamming_prep_batch_kernel(const uint8_t* __restrict__ t, int nt_stride, const ui
     const int t_rows = NTp * BN, q_rows = NQBp * rq;
     const long long total_t = (long long)nb * t_rows, total = total_t + (long long)nb * q_rows;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = 0xFFFFFFFFu;
-    const int lane_bytes = 2 * w16;
+    const int row_bytes = 16 * w16;
+    const size_t out_row = (size_t)row_bytes * (FP8 ? 8 : 16);
     unsigned tmax = 0;
     for (long long base = (long long)(blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4; base < total; base += (long long)warps_per_grid * 4) {
         const long long R = base + sub;
@@ -1290,16 +1340,13 @@ hamming_prep_batch_kernel(const uint8_t* __restrict__ t, int nt_stride, const ui
         const int n_real = live ? (is_t ? dims[pr].y : dims[pr].x) : 0;
         const size_t row = (size_t)pr * stride + r;                              // operand row in the pair-strided layout
         unsigned pc = 0;
-        if (live && r < stride) {
-            uint4* dst = reinterpret_cast<uint4*>((char*)(is_t ? tp : qp) + row * 256 * w16 + (size_t)sl * 16 * lane_bytes);
-            if (r < n_real) pc = unpack_bits_row((is_t ? t : q) + row * 16 * w16 + (size_t)sl * lane_bytes, lane_bytes, is_t ? 0x3F80u : 0xC000u, dst);
-            else for (int b = 0; b < lane_bytes; ++b) dst[b] = make_uint4(0, 0, 0, 0);          // padding inside the stride: finite operands
-        }
+        if (live && r < stride)                                                  // rows beyond the stride belong to the next pair (or to nobody)
+            pc = unpack_bits_row<FP8>((is_t ? t : q) + row * row_bytes, row_bytes, sl, is_t, r < n_real, (char*)(is_t ? tp : qp) + row * out_row);
 #pragma unroll
         for (int o = 4; o >= 1; o >>= 1) pc += __shfl_xor_sync(0xffffffffu, pc, o);
         if (live && sl == 0) {
-            if (is_t) write_aug(taug + 2 * (size_t)Rl, true, r < n_real ? (float)pc : INFINITY, true);
-            else { qnorm[Rl] = (float)pc; write_aug(qaug + 2 * (size_t)Rl, false, 0.f, true); }
+            if (!is_t) qnorm[Rl] = (float)pc;
+            write_aug_bits<FP8>((is_t ? taug : qaug) + 2 * (size_t)Rl, is_t, pc, is_t && r >= n_real);
         }
         if (live && is_t && r < n_real) tmax = max(tmax, pc);
     }
@@ -1340,12 +1387,13 @@ hamming_certify_batch_kernel(int nb, int nq_stride, const int2* __restrict__ dim
 
 struct TcBatchPlan { int rq, NQBp, NTp, NQB, G, max_slots, kp16; long long U; size_t off_qnorm, off_tp, off_qp, off_taug, off_qaug, off_cand, off_gthr, total; };
 
-TcBatchPlan make_batch_plan(int nq_stride, int nt_stride, int w16, int nb, int sm_count)
+TcBatchPlan make_batch_plan(int nq_stride, int nt_stride, int w16, int nb, int sm_count, int fmt)
 {
     TcBatchPlan P;
     const int dim = w16 * 128;
     P.kp16 = dim;
-    P.rq = dim > 256 ? UM : BM;
+    P.rq = dim > (fmt == 2 ? 512 : 256) ? UM : BM;
+    const size_t elt_row = fmt == 2 ? (size_t)dim : (size_t)dim * 2;
     P.NQBp = (nq_stride + P.rq - 1) / P.rq; P.NTp = (nt_stride + BN - 1) / BN;
     P.NQB = nb * P.NQBp;
     P.U = (long long)P.NQB * P.NTp;
@@ -1357,8 +1405,8 @@ TcBatchPlan make_batch_plan(int nq_stride, int nt_stride, int w16, int nb, int s
     }
     size_t o = 256;
     P.off_qnorm = o; o = align256(o + (size_t)P.NQB * P.rq * 4);
-    P.off_tp = o;    o = align256(o + (size_t)nb * nt_stride * dim * 2);
-    P.off_qp = o;    o = align256(o + (size_t)nb * nq_stride * dim * 2);
+    P.off_tp = o;    o = align256(o + (size_t)nb * nt_stride * elt_row);
+    P.off_qp = o;    o = align256(o + (size_t)nb * nq_stride * elt_row);
     P.off_taug = o;  o = align256(o + (size_t)nb * P.NTp * BN * AUG_BYTES);
     P.off_qaug = o;  o = align256(o + (size_t)P.NQB * P.rq * AUG_BYTES);
     P.off_cand = o;  o = align256(o + (size_t)P.NQB * P.max_slots * LPS * P.rq * 32);
@@ -1369,9 +1417,9 @@ TcBatchPlan make_batch_plan(int nq_stride, int nt_stride, int w16, int nb, int s
 
 // pairs per ranking launch: the train operands of the pairs in flight should stay L2-resident (every query block of a pair
 // re-reads the pair's train tiles), and one launch should still hold a few thousand work units
-int hamming_tc_group(int nt_stride, int w16, int nb)
+int hamming_tc_group(int nt_stride, int w16, int nb, int fmt)
 {
-    const size_t per_pair = (size_t)nt_stride * w16 * 256;
+    const size_t per_pair = (size_t)nt_stride * w16 * (fmt == 2 ? 128 : 256);
     int g = (int)std::max<size_t>(1, ((size_t)80 << 20) / std::max<size_t>(per_pair, 1));
     return std::min(std::min(g, 64), nb);
 }
@@ -1386,24 +1434,26 @@ bool mpl_hamming_tc_batch_supported(int nq_stride, int nt_stride, int w16)
 size_t mpl_hamming_tc_batch_scratch_bytes(int nq_stride, int nt_stride, int w16, int nb, int sm_count)
 {
     if (!mpl_hamming_tc_batch_supported(nq_stride, nt_stride, w16) || nb <= 0) return 16;
-    return make_batch_plan(nq_stride, nt_stride, w16, hamming_tc_group(nt_stride, w16, nb), sm_count).total;
+    return std::max(make_batch_plan(nq_stride, nt_stride, w16, hamming_tc_group(nt_stride, w16, nb, 1), sm_count, 1).total,
+                    make_batch_plan(nq_stride, nt_stride, w16, hamming_tc_group(nt_stride, w16, nb, 2), sm_count, 2).total);
 }
 
 int mpl_hamming_tc_top2_batch(const uint8_t* d_q, int nq_stride, const uint8_t* d_t, int nt_stride, int w16, int nb, const int2* d_dims,
-                              void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st)
+                              void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st, int fmt)
 {
     if (nb <= 0) return MPL_OK;
+    if (fmt != 1) fmt = 2;
     if (!mpl_hamming_tc_batch_supported(nq_stride, nt_stride, w16)) { mpl_set_error("hamming tensor-core batch: unsupported shape (w16=%d)", w16); return MPL_ERR_BAD_ARG; }
-    const int group = hamming_tc_group(nt_stride, w16, nb);
-    const size_t need = make_batch_plan(nq_stride, nt_stride, w16, group, sm_count).total;
+    const int group = hamming_tc_group(nt_stride, w16, nb, fmt);
+    const size_t need = make_batch_plan(nq_stride, nt_stride, w16, group, sm_count, fmt).total;
     if (!d_scratch || scratch_bytes < need || ((uintptr_t)d_scratch & 255) != 0) { mpl_set_error("hamming tensor-core batch: scratch %zu < %zu bytes or not 256-byte aligned", scratch_bytes, need); return MPL_ERR_BAD_ARG; }
     MPL_CUDA_CHECK(cudaFuncSetAttribute(l2_tc_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, U8 = CU_TENSOR_MAP_DATA_TYPE_UINT8;
     char* base = (char*)d_scratch;
     const size_t rowb = (size_t)w16 * 16;
     for (int g0 = 0; g0 < nb; g0 += group) {
         const int gn = std::min(group, nb - g0);
-        const TcBatchPlan P = make_batch_plan(nq_stride, nt_stride, w16, gn, sm_count);
+        const TcBatchPlan P = make_batch_plan(nq_stride, nt_stride, w16, gn, sm_count, fmt);
         TcHeader* hdr = (TcHeader*)base;
         float* qnorm = (float*)(base + P.off_qnorm);
         void* tp = base + P.off_tp; void* qp = base + P.off_qp;
@@ -1412,16 +1462,24 @@ int mpl_hamming_tc_top2_batch(const uint8_t* d_q, int nq_stride, const uint8_t* 
         alignas(64) TcMaps maps;
         memset(&maps, 0, sizeof(maps));
         int rc;
-        if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, gn * nq_stride, 64, P.rq))) return rc;
-        if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, gn * nt_stride, 64, BN))) return rc;
-        if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, P.NQB * P.rq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
-        if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, gn * P.NTp * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        if (fmt == 2) {
+            if ((rc = encode_map(&maps.a8, U8, 1, qp, P.kp16, gn * nq_stride, 128, P.rq))) return rc;
+            if ((rc = encode_map(&maps.b8, U8, 1, tp, P.kp16, gn * nt_stride, 128, BN))) return rc;
+            if ((rc = encode_map(&maps.aa8, U8, 1, qaug, 32, P.NQB * P.rq, 32, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+            if ((rc = encode_map(&maps.ba8, U8, 1, taug, 32, gn * P.NTp * BN, 32, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        } else {
+            if ((rc = encode_map(&maps.a16, BF, 2, qp, P.kp16, gn * nq_stride, 64, P.rq))) return rc;
+            if ((rc = encode_map(&maps.b16, BF, 2, tp, P.kp16, gn * nt_stride, 64, BN))) return rc;
+            if ((rc = encode_map(&maps.aa16, BF, 2, qaug, 16, P.NQB * P.rq, 16, P.rq, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+            if ((rc = encode_map(&maps.ba16, BF, 2, taug, 16, gn * P.NTp * BN, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+        }
         MPL_CUDA_CHECK(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), st));
         {
             MplProfScope prof(MPL_PROF_L2_PREP, st);
             const long long rows = (long long)gn * P.NTp * BN + (long long)P.NQB * P.rq;
             long long blocks = (rows + 31) / 32; if (blocks > sm_count * 16) blocks = sm_count * 16;
-            hamming_prep_batch_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_t + (size_t)g0 * nt_stride * rowb, nt_stride, d_q + (size_t)g0 * nq_stride * rowb, nq_stride,
+            auto prep = fmt == 2 ? hamming_prep_batch_kernel<true> : hamming_prep_batch_kernel<false>;
+            prep<<<(unsigned)blocks, 256, 0, st>>>(d_t + (size_t)g0 * nt_stride * rowb, nt_stride, d_q + (size_t)g0 * nq_stride * rowb, nq_stride,
                                                                         w16, gn, d_dims + g0, P.NTp, P.NQBp, P.rq, tp, qp, qnorm, taug, qaug, hdr, gthr, P.NQB * P.rq);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         }
@@ -1430,7 +1488,7 @@ int mpl_hamming_tc_top2_batch(const uint8_t* d_q, int nq_stride, const uint8_t* 
             TcParams prm;
             prm.nq = gn * nq_stride; prm.nt = nt_stride; prm.NT = P.NTp; prm.U = P.U; prm.max_slots = P.max_slots; prm.rq = P.rq;
             prm.NQBp = P.NQBp; prm.q_pair_rows = nq_stride; prm.t_pair_rows = nt_stride;
-            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
+            prm.slabs16 = P.kp16 / 64; prm.slabs32 = 0; prm.slabs8 = fmt == 2 ? P.kp16 / 128 : 0; prm.cand = cand; prm.gthr = gthr; prm.hdr = hdr;
             l2_tc_rank_kernel<<<P.G, TC_THREADS, SMEM_BYTES, st>>>(maps, prm);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         }

@@ -57,9 +57,9 @@ int    mpl_hamming_path();             // capi.cu: mpl_set_hamming_path (0 auto,
 bool   mpl_hamming_tc_batch_supported(int nq_stride, int nt_stride, int w16);
 size_t mpl_hamming_tc_batch_scratch_bytes(int nq_stride, int nt_stride, int w16, int nb, int sm_count);
 int    mpl_hamming_tc_top2_batch(const uint8_t* d_q, int nq_stride, const uint8_t* d_t, int nt_stride, int w16, int nb, const int2* d_dims,
-                                 void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st);
+                                 void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st, int fmt);
 // Hamming distances as a bf16 contraction on the same ranking kernel (128 / 256 / 512-bit rows: w16 = 1, 2, 4)
 bool   mpl_hamming_tc_supported(int nq, int nt, int w16);
 size_t mpl_hamming_tc_scratch_bytes(int nq, int nt, int w16, int sm_count);
 int    mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int w16, long long train_offset, void* d_scratch,
-                           size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st);
+                           size_t scratch_bytes, mpl_key64* d_keys_out, int sm_count, cudaStream_t st, int fmt /* 2 = e4m3, 1 = bf16 */);

@@ -303,7 +303,7 @@ int enqueue_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, 
         MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         if (P.use_tc) {
             if ((rc = mpl_hamming_tc_top2_batch((const uint8_t*)(D + A.dq), P.nq_stride, (const uint8_t*)(D + A.dt), P.nt_stride, P.w16, nb, d_dims,
-                                                D + A.l2scr, P.l2_scratch, d_keys, mpl_ctx()->sm_count, st))) return rc;
+                                                D + A.l2scr, P.l2_scratch, d_keys, mpl_ctx()->sm_count, st, mpl_hamming_path() == 3 ? 1 : 2))) return rc;
         } else if (P.splits > 1) {
             // a batch of a few pairs cannot fill the GPU with one CTA row per pair: split the train rows as the single-pair
             // matcher does and merge the per-split keys (one merge launch per pair; only taken for nb <= 8)
@@ -467,7 +467,7 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
     P.use_tc = 0;
     if (!P.is_float && mpl_hamming_tc_batch_supported(P.nq_stride, P.nt_stride, P.w16)) {
         const int path = mpl_hamming_path();
-        if (path == 2 || (path == 0 && P.nq_stride >= 512 && P.nt_stride >= 512)) P.use_tc = 1;
+        if (path >= 2 || (path == 0 && P.nq_stride >= 512 && P.nt_stride >= 512)) P.use_tc = 1;
     }
     if (P.use_tc) P.l2_scratch = mpl_hamming_tc_batch_scratch_bytes(P.nq_stride, P.nt_stride, P.w16, bs, ctx->sm_count) + 256;
     if (!P.is_float && !P.use_tc && bs <= 8) {

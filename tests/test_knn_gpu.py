@@ -52,15 +52,16 @@ def test_hamming_vs_oracle(m, nq, nt, nb):
 
 @pytest.mark.parametrize("nq,nt,nb", [(1, 2, 32), (17, 5000, 32), (1500, 3000, 32), (1025, 257, 64), (300, 4097, 61), (64, 700, 16),
                                       (257, 129, 32), (700, 70000, 32), (200, 250000, 32), (300, 60000, 64), (8192, 8192, 32)])
-def test_hamming_tensor_core_path_vs_oracle(m, nq, nt, nb):
-    """mpl_set_hamming_path(2): the bits as bf16 on the float ranking kernel's exact-integer mode (hamming = |q| + |t| - 2 q.t); the
-    last three shapes walk the train set in chunks / use 128-row query blocks (512-bit rows).  Same keys as the popc kernel."""
+@pytest.mark.parametrize("path", [2, 3])
+def test_hamming_tensor_core_path_vs_oracle(m, nq, nt, nb, path):
+    """mpl_set_hamming_path(2 / 3): the bits as e4m3 bytes / bf16 on the float ranking kernel's exact-integer mode (hamming = |q| + |t| -
+    2 q.t); the large shapes walk the train set in chunks, 512-bit rows use 128-row query blocks in bf16.  Same keys as the popc kernel."""
     q, t = datagen.binary_descriptors(nq, nt, nb, seed=nq * 7 + nt)
     if nt >= 5000:
         t[nt // 2] = t[3]; t[nt - 1] = t[3]; q[0] = t[3]                # exact duplicates in different tiles / chunks: ties by index
     import ctypes
     lib = m._lib.load()
-    lib.mpl_set_hamming_path(2)
+    lib.mpl_set_hamming_path(path)
     lib.mpl_prof_enable(1)
     ms, cnt = ctypes.c_double(0), ctypes.c_longlong(0)
     lib.mpl_prof_read(2, ctypes.byref(ms), ctypes.byref(cnt))               # reading clears the ranking kernel's timer

@@ -122,15 +122,16 @@ def test_batch_hamming_paths_identical(P, nb):
         pairs.append((q, t, p1, p2))
     lib = _lib.load()
     out = {}
-    for path in (1, 2):
+    for path in (1, 2, 3):
         lib.mpl_set_hamming_path(path)
         try:
             out[path] = P.matchAndEstimatePoseBatch(pairs * 3, "LINEAR", True, th, 64, 0.999, True, seeds=list(range(len(pairs) * 3)))
         finally:
             lib.mpl_set_hamming_path(0)
-    for a, b in zip(out[1], out[2]):
-        assert np.array_equal(a["matches"], b["matches"]) and np.array_equal(a["mask"], b["mask"]) and a["count"] == b["count"]
-        assert np.array_equal(a["E"], b["E"])
+    for tc in (2, 3):
+        for a, b in zip(out[1], out[tc]):
+            assert np.array_equal(a["matches"], b["matches"]) and np.array_equal(a["mask"], b["mask"]) and a["count"] == b["count"]
+            assert np.array_equal(a["E"], b["E"])
     for r, (q, t, p1, p2) in zip(out[2][:4], pairs[:4]):
         assert np.array_equal(r["matches"], oracle_matches(q, t, "LINEAR"))
 

@@ -12,7 +12,7 @@ pool = [bench.make_c4_pair(1004 + i) for i in range(4)]
 pairs = [tuple(pool[i % 4][0]) for i in range(n_pairs)]
 th = pool[0][1]
 PROF = dict(hamming=0, l2_exact=1, l2_tc=2, l2_rerank=3, merge=4, solve=5, score=6, l2_prep=7)
-for path in (1, 0):
+for path in (1, 3, 2):
     lib.mpl_set_hamming_path(path)
     for h in (0, 1000):
         poselib.matchAndEstimatePoseBatch(pairs[:64], "LINEAR", True, th, h, 0.999, True, seeds=list(range(64)))

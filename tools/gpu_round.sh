@@ -11,9 +11,9 @@ fi
 if [ -n "$NCU" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 # kernel names are matched on the demangled name (template arguments included); NCU_KERNELS overrides the list
-# the ranking kernel in Hamming mode (bits as bf16): a full 98 304-row chunk of a 10 000 x 1.25 M scan (the tool runs the popc path first,
-# so every l2_tc_rank_kernel launch of this command is a Hamming chunk)
-timeout 600 ncu --set full --clock-control none --import-source on -k "regex:l2_tc_rank_kernel" -s 16 -c 1 -f -o gpurun_out/full_l2_tc_rank_kernel_hamming python tools/hamming_tc_time.py 10000 1250000 32 > gpurun_out/ncu_full_tc_hamming.log 2>&1; echo "ncu full tc hamming rc=$?"
+# the ranking kernel in Hamming mode: the tool runs popc, then the bf16 form (13 chunks x 3 repetitions = launches 0..38), then e4m3
+# (7 chunks x 3): launch 41 is a full 196 608-row e4m3 chunk of the 10 000 x 1.25 M scan
+timeout 600 ncu --set full --clock-control none --import-source on -k "regex:l2_tc_rank_kernel" -s 41 -c 1 -f -o gpurun_out/full_l2_tc_rank_kernel_hamming python tools/hamming_tc_time.py 10000 1250000 32 > gpurun_out/ncu_full_tc_hamming.log 2>&1; echo "ncu full tc hamming rc=$?"
 for k in ${NCU_KERNELS:-lmeds_median_kernel hamming_prep_kernel}; do
   f=$(echo $k | tr -d '<>')
   timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:$k" -s 1 -c 1 -f -o gpurun_out/full_$f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_$f.log 2>&1; echo "ncu full $k rc=$?"

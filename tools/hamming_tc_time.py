@@ -20,7 +20,7 @@ for nq, nt, nb in shapes:
     sb = int(lib.mpl_knn_hamming_scratch_bytes(nq, nt, w16)); scr = torch.empty(sb + 256, dtype=torch.uint8, device=dev)
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     res = {}; keys = {}
-    for path in (1, 2):
+    for path in (1, 3, 2):
         lib.mpl_set_hamming_path(path)
         k = torch.empty((nq, 2), dtype=torch.int64, device=dev)
         ts = []
@@ -34,9 +34,9 @@ for nq, nt, nb in shapes:
             if i >= 2 or reps == 3 and i >= 1: ts.append(e0.elapsed_time(e1))
         res[path] = float(np.median(ts)); keys[path] = k
     lib.mpl_set_hamming_path(0)
-    same = bool(torch.equal(keys[1], keys[2]))
-    r = dict(nq=nq, nt=nt, nbytes=nb, popc_ms=res[1], tc_ms=res[2], speedup=res[1] / res[2], keys_identical=same,
-             popc_pairs_per_s=nq * nt / res[1] * 1e3, tc_pairs_per_s=nq * nt / res[2] * 1e3, scratch_mb=sb / 2**20)
+    same = bool(torch.equal(keys[1], keys[2])) and bool(torch.equal(keys[1], keys[3]))
+    r = dict(nq=nq, nt=nt, nbytes=nb, popc_ms=res[1], tc_bf16_ms=res[3], tc_e4m3_ms=res[2], speedup_e4m3=res[1] / res[2], keys_identical=same,
+             popc_pairs_per_s=nq * nt / res[1] * 1e3, tc_e4m3_pairs_per_s=nq * nt / res[2] * 1e3, scratch_mb=sb / 2**20)
     print(json.dumps(r)); out.append(r)
     del dq, dt, scr
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
