@@ -145,7 +145,9 @@ int mpl_allgather_merge_top2_dev(const void* d_keys_local, int nq, int rank, int
  * Descriptor rows must be in the library's device layout: row stride = w16*16 bytes, zero padded
  * (mpl_pack_rows_u8_dev produces it; 32-byte ORB rows already are, with w16 = 2).
  * keys_out[nq*2]: 64-bit keys (dist << 32 | global trainIdx) of the two nearest train rows of this
- * shard, global trainIdx = train_offset + local row.  scratch: mpl_knn_hamming_scratch_bytes().
+ * shard, global trainIdx = train_offset + local row.  scratch: mpl_knn_hamming_scratch_bytes() -- sized for either Hamming
+ * path (mpl_set_hamming_path): the popc scan's per-split partial keys or the tensor-core path's operand images of one train chunk,
+ * lists and per-chunk partial keys (C5 shard: 80 MB); 256-byte aligned, or the call stays on the popc scan.
  * mpl_merge_top2_dev: merge n_parts key lists laid out [part][nq][2] (e.g. the NCCL all-gather of
  * every rank's keys_out) into idx/dist (is_float: 0 int32 Hamming, 1 float bits) and/or merged keys. */
 size_t mpl_knn_hamming_scratch_bytes(int nq, int nt, int w16);

@@ -111,8 +111,14 @@ __global__ void gather_models_kernel(const double* __restrict__ models, const in
     if (j < n_models[s]) dense[(size_t)(offsets[s] + j) * 9 + (r - j * 9)] = models[(size_t)s * 90 + r];
 }
 
-constexpr int kScoreThreads = 128;
-constexpr int kChunk = 1024;                 // correspondences per TMA stage (32 KB)
+#ifndef MPL_SCORE_THREADS
+#define MPL_SCORE_THREADS 128
+#endif
+#ifndef MPL_SCORE_CHUNK
+#define MPL_SCORE_CHUNK 1024
+#endif
+constexpr int kScoreThreads = MPL_SCORE_THREADS;
+constexpr int kChunk = MPL_SCORE_CHUNK;      // correspondences per TMA stage (32 B each)
 constexpr int kScoreStages = 2;
 
 // One Sampson evaluation in the reference's operation order (five-point.cpp:490-503).
