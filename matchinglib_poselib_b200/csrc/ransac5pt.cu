@@ -115,11 +115,14 @@ __global__ void gather_models_kernel(const double* __restrict__ models, const in
 #define MPL_SCORE_THREADS 128
 #endif
 #ifndef MPL_SCORE_CHUNK
-#define MPL_SCORE_CHUNK 1024
+#define MPL_SCORE_CHUNK 256
 #endif
 constexpr int kScoreThreads = MPL_SCORE_THREADS;
 constexpr int kChunk = MPL_SCORE_CHUNK;      // correspondences per TMA stage (32 B each)
-constexpr int kScoreStages = 2;
+#ifndef MPL_SCORE_STAGES
+#define MPL_SCORE_STAGES 2
+#endif
+constexpr int kScoreStages = MPL_SCORE_STAGES;
 
 // One Sampson evaluation in the reference's operation order (five-point.cpp:490-503).
 __device__ __forceinline__ float sampson_err(const double (&E)[9], const double4 c)
