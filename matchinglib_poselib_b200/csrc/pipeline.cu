@@ -22,6 +22,7 @@
 #include <float.h>
 #include <string.h>
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace {
@@ -455,7 +456,10 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
     // sub-batch size: the model slots (720 B per sample) are the big array -- keep a lane's arena under ~1 GiB
     const size_t per_pair = (size_t)std::max(P.h, 1) * (720 + 20 + 4 + 120) + (size_t)P.nq_stride * (P.row_bytes + 16 + P.pe + 16 + 32 + 4 + 2 + P.cols)
                             + (size_t)P.nt_stride * (P.row_bytes + P.pe + P.cols);
-    int bs = (int)std::min<size_t>(256, std::max<size_t>(1, ((size_t)1 << 30) / per_pair));
+    // sub-batch cap: MPL_PAIR_BS (experiments; default 256) and an arena budget of 1 GiB per lane (2 GiB when the cap is raised)
+    size_t bs_cap = 256;
+    if (const char* e = getenv("MPL_PAIR_BS")) { const long v = atol(e); if (v >= 1 && v <= 4096) bs_cap = (size_t)v; }
+    int bs = (int)std::min<size_t>(bs_cap, std::max<size_t>(1, ((size_t)(bs_cap > 256 ? 2 : 1) << 30) / per_pair));
     if (P.is_float) bs = std::min(bs, 32);                                       // one tensor-core pipeline per pair on the lane's stream
     bs = std::min(bs, n_pairs);
     // two lanes need at least two sub-batches; split small batches in halves so that uploads and kernels overlap
