@@ -271,6 +271,27 @@ l2_exact_list_kernel(const float* __restrict__ q, const int* __restrict__ qlist,
     if (!is_last) return;
     __threadfence();
     const ulonglong2* part2 = reinterpret_cast<const ulonglong2*>(partial);
+    if (n <= kFewQueries) {
+        // few queries, hundreds of row ranges each: one WARP per query walks the ranges lane-parallel (a single thread per
+        // query would chain ~600 L2 round trips), then folds the 32 partial pairs
+        const int lane = threadIdx.x & 31;
+        for (int p = threadIdx.x >> 5; p < n; p += (int)(blockDim.x >> 5)) {
+            mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
+            for (int s = lane; s < splits; s += 32) {
+                const ulonglong2 v = __ldcg(part2 + (size_t)s * n + p);
+                top2_push(b0, b1, v.x);
+                b1 = min(b1, v.y);
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) {
+                const mpl_key64 o0 = __shfl_xor_sync(0xffffffffu, b0, off), o1 = __shfl_xor_sync(0xffffffffu, b1, off);
+                top2_push(b0, b1, o0);
+                b1 = min(b1, o1);
+            }
+            if (lane == 0) keys_out[qlist[p]] = make_ulonglong2(b0, b1);
+        }
+        return;
+    }
     for (int p = threadIdx.x; p < n; p += blockDim.x) {
         mpl_key64 b0 = MPL_KEY_INVALID, b1 = MPL_KEY_INVALID;
         for (int s = 0; s < splits; ++s) {
