@@ -1299,7 +1299,8 @@ int mpl_hamming_tc_top2(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, 
         }
         {
             MplProfScope prof(MPL_PROF_L2_RERANK, st);
-            l2_certify_kernel<2><<<(nq + 7) / 8, 256, 0, st>>>(nullptr, nq, 0, nullptr, ntc, 0, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots,
+            l2_certify_kernel<2><<<(nq + 255) / 256, 256, 0, st>>>(                     // exact-integer branch only: one THREAD per query
+                nullptr, nq, 0, nullptr, ntc, 0, dim, qnorm, cand, P.NT, P.U, P.G, P.max_slots,
                                                                train_offset + t0, hdr, parts + (size_t)c * nq * 2, flist, P.rq);
             MPL_CUDA_CHECK(cudaGetLastError()); mpl_count_launch();
         }
