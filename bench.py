@@ -610,7 +610,7 @@ def bench_pair_batch_c4(g, world=1, rank=0, dist=None, n_pairs=None):
     full = poselib.PairBatch(pairs, "LINEAR", True, th, h, 0.999, True, seeds=seeds)
     b_match = poselib.PairBatch(pairs, "LINEAR", True, th, 0, 0.999, False, seeds=seeds)
     b_norefit = poselib.PairBatch(pairs, "LINEAR", True, th, h, 0.999, False, seeds=seeds)
-    poselib.PairBatch(pairs[:min(len(pairs), 512)], "LINEAR", True, th, h, 0.999, True, seeds=seeds[:512]).run()   # warm-up: arenas, first DMA of the pinned pages
+    poselib.PairBatch(pairs[:min(len(pairs), 1024)], "LINEAR", True, th, h, 0.999, True, seeds=seeds[:1024]).run()   # warm-up: full-size arenas of all three lanes (4 sub-batches of 256), first DMA of the pinned pages
     l0 = g.launches()
     torch.cuda.synchronize()
     sync()

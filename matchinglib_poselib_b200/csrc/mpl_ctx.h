@@ -33,7 +33,7 @@ struct MplCtx {
     size_t total_mem = 0;
     cudaStream_t stream = nullptr;
     MplBuf bufs[MPL_BUF_COUNT];
-    MplLane lanes[2];
+    MplLane lanes[4];               // MPL_MAX_LANES; pipeline.cu uses the first n_lanes of them
 };
 
 MplCtx*     mpl_ctx();

@@ -8,7 +8,7 @@
 //   Remove_LensDist -> LensDist_Oulu (10 iterations, proof test)   pose_helper.cpp:1169-1279
 //   p1, p2 <- n x 2 CV_64F                                         main.cpp:1588-1596
 //   estimateEssentialMat(E, p1, p2, "RANSAC", th, refine, mask)    pose_estim.cpp:857-890 -> modelest.cpp:343-474
-// Here a call takes any number of pairs; they are processed in sub-batches on two pipeline lanes (own stream, device arena
+// Here a call takes any number of pairs; they are processed in sub-batches on three pipeline lanes (own stream, device arena
 // and pinned host area each), so the uploads of one sub-batch overlap the kernels of the other and ONE host thread keeps
 // the GPU busy.  Per sub-batch: H2D of descriptors / keypoints -> batched row packing -> Hamming scan with blockIdx.z = pair
 // (float descriptors: the tensor-core L2 path per pair) -> ratio test + cv::DMatch compaction + keypoint gather + camera
@@ -462,8 +462,12 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
     int bs = (int)std::min<size_t>(bs_cap, std::max<size_t>(1, ((size_t)(bs_cap > 256 ? 2 : 1) << 30) / per_pair));
     if (P.is_float) bs = std::min(bs, 32);                                       // one tensor-core pipeline per pair on the lane's stream
     bs = std::min(bs, n_pairs);
-    // two lanes need at least two sub-batches; split small batches in halves so that uploads and kernels overlap
-    if (n_pairs >= 16 && n_pairs <= bs) bs = (n_pairs + 1) / 2;
+    // lanes in flight (MPL_PAIR_LANES, 1 .. 4): a sub-batch is a chain of dependent launches (uploads, scan, RANSAC chunks with a solve
+    // latency each, refit, downloads) of ~18 ms whatever its size, so a call of a few hundred pairs wants several sub-batches side by side
+    int n_lanes = 3;                                                             // measured at C4: 2 lanes 25.7 k, 3 lanes 29.4 k, 4 lanes 29.6 k pairs/s (4 hurts calls of ~500 pairs)
+    if (const char* e = getenv("MPL_PAIR_LANES")) { const long v = atol(e); if (v >= 1 && v <= 4) n_lanes = (int)v; }
+    // the lanes need at least one sub-batch each; split small batches so that uploads and kernels overlap
+    if (n_pairs >= 8 * n_lanes && n_pairs <= bs * (n_lanes - 1) + bs / 2) bs = std::min(bs, (n_pairs + n_lanes - 1) / n_lanes);
     P.bs = bs;
     P.splits = 1;
     // Hamming scan: tensor cores (bits as bf16, knn_l2_tc.cu) when the rows are 16 / 32 / 64 bytes and the pairs are big enough to
@@ -479,18 +483,19 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
         if (sp > 1 && (P.nt_stride + sp - 1) / sp >= 32) P.splits = sp;
     }
     const int n_sub = (n_pairs + bs - 1) / bs;
-    for (auto& L : ctx->lanes) if (!L.stream) MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
-    int inflight_p0[2] = {0, 0}, inflight_nb[2] = {0, 0};
+    for (int i = 0; i < n_lanes; ++i) if (!ctx->lanes[i].stream) MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->lanes[i].stream, cudaStreamNonBlocking));
+    int inflight_p0[4] = {0, 0, 0, 0}, inflight_nb[4] = {0, 0, 0, 0};
     rc = MPL_OK;
     for (int k = 0; k < n_sub && rc == MPL_OK; ++k) {
-        MplLane& L = ctx->lanes[k & 1];
-        if (L.busy) { rc = finish_sub_batch(L, P, pairs, inflight_p0[k & 1], inflight_nb[k & 1], want_samples, results); L.busy = 0; if (rc) break; }
+        const int li = k % n_lanes;
+        MplLane& L = ctx->lanes[li];
+        if (L.busy) { rc = finish_sub_batch(L, P, pairs, inflight_p0[li], inflight_nb[li], want_samples, results); L.busy = 0; if (rc) break; }
         const int p0 = k * bs, nb = std::min(bs, n_pairs - p0);
         rc = enqueue_sub_batch(L, P, pairs, p0, nb, prm, want_samples);
-        if (rc == MPL_OK) { L.busy = 1; inflight_p0[k & 1] = p0; inflight_nb[k & 1] = nb; }
+        if (rc == MPL_OK) { L.busy = 1; inflight_p0[li] = p0; inflight_nb[li] = nb; }
     }
-    for (int j = 0; j < 2; ++j) {                                   // drain in submission order
-        const int lane = (n_sub + j) & 1;
+    for (int j = 0; j < n_lanes; ++j) {                             // drain in submission order
+        const int lane = (n_sub + j) % n_lanes;
         MplLane& L = ctx->lanes[lane];
         if (!L.busy) continue;
         if (rc == MPL_OK) rc = finish_sub_batch(L, P, pairs, inflight_p0[lane], inflight_nb[lane], want_samples, results);
