@@ -143,7 +143,10 @@ solve_chunk_kernel(const double4* __restrict__ corr, size_t corr_stride, const M
 
 // ---- score ----------------------------------------------------------------------------------------------------
 constexpr int kScoreThreads = 128;
-constexpr int kChunk = 512;                  // correspondences per TMA stage (16 KB)
+#ifndef MPL_SLOTS_CHUNK
+#define MPL_SLOTS_CHUNK 512
+#endif
+constexpr int kChunk = MPL_SLOTS_CHUNK;      // correspondences per TMA stage (32 B each)
 constexpr int kScoreStages = 2;
 constexpr int kGroupSamples = 16;            // samples per CTA: <= 160 slots, ~77 valid on average (4.8 real roots per sample)
 
