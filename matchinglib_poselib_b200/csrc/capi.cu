@@ -251,6 +251,21 @@ extern "C" void* mpl_host_alloc(size_t bytes)
     return al;
 }
 
+// True when [p, p + bytes) lies inside one mpl_host_alloc region: pinned, registered with cudaHostRegisterDefault (mapped and portable under
+// unified addressing), i.e. kernels may read it through the same pointer.  The registration covers whole 2 MiB pages, so a 16-byte read that
+// starts inside the range never leaves mapped memory.
+bool mpl_host_is_mapped(const void* p, size_t bytes)
+{
+    std::lock_guard<std::mutex> g(g_host_mu);
+    auto it = g_host_allocs.upper_bound(const_cast<void*>(p));
+    if (it == g_host_allocs.begin()) return false;
+    --it;
+    const char* al = (const char*)it->first;
+    const size_t H = (size_t)2 << 20;
+    const char* reg_end = al + (it->second.second - H);                         // mpl_host_alloc registers (mmap size - 2 MiB) bytes from the aligned start
+    return (const char*)p >= al && (const char*)p + bytes <= reg_end;
+}
+
 extern "C" int mpl_host_free(void* p)
 {
     if (!p) return MPL_OK;

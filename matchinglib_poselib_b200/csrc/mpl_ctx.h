@@ -52,6 +52,7 @@ int    mpl_l2tc_top2(const float* d_q, int nq, size_t q_ld, const float* d_t, in
                      long long train_offset, void* d_scratch, size_t scratch_bytes, mpl_key64* d_keys_out,
                      int sm_count, cudaStream_t st);
 int    mpl_l2tc_last_fallbacks(const void* d_scratch, unsigned* count, unsigned* tf32_mode, cudaStream_t st);
+bool   mpl_host_is_mapped(const void* p, size_t bytes);   // capi.cu: inside an mpl_host_alloc region (device-readable pinned memory)
 int    mpl_hamming_path();             // capi.cu: mpl_set_hamming_path (0 auto, 1 popc, 2 tensor cores)
 // the same for a batch of pairs with a common geometry in one ranking launch per group of pairs (dims[pair] = (n1, n2))
 bool   mpl_hamming_tc_batch_supported(int nq_stride, int nt_stride, int w16);

@@ -136,6 +136,36 @@ def test_batch_hamming_paths_identical(P, nb):
         assert np.array_equal(r["matches"], oracle_matches(q, t, "LINEAR"))
 
 
+def test_pinned_host_buffers_upload_through_the_gather_kernel(P):
+    """MPL_PAIR_ZEROCOPY=1 (experiment, off by default): buffers in mpl_host_alloc memory (matchinglib.pinned_array) are read by one gather
+    kernel per sub-batch instead of four copies per pair; plain numpy buffers take the copies.  Same results; odd sizes exercise the
+    16-byte body / byte tail of the gather."""
+    import os
+    from matchinglib_poselib_b200 import matchinglib
+    shapes = [(700, 900, 61), (901, 333, 61), (5, 1200, 61), (0, 40, 61), (1201, 1201, 61), (64, 64, 61)]
+    plain, pinned, th = [], [], None
+    for i, (n1, n2, nb) in enumerate(shapes):
+        q, t, p1, p2, th = make_pair(n1, n2, nb, seed=700 + i)
+        plain.append((q, t, p1, p2))
+        pin = []
+        for a in (q, t, p1, p2):
+            v = matchinglib.pinned_array(a.shape, a.dtype) if a.size else a
+            if a.size:
+                v[...] = a
+            pin.append(v)
+        pinned.append(tuple(pin))
+    seeds = list(range(len(shapes)))
+    ra = P.matchAndEstimatePoseBatch(plain, "LINEAR", True, th, 96, 0.999, True, seeds=seeds)
+    os.environ["MPL_PAIR_ZEROCOPY"] = "1"
+    try:
+        rb = P.matchAndEstimatePoseBatch(pinned, "LINEAR", True, th, 96, 0.999, True, seeds=seeds)
+    finally:
+        del os.environ["MPL_PAIR_ZEROCOPY"]
+    for a, b in zip(ra, rb):
+        assert np.array_equal(a["matches"], b["matches"]) and np.array_equal(a["mask"], b["mask"]) and a["count"] == b["count"] and np.array_equal(a["E"], b["E"])
+    assert np.array_equal(rb[0]["matches"], oracle_matches(plain[0][0], plain[0][1], "LINEAR"))
+
+
 def test_c4_unit_vs_oracle(P):
     """The unit of BASELINE config C4 at its own size: AKAZE-like 61-byte descriptors 5000 x 5000 + RANSAC 1000 samples + refit."""
     q, t, p1, p2, th = make_pair(5000, 5000, 61, seed=1004)
