@@ -22,6 +22,8 @@
 #include <float.h>
 #include <string.h>
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <vector>
 
@@ -183,6 +185,9 @@ __global__ void pack_pairs_kernel(const uint8_t* __restrict__ raw, const unsigne
 // Upload of a sub-batch without the copy engine: when every buffer of the sub-batch lies in mpl_host_alloc memory (pinned and mapped), ONE
 // kernel reads the host buffers over PCIe (16-byte loads, thousands in flight) instead of four cudaMemcpyAsync per pair, whose set-up
 // cost kept the link at half its rate for copies of 80 - 300 KB.  One grid row per buffer.
+// host-side time of a call by phase (MPL_PAIR_TRACE=1 prints it): where the single host thread spends the call
+thread_local double g_trace_wait = 0, g_trace_enqueue = 0, g_trace_total = 0;
+
 struct CopyItem { const char* src; unsigned long long dst_off; unsigned long long bytes; };
 __global__ void __launch_bounds__(256)
 gather_copy_kernel(const CopyItem* __restrict__ items, char* __restrict__ base)
@@ -421,7 +426,9 @@ int enqueue_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, 
 // Wait for a lane's sub-batch and hand its results to the caller's buffers.
 int finish_sub_batch(MplLane& L, const BatchPlan& P, const mpl_pair_io* pairs, int p0, int nb, bool want_samples, mpl_pair_result* results)
 {
+    const auto t_a = std::chrono::steady_clock::now();
     MPL_CUDA_CHECK(cudaStreamSynchronize(L.stream));
+    g_trace_wait += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_a).count();
     const HostArea H = make_host_area(P, want_samples);
     const char* HS = (const char*)L.host;
     const MplPairState* S = (const MplPairState*)(HS + H.state);
@@ -529,6 +536,8 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
         if (sp > 1 && (P.nt_stride + sp - 1) / sp >= 32) P.splits = sp;
     }
     const int n_sub = (n_pairs + bs - 1) / bs;
+    const auto t_call = std::chrono::steady_clock::now();
+    g_trace_wait = g_trace_enqueue = 0;
     for (int i = 0; i < n_lanes; ++i) if (!ctx->lanes[i].stream) MPL_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->lanes[i].stream, cudaStreamNonBlocking));
     int inflight_p0[4] = {0, 0, 0, 0}, inflight_nb[4] = {0, 0, 0, 0};
     rc = MPL_OK;
@@ -537,7 +546,9 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
         MplLane& L = ctx->lanes[li];
         if (L.busy) { rc = finish_sub_batch(L, P, pairs, inflight_p0[li], inflight_nb[li], want_samples, results); L.busy = 0; if (rc) break; }
         const int p0 = k * bs, nb = std::min(bs, n_pairs - p0);
+        const auto t_e = std::chrono::steady_clock::now();
         rc = enqueue_sub_batch(L, P, pairs, p0, nb, prm, want_samples);
+        g_trace_enqueue += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_e).count();
         if (rc == MPL_OK) { L.busy = 1; inflight_p0[li] = p0; inflight_nb[li] = nb; }
     }
     for (int j = 0; j < n_lanes; ++j) {                             // drain in submission order
@@ -547,6 +558,11 @@ extern "C" int mpl_match_pose_batch(const mpl_pair_io* pairs, int n_pairs, const
         if (rc == MPL_OK) rc = finish_sub_batch(L, P, pairs, inflight_p0[lane], inflight_nb[lane], want_samples, results);
         else cudaStreamSynchronize(L.stream);
         L.busy = 0;
+    }
+    if (getenv("MPL_PAIR_TRACE")) {
+        g_trace_total = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_call).count();
+        fprintf(stderr, "mpl_match_pose_batch: %d pairs, %d sub-batches of %d on %d lanes: %.1f ms; host thread: enqueue %.1f ms, waiting for the GPU %.1f ms, copy-out %.1f ms\n",
+                n_pairs, n_sub, bs, n_lanes, g_trace_total * 1e3, g_trace_enqueue * 1e3, g_trace_wait * 1e3, (g_trace_total - g_trace_enqueue - g_trace_wait) * 1e3);
     }
     return rc;
 }
