@@ -1,5 +1,5 @@
 """SASS opcode counts per kernel of libmplb200.so -> profiles/rN_sass_opcodes.txt (the mnemonics that prove the hardware paths:
-UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTCBAR = tcgen05.commit, UTMALDG = TMA tile copy, UBLKCP = 1-D TMA bulk copy, SYNCS =
+UTCHMMA = tcgen05.mma kind::f16 / tf32, UTCQMMA = kind::f8f6f4, LDTM = tcgen05.ld, UTCBAR = tcgen05.commit, UTMALDG = TMA tile copy, UBLKCP = 1-D TMA bulk copy, SYNCS =
 mbarrier, POPC / LOP3 / VIMNMX = the Hamming integer path, DFMA / DMUL / DADD = fp64, LDL / STL = local memory).
     python tools/sass_opcodes.py profiles/r2_sass_opcodes.txt"""
 import collections
@@ -10,7 +10,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "matchinglib_poselib_b200", "lib", "libmplb200.so")
-OPS = ["UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UBLKCP", "SYNCS", "POPC", "LOP3", "VIMNMX", "DFMA", "DMUL", "DADD", "MUFU", "LDL", "STL",
+OPS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "UTMALDG", "UBLKCP", "SYNCS", "POPC", "LOP3", "VIMNMX", "DFMA", "DMUL", "DADD", "MUFU", "LDL", "STL",
        "ATOM", "ATOMS", "ATOMG", "RED", "SHFL", "VOTE", "UCGABAR_ARV"]
 
 
